@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the ExplaiNN hot path on B200.
+
+    python bench.py [--gpus N --steps K --warmup W] [--workload cfg3|cfg2|cfg1] [--impl reference]
+
+Metric (BASELINE.json): sequences/s of the ExplaiNN training step (forward + loss + backward + Adam)
+on synthetic one-hot DNA.  Default workload = cfg3, the configuration the metric is quoted on at
+1/2/4/8 GPUs: ExplaiNN(300 units, k=19, 600 bp, 50 outputs), MSE, Adam lr 0.003, batch 4096 per GPU
+(weak scaling; one rank per GPU, per-rank BatchNorm statistics, one flat gradient all-reduce per step).
+
+`value`   : K steps with the float one-hot batches already resident in HBM.
+`e2e`     : the same step through the reference-facing API with HOST buffers: pinned one-hot floats are
+            copied to the device every step and the loss is read back (`loss.item()`), as
+            selene/__init__.py:283-295 does.
+`roofline`: the dominant kernel (frontend_fwd_kernel) timed with CUDA events inside the timed region.
+`cpu_baseline` / `--impl reference`: the oracle port (oracle/explainn_oracle.py, torch CPU, the reference's
+            own arithmetic) timed on the host cores on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (cnn_units, kernel, length, features, loss kind, per-GPU batch)
+    "cfg3": (300, 19, 600, 50, "linear", 4096),
+    "cfg2": (300, 19, 60, 66, "linear", 4096),
+    "cfg1": (100, 19, 200, 1, "binary", 8192),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), d.get("bf16_tflops", 1590.0), "measured"
+    return 6650.0, 1400.0, 1590.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def synthetic_batches(n_batches, B, L, F, kind, seed):
+    from oracle.explainn_oracle import random_onehot  # synthetic generator only (no oracle arithmetic)
+    xs, ys = [], []
+    g = torch.Generator().manual_seed(seed)
+    for i in range(n_batches):
+        xs.append(random_onehot(B, L, seed=seed + i))
+        ys.append(torch.randn(B, F, generator=g) if kind == "linear" else (torch.rand(B, F, generator=g) < 0.5).float())
+    return xs, ys
+
+
+def cpu_reference_rate(cfg, steps, warmup, sample_B):
+    """The oracle port on the host cores: full train step (forward, loss, backward, Adam) per step."""
+    from oracle import explainn_oracle as O
+    U, k, L, F, kind, _ = cfg
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    from explainn_b200.architectures import ExplaiNN
+    torch.manual_seed(0)
+    sd = {k_: v.detach().clone() for k_, v in ExplaiNN(U, k, L, F).state_dict().items()}
+    xs, ys = synthetic_batches(1, sample_B, L, F, kind, 1234)
+    g = torch.Generator().manual_seed(1)
+    mask = (torch.rand(sample_B, U, 100, generator=g) >= 0.3).to(torch.uint8)
+    m = {k_: torch.zeros_like(sd[k_]) for k_ in O.PARAM_KEYS}
+    v = {k_: torch.zeros_like(sd[k_]) for k_ in O.PARAM_KEYS}
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = O.explainn_train_step(sd, xs[0], ys[0], kind, dropout_mask=mask)
+        for k_ in O.PARAM_KEYS:
+            sd[k_], m[k_], v[k_] = O.adam_step(sd[k_], r["grads"][k_].reshape(sd[k_].shape), m[k_], v[k_], it + 1, 0.003)
+        for k_, val in r["running"].items():
+            sd[k_] = val
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+    dt = sum(times)
+    return steps * sample_B / dt, dt / steps * 1e3, cores
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: workload's)")
+    ap.add_argument("--cpu-sample", type=int, default=128, help="sequences per CPU-baseline step")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    cfg = WORKLOADS[args.workload]
+    U, k, L, F, kind, B = cfg
+    if args.batch:
+        B = args.batch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    workload_name = f"ExplaiNN({U} units,k={k},{L}bp,{F} outputs) train step {kind} loss, Adam lr 0.003"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        rate, ms, cores = cpu_reference_rate(cfg, max(2, min(args.steps, 8)), 1, args.cpu_sample)
+        print(json.dumps({
+            "impl": "reference", "metric": "sequences/sec ExplaiNN fwd+bwd training step", "value": rate,
+            "unit": "sequences/s", "n_gpus": args.gpus, "steps": max(2, min(args.steps, 8)), "warmup": 1,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": workload_name, "per_step_sample": args.cpu_sample},
+            "cpu_baseline": {"value": rate, "unit": "sequences/s", "cores": cores, "kind": "port",
+                             "sample": f"{args.cpu_sample} sequences per step, oracle port of the reference's "
+                                       f"torch CPU path (the Python reference cannot travel to the GPU box)"},
+            "e2e": {"value": rate, "unit": "sequences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    from explainn_b200 import ops, parallel
+    from explainn_b200.architectures import ExplaiNN, get_loss, get_optimizer
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    parallel.init_from_env("nccl")
+    import torch.distributed as dist
+
+    torch.manual_seed(0)
+    model = ExplaiNN(U, k, L, F).to(dev).train()
+    parallel.broadcast_parameters(model)
+    crit = get_loss(kind)
+    opt = get_optimizer(model.parameters(), 0.003)
+    bucket = parallel.GradBucket(model.parameters())
+
+    # inputs rotate over NB distinct batches so that consecutive steps never re-read an L2-resident input
+    NB = max(2, int(140e6 // (B * 4 * L * 4)) + 1)
+    xs_h, ys_h = synthetic_batches(NB, B, L, F, kind, 1234 + 1000 * rank)
+    xs_pin = [x.pin_memory() for x in xs_h]
+    ys_pin = [y.pin_memory() for y in ys_h]
+    xs_d = [x.to(dev) for x in xs_h]
+    ys_d = [y.to(dev) for y in ys_h]
+
+    # event pairs around the dominant kernel (launched on torch's current stream)
+    fe_events = []
+    orig_frontend = ops.frontend_fwd
+
+    def timed_frontend(*a, **kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = orig_frontend(*a, **kw)
+        e1.record()
+        fe_events.append((e0, e1))
+        return out
+
+    def step(x, y, read_loss):
+        pred = model(x)
+        loss = crit(pred, y)
+        opt.zero_grad()
+        loss.backward()
+        bucket.allreduce_mean()
+        opt.step()
+        return loss.item() if read_loss else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for i in range(args.warmup):
+        step(xs_d[i % NB], ys_d[i % NB], False)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ops.frontend_fwd = timed_frontend
+    k0 = ops.kernel_launches
+    ms_dev = timed(lambda i: step(xs_d[i % NB], ys_d[i % NB], False), args.steps)
+    launches = ops.kernel_launches - k0
+    ops.frontend_fwd = orig_frontend
+    fe_ms = sum(a.elapsed_time(b) for a, b in fe_events) / max(1, len(fe_events))
+
+    def e2e_step(i):
+        x = xs_pin[i % NB].to(dev, non_blocking=True)
+        y = ys_pin[i % NB].to(dev, non_blocking=True)
+        step(x, y, True)
+
+    for i in range(2):
+        e2e_step(i)
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank != 0:
+        return
+    value = world * B * args.steps / (ms_dev / 1e3)
+    e2e = world * B * args.steps / (ms_e2e / 1e3)
+    hbm, tf_sus, tf_burst, which = peaks()
+    Lc = L - k + 1
+    flops_per_seq = 2.0 * U * Lc * 4 * k          # dense-equivalent conv flops
+    achieved = flops_per_seq * B / (fe_ms / 1e3) / 1e12
+    cpu_rate, cpu_ms, cores = cpu_reference_rate(cfg, 4, 1, args.cpu_sample)
+    print(json.dumps({
+        "metric": "sequences/sec ExplaiNN fwd+bwd training step", "value": value, "unit": "sequences/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name, "per_gpu_batch": B, "global_batch": B * world,
+                   "parallelism": f"dp{world}, per-rank BatchNorm statistics, one flat gradient all-reduce",
+                   "l2": f"inputs rotate over {NB} distinct batches ({NB * B * 16 * L / 1e6:.0f} MB > 126 MB L2); "
+                         f"intermediates exceed L2"},
+        "e2e": {"value": e2e, "unit": "sequences/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": B * 4 * L * 4 + B * F * 4, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches,
+        "roofline": {"kernel": "frontend_fwd_kernel (conv+BN+exp+maxpool)", "bound": "tensor", "achieved": achieved,
+                     "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": None,
+                     "peak_source": f"bf16_tflops_sustained, {which}", "kernel_ms": fe_ms,
+                     "kernel_share_of_step": fe_ms / (ms_dev / args.steps),
+                     "algorithmic_flops_per_seq": flops_per_seq},
+        "cpu_baseline": {"value": cpu_rate, "unit": "sequences/s", "cores": cores, "kind": "port",
+                         "sample": f"4 train steps of {args.cpu_sample} sequences, oracle port (torch CPU)"},
+        "clocks": clocks,
+    }))
+
+
+if __name__ == "__main__":
+    main()

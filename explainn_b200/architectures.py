@@ -1,0 +1,389 @@
+"""Drop-in for the reference's `architectures` package on the hot path.
+
+Mirrors explainn/architectures/__init__.py: `ExplaiNN` (:41-114), `PWM` (:116-170),
+`get_loss` / `get_metrics` / `get_optimizer` (:446-464), with the same constructor
+arguments, `_options`, `state_dict()` keys and shapes (`linears.0.weight` (U,4,k),
+`linears.6.weight` (100U,n,1), `linears.10.weight` (U,100,1), `final.weight` (F,U) ...),
+and a `linears` container that still answers `linears(x_rep)`, `linears[:3](x_rep)`
+(test.py:151,159) and `linears[0].weight` (interpret.py:154, train.py:318-324).
+
+Every layer object is a parameter holder only: the arithmetic runs in the fused
+sm_100a kernels of explainn_b200/csrc through the C ABI (ops.py).  Calling a
+single layer on its own raises -- there is no torch-library or CPU fallback.
+"""
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+_FULL_KEYS = [str(i) for i in range(14)]
+
+
+def _fused_only(self, *a, **k):
+    raise RuntimeError(
+        f"{type(self).__name__} is a parameter holder inside the fused ExplaiNN unit bank; call "
+        "`model.linears(x)`, `model.linears[:3](x)`, `model.linears[:4](x)` or `model(x)` instead")
+
+
+class FusedConv1d(nn.Conv1d):
+    """nn.Conv1d initialisation, parameters and state_dict; no stand-alone forward."""
+    forward = _fused_only
+
+
+class FusedBatchNorm1d(nn.BatchNorm1d):
+    forward = _fused_only
+
+
+class ExpAct(nn.Module):
+    """Exponential activation (architectures/__init__.py:12-19), fused into the front-end kernel."""
+    forward = _fused_only
+
+
+class UnSqueeze(nn.Module):
+    forward = _fused_only
+
+
+class _FusedMaxPool1d(nn.MaxPool1d):
+    forward = _fused_only
+
+
+class _FusedFlatten(nn.Flatten):
+    forward = _fused_only
+
+
+class _FusedReLU(nn.ReLU):
+    forward = _fused_only
+
+
+class _FusedDropout(nn.Dropout):
+    forward = _fused_only
+
+
+def _check_param(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} lives on {t.device}: move the model to a CUDA device "
+                           "(explainn_b200 has no CPU fallback)")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name}: the B200 path computes in float32, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _bn_momentum(bn):
+    if bn.momentum is None:
+        raise NotImplementedError("cumulative-average BatchNorm (momentum=None) is not supported")
+    return bn.momentum
+
+
+class _UnitBankFn(torch.autograd.Function):
+    """Training-mode forward/backward of the whole unit bank (a3, a4, a6)."""
+
+    @staticmethod
+    def forward(ctx, planes, L, bank, drop_mask, conv_w, conv_b, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3):
+        bn1, bn2, bn3, drop = bank[1], bank[7], bank[11], bank[9]
+        B = planes.shape[0]
+        U, _, k = conv_w.shape
+        Lc = L - k + 1
+        n_pos = B * Lc
+        with torch.no_grad():
+            cnt1, cnt2 = ops.cooc_counts(planes, L, k)
+            scale1, shift1, stats1, cov_w = ops.bn1_train_prepare(
+                cnt1, cnt2, n_pos, conv_w, conv_b, g1, be1, bn1.eps, _bn_momentum(bn1),
+                bn1.running_mean, bn1.running_var)
+            pool, zmax, arg = ops.frontend_fwd(planes, L, conv_w, scale1, shift1, need_argmax=True)
+            hpre = ops.fc1_fwd(pool, w1, b1)
+            scale2, shift2, stats2 = ops.bn_train_prepare(
+                hpre.view(B, U * ops.HIDDEN), g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean, bn2.running_var)
+            p = float(drop.p) if drop.training else 0.0
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and drop_mask is None) else 0
+            opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, drop_mask)
+            scale3, shift3, stats3 = ops.bn_train_prepare(
+                opre, g3, be3, bn3.eps, _bn_momentum(bn3), bn3.running_mean, bn3.running_var)
+            o, _ = ops.head_fwd(opre, scale3, shift3)
+            for bn in (bn1, bn2, bn3):
+                if bn.num_batches_tracked is not None:
+                    bn.num_batches_tracked += 1
+        ctx.save_for_backward(planes, conv_w, g1, w1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
+                              scale2, shift2, stats1, stats2, stats3, cov_w, cnt1)
+        ctx.meta = (L, k, n_pos, p, seed, drop_mask)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        (planes, conv_w, g1, w1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
+         scale2, shift2, stats1, stats2, stats3, cov_w, cnt1) = ctx.saved_tensors
+        L, k, n_pos, p, seed, drop_mask = ctx.meta
+        B, U = o.shape
+        n = pool.shape[2]
+        with torch.no_grad():
+            g = do.contiguous().clone()
+            dg3, dbe3, dopre = ops.bn_bwd(g, o, opre, stats3, g3)
+            dw2, db2, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, p, seed, drop_mask)
+            dg2, dbe2, dhpre = ops.bn_bwd(gh.view(B, U * ops.HIDDEN), None, hpre.view(B, U * ops.HIDDEN), stats2, g2)
+            dw1, db1, dy = ops.fc1_bwd(dhpre.view(B, U, ops.HIDDEN), pool, w1)
+            dcw, dcb, dg1, dbe1 = ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos)
+        return (None, None, None, None, dcw, dcb, dg1, dbe1, dw1.view(U * ops.HIDDEN, n, 1), db1,
+                dg2, dbe2, dw2.view(U, ops.HIDDEN, 1), db2, dg3, dbe3)
+
+
+class _FinalLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        return ops.linear_fwd(x, w, b)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dx, dw, db = ops.linear_bwd(dy.contiguous(), w, x)
+        return dx, dw, db
+
+
+class FusedLinear(nn.Linear):
+    """`final` (architectures/__init__.py:104): nn.Linear parameters, our GEMM kernels."""
+
+    def forward(self, x):
+        w = _check_param(self.weight, "final.weight")
+        b = _check_param(self.bias, "final.bias")
+        if x.dtype != torch.float32 or not x.is_cuda:
+            raise RuntimeError("final(x): x must be a float32 CUDA tensor")
+        x2 = x.contiguous().view(-1, w.shape[1])
+        if torch.is_grad_enabled() and (x2.requires_grad or w.requires_grad or b.requires_grad):
+            y = _FinalLinearFn.apply(x2, w, b)
+        else:
+            y = ops.linear_fwd(x2.detach(), w.detach(), b.detach())
+        return y.view(*x.shape[:-1], w.shape[0])
+
+
+class UnitBank(nn.Sequential):
+    """`linears` of the reference (architectures/__init__.py:72-102) as one fused operator.
+
+    Index / slice access keeps working (`linears[0].weight`, `linears[:3]`).  Supported
+    call forms: the full bank -> unit outputs (B,U); `[:3]` -> activations (B,U,Lc);
+    `[:4]` -> max-pooled activations (B,U,n).  Input is the float one-hot (B,4,L) or the
+    reference's U-times repeated (B,4U,L) tensor (only its first 4 channels are read), or
+    already packed planes wrapped in `PackedDNA`.
+    """
+
+    def _kind(self):
+        keys = list(self._modules.keys())
+        if keys == _FULL_KEYS:
+            return "outputs"
+        if keys == ["0", "1", "2"]:
+            return "acts"
+        if keys == ["0", "1", "2", "3"]:
+            return "pool"
+        raise NotImplementedError(
+            f"slice {keys} of the fused unit bank is not callable; supported: full, [:3], [:4]")
+
+    def _pack(self, x):
+        if isinstance(x, PackedDNA):
+            return x.planes, x.length
+        if not isinstance(x, torch.Tensor) or x.dim() != 3:
+            raise ValueError("expected a (B, 4, L) or (B, 4*cnn_units, L) float32 tensor")
+        if not x.is_cuda:
+            raise RuntimeError("explainn_b200 runs on CUDA tensors only; there is no CPU fallback")
+        U = self[0].out_channels
+        if x.shape[1] not in (4, 4 * U):
+            raise ValueError(f"expected 4 or {4 * U} input channels, got {x.shape[1]}")
+        return ops.pack_onehot(x), x.shape[2]
+
+    def _front_affine(self, planes, L):
+        """(scale, shift) of BN1 folded with the conv bias; batch statistics in train mode."""
+        conv, bn1 = self[0], self[1]
+        cw = _check_param(conv.weight, "linears.0.weight")
+        cb = _check_param(conv.bias, "linears.0.bias")
+        g1 = _check_param(bn1.weight, "linears.1.weight")
+        be1 = _check_param(bn1.bias, "linears.1.bias")
+        k = cw.shape[2]
+        if bn1.training:
+            cnt1, cnt2 = ops.cooc_counts(planes, L, k)
+            n_pos = planes.shape[0] * (L - k + 1)
+            scale, shift, _, _ = ops.bn1_train_prepare(cnt1, cnt2, n_pos, cw, cb, g1, be1, bn1.eps,
+                                                       _bn_momentum(bn1), bn1.running_mean, bn1.running_var)
+            bn1.num_batches_tracked += 1
+        else:
+            scale, shift = ops.bn_fold_eval(g1, be1, bn1.running_mean, bn1.running_var, cb, bn1.eps)
+        return cw, scale, shift
+
+    def forward(self, x, dropout_mask=None):
+        kind = self._kind()
+        planes, L = self._pack(x)
+        conv = self[0]
+        if L < conv.kernel_size[0]:
+            raise ValueError("sequence shorter than the kernel")
+        if kind in ("acts", "pool"):
+            with torch.no_grad():
+                cw, scale, shift = self._front_affine(planes, L)
+                if kind == "acts":
+                    return ops.frontend_acts(planes, L, cw.detach(), scale, shift)[0]
+                return ops.frontend_fwd(planes, L, cw.detach(), scale, shift, need_argmax=False)[0]
+        bn1, fc1, bn2, drop, fc2, bn3 = self[1], self[6], self[7], self[9], self[10], self[11]
+        names = ["linears.0.weight", "linears.0.bias", "linears.1.weight", "linears.1.bias", "linears.6.weight",
+                 "linears.6.bias", "linears.7.weight", "linears.7.bias", "linears.10.weight", "linears.10.bias",
+                 "linears.11.weight", "linears.11.bias"]
+        params = [conv.weight, conv.bias, bn1.weight, bn1.bias, fc1.weight, fc1.bias, bn2.weight, bn2.bias,
+                  fc2.weight, fc2.bias, bn3.weight, bn3.bias]
+        params = [_check_param(p, nme) for p, nme in zip(params, names)]
+        modes = (bn1.training, bn2.training, bn3.training)
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        if all(modes):
+            if need_grad:
+                return _UnitBankFn.apply(planes, L, self, dropout_mask, *params)
+            with torch.no_grad():
+                return _UnitBankFn.forward(_NoCtx(), planes, L, self, dropout_mask, *[p.detach() for p in params])
+        if need_grad:
+            raise NotImplementedError("backward through eval-mode BatchNorm is not implemented: "
+                                      "call model.train() for training steps or wrap inference in torch.no_grad()")
+        if any(modes):
+            raise NotImplementedError("mixed train/eval BatchNorm modes inside the unit bank are not supported")
+        with torch.no_grad():
+            cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = [p.detach() for p in params]
+            scale1, shift1 = ops.bn_fold_eval(g1, be1, bn1.running_mean, bn1.running_var, cb, bn1.eps)
+            pool, _, _ = ops.frontend_fwd(planes, L, cw, scale1, shift1, need_argmax=False)
+            hpre = ops.fc1_fwd(pool, w1, b1)
+            scale2, shift2 = ops.bn_fold_eval(g2, be2, bn2.running_mean, bn2.running_var, None, bn2.eps)
+            p = float(drop.p) if drop.training else 0.0
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and dropout_mask is None) else 0
+            opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, dropout_mask)
+            scale3, shift3 = ops.bn_fold_eval(g3, be3, bn3.running_mean, bn3.running_var, None, bn3.eps)
+            o, _ = ops.head_fwd(opre, scale3, shift3)
+            return o
+
+
+class _NoCtx:
+    """Stand-in ctx so the training forward can run without recording a graph."""
+
+    def save_for_backward(self, *a):
+        pass
+
+
+class PackedDNA:
+    """A batch already in the packed `planes` layout (include/explainn_b200.h) plus its length."""
+
+    def __init__(self, planes, length):
+        self.planes = planes
+        self.length = int(length)
+
+    @classmethod
+    def from_onehot(cls, x):
+        return cls(ops.pack_onehot(x), x.shape[2])
+
+    def revcomp(self):
+        return PackedDNA(ops.revcomp_planes(self.planes, self.length), self.length)
+
+    def __len__(self):
+        return self.planes.shape[0]
+
+
+class _Model(nn.Module):
+
+    def load_weights(self, weight_file):
+        """Legacy loader (architectures/__init__.py:27-39): values are matched to keys by
+        position and a trailing size-1 dimension is squeezed."""
+        sd = torch.load(weight_file)
+        keys = list(self.state_dict().keys())
+        remapped = OrderedDict()
+        for key, v in zip(keys, sd.values()):
+            if v.dim() > 1 and v.shape[-1] == 1:
+                v = v.squeeze(-1)
+            remapped[key] = v
+        self.load_state_dict(remapped)
+
+
+class ExplaiNN(_Model):
+    """ExplaiNN: explainable neural networks -- B200-native drop-in (architectures/__init__.py:41-114)."""
+
+    def __init__(self, cnn_units, kernel_size, sequence_length, n_features=1, weights_file=None):
+        super().__init__()
+        self._options = {
+            "cnn_units": cnn_units,
+            "kernel_size": kernel_size,
+            "sequence_length": sequence_length,
+            "n_features": n_features,
+            "weights_file": weights_file,
+        }
+        n = math.floor((sequence_length - kernel_size + 1) / 7.)
+        self._channels_after_maxpool = n
+        # same construction order as the reference, so the same seed gives the same initial weights
+        self.linears = UnitBank(
+            FusedConv1d(in_channels=4 * cnn_units, out_channels=cnn_units, kernel_size=kernel_size,
+                        groups=cnn_units),
+            FusedBatchNorm1d(cnn_units),
+            ExpAct(),
+            _FusedMaxPool1d(7, 7),
+            _FusedFlatten(),
+            UnSqueeze(),
+            FusedConv1d(in_channels=n * cnn_units, out_channels=100 * cnn_units, kernel_size=1, groups=cnn_units),
+            FusedBatchNorm1d(100 * cnn_units, 1e-05, 0.1, True),
+            _FusedReLU(),
+            _FusedDropout(0.3),
+            FusedConv1d(in_channels=100 * cnn_units, out_channels=cnn_units, kernel_size=1, groups=cnn_units),
+            FusedBatchNorm1d(cnn_units, 1e-05, 0.1, True),
+            _FusedReLU(),
+            _FusedFlatten(),
+        )
+        self.final = FusedLinear(cnn_units, n_features)
+        if weights_file is not None:
+            self.load_weights(weights_file)
+
+    def forward(self, x, dropout_mask=None):
+        """x: float32 one-hot (B,4,L) on CUDA (or PackedDNA) -> logits (B,F).  The reference's
+        `x.repeat(1, cnn_units, 1)` (:111) is never materialised."""
+        return self.final(self.linears(x, dropout_mask=dropout_mask))
+
+
+class PWM(nn.Module):
+    """PWM scorer (architectures/__init__.py:116-170): log-odds correlation on both strands,
+    per-sequence max or sum, as one fused scan kernel."""
+
+    def __init__(self, pwms, sequence_length, scoring="sum"):
+        super().__init__()
+        groups, _, kernel_size = pwms.shape
+        self._options = {
+            "groups": groups,
+            "kernel_size": kernel_size,
+            "sequence_length": sequence_length,
+            "scoring": scoring,
+        }
+        self.conv1d = FusedConv1d(in_channels=4 * groups, out_channels=groups, kernel_size=kernel_size,
+                                  groups=groups)
+        self.conv1d.bias.data = torch.zeros(groups)
+        self.conv1d.weight.data = torch.as_tensor(pwms, dtype=torch.float32).clone()
+        for p in self.conv1d.parameters():
+            p.requires_grad = False
+
+    def forward(self, x, return_argmax=False):
+        if isinstance(x, PackedDNA):
+            planes, L = x.planes, x.length
+        else:
+            if not x.is_cuda:
+                raise RuntimeError("explainn_b200 runs on CUDA tensors only; there is no CPU fallback")
+            planes, L = ops.pack_onehot(x), x.shape[2]
+        w = _check_param(self.conv1d.weight, "conv1d.weight")
+        mode = "max" if self._options["scoring"] == "max" else "sum"
+        out, arg = ops.pwm_scan(planes, L, w, mode, want_argmax=return_argmax and mode == "max")
+        return (out, arg) if return_argmax else out
+
+
+def get_loss(input_data="binary"):
+    """architectures/__init__.py:446-456"""
+    return nn.BCEWithLogitsLoss() if input_data == "binary" else nn.MSELoss()
+
+
+def get_metrics(input_data="binary"):
+    """architectures/__init__.py:458-461 (host-side metrics, imported lazily)"""
+    if input_data == "binary":
+        from sklearn.metrics import average_precision_score, roc_auc_score
+        return dict(aucROC=roc_auc_score, aucPR=average_precision_score)
+    from scipy.stats import pearsonr, spearmanr
+    return dict(Pearson=pearsonr, Spearman=spearmanr)
+
+
+def get_optimizer(params, lr=1e-03):
+    """architectures/__init__.py:463-464: Adam with torch defaults; the update runs in the fused
+    xnn_adam_step kernel and the state layout stays torch.optim.Adam's."""
+    from .optim import FusedAdam
+    return FusedAdam(params, lr=lr)

@@ -1,0 +1,393 @@
+"""Torch-tensor wrappers over the C-ABI entry points (include/explainn_b200.h).
+
+PyTorch is plumbing here: it owns device memory and the current stream; every
+computation is a hand-written sm_100a kernel in explainn_b200/csrc.  All ops raise
+on non-CUDA tensors -- there is no CPU fallback.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+HIDDEN = 100  # explainn/architectures/__init__.py:86
+POOL = 7      # explainn/architectures/__init__.py:81
+
+_launches = 0  # C-ABI calls issued (bench.py reports kernel launches from the per-call table below)
+
+# kernels launched by each entry point (for bench.py's gpu_launches claim)
+KERNELS_PER_CALL = {
+    "xnn_pack_onehot_f32": 1, "xnn_pack_ascii": 1, "xnn_unpack_onehot_f32": 1, "xnn_revcomp_planes": 1,
+    "xnn_cooc_counts": 1, "xnn_bn1_train_prepare": 1, "xnn_bn_fold_eval": 1, "xnn_frontend_fwd": 1,
+    "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
+    "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
+    "xnn_frontend_bwd": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
+    "xnn_pwm_scan": 1, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
+}
+kernel_launches = 0
+
+
+def _call(name, *args):
+    global _launches, kernel_launches
+    lib = _lib.load()
+    _launches += 1
+    kernel_launches += KERNELS_PER_CALL.get(name, 1)
+    _lib.check(getattr(lib, name)(*args), name)
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _req(t, dtype, name, contiguous=True):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name}: expected a torch.Tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: explainn_b200 kernels run on CUDA tensors only (got {t.device}); "
+                           "there is no CPU fallback")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+    if contiguous and not t.is_contiguous():
+        raise ValueError(f"{name}: expected a contiguous tensor")
+    return t
+
+
+def planes_words(L):
+    return (L + 31) // 32
+
+
+def sm_count():
+    out = ctypes.c_int(0)
+    _lib.check(_lib.load().xnn_sm_count(ctypes.byref(out)), "xnn_sm_count")
+    return out.value
+
+
+# ---- a16: encoding -------------------------------------------------------------
+def pack_onehot(x, check=False):
+    """float32 one-hot (B,C>=4,L) (channels 0..3 are read) -> planes int32 (B,3,ceil(L/32)).
+
+    Mirrors the input contract of explainn/sequence/__init__.py:8-29 (all-zero column = N)."""
+    _req(x, torch.float32, "x", contiguous=False)
+    if x.dim() != 3 or x.shape[1] < 4:
+        raise ValueError("x must be (B, 4*m, L)")
+    if x.stride(2) != 1:
+        x = x.contiguous()
+    B, _, L = x.shape
+    planes = torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=x.device)
+    bad = torch.zeros(1, dtype=torch.int32, device=x.device) if check else None
+    _call("xnn_pack_onehot_f32", _p(x), x.stride(0), x.stride(1), B, L, _p(planes), _p(bad), _stream())
+    if check and int(bad.item()) != 0:
+        raise ValueError("input has columns that are neither one-hot nor all-zero")
+    return planes
+
+
+def pack_ascii(seqs):
+    """uint8 ASCII (B,L) -> planes."""
+    _req(seqs, torch.uint8, "seqs")
+    B, L = seqs.shape
+    planes = torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=seqs.device)
+    _call("xnn_pack_ascii", _p(seqs), seqs.stride(0), B, L, _p(planes), _stream())
+    return planes
+
+
+def unpack_onehot(planes, L):
+    _req(planes, torch.int32, "planes")
+    B = planes.shape[0]
+    x = torch.empty((B, 4, L), dtype=torch.float32, device=planes.device)
+    _call("xnn_unpack_onehot_f32", _p(planes), B, L, _p(x), _stream())
+    return x
+
+
+def revcomp_planes(planes, L):
+    _req(planes, torch.int32, "planes")
+    out = torch.empty_like(planes)
+    _call("xnn_revcomp_planes", _p(planes), planes.shape[0], L, _p(out), _stream())
+    return out
+
+
+# ---- a3: front end -----------------------------------------------------------------
+def cooc_counts(planes, L, k):
+    _req(planes, torch.int32, "planes")
+    cnt1 = torch.zeros(4 * k, dtype=torch.int64, device=planes.device)
+    cnt2 = torch.zeros((4 * k, 4 * k), dtype=torch.int64, device=planes.device)
+    _call("xnn_cooc_counts", _p(planes), planes.shape[0], L, k, _p(cnt1), _p(cnt2), _stream())
+    return cnt1, cnt2
+
+
+def bn1_train_prepare(cnt1, cnt2, n_pos, conv_w, conv_b, gamma, beta, eps, momentum, running_mean, running_var):
+    U, _, k = conv_w.shape
+    dev = conv_w.device
+    scale = torch.empty(U, dtype=torch.float32, device=dev)
+    shift = torch.empty(U, dtype=torch.float32, device=dev)
+    stats = torch.empty((U, 4), dtype=torch.float64, device=dev)
+    cov_w = torch.empty((U, 4 * k), dtype=torch.float64, device=dev)
+    _call("xnn_bn1_train_prepare", _p(cnt1), _p(cnt2), int(n_pos), _p(_req(conv_w, torch.float32, "conv_w")),
+          _p(conv_b), _p(gamma), _p(beta), float(eps), float(momentum), U, k, _p(running_mean), _p(running_var),
+          _p(scale), _p(shift), _p(stats), _p(cov_w), _stream())
+    return scale, shift, stats, cov_w
+
+
+def bn_fold_eval(gamma, beta, running_mean, running_var, pre_bias, eps):
+    C = gamma.numel()
+    scale = torch.empty(C, dtype=torch.float32, device=gamma.device)
+    shift = torch.empty(C, dtype=torch.float32, device=gamma.device)
+    _call("xnn_bn_fold_eval", _p(_req(gamma, torch.float32, "gamma")), _p(beta), _p(running_mean),
+          _p(running_var), _p(pre_bias), float(eps), C, _p(scale), _p(shift), _stream())
+    return scale, shift
+
+
+def frontend_fwd(planes, L, conv_w, scale, shift, need_argmax):
+    _req(planes, torch.int32, "planes")
+    _req(conv_w, torch.float32, "conv_w")
+    B = planes.shape[0]
+    U, _, k = conv_w.shape
+    n = (L - k + 1) // POOL
+    dev = planes.device
+    pool = torch.empty((B, U, n), dtype=torch.float32, device=dev)
+    zmax = torch.empty((B, U, n), dtype=torch.float32, device=dev) if need_argmax else None
+    arg = torch.empty((B, U, n), dtype=torch.uint8, device=dev) if need_argmax else None
+    _call("xnn_frontend_fwd", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(pool), _p(zmax),
+          _p(arg), _stream())
+    return pool, zmax, arg
+
+
+def frontend_acts(planes, L, conv_w, scale, shift, f32=True, f16=False):
+    _req(planes, torch.int32, "planes")
+    _req(conv_w, torch.float32, "conv_w")
+    B = planes.shape[0]
+    U, _, k = conv_w.shape
+    Lc = L - k + 1
+    dev = planes.device
+    a32 = torch.empty((B, U, Lc), dtype=torch.float32, device=dev) if f32 else None
+    a16 = torch.empty((B, U, Lc), dtype=torch.float16, device=dev) if f16 else None
+    _call("xnn_frontend_acts", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(a32), _p(a16),
+          _stream())
+    return a32, a16
+
+
+# ---- a4/a5: MLP + final -------------------------------------------------------------
+def fc1_fwd(pool, w1, b1):
+    B, U, n = pool.shape
+    hpre = torch.empty((B, U, HIDDEN), dtype=torch.float32, device=pool.device)
+    _call("xnn_fc1_fwd", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")), _p(b1), B, U, n,
+          _p(hpre), _stream())
+    return hpre
+
+
+def _work(nbytes, dev):
+    return torch.empty((int(nbytes) + 7) // 8, dtype=torch.float64, device=dev)
+
+
+def bn_train_prepare(x2d, gamma, beta, eps, momentum, running_mean, running_var):
+    """x2d: (B, C) view of the BatchNorm input; returns scale, shift, stats."""
+    B, C = x2d.shape
+    if B < 2:
+        raise ValueError("Expected more than 1 value per channel when training")
+    lib = _lib.load()
+    dev = x2d.device
+    scale = torch.empty(C, dtype=torch.float32, device=dev)
+    shift = torch.empty(C, dtype=torch.float32, device=dev)
+    stats = torch.empty((C, 4), dtype=torch.float64, device=dev)
+    work = _work(lib.xnn_bn_work_bytes(B, C), dev)
+    _call("xnn_bn_train_prepare", _p(_req(x2d, torch.float32, "x")), B, C, _p(gamma), _p(beta), float(eps),
+          float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift), _p(stats), _p(work), _stream())
+    return scale, shift, stats
+
+
+def fc2_fwd(hpre, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None):
+    B, U, _ = hpre.shape
+    opre = torch.empty((B, U), dtype=torch.float32, device=hpre.device)
+    if mask is not None:
+        _req(mask, torch.uint8, "mask")
+    _call("xnn_fc2_fwd", _p(_req(hpre, torch.float32, "hpre")), _p(scale2), _p(shift2),
+          _p(_req(w2, torch.float32, "w2")), _p(b2), B, U, float(drop_p), int(seed), _p(mask), _p(opre), _stream())
+    return opre
+
+
+def head_fwd(opre, scale3, shift3, wf=None, bf=None):
+    B, U = opre.shape
+    o = torch.empty((B, U), dtype=torch.float32, device=opre.device)
+    logits = None
+    F = 1
+    if wf is not None:
+        F = wf.shape[0]
+        logits = torch.empty((B, F), dtype=torch.float32, device=opre.device)
+    _call("xnn_head_fwd", _p(_req(opre, torch.float32, "opre")), _p(scale3), _p(shift3), _p(wf), _p(bf), B, U, F,
+          _p(o), _p(logits), _stream())
+    return o, logits
+
+
+def linear_fwd(x, w, b):
+    B, U = x.shape
+    F = w.shape[0]
+    y = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    _call("xnn_linear_fwd", _p(_req(x, torch.float32, "x")), _p(_req(w, torch.float32, "w")),
+          _p(_req(b, torch.float32, "b")), B, U, F, _p(y), _stream())
+    return y
+
+
+# ---- a6: backward ----------------------------------------------------------------------
+def linear_bwd(dy, w, x):
+    B, F = dy.shape
+    U = w.shape[1]
+    dev = dy.device
+    lib = _lib.load()
+    dx = torch.empty((B, U), dtype=torch.float32, device=dev)
+    dw = torch.empty((F, U), dtype=torch.float32, device=dev)
+    db = torch.empty(F, dtype=torch.float32, device=dev)
+    work = _work(lib.xnn_linear_bwd_work_bytes(B, U, F), dev)
+    _call("xnn_linear_bwd", _p(_req(dy, torch.float32, "dy")), _p(w), _p(_req(x, torch.float32, "x")), B, U, F,
+          _p(dx), _p(dw), _p(db), _p(work), _stream())
+    return dx, dw, db
+
+
+def bn_bwd(g2d, relu_out, xpre2d, stats, gamma, inplace=True):
+    B, C = g2d.shape
+    dev = g2d.device
+    lib = _lib.load()
+    dgamma = torch.empty(C, dtype=torch.float32, device=dev)
+    dbeta = torch.empty(C, dtype=torch.float32, device=dev)
+    dx = g2d if inplace else torch.empty_like(g2d)
+    work = _work(lib.xnn_bn_work_bytes(B, C), dev)
+    _call("xnn_bn_bwd", _p(_req(g2d, torch.float32, "g")), _p(relu_out), _p(_req(xpre2d, torch.float32, "xpre")),
+          _p(stats), _p(gamma), B, C, _p(dgamma), _p(dbeta), _p(dx), _p(work), _stream())
+    return dgamma, dbeta, dx
+
+
+def fc2_bwd(dopre, hpre, scale2, shift2, w2, drop_p=0.0, seed=0, mask=None):
+    B, U, _ = hpre.shape
+    dev = hpre.device
+    lib = _lib.load()
+    dw2 = torch.empty((U, HIDDEN), dtype=torch.float32, device=dev)
+    db2 = torch.empty(U, dtype=torch.float32, device=dev)
+    g2 = torch.empty_like(hpre)
+    work = _work(lib.xnn_fc2_bwd_work_bytes(B, U), dev)
+    _call("xnn_fc2_bwd", _p(_req(dopre, torch.float32, "dopre")), _p(hpre), _p(scale2), _p(shift2), _p(w2), B, U,
+          float(drop_p), int(seed), _p(mask), _p(dw2), _p(db2), _p(g2), _p(work), _stream())
+    return dw2, db2, g2
+
+
+def fc1_bwd(dhpre, pool, w1):
+    B, U, n = pool.shape
+    dev = pool.device
+    lib = _lib.load()
+    dw1 = torch.empty((U * HIDDEN, n), dtype=torch.float32, device=dev)
+    db1 = torch.empty(U * HIDDEN, dtype=torch.float32, device=dev)
+    dy = torch.empty_like(pool)
+    work = _work(lib.xnn_fc1_bwd_work_bytes(B, U, n), dev)
+    _call("xnn_fc1_bwd", _p(_req(dhpre, torch.float32, "dhpre")), _p(pool), _p(w1), B, U, n, _p(dw1), _p(db1),
+          _p(dy), _p(work), _stream())
+    return dw1, db1, dy
+
+
+def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos):
+    B, U, n = dy.shape
+    dev = dy.device
+    lib = _lib.load()
+    dconv_w = torch.empty((U, 4, k), dtype=torch.float32, device=dev)
+    dconv_b = torch.empty(U, dtype=torch.float32, device=dev)
+    dgamma = torch.empty(U, dtype=torch.float32, device=dev)
+    dbeta = torch.empty(U, dtype=torch.float32, device=dev)
+    work = _work(lib.xnn_frontend_bwd_work_bytes(B, U, k), dev)
+    _call("xnn_frontend_bwd", _p(planes), B, L, U, k, _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
+          _p(gamma), _p(stats), _p(cov_w), _p(cnt1), int(n_pos), _p(dconv_w), _p(dconv_b), _p(dgamma), _p(dbeta),
+          _p(work), _stream())
+    return dconv_w, dconv_b, dgamma, dbeta
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
+    for t, nme in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        _req(t, torch.float32, nme)
+    _call("xnn_adam_step", _p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), float(lr), float(beta1),
+          float(beta2), float(eps), float(weight_decay), int(step), float(grad_scale), _stream())
+
+
+# ---- a7-a10: interpret ----------------------------------------------------------------------
+def act_max(planes, L, conv_w, scale, shift, idx=None):
+    """fp16-rounded per-unit maximum activation over the listed sequences -> float32 (U,)."""
+    B = planes.shape[0]
+    U, _, k = conv_w.shape
+    n_idx = B if idx is None else idx.numel()
+    bits = torch.zeros(U, dtype=torch.int32, device=planes.device)
+    if idx is not None:
+        _req(idx, torch.int32, "idx")
+    _call("xnn_act_max", _p(_req(planes, torch.int32, "planes")), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
+          _p(idx), n_idx, _p(bits), _stream())
+    return bits.view(torch.float32)
+
+
+def site_counts(planes, L, conv_w, scale, shift, thr, idx=None):
+    B = planes.shape[0]
+    U, _, k = conv_w.shape
+    n_idx = B if idx is None else idx.numel()
+    counts = torch.zeros((U, n_idx), dtype=torch.int32, device=planes.device)
+    _call("xnn_site_counts", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
+          _p(_req(thr, torch.float32, "thr")), _p(idx), n_idx, _p(counts), _stream())
+    return counts
+
+
+def site_emit(planes, L, conv_w, scale, shift, thr, offsets, cap, idx=None, pfm=None, sites=None):
+    B = planes.shape[0]
+    U, _, k = conv_w.shape
+    n_idx = B if idx is None else idx.numel()
+    if pfm is None:
+        pfm = torch.zeros((U, 4, k), dtype=torch.int32, device=planes.device)
+    site_cap = 0 if sites is None else sites.shape[1]
+    _call("xnn_site_emit", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(thr), _p(idx), n_idx,
+          _p(_req(offsets, torch.int64, "offsets")), int(cap), _p(pfm), _p(sites), int(site_cap), _stream())
+    return pfm
+
+
+# ---- a11: PWM module ---------------------------------------------------------------------------
+def pwm_scan(planes, L, pwm_w, mode, want_argmax=False):
+    B = planes.shape[0]
+    G, _, w = pwm_w.shape
+    out = torch.empty((B, G), dtype=torch.float32, device=planes.device)
+    arg = torch.empty((B, G), dtype=torch.int32, device=planes.device) if want_argmax else None
+    _call("xnn_pwm_scan", _p(_req(planes, torch.int32, "planes")), B, L, G, w,
+          _p(_req(pwm_w, torch.float32, "pwm_w")), 1 if mode == "max" else 0, _p(out), _p(arg), _stream())
+    return out, arg
+
+
+# ---- a13/a14: PWMScan semantics -------------------------------------------------------------------
+def lpm_scan_sum(codes, offsets, lpm, bg, forward_only=False):
+    R = offsets.numel() - 1
+    per_rec = int(bg.dim() == 2)
+    w = lpm.shape[1]
+    out = torch.empty(R, dtype=torch.float64, device=codes.device)
+    _call("xnn_lpm_scan_sum", _p(_req(codes, torch.int8, "codes")), _p(_req(offsets, torch.int64, "offsets")), R, w,
+          _p(_req(lpm, torch.float64, "lpm")), _p(_req(bg, torch.float64, "bg")), per_rec, int(forward_only), _p(out),
+          _stream())
+    return out
+
+
+def lpm_scan_best(codes, offsets, lpm, bg, forward_only=False, tie_cap=16):
+    R = offsets.numel() - 1
+    per_rec = int(bg.dim() == 2)
+    w = lpm.shape[1]
+    dev = codes.device
+    best = torch.empty(R, dtype=torch.float64, device=dev)
+    pos = torch.empty(R, dtype=torch.int32, device=dev)
+    strand = torch.empty(R, dtype=torch.int8, device=dev)
+    nties = torch.empty(R, dtype=torch.int32, device=dev)
+    ties = torch.full((R, max(tie_cap, 1)), -1, dtype=torch.int32, device=dev)
+    _call("xnn_lpm_scan_best", _p(_req(codes, torch.int8, "codes")), _p(_req(offsets, torch.int64, "offsets")), R, w,
+          _p(_req(lpm, torch.float64, "lpm")), _p(_req(bg, torch.float64, "bg")), per_rec, int(forward_only), _p(best),
+          _p(pos), _p(strand), _p(nties), _p(ties), int(tie_cap), _stream())
+    return best, pos, strand, nties, ties
+
+
+def ipwm_scan_best(codes, offsets, pwm, forward_only=False):
+    R = offsets.numel() - 1
+    w = pwm.shape[1]
+    dev = codes.device
+    best = torch.empty(R, dtype=torch.int32, device=dev)
+    pos = torch.empty(R, dtype=torch.int32, device=dev)
+    strand = torch.empty(R, dtype=torch.int8, device=dev)
+    _call("xnn_ipwm_scan_best", _p(_req(codes, torch.int8, "codes")), _p(_req(offsets, torch.int64, "offsets")), R, w,
+          _p(_req(pwm, torch.int32, "pwm")), int(forward_only), _p(best), _p(pos), _p(strand), _stream())
+    return best, pos, strand

@@ -1,0 +1,434 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the golden vectors of the reference.
+
+Tolerances (BASELINE.json north_star): logits and unit activations within 1e-5 relative in fp32;
+site indices, arg-max positions and integer scores bit-exact.  `assert_close` adds an absolute
+floor of 1e-5 * max|ref| because a relative error on entries near zero is ill-posed.
+"""
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import _util as U
+from oracle import explainn_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _model_from_golden(d, train=False):
+    from explainn_b200.architectures import ExplaiNN
+    Uu, k, L, F, _ = [int(v) for v in d["opts"]]
+    m = ExplaiNN(Uu, k, L, F)
+    m.load_state_dict(U.golden_sd(d))
+    m.to(DEV)
+    m.train(train)
+    return m
+
+
+def _random_model(Uu, k, L, F, seed=0, bn_seed=7):
+    from explainn_b200.architectures import ExplaiNN
+    torch.manual_seed(seed)
+    m = ExplaiNN(Uu, k, L, F)
+    g = torch.Generator().manual_seed(bn_seed)
+    with torch.no_grad():
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.BatchNorm1d):
+                n = mod.num_features
+                mod.running_mean.copy_(torch.randn(n, generator=g) * 0.1)
+                mod.running_var.copy_(torch.rand(n, generator=g) + 0.5)
+                mod.weight.copy_(torch.rand(n, generator=g) + 0.5)
+                mod.weight[torch.rand(n, generator=g) < 0.1] *= -1
+                mod.bias.copy_(torch.randn(n, generator=g) * 0.1)
+    return m
+
+
+def _sd_cpu(m):
+    return {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+
+
+# ---------------------------------------------------------------------------------------------------
+# a16: packing
+# ---------------------------------------------------------------------------------------------------
+def test_pack_roundtrip_and_revcomp():
+    from explainn_b200 import ops
+    for L in (19, 32, 60, 200, 601):
+        x = O.random_onehot(37, L, seed=L, n_frac=0.05)
+        xd = x.to(DEV)
+        planes = ops.pack_onehot(xd, check=True)
+        assert torch.equal(ops.unpack_onehot(planes, L).cpu(), x)
+        # the reference's U-times repeated tensor is accepted as is (only the first 4 channels are read)
+        assert torch.equal(ops.pack_onehot(xd.repeat(1, 3, 1)), planes)
+        rc = ops.unpack_onehot(ops.revcomp_planes(planes, L), L).cpu().numpy()
+        assert np.array_equal(rc, O.rc_one_hot(x.numpy()))
+    bad = torch.full((2, 4, 40), 0.25, device=DEV)
+    with pytest.raises(ValueError):
+        ops.pack_onehot(bad, check=True)
+
+
+def test_pack_ascii_matches_one_hot_encode():
+    from explainn_b200 import sequence as S, ops
+    rng = np.random.default_rng(0)
+    seqs = ["".join(rng.choice(list("ACGTacgtNnRY"), size=77)) for _ in range(20)]
+    packed = S.pack_strings(seqs, DEV)
+    got = ops.unpack_onehot(packed.planes, 77).cpu().numpy()
+    assert np.array_equal(got, np.stack([O.one_hot_encode(s) for s in seqs]))
+
+
+def test_cooc_counts_brute_force():
+    from explainn_b200 import ops
+    for (B, L, k) in ((5, 40, 19), (9, 67, 11), (3, 33, 32), (4, 200, 19)):
+        x = O.random_onehot(B, L, seed=B * L, n_frac=0.04)
+        cnt1, cnt2 = ops.cooc_counts(ops.pack_onehot(x.to(DEV)), L, k)
+        phi = x.unfold(2, k, 1).permute(0, 2, 1, 3).reshape(-1, 4 * k).double()   # feature index c*k+j
+        assert np.array_equal(cnt1.cpu().numpy(), phi.sum(0).long().numpy())
+        assert np.array_equal(cnt2.cpu().numpy(), (phi.T @ phi).long().numpy())
+
+
+# ---------------------------------------------------------------------------------------------------
+# a1-a5, a7: inference forward
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["eval_small.npz", "eval_cfg1.npz", "eval_k11.npz"])
+def test_eval_forward_golden(name):
+    d = U.load_npz(name)
+    m = _model_from_golden(d)
+    x = torch.tensor(d["x"], device=DEV)
+    with torch.no_grad():
+        logits = m(x)
+        xr = x.repeat(1, m._options["cnn_units"], 1)      # the call pattern of test.py:147-160
+        outs = m.linears(xr)
+        preds = m.final(outs)
+        acts = m.linears[:3](xr)
+    U.assert_close(logits.cpu().numpy(), d["logits"], what="logits")
+    U.assert_close(preds.cpu().numpy(), d["logits"], what="final(linears(x_rep))")
+    U.assert_close(outs.cpu().numpy(), d["outs"], what="unit outputs")
+    U.assert_close(acts.cpu().numpy(), d["acts"], what="activations")
+    ref_pool = torch.nn.functional.max_pool1d(torch.tensor(d["acts"]), 7, 7).numpy()
+    with torch.no_grad():
+        U.assert_close(m.linears[:4](x).cpu().numpy(), ref_pool, what="pooled activations")
+
+
+@pytest.mark.parametrize("cfg", [(300, 19, 60, 66, 64), (300, 19, 600, 50, 6), (33, 24, 100, 2, 17),
+                                 (100, 19, 200, 1, 300)])
+def test_eval_forward_vs_oracle(cfg):
+    Uu, k, L, F, B = cfg
+    m = _random_model(Uu, k, L, F).eval()
+    sd = _sd_cpu(m)
+    m.to(DEV)
+    x = O.random_onehot(B, L, seed=1234, n_frac=0.01)
+    ref = O.explainn_forward(sd, x, train=False)
+    with torch.no_grad():
+        logits = m(x.to(DEV))
+        outs = m.linears(x.to(DEV))
+    U.assert_close(logits.cpu().numpy(), ref["logits"].numpy(), what="logits")
+    U.assert_close(outs.cpu().numpy(), ref["outs"].numpy(), what="unit outputs")
+
+
+def test_packed_input_equals_float_input():
+    from explainn_b200.architectures import PackedDNA
+    m = _random_model(20, 19, 120, 3).eval().to(DEV)
+    x = O.random_onehot(11, 120, seed=3, n_frac=0.02).to(DEV)
+    with torch.no_grad():
+        assert torch.equal(m(x), m(PackedDNA.from_onehot(x)))
+
+
+# ---------------------------------------------------------------------------------------------------
+# a6: training step
+# ---------------------------------------------------------------------------------------------------
+ZERO_CLASS = {"linears.0.bias", "linears.1.bias", "linears.6.bias", "linears.10.bias"}
+
+
+def _check_grads(named_grads, ref_grads, rtol, atol_scale):
+    for k, ref in ref_grads.items():
+        got = named_grads[k].reshape(ref.shape)
+        if k in ZERO_CLASS:
+            # mathematically zero gradients (bias / BN1 shift in front of a train-mode BatchNorm):
+            # the reference returns round-off noise; absolute comparison only
+            assert np.abs(got - ref).max() < 2e-6, k
+        else:
+            U.assert_close(got, ref, rtol=rtol, atol_scale=atol_scale, what="grad " + k)
+
+
+@pytest.mark.parametrize("name,kind", [("train_mse.npz", "linear"), ("train_bce.npz", "binary")])
+def test_train_step_golden(name, kind):
+    from explainn_b200.architectures import get_loss, get_optimizer
+    d = U.load_npz(name)
+    m = _model_from_golden(d, train=True)
+    m.linears[9].p = 0.0
+    opt = get_optimizer(m.parameters(), 0.003)
+    x, y = torch.tensor(d["x"], device=DEV), torch.tensor(d["y"], device=DEV)
+    logits = m(x)
+    loss = get_loss(kind)(logits, y)
+    opt.zero_grad()
+    loss.backward()
+    U.assert_close(logits.detach().cpu().numpy(), d["logits"], what="train-mode logits")
+    U.assert_close(loss.item(), d["loss"], what="loss")
+    grads = {k: p.grad.detach().cpu().numpy() for k, p in m.named_parameters()}
+    _check_grads(grads, {k: d["grad." + k] for k in grads}, rtol=2e-4, atol_scale=2e-5)
+    opt.step()
+    after = _sd_cpu(m)
+    for k in after:
+        if k.endswith("num_batches_tracked"):
+            assert int(after[k]) == int(d["after." + k])
+        elif "running" in k:
+            U.assert_close(after[k].numpy(), d["after." + k], what=k)
+        elif k not in ZERO_CLASS:
+            # Adam normalises the step: parameters agree wherever the gradient is not noise-class
+            U.assert_close(after[k].numpy(), d["after." + k], rtol=1e-4, atol_scale=1e-4, what="after " + k)
+
+
+@pytest.mark.parametrize("cfg", [(40, 19, 200, 5, 64, "linear"), (300, 19, 60, 66, 32, "linear"),
+                                 (17, 11, 95, 1, 48, "binary")])
+def test_train_step_vs_fp64_oracle(cfg):
+    """gradients against the fp64 evaluation of the oracle, with an injected dropout mask (p = 0.3)"""
+    from explainn_b200.architectures import get_loss
+    Uu, k, L, F, B, kind = cfg
+    m = _random_model(Uu, k, L, F).train()
+    sd = _sd_cpu(m)
+    m.to(DEV)
+    x = O.random_onehot(B, L, seed=99, n_frac=0.01)
+    g = torch.Generator().manual_seed(5)
+    y = torch.randn(B, F, generator=g) if kind == "linear" else (torch.rand(B, F, generator=g) < 0.5).float()
+    mask = (torch.rand(B, Uu, 100, generator=g) >= 0.3).to(torch.uint8)
+    ref = O.explainn_train_step(sd, x, y, kind, dropout_mask=mask, dtype=torch.float64)
+    logits = m(x.to(DEV), dropout_mask=mask.to(DEV))
+    loss = get_loss(kind)(logits, y.to(DEV))
+    loss.backward()
+    U.assert_close(logits.detach().cpu().numpy(), ref["logits"].numpy(), what="logits")
+    U.assert_close(loss.item(), ref["loss"].numpy(), what="loss")
+    grads = {k_: p.grad.detach().cpu().numpy() for k_, p in m.named_parameters()}
+    for k_, r in ref["grads"].items():
+        got = grads[k_].reshape(r.shape)
+        if k_ in ZERO_CLASS:
+            assert np.abs(got).max() < 2e-6 * max(1.0, float(np.abs(r.numpy()).max()) * 1e6), k_
+        else:
+            U.assert_close(got, r.numpy(), rtol=1e-4, atol_scale=1e-5, what="grad " + k_)
+    after = _sd_cpu(m)
+    for k_, v in ref["running"].items():
+        U.assert_close(after[k_].numpy(), v.numpy(), what=k_)
+
+
+def test_dropout_statistics_and_determinism():
+    m = _random_model(16, 19, 80, 2).train().to(DEV)
+    x = O.random_onehot(64, 80, seed=1).to(DEV)
+    torch.manual_seed(3)
+    a = m(x)
+    torch.manual_seed(3)
+    b = m(x)
+    torch.manual_seed(4)
+    c = m(x)
+    assert torch.equal(a, b) and not torch.equal(a, c)
+
+
+def test_fused_adam_matches_torch_adam():
+    from explainn_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    p = torch.randn(10007, generator=g)
+    ref_p = p.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref_p], lr=0.003)
+    pd, m, v = p.to(DEV), torch.zeros(10007, device=DEV), torch.zeros(10007, device=DEV)
+    for step in range(1, 4):
+        grad = torch.randn(10007, generator=g)
+        ref_p.grad = grad.clone()
+        opt.step()
+        ops.adam_step(pd, grad.to(DEV), m, v, 0.003, 0.9, 0.999, 1e-8, 0.0, step)
+        U.assert_close(pd.cpu().numpy(), ref_p.detach().numpy(), rtol=2e-6, what=f"adam step {step}")
+
+
+# ---------------------------------------------------------------------------------------------------
+# a7-a10: interpret
+# ---------------------------------------------------------------------------------------------------
+def test_interpret_golden():
+    from explainn_b200 import interpret as I
+    d = U.load_npz("interpret_small.npz")
+    e = U.load_npz("eval_small.npz")
+    m = _model_from_golden(e)
+    k = int(e["opts"][1])
+    x2 = torch.tensor(d["x2"], device=DEV)
+    codes = O.codes_from_onehot(d["x2"])
+    half = len(codes) // 2
+    for sfx, rc in (("", False), ("_rc", True)):
+        idxs = d["idxs" + sfx]
+        thr = I.act_thresholds(m, x2, idxs, rc)
+        assert thr.dtype == np.float16 and np.array_equal(thr, d["thr" + sfx]), sfx
+        res = I.sites_and_pfms(m, x2, thr, idxs, rc, return_sites=True)
+        for u in range(len(thr)):
+            ref_lines = str(d["sites_fasta" + sfx][u]).splitlines()
+            ref_hdr = [ln for ln in ref_lines if ln.startswith(">")]
+            ref_kmers = [ln for ln in ref_lines if not ln.startswith(">")]
+            got = res["sites"][u]
+            hdr = [f">seq{i + (half if s else 0)}_{'-' if s else '+'}_from={p}_to={p + k}" for i, s, p in got]
+            assert hdr == ref_hdr, (sfx, u)
+            assert res["counts"][u] == len(ref_hdr)
+            assert np.array_equal(res["pfms"][u], O.sites_to_pfm(ref_kmers, k)), (sfx, u)
+
+
+def test_interpret_vs_oracle_with_cap():
+    from explainn_b200 import interpret as I
+    m = _random_model(24, 19, 200, 1).eval()
+    sd = _sd_cpu(m)
+    m.to(DEV)
+    x = O.random_onehot(300, 200, seed=8, n_frac=0.01)
+    acts16 = O.explainn_forward(sd, x, train=False)["acts"].numpy().astype(np.float16)
+    idxs = np.arange(0, 300, 2)
+    thr_ref = O.act_thresholds(acts16, idxs)
+    thr = I.act_thresholds(m, x.to(DEV), idxs)
+    # knife-edge audit: an fp32 1-ulp difference may flip an fp16 rounding of the maximum
+    assert (thr != thr_ref).sum() <= 1
+    codes = O.codes_from_onehot(x.numpy())
+    cap = 57
+    res = I.sites_and_pfms(m, x.to(DEV), thr_ref, idxs, cap=cap, return_sites=True, chunk=64)
+    mismatched_units = 0
+    for u in range(24):
+        ref_sites = O.sites(acts16[:, u, :], idxs, thr_ref[u], cap=cap)
+        got = [tuple(int(v) for v in r) for r in res["sites"][u]]
+        if got != ref_sites:
+            mismatched_units += 1      # knife-edge fp16 flips only; audited below
+            a = acts16[:, u, :].astype(np.float32)
+            sym = set(got) ^ set(ref_sites)
+            for (i, s, p) in sym:
+                assert abs(a[i, p] - float(thr_ref[u])) <= 2 * np.spacing(np.float16(thr_ref[u])).astype(np.float32)
+        else:
+            assert np.array_equal(res["pfms"][u], O.pfm_from_sites(codes, ref_sites, 19))
+            assert res["counts"][u] == len(ref_sites) <= cap
+    assert mismatched_units <= 2
+
+
+def test_acts_outs_preds_dropin():
+    from explainn_b200 import interpret as I
+    d = U.load_npz("interpret_small.npz")
+    m = _model_from_golden(U.load_npz("eval_small.npz"))
+    acts, outs, preds = I.acts_outs_preds(m, torch.tensor(d["x2"], device=DEV), batch_size=5)
+    assert acts.dtype == np.float16 and acts.shape == d["acts16"].shape
+    assert (acts != d["acts16"]).sum() <= max(3, acts.size // 5000)      # fp16 rounding knife edges
+    U.assert_close(outs.astype(np.float32), d["outs16"].astype(np.float32), rtol=2e-3, what="outs16")
+    U.assert_close(preds.astype(np.float32), d["preds16"].astype(np.float32), rtol=2e-3, what="preds16")
+
+
+# ---------------------------------------------------------------------------------------------------
+# a11/a12: PWM module
+# ---------------------------------------------------------------------------------------------------
+def test_pwm_module_golden_and_argmax():
+    from explainn_b200.architectures import PWM
+    d = U.load_npz("pwm_small.npz")
+    x = torch.tensor(d["x"], device=DEV)
+    for scoring in ("max", "sum"):
+        m = PWM(d["pwms_log"], 40, scoring).to(DEV)
+        assert m._options == {"groups": 4, "kernel_size": 12, "sequence_length": 40, "scoring": scoring}
+        U.assert_close(m(x).cpu().numpy(), d[scoring], what=scoring)
+    v, arg = PWM(d["pwms_log"], 40, "max").to(DEV)(x, return_argmax=True)
+    ref_v, ref_i = O.pwm_module_scores(d["pwms_log"], d["x"], "max")
+    assert np.array_equal(arg.cpu().numpy(), ref_i)
+
+
+def test_pwm_module_vs_oracle_wide():
+    from explainn_b200.architectures import PWM
+    rng = np.random.default_rng(3)
+    pw = np.log(np.maximum(rng.dirichlet([0.5] * 4, size=(70, 35)).transpose(0, 2, 1), 1e-4))
+    x = O.random_onehot(9, 300, seed=2, n_frac=0.01)
+    for scoring in ("max", "sum"):
+        got = PWM(pw, 300, scoring).to(DEV)(x.to(DEV)).cpu().numpy()
+        ref, _ = O.pwm_module_scores(pw, x.numpy(), scoring)
+        U.assert_close(got, ref, what=scoring)
+    # size-independent property: max scores are invariant under reverse complement of the input
+    from explainn_b200.architectures import PackedDNA
+    m = PWM(pw, 300, "max").to(DEV)
+    p = PackedDNA.from_onehot(x.to(DEV))
+    assert torch.equal(m(p), m(p.revcomp()))
+
+
+# ---------------------------------------------------------------------------------------------------
+# a13-a15: PWMScan semantics
+# ---------------------------------------------------------------------------------------------------
+def test_pwmscan_reproduces_reference_tool_output():
+    from explainn_b200 import pwmscan
+    g = U.pwmscan_golden()
+    headers, codes, offsets = pwmscan.read_fasta(io.StringIO(g["fasta"]))
+    lpm = U.parse_matrix_text(g["lpm"])
+    ipwm = U.parse_matrix_text(g["pwm"], integer=True)
+    for name, run in g["runs"].items():
+        opts = run["opts"]
+        kw = dict(best="-b" in opts, forward="-f" in opts, unorm="-u" in opts, seqnorm="-q" in opts)
+        if "-w" in opts:
+            kw["pweight"] = float(opts[opts.index("-w") + 1])
+        if "-p" in opts:
+            kw["prob"] = opts[opts.index("-p") + 1]
+        if "--pwm" in opts:
+            ps = pwmscan.PwmScoring(ipwm, mode="pwm", forward="-f" in opts, device=DEV)
+        else:
+            ps = pwmscan.PwmScoring(lpm, mode="lpm", device=DEV, **kw)
+        res = ps.score(codes, offsets)
+        lines = ps.format(headers, codes, offsets, res, nohdr="-r" in opts)
+        assert lines == run["stdout"].splitlines(), name
+
+
+def test_pwmscan_vs_c_oracle_random():
+    from explainn_b200 import ops
+    rng = np.random.default_rng(11)
+    lengths = [0 + 40] * 50 + [7, 19, 20, 1000, 5003]
+    codes, offsets = U.random_codes(rng, lengths, n_frac=0.02)
+    for w in (6, 19, 33):
+        lpm = rng.dirichlet([0.6] * 4, size=w).T
+        lpm5 = np.vstack([lpm, np.full((1, w), 0.25)])
+        bg = np.array([0.29, 0.21, 0.21, 0.29, 0.25])
+        cd, od = torch.tensor(codes, device=DEV), torch.tensor(offsets, device=DEV)
+        l5, bgd = torch.tensor(lpm5, device=DEV), torch.tensor(bg, device=DEV)
+        for fwd in (False, True):
+            s = ops.lpm_scan_sum(cd, od, l5, bgd, fwd).cpu().numpy()
+            U.assert_close(s, U.oracle_lpm_sum(codes, offsets, lpm5, bg, fwd), rtol=1e-12, atol_scale=1e-13,
+                           what="lpm sum")
+            best, pos, strand, nties, _ = [t.cpu().numpy() for t in ops.lpm_scan_best(cd, od, l5, bgd, fwd)]
+            rb, rp, rs, rn, _ = U.oracle_lpm_best(codes, offsets, lpm5, bg, fwd)
+            assert np.array_equal(best, rb) and np.array_equal(pos, rp)          # each window product is bit-exact
+            assert np.array_equal(strand, rs) and np.array_equal(nties, rn)
+            ip = np.round(100 * np.log2(lpm / 0.25)).astype(np.int32)
+            p5 = np.vstack([ip, np.full((1, w), -2 ** 31)]).astype(np.int32)
+            b, p, st = [t.cpu().numpy() for t in ops.ipwm_scan_best(cd, od, torch.tensor(p5, device=DEV), fwd)]
+            ob, op_, os_ = U.oracle_ipwm_best(codes, offsets, p5, fwd)
+            assert np.array_equal(b, ob) and np.array_equal(p, op_) and np.array_equal(st, os_)   # bit-exact
+
+
+# ---------------------------------------------------------------------------------------------------
+# full-size properties (BASELINE.json sizes; no oracle at this scale)
+# ---------------------------------------------------------------------------------------------------
+def test_cfg3_train_step_properties():
+    """cfg3 (300 units, 600 bp, 50 outputs): batch-permutation invariance of loss and gradients (BatchNorm
+    statistics and every reduction are order-independent up to fp32 rounding) and finite outputs."""
+    m = _random_model(300, 19, 600, 50).train().to(DEV)
+    m.linears[9].p = 0.0
+    x = O.random_onehot(256, 600, seed=1234).to(DEV)
+    y = torch.randn(256, 50, generator=torch.Generator().manual_seed(1)).to(DEV)
+    perm = torch.randperm(256, generator=torch.Generator().manual_seed(2)).to(DEV)
+    outs = []
+    for xx, yy in ((x, y), (x[perm].contiguous(), y[perm].contiguous())):
+        m.zero_grad()
+        loss = torch.nn.functional.mse_loss(m(xx), yy)
+        loss.backward()
+        outs.append((loss.item(), {k: p.grad.clone() for k, p in m.named_parameters()}))
+    assert np.isfinite(outs[0][0])
+    U.assert_close(outs[1][0], outs[0][0], what="loss under batch permutation")
+    for k in outs[0][1]:
+        if k not in ZERO_CLASS:
+            U.assert_close(outs[1][1][k].cpu().numpy(), outs[0][1][k].cpu().numpy(), rtol=1e-4, atol_scale=1e-4,
+                           what=k)
+
+
+def test_cfg1_strand_symmetry_property():
+    """interpret path at scale: thresholds over [x ; rc(x)] with rev_complement equal the max of the two
+    single-strand thresholds (fp16 values, exact)."""
+    from explainn_b200 import interpret as I
+    from explainn_b200.architectures import PackedDNA
+    m = _random_model(100, 19, 200, 1).eval().to(DEV)
+    x = O.random_onehot(20000, 200, seed=1234).to(DEV)
+    p = PackedDNA.from_onehot(x)
+    both = PackedDNA(torch.cat((p.planes, p.revcomp().planes)), 200)
+    t_both = I.act_thresholds(m, both, None, True)
+    t_f, t_r = I.act_thresholds(m, p), I.act_thresholds(m, p.revcomp())
+    assert np.array_equal(t_both, np.maximum(t_f, t_r))
+    res = I.sites_and_pfms(m, both, t_both, None, True)
+    assert (res["pfms"].sum(1) <= res["counts"][:, None]).all()      # every site adds at most 1 per column
+    assert (res["pfms"].sum(1).max(1) == res["counts"]).all()        # no N bases in this input: exactly 1

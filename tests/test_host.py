@@ -1,0 +1,120 @@
+"""CPU: host-side logic and the C-ABI surface (no compute calls -- there is no GPU here)."""
+import ctypes
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import _util as U
+from explainn_b200 import _lib
+
+
+def test_library_exports_every_declared_symbol():
+    protos = _lib.parse_header()
+    assert len(protos) >= 30
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in protos:
+        assert hasattr(lib, name), f"{name} declared in include/explainn_b200.h but not exported"
+    assert _lib.load().xnn_version() >= 100
+
+
+def test_work_size_queries_need_no_gpu():
+    lib = _lib.load()
+    assert lib.xnn_bn_work_bytes(4096, 30000) > 0
+    assert lib.xnn_fc1_bwd_work_bytes(4096, 300, 83) > 0
+    assert lib.xnn_frontend_bwd_work_bytes(4096, 300, 19) == 64 * 300 * 78 * 8
+
+
+def test_module_surface_matches_reference_state_dict():
+    from explainn_b200.architectures import ExplaiNN
+    d = U.load_npz("eval_small.npz")
+    Uu, k, L, F, _ = [int(v) for v in d["opts"]]
+    m = ExplaiNN(Uu, k, L, F)
+    sd = m.state_dict()
+    ref = U.golden_sd(d)
+    assert list(sd.keys()) == list(ref.keys())
+    for key in sd:
+        assert tuple(sd[key].shape) == tuple(ref[key].shape), key
+    m.load_state_dict(ref)
+    assert m._options == {"cnn_units": Uu, "kernel_size": k, "sequence_length": L, "n_features": F,
+                          "weights_file": None}
+    assert m.linears[0].weight.shape == (Uu, 4, k) and m.final.weight.shape == (F, Uu)
+    assert m.linears[:3]._kind() == "acts" and m.linears[:4]._kind() == "pool"
+    # same construction order as the reference -> identical default initialisation under the same seed
+    torch.manual_seed(0)
+    m2 = ExplaiNN(100, 19, 200, 1)
+    c = U.load_npz("eval_cfg1.npz")
+    assert np.array_equal(m2.linears[0].weight.detach().numpy(), c["sd.linears.0.weight"])
+    assert np.array_equal(m2.final.weight.detach().numpy(), c["sd.final.weight"])
+
+
+def test_no_cpu_fallback():
+    from explainn_b200.architectures import ExplaiNN, PWM
+    m = ExplaiNN(4, 5, 30, 1).eval()
+    x = torch.zeros(2, 4, 30)
+    with pytest.raises(RuntimeError):
+        m(x)
+    with pytest.raises(RuntimeError):
+        m.linears[0](x)           # layers are parameter holders, not a torch-library path
+    with pytest.raises(RuntimeError):
+        PWM(np.zeros((2, 4, 5)), 30)(x)
+
+
+def test_get_pwms_matches_reference():
+    from explainn_b200 import pwm_scoring
+    d = U.load_npz("pwm_small.npz")
+    pw, names = pwm_scoring.get_pwms(os.path.join(U.GOLDEN, "small.meme"), resize_pwms=True, return_log=True)
+    assert list(names) == list(d["names"])
+    assert np.array_equal(np.asarray(pw), d["pwms_log"])   # bit-exact: same float ops on the host
+    raw, _ = pwm_scoring.get_pwms(os.path.join(U.GOLDEN, "small.meme"))
+    assert [len(p[0]) for p in raw] == list(d["raw_widths"])
+
+
+def test_resize_tie_rule():
+    from explainn_b200.pwm_scoring import resize_pwm
+    cols = [[.7, .1, .1, .1], [.25, .25, .25, .25]]
+    out = resize_pwm(cols, 4)
+    assert len(out) == 4 and out.count([.25, .25, .25, .25]) == 3
+
+
+def test_sequence_helpers():
+    from explainn_b200 import sequence as S
+    from oracle import explainn_oracle as O
+    s = "ACGTNacgtnRYA"
+    assert np.array_equal(S.one_hot_encode(s), O.one_hot_encode(s))
+    assert S.one_hot_decode(S.one_hot_encode(s)) == "ACGTNACGTNNNA"
+    assert S.rc("ACGTNNa") == "tNNACGT"
+    e = S.one_hot_encode("AACGT")
+    assert np.array_equal(S.rc_one_hot_encoding(e), S.one_hot_encode("ACGTT"))
+
+
+def test_fasta_and_matrix_readers():
+    from explainn_b200 import pwmscan
+    g = U.pwmscan_golden()
+    headers, codes, offsets = pwmscan.read_fasta(io.StringIO(g["fasta"]))
+    assert "withN" in headers and "multi" in headers and len(headers) == len(offsets) - 1
+    i = headers.index("multi")
+    assert offsets[i + 1] - offsets[i] == 45          # two sequence lines joined
+    i = headers.index("lower")
+    assert set(codes[offsets[i]:offsets[i + 1]].tolist()) <= {0, 1, 2, 3}
+    assert (codes[offsets[headers.index("withN")]:offsets[headers.index("withN") + 1]] == 4).sum() == 5
+    tmp = os.path.join(U.ROOT, "tests", "golden", "_tmp.lpm")
+    try:
+        open(tmp, "w").write(g["lpm"])
+        m = pwmscan.read_matrix(tmp)
+        assert m.shape == (4, 19) and np.allclose(m, U.parse_matrix_text(g["lpm"]))
+    finally:
+        os.remove(tmp)
+
+
+def test_jaspar_writer_matches_fixture():
+    import json
+    from explainn_b200.interpret import pfm_to_jaspar
+    from oracle import explainn_oracle as O
+    fx = json.load(open(os.path.join(U.GOLDEN, "sites_jaspar_fixtures.json")))
+    for name, pair in fx.items():
+        pfm = O.parse_jaspar(pair["jaspar"])
+        title = pair["jaspar"].splitlines()[0][1:].split(" ", 1)
+        assert pfm_to_jaspar(pfm, title[0], title[1]).strip() == pair["jaspar"].strip(), name
