@@ -42,11 +42,13 @@ pwm_scan_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G
             float best = -INFINITY;      // max mode: value and index on the [fwd | rev] axis
             int bidx = 0x7fffffff;
             for (int p = lane; p < Lw; p += 32) {
+                // sr is summed from the window's last base backwards: the same order in which the
+                // forward score of the reverse-complemented sequence is summed, so scores are
+                // bit-identical under reverse complement of the input
                 float sf = 0.0f, sr = 0.0f;
                 for (int j = 0; j < w; ++j) {
-                    const int c = codes[p + j];
-                    sf += lf[c * w + j];
-                    sr += lr[c * w + j];
+                    sf += lf[(int)codes[p + j] * w + j];
+                    sr += lr[(int)codes[p + w - 1 - j] * w + (w - 1 - j)];
                 }
                 if (mode == 0) {
                     acc += sf + sr;

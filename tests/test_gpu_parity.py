@@ -373,7 +373,7 @@ def test_pwmscan_vs_c_oracle_random():
     codes, offsets = U.random_codes(rng, lengths, n_frac=0.02)
     for w in (6, 19, 33):
         lpm = rng.dirichlet([0.6] * 4, size=w).T
-        lpm5 = np.vstack([lpm, np.full((1, w), 0.25)])
+        lpm5 = np.ascontiguousarray(np.vstack([lpm, np.full((1, w), 0.25)]))
         bg = np.array([0.29, 0.21, 0.21, 0.29, 0.25])
         cd, od = torch.tensor(codes, device=DEV), torch.tensor(offsets, device=DEV)
         l5, bgd = torch.tensor(lpm5, device=DEV), torch.tensor(bg, device=DEV)
@@ -386,7 +386,7 @@ def test_pwmscan_vs_c_oracle_random():
             assert np.array_equal(best, rb) and np.array_equal(pos, rp)          # each window product is bit-exact
             assert np.array_equal(strand, rs) and np.array_equal(nties, rn)
             ip = np.round(100 * np.log2(lpm / 0.25)).astype(np.int32)
-            p5 = np.vstack([ip, np.full((1, w), -2 ** 31)]).astype(np.int32)
+            p5 = np.ascontiguousarray(np.vstack([ip, np.full((1, w), -2 ** 31)]).astype(np.int32))
             b, p, st = [t.cpu().numpy() for t in ops.ipwm_scan_best(cd, od, torch.tensor(p5, device=DEV), fwd)]
             ob, op_, os_ = U.oracle_ipwm_best(codes, offsets, p5, fwd)
             assert np.array_equal(b, ob) and np.array_equal(p, op_) and np.array_equal(st, os_)   # bit-exact
