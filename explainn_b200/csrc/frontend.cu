@@ -289,7 +289,7 @@ static size_t frontend_fwd_smem(int k, int n, int L) {
     return (size_t)5 * k * 32 * 4 + (size_t)32 * ns * (4 + 4 + 1) + Lpad + 16;
 }
 
-extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int k, const float* conv_w,
+extern "C" int xnn_frontend_fwd_lut(const uint32_t* planes, int B, int L, int U, int k, const float* conv_w,
                                 const float* scale, const float* shift, float* pool, float* zmax,
                                 uint8_t* argmax, xnn_stream_t s) {
     XNN_CHECK_ARG(planes && conv_w && scale && shift && pool, "NULL pointer");

@@ -18,7 +18,7 @@ _launches = 0  # C-ABI calls issued (bench.py reports kernel launches from the p
 # kernels launched by each entry point (for bench.py's gpu_launches claim)
 KERNELS_PER_CALL = {
     "xnn_pack_onehot_f32": 1, "xnn_pack_ascii": 1, "xnn_unpack_onehot_f32": 1, "xnn_revcomp_planes": 1,
-    "xnn_cooc_counts": 1, "xnn_bn1_train_prepare": 1, "xnn_bn_fold_eval": 1, "xnn_frontend_fwd": 1,
+    "xnn_cooc_counts": 1, "xnn_bn1_train_prepare": 1, "xnn_bn_fold_eval": 1, "xnn_frontend_fwd": 2, "xnn_frontend_fwd_lut": 1,
     "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
@@ -140,7 +140,7 @@ def bn_fold_eval(gamma, beta, running_mean, running_var, pre_bias, eps):
     return scale, shift
 
 
-def frontend_fwd(planes, L, conv_w, scale, shift, need_argmax):
+def frontend_fwd(planes, L, conv_w, scale, shift, need_argmax, lut=False):
     _req(planes, torch.int32, "planes")
     _req(conv_w, torch.float32, "conv_w")
     B = planes.shape[0]
@@ -150,8 +150,13 @@ def frontend_fwd(planes, L, conv_w, scale, shift, need_argmax):
     pool = torch.empty((B, U, n), dtype=torch.float32, device=dev)
     zmax = torch.empty((B, U, n), dtype=torch.float32, device=dev) if need_argmax else None
     arg = torch.empty((B, U, n), dtype=torch.uint8, device=dev) if need_argmax else None
+    if lut:
+        _call("xnn_frontend_fwd_lut", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(pool), _p(zmax),
+              _p(arg), _stream())
+        return pool, zmax, arg
+    work = _work(_lib.load().xnn_frontend_work_bytes(U, k), dev)
     _call("xnn_frontend_fwd", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(pool), _p(zmax),
-          _p(arg), _stream())
+          _p(arg), _p(work), _stream())
     return pool, zmax, arg
 
 

@@ -100,7 +100,12 @@ int xnn_bn_fold_eval(const float* gamma, const float* beta, const float* running
  *   pool   float [B][U][n]  (required)
  *   zmax   float [B][U][n]  z at the arg-max (NULL in inference)
  *   argmax uint8 [B][U][n]  offset 0..6 of the arg-max (NULL in inference) */
+size_t xnn_frontend_work_bytes(int U, int k);
 int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int k,
+                     const float* conv_w, const float* scale, const float* shift,
+                     float* pool, float* zmax, uint8_t* argmax, void* work, xnn_stream_t s);
+/* debugging cross-check only: the same contract on the FP32 pipe (shared-memory gather-sum) */
+int xnn_frontend_fwd_lut(const uint32_t* planes, int B, int L, int U, int k,
                      const float* conv_w, const float* scale, const float* shift,
                      float* pool, float* zmax, uint8_t* argmax, xnn_stream_t s);
 /* Per-position unit activations = linears[:3] (test.py:159-160):
