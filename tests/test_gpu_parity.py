@@ -201,12 +201,23 @@ def test_train_step_vs_fp64_oracle(cfg):
     U.assert_close(logits.detach().cpu().numpy(), ref["logits"].numpy(), what="logits")
     U.assert_close(loss.item(), ref["loss"].numpy(), what="loss")
     grads = {k_: p.grad.detach().cpu().numpy() for k_, p in m.named_parameters()}
+    # knife-edge units (a ReLU argument or a pool-window runner-up within 5e-6 of the kink in the fp64
+    # oracle) have a discontinuous gradient there: audited and excluded, and there must be few of them
+    knife = ref["knife_units"]
+    assert len(knife) <= max(3, Uu // 10), f"too many knife-edge units: {knife}"
+    keep = np.ones(Uu, dtype=bool)
+    keep[knife] = False
     for k_, r in ref["grads"].items():
         got = grads[k_].reshape(r.shape)
+        rn = r.numpy()
         if k_ in ZERO_CLASS:
-            assert np.abs(got).max() < 2e-6 * max(1.0, float(np.abs(r.numpy()).max()) * 1e6), k_
-        else:
-            U.assert_close(got, r.numpy(), rtol=1e-4, atol_scale=1e-5, what="grad " + k_)
+            assert np.abs(got).max() < 2e-6 * max(1.0, float(np.abs(rn).max()) * 1e6), k_
+            continue
+        if k_ == "final.weight":
+            got, rn = got[:, keep], rn[:, keep]
+        elif k_ != "final.bias":
+            got, rn = got.reshape(Uu, -1)[keep], rn.reshape(Uu, -1)[keep]
+        U.assert_close(got, rn, rtol=1e-4, atol_scale=1e-5, what="grad " + k_)
     after = _sd_cpu(m)
     for k_, v in ref["running"].items():
         U.assert_close(after[k_].numpy(), v.numpy(), what=k_)
