@@ -492,11 +492,20 @@ frontend_bwd_finalize_kernel(const double* __restrict__ part, int slices, int U,
     }
 }
 
-extern "C" size_t xnn_frontend_bwd_work_bytes(int B, int U, int k) {
-    return (size_t)bwd_slices(B) * U * (4 * k + 2) * sizeof(double);
+namespace xnn {
+int frontend_bwd_simt_slices(int B) { return bwd_slices(B); }
+int launch_frontend_bwd_finalize(const double* part, int slices, int U, int k, const float* gamma,
+                                 const double* stats, const double* cov_w, const long long* cnt1, long long n_pos,
+                                 float* dconv_w, float* dconv_b, float* dgamma, float* dbeta, cudaStream_t st) {
+    frontend_bwd_finalize_kernel<<<U, 128, 0, st>>>(part, slices, U, k, gamma, stats, cov_w, cnt1, n_pos, dconv_w,
+                                                    dconv_b, dgamma, dbeta);
+    return cudaGetLastError() != cudaSuccess;
 }
+}  // namespace xnn
 
-extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int k, const float* dy,
+// debugging cross-check only: the same contract on the FP64 pipe (sparse scatter, no tensor cores);
+// work: xnn_frontend_bwd_work_bytes
+extern "C" int xnn_frontend_bwd_simt(const uint32_t* planes, int B, int L, int U, int k, const float* dy,
                                 const float* zmax, const uint8_t* argmax, const float* gamma,
                                 const double* stats, const double* cov_w, const long long* cnt1, long long n_pos,
                                 float* dconv_w, float* dconv_b, float* dgamma, float* dbeta, void* work,

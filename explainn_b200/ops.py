@@ -21,7 +21,7 @@ KERNELS_PER_CALL = {
     "xnn_cooc_counts": 1, "xnn_bn1_train_prepare": 1, "xnn_bn_fold_eval": 1, "xnn_frontend_fwd": 2, "xnn_frontend_fwd_lut": 1,
     "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
-    "xnn_frontend_bwd": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
+    "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
     "xnn_pwm_scan": 1, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
 }
 kernel_launches = 0
@@ -289,7 +289,7 @@ def fc1_bwd(dhpre, pool, w1):
     return dw1, db1, dy
 
 
-def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos):
+def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos, simt=False):
     B, U, n = dy.shape
     dev = dy.device
     lib = _lib.load()
@@ -298,7 +298,8 @@ def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_po
     dgamma = torch.empty(U, dtype=torch.float32, device=dev)
     dbeta = torch.empty(U, dtype=torch.float32, device=dev)
     work = _work(lib.xnn_frontend_bwd_work_bytes(B, U, k), dev)
-    _call("xnn_frontend_bwd", _p(planes), B, L, U, k, _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
+    _call("xnn_frontend_bwd_simt" if simt else "xnn_frontend_bwd", _p(planes), B, L, U, k,
+          _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
           _p(gamma), _p(stats), _p(cov_w), _p(cnt1), int(n_pos), _p(dconv_w), _p(dconv_b), _p(dgamma), _p(dbeta),
           _p(work), _stream())
     return dconv_w, dconv_b, dgamma, dbeta

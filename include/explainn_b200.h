@@ -186,6 +186,13 @@ int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int k,
                      const long long* cnt1, long long n_pos,
                      float* dconv_w, float* dconv_b, float* dgamma, float* dbeta,
                      void* work, xnn_stream_t s);
+/* debugging cross-check only: the same contract as a sparse FP64 scatter (no tensor cores) */
+int xnn_frontend_bwd_simt(const uint32_t* planes, int B, int L, int U, int k,
+                     const float* dy, const float* zmax, const uint8_t* argmax,
+                     const float* gamma, const double* stats, const double* cov_w,
+                     const long long* cnt1, long long n_pos,
+                     float* dconv_w, float* dconv_b, float* dgamma, float* dbeta,
+                     void* work, xnn_stream_t s);
 /* Fused Adam over a flat fp32 buffer (torch.optim.Adam defaults,
  * architectures/__init__.py:463-464): step is the 1-based step count. */
 int xnn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,

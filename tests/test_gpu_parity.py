@@ -153,6 +153,54 @@ def _check_grads(named_grads, ref_grads, rtol, atol_scale):
             U.assert_close(got, ref, rtol=rtol, atol_scale=atol_scale, what="grad " + k)
 
 
+@pytest.mark.parametrize("cfg", [(300, 19, 600, 9), (100, 19, 200, 33), (37, 11, 95, 5), (130, 32, 120, 7),
+                                 (5, 3, 40, 3)])
+def test_frontend_bwd_tensor_core_vs_brute_force(cfg):
+    """conv weight gradient on tcgen05 (Toeplitz MN-major operand) against a brute-force scatter in fp64
+    and against the FP64 SIMT kernel"""
+    from explainn_b200 import ops
+    Uu, k, L, B = cfg
+    n = (L - k + 1) // 7
+    g = torch.Generator().manual_seed(L + Uu)
+    x = O.random_onehot(B, L, seed=3 + L, n_frac=0.02)
+    planes = ops.pack_onehot(x.to(DEV))
+    dy = torch.randn(B, Uu, n, generator=g)
+    zmax = torch.randn(B, Uu, n, generator=g)
+    arg = torch.randint(0, 7, (B, Uu, n), generator=g).to(torch.uint8)
+    conv_w = torch.randn(Uu, 4, k, generator=g) * 0.2
+    gamma = torch.rand(Uu, generator=g) + 0.5
+    cnt1, cnt2 = ops.cooc_counts(planes, L, k)
+    n_pos = B * (L - k + 1)
+    zeros = torch.zeros(Uu, device=DEV)
+    _, _, stats, cov_w = ops.bn1_train_prepare(cnt1, cnt2, n_pos, conv_w.to(DEV), zeros, gamma.to(DEV), zeros, 1e-5,
+                                               0.1, None, None)
+    args = (planes, L, k, dy.to(DEV), zmax.to(DEV), arg.to(DEV), gamma.to(DEV), stats, cov_w, cnt1, n_pos)
+    tc = [t.cpu().numpy() for t in ops.frontend_bwd(*args)]
+    simt = [t.cpu().numpy() for t in ops.frontend_bwd(*args, simt=True)]
+    for a, b_, nme in zip(tc, simt, ("dconv_w", "dconv_b", "dgamma", "dbeta")):
+        U.assert_close(a, b_, rtol=1e-5, atol_scale=2e-6, what=nme + " tc vs simt")
+    # brute force of the sparse scatter term G_u[c,j] = sum dy * x[b,c,7q+arg+j] (fp64)
+    xs = x.numpy().astype(np.float64)
+    G = np.zeros((Uu, 4, k))
+    dyn, an = dy.numpy().astype(np.float64), arg.numpy().astype(np.int64)
+    for b in range(B):
+        for q in range(n):
+            st = 7 * q + an[b, :, q]
+            for j in range(k):
+                G[:, :, j] += dyn[b, :, q, None] * xs[b][:, st + j].T
+    st_ = stats.cpu().numpy()
+    invstd, N = st_[:, 2], float(n_pos)
+    db, dg = dyn.sum(axis=(0, 2)), (dyn * ((zmax.numpy().astype(np.float64) - st_[None, :, 3, None]) *
+                                           invstd[None, :, None])).sum(axis=(0, 2))
+    c1 = cnt1.cpu().numpy().astype(np.float64).reshape(4, k)
+    cw = cov_w.cpu().numpy().reshape(Uu, 4, k)
+    ref = (gamma.numpy().astype(np.float64) * invstd)[:, None, None] * (
+        G - (db / N)[:, None, None] * c1[None] - (dg * invstd)[:, None, None] * cw)
+    U.assert_close(tc[0], ref, rtol=1e-5, atol_scale=2e-6, what="dconv_w vs brute force")
+    U.assert_close(tc[2], dg, rtol=1e-5, atol_scale=2e-6, what="dgamma")
+    U.assert_close(tc[3], db, rtol=1e-5, atol_scale=2e-6, what="dbeta")
+
+
 @pytest.mark.parametrize("name,kind", [("train_mse.npz", "linear"), ("train_bce.npz", "binary")])
 def test_train_step_golden(name, kind):
     from explainn_b200.architectures import get_loss, get_optimizer
