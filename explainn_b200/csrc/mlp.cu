@@ -197,6 +197,17 @@ bn_train_finalize_kernel(const double* __restrict__ part, int tiles, int B, int 
     }
 }
 
+namespace xnn {
+// part: [tiles][2][C] partial (sum, sum of squares) in fp64 -> scale/shift/stats (+ running stats)
+int launch_bn_train_finalize(const double* part, int tiles, int B, int C, const float* gamma, const float* beta,
+                             float eps, float momentum, float* running_mean, float* running_var, float* scale,
+                             float* shift, double* stats, cudaStream_t st) {
+    bn_train_finalize_kernel<<<ceil_div(C, 256), 256, 0, st>>>(part, tiles, B, C, gamma, beta, eps, momentum,
+                                                              running_mean, running_var, scale, shift, stats);
+    return cudaGetLastError() != cudaSuccess;
+}
+}  // namespace xnn
+
 extern "C" int xnn_bn_train_prepare(const float* x, int B, int C, const float* gamma, const float* beta,
                                     float eps, float momentum, float* running_mean, float* running_var,
                                     float* scale, float* shift, double* stats, void* work, xnn_stream_t s) {

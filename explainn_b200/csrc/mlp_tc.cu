@@ -1,0 +1,378 @@
+// a4 / a6 on the tensor cores -- each unit's Linear(n->100) -> BN -> ReLU -> Dropout -> Linear(100->1)
+// (explainn/architectures/__init__.py:84-98) as a grouped GEMM on tcgen05, forward and backward, with the
+// (B, 100*U) hidden activations never written to HBM: every pass recomputes its FC1 tile
+//   hpre_u[b, m] = b1[u,m] + sum_q W1[100u+m, q] * pool[b, u, q]
+// in TMEM (it costs ~1/10 of the HBM traffic it saves) and fuses what follows into the epilogue:
+//   pass F1  BatchNorm statistics of hpre                       (thread = hidden channel, columns = batch)
+//   pass F2  BN + ReLU + dropout + Linear(100->1) -> opre        (thread = batch row, columns = hidden)
+//   pass B1  BN-backward reductions sum g, sum g*x, dW2, db2     (thread = hidden channel)
+//   pass B2  dhpre -> dW1 (accumulated in TMEM), dpool -> dy     (mlp_tc_bwd.cu)
+//
+// fp32 parity on tensor cores: kind::tf32 with an error-compensated split of BOTH operands,
+// x = hi + lo (each tf32, round-to-nearest), x*y ~= hi*hi' + hi*lo' + lo*hi' accumulated in fp32 (TMEM):
+// relative error ~2^-22 per product, i.e. fp32 round-off level.
+//
+// Operand staging (shared memory, no swizzle): an [R rows][K] fp32 matrix is kept as float4 [K/4][R]
+// ("chunk-major").  As a K-major UMMA operand that is LBO = 16R (next 4 K), SBO = 128 (next 8 rows);
+// the SAME bytes read as an MN-major operand (LBO = 128, SBO = 16R) are the transposed matrix, which
+// is how the backward pass gets W1^T, pool^T and dhpre^T without a second copy.
+#include "common.cuh"
+#include "umma.cuh"
+using namespace xnn;
+
+#define MT_THREADS 128
+#define MT_ROWS 128
+#define MT_H XNN_HIDDEN          // 100
+#define MT_NMAX 96               // largest pool width n handled on this path
+#define MT_PHILOX_CALLS 13       // 8 sixteen-bit draws per call -> 104 >= 100 hidden channels
+
+namespace xnn {
+
+__device__ __forceinline__ uint4 philox4(unsigned long long seed, unsigned long long idx) {
+    uint32_t c0 = (uint32_t)idx, c1 = (uint32_t)(idx >> 32), c2 = 0x9E3779B9u, c3 = 0xBB67AE85u;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+// keep-bits of one (sequence, unit) row of the hidden layer: bit m of kb[m/32] = keep channel m.
+// Injected byte mask (tests), or Philox draws (16 bits each, keep if draw >= p*65536), or all ones.
+__device__ __forceinline__ void dropout_keep_bits(float p, unsigned long long seed, long long bu,
+                                                  const uint8_t* __restrict__ mask_u8, uint32_t kb[4]) {
+    kb[0] = kb[1] = kb[2] = kb[3] = 0u;
+    if (mask_u8) {
+        const uint8_t* mr = mask_u8 + bu * MT_H;
+#pragma unroll
+        for (int m = 0; m < MT_H; ++m) kb[m >> 5] |= (mr[m] ? 1u : 0u) << (m & 31);
+    } else if (p > 0.0f) {
+        const uint32_t thr = (uint32_t)(p * 65536.0f + 0.5f);
+#pragma unroll
+        for (int i = 0; i < MT_PHILOX_CALLS; ++i) {
+            const uint4 r = philox4(seed, (unsigned long long)bu * 16ull + (unsigned long long)i);
+            const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                const int m = 8 * i + s;
+                const uint32_t d16 = (w[s >> 1] >> (16 * (s & 1))) & 0xFFFFu;
+                if (m < MT_H) kb[m >> 5] |= (d16 >= thr ? 1u : 0u) << (m & 31);
+            }
+        }
+    } else {
+        kb[0] = kb[1] = kb[2] = 0xFFFFFFFFu; kb[3] = 0xFu;
+    }
+}
+
+// stage one fp32 row (n values, rest zero up to 4*chunks) as tf32 hi / lo float4 chunks:
+// dst_hi[c*R + row], dst_lo[c*R + row]
+__device__ __forceinline__ void stage_row_split(const float* __restrict__ src, int n, int chunks, int R, int row,
+                                                float4* __restrict__ dst_hi, float4* __restrict__ dst_lo) {
+#pragma unroll 4
+    for (int c = 0; c < chunks; ++c) {
+        float v[4], h[4], l[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int q = 4 * c + e;
+            v[e] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) umma::split_tf32(v[e], h[e], l[e]);
+        dst_hi[c * R + row] = make_float4(h[0], h[1], h[2], h[3]);
+        dst_lo[c * R + row] = make_float4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+}  // namespace xnn
+
+struct MlpArgs {
+    const float* pool;      // (B,U,n)
+    const float* w1;        // (100U,n)
+    const float* b1;        // (100U)
+    const float* scale2;    // (100U)   F2 / B1
+    const float* shift2;    // (100U)
+    const float* w2;        // (U,100)
+    const float* b2;        // (U)      F2
+    const float* dopre;     // (B,U)    B1
+    const uint8_t* mask_u8; // (B,U,100) injected dropout mask (F2) or NULL
+    uint32_t* maskbits;     // (B,U,4)  keep bits: written by F2, read by B1 (may be NULL when p == 0 and no mask)
+    float* opre;            // (B,U)    F2
+    double* part;           // [slots][nstat][C] partial sums (F1: 2, B1: 4)
+    int B, U, n, T, slots;
+    float drop_p;
+    unsigned long long seed;
+};
+
+enum { MLP_STATS = 0, MLP_APPLY = 1, MLP_BWD_STATS = 2 };
+
+struct MtShared {
+    uint64_t bar;
+    uint32_t tmem_slot;
+    uint32_t pad;
+};
+
+// ---------------------------------------------------------------------------
+// FC1 tile on tcgen05 + fused epilogue.  One CTA per SM walks a contiguous range of the flattened
+// (unit, batch tile) space, so W1 of a unit is staged once per CTA (at most ~3 units per CTA).
+// ---------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(MT_THREADS)
+mlp_fc1_kernel(MlpArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Kp = (n + 7) & ~7, chunks = Kp >> 2, ksteps = Kp >> 3;
+    const uint32_t piece_bytes = (uint32_t)chunks * 2048u;           // [chunks][128 rows] float4
+    float4* w1s = reinterpret_cast<float4*>(smem_raw);               // [2][chunks][128]
+    float4* ps = reinterpret_cast<float4*>(smem_raw + 2 * piece_bytes);   // [2][chunks][128]
+    unsigned char* tail = smem_raw + 4 * piece_bytes;
+    float4* s_c4 = reinterpret_cast<float4*>(tail);                  // [128] (b1, scale2, shift2, w2) per channel
+    float* s_dopre = reinterpret_cast<float*>(tail + 2048);          // [128]
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 2048 + 512);   // [128][4]
+    MtShared* sh = reinterpret_cast<MtShared*>(tail + 2048 + 512 + 2048);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw);
+        for (uint32_t i = tid; i < 4 * piece_bytes / 16; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 128);
+    if (tid == 0) umma::mbar_init(&sh->bar, 1);
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t w_addr = umma::smem_u32(w1s), p_addr = umma::smem_u32(ps);
+    // F1 / B1: D[hidden][batch] (A = W1, N = 128 batch rows); F2: D[batch][hidden] (A = pool tile, N = 112)
+    constexpr int NDIM = (MODE == MLP_APPLY) ? 112 : 128;
+    const uint32_t idesc = umma::idesc_tf32_f32(128, NDIM, 0, 0);
+    const uint32_t a_addr = (MODE == MLP_APPLY) ? p_addr : w_addr;
+    const uint32_t b_addr = (MODE == MLP_APPLY) ? w_addr : p_addr;
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+
+    int cur_u = -1;
+    uint32_t phase = 0;
+    float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f;   // per-channel constants (thread = channel modes)
+    double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+
+    auto flush = [&](int u) {
+        if (MODE == MLP_APPLY) return;
+        int j = blockIdx.x;
+        const long long start = (long long)u * T;
+        while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+        const int slot = blockIdx.x - j;
+        if (tid < MT_H && slot < a.slots) {
+            const int c = u * MT_H + tid;
+            constexpr int NS = (MODE == MLP_STATS) ? 2 : 4;
+            double* o = a.part + (long long)slot * NS * C + c;
+            o[0] = s1; o[(long long)C] = s2;
+            if (MODE == MLP_BWD_STATS) { o[2LL * C] = s3; o[3LL * C] = s4; }
+        }
+        s1 = s2 = s3 = s4 = 0.0;
+    };
+
+    for (long long tile = lo; tile < hi; ++tile) {
+        const int u = (int)(tile / T), t = (int)(tile % T);
+        const int b0 = t * MT_ROWS, rows = min(MT_ROWS, B - b0);
+        if (u != cur_u) {
+            if (cur_u >= 0) flush(cur_u);
+            cur_u = u;
+            // W1 of this unit: thread m stages row m (rows >= 100 stay zero)
+            if (tid < MT_H)
+                stage_row_split(a.w1 + ((long long)u * MT_H + tid) * n, n, chunks, 128, tid, w1s, w1s + chunks * 128);
+            const int ch = u * MT_H + tid;
+            const bool ok = tid < MT_H;
+            b1m = ok ? a.b1[ch] : 0.f;
+            if (MODE != MLP_STATS) {
+                scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f; w2m = ok ? a.w2[ch] : 0.f;
+                if (MODE == MLP_APPLY) s_c4[tid] = make_float4(b1m, scm, shm, w2m);
+            }
+        }
+        // pool tile: thread r stages batch row b0 + r (zeros past the batch)
+        {
+            const float* src = (tid < rows) ? a.pool + ((long long)(b0 + tid) * U + u) * n : nullptr;
+            stage_row_split(src, n, chunks, 128, tid, ps, ps + chunks * 128);
+        }
+        if (MODE == MLP_BWD_STATS) {
+            const long long bu = (long long)(b0 + tid) * U + u;
+            s_dopre[tid] = (tid < rows) ? a.dopre[bu] : 0.f;
+            uint4 kb = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFu);
+            if (a.maskbits && tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
+            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = kb;
+        }
+        umma::fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            umma::fence_after_sync();
+            uint32_t acc = 0;
+#pragma unroll 1
+            for (int pass = 0; pass < 3; ++pass) {
+                // small terms first: lo*hi, hi*lo, then hi*hi   (piece 0 = hi, 1 = lo)
+                const uint32_t ap = (pass == 0) ? 1u : 0u, bp = (pass == 1) ? 1u : 0u;
+#pragma unroll 1
+                for (int ks = 0; ks < ksteps; ++ks) {
+                    const uint64_t ad = umma::smem_desc(a_addr + ap * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
+                    const uint64_t bd = umma::smem_desc(b_addr + bp * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
+                    umma::mma_tf32(tmem, ad, bd, idesc, acc);
+                    acc = 1;
+                }
+            }
+            umma::commit(&sh->bar);
+        }
+        umma::mbar_wait(&sh->bar, phase);
+        phase ^= 1u;
+        umma::fence_after_sync();
+        const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+
+        if (MODE == MLP_STATS || MODE == MLP_BWD_STATS) {
+            // thread = hidden channel (TMEM lane), columns = batch rows of the tile
+            for (int c0 = 0; c0 < rows; c0 += 16) {
+                uint32_t v[16];
+                umma::tmem_ld16(trow + c0, v);
+                umma::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    if (c0 + i < rows) {
+                        const float x = __uint_as_float(v[i]) + b1m;
+                        if (MODE == MLP_STATS) {
+                            s1 += (double)x;
+                            s2 += (double)x * (double)x;
+                        } else {
+                            const float pre = fmaf(x, scm, shm);
+                            const uint32_t keep = (s_mask[4 * (c0 + i) + (tid >> 5)] >> (tid & 31)) & 1u;
+                            const float ds = keep ? inv_keep : 0.0f;
+                            const float d = s_dopre[c0 + i];
+                            const float hact = fmaxf(pre, 0.0f) * ds;
+                            const float g2 = (pre > 0.0f) ? d * w2m * ds : 0.0f;
+                            s1 += (double)g2;
+                            s2 += (double)g2 * (double)x;
+                            s3 += (double)d * (double)hact;
+                            s4 += (double)d;
+                        }
+                    }
+                }
+            }
+        } else {
+            // thread = batch row, columns = hidden channels
+            const long long bu = (long long)(b0 + tid) * U + u;
+            uint32_t kb[4];
+            if (tid < rows) dropout_keep_bits(a.drop_p, a.seed, bu, a.mask_u8, kb);
+            else { kb[0] = kb[1] = kb[2] = kb[3] = 0u; }
+            float accv = 0.0f;
+#pragma unroll
+            for (int c0 = 0; c0 < 112; c0 += 16) {
+                uint32_t v[16];
+                umma::tmem_ld16(trow + c0, v);
+                umma::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int m = c0 + i;
+                    if (m < MT_H) {
+                        const float4 c4 = s_c4[m];
+                        float h = fmaxf(fmaf(__uint_as_float(v[i]) + c4.x, c4.y, c4.z), 0.0f);
+                        h = ((kb[m >> 5] >> (m & 31)) & 1u) ? h * inv_keep : 0.0f;
+                        accv = fmaf(h, c4.w, accv);
+                    }
+                }
+            }
+            if (tid < rows) {
+                a.opre[bu] = accv + a.b2[u];
+                if (a.maskbits) *reinterpret_cast<uint4*>(a.maskbits + bu * 4) = make_uint4(kb[0], kb[1], kb[2], kb[3]);
+            }
+        }
+        umma::fence_before_sync();
+        __syncthreads();   // accumulator drained, staging buffers free
+    }
+    if (cur_u >= 0) flush(cur_u);
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 128);
+}
+
+namespace xnn {
+int launch_bn_train_finalize(const double* part, int tiles, int B, int C, const float* gamma, const float* beta,
+                             float eps, float momentum, float* running_mean, float* running_var, float* scale,
+                             float* shift, double* stats, cudaStream_t st);
+}
+
+// ---- launch geometry shared by the passes ---------------------------------------------------------
+static int mt_tiles(int B) { return (B + MT_ROWS - 1) / MT_ROWS; }
+static int mt_grid(int B, int U) {
+    const long long tiles = (long long)U * mt_tiles(B);
+    const int sms = num_sms();
+    return (int)(tiles < sms ? tiles : sms);
+}
+// upper bound on the number of CTAs whose range touches one unit
+static int mt_slots(int B, int U) {
+    const int T = mt_tiles(B), G = mt_grid(B, U);
+    const long long per = ((long long)U * T) / G;   // >= 1
+    return (int)((T + per - 1) / per) + 1;
+}
+static size_t mt_smem(int n) {
+    const int chunks = ((n + 7) & ~7) >> 2;
+    return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + sizeof(MtShared) + 16;
+}
+
+template <int MODE>
+static int mt_launch(const MlpArgs& a, cudaStream_t st) {
+    const size_t smem = mt_smem(a.n);
+    if (cudaFuncSetAttribute(mlp_fc1_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return 1;
+    mlp_fc1_kernel<MODE><<<mt_grid(a.B, a.U), MT_THREADS, smem, st>>>(a);
+    return cudaGetLastError() != cudaSuccess;
+}
+
+extern "C" int xnn_mlp_supported(int n) { return n >= 1 && n <= MT_NMAX; }
+
+extern "C" size_t xnn_mlp_bn2_work_bytes(int B, int U) {
+    if (B < 1 || U < 1) return 0;
+    return (size_t)mt_slots(B, U) * 2 * U * MT_H * sizeof(double);
+}
+
+extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
+                                         const float* gamma, const float* beta, float eps, float momentum,
+                                         float* running_mean, float* running_var, float* scale, float* shift,
+                                         double* stats, void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(pool && w1 && b1 && gamma && beta && scale && shift && stats && work, "NULL pointer");
+    XNN_CHECK_ARG(B >= 2 && U >= 1, "train-mode BatchNorm needs more than 1 value per channel");
+    XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
+    cudaStream_t st = to_stream(s);
+    MlpArgs a{};
+    a.pool = pool; a.w1 = w1; a.b1 = b1; a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U);
+    a.part = (double*)work;
+    XNN_CUDA(cudaMemsetAsync(work, 0, xnn_mlp_bn2_work_bytes(B, U), st));
+    if (mt_launch<MLP_STATS>(a, st)) { set_error("xnn_mlp_bn2_train_prepare: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    if (launch_bn_train_finalize(a.part, a.slots, B, U * MT_H, gamma, beta, eps, momentum, running_mean, running_var,
+                                 scale, shift, stats, st)) {
+        set_error("xnn_mlp_bn2_train_prepare: finalize launch failed");
+        return XNN_ERR_CUDA;
+    }
+    return XNN_OK;
+}
+
+extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
+                           const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
+                           unsigned long long seed, const uint8_t* mask, uint32_t* maskbits, float* opre,
+                           xnn_stream_t s) {
+    XNN_CHECK_ARG(pool && w1 && b1 && scale2 && shift2 && w2 && b2 && opre, "NULL pointer");
+    XNN_CHECK_ARG(B >= 0 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
+    XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
+    XNN_CHECK_ARG(maskbits == nullptr || ((uintptr_t)maskbits & 15) == 0, "maskbits must be 16-byte aligned");
+    if (B == 0) return XNN_OK;
+    MlpArgs a{};
+    a.pool = pool; a.w1 = w1; a.b1 = b1; a.scale2 = scale2; a.shift2 = shift2; a.w2 = w2; a.b2 = b2;
+    a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = 0;
+    a.drop_p = drop_p; a.seed = seed; a.mask_u8 = mask; a.maskbits = maskbits; a.opre = opre;
+    if (mt_launch<MLP_APPLY>(a, to_stream(s))) { set_error("xnn_mlp_fwd: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    return XNN_OK;
+}

@@ -22,7 +22,7 @@ KERNELS_PER_CALL = {
     "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
-    "xnn_pwm_scan": 1, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
+    "xnn_pwm_scan": 1, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
 }
 kernel_launches = 0
 
@@ -211,6 +211,42 @@ def fc2_fwd(hpre, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None):
     _call("xnn_fc2_fwd", _p(_req(hpre, torch.float32, "hpre")), _p(scale2), _p(shift2),
           _p(_req(w2, torch.float32, "w2")), _p(b2), B, U, float(drop_p), int(seed), _p(mask), _p(opre), _stream())
     return opre
+
+
+def mlp_supported(n):
+    return bool(_lib.load().xnn_mlp_supported(int(n)))
+
+
+def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var):
+    """BatchNorm (linears.7) batch statistics of hpre = FC1(pool) without materialising hpre (tcgen05)."""
+    B, U, n = pool.shape
+    if B < 2:
+        raise ValueError("Expected more than 1 value per channel when training")
+    lib = _lib.load()
+    dev = pool.device
+    C = U * HIDDEN
+    scale = torch.empty(C, dtype=torch.float32, device=dev)
+    shift = torch.empty(C, dtype=torch.float32, device=dev)
+    stats = torch.empty((C, 4), dtype=torch.float64, device=dev)
+    work = _work(lib.xnn_mlp_bn2_work_bytes(B, U), dev)
+    _call("xnn_mlp_bn2_train_prepare", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")),
+          _p(b1), B, U, n, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var),
+          _p(scale), _p(shift), _p(stats), _p(work), _stream())
+    return scale, shift, stats
+
+
+def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None, want_bits=False):
+    """opre (B,U) = FC2(drop(relu(BN2(FC1(pool))))) in one tcgen05 pass; optional keep-bits (B,U,4) int32."""
+    B, U, n = pool.shape
+    dev = pool.device
+    opre = torch.empty((B, U), dtype=torch.float32, device=dev)
+    bits = torch.empty((B, U, 4), dtype=torch.int32, device=dev) if want_bits else None
+    if mask is not None:
+        _req(mask, torch.uint8, "mask")
+    _call("xnn_mlp_fwd", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")), _p(b1),
+          _p(scale2), _p(shift2), _p(_req(w2, torch.float32, "w2")), _p(b2), B, U, n, float(drop_p), int(seed),
+          _p(mask), _p(bits), _p(opre), _stream())
+    return opre, bits
 
 
 def head_fwd(opre, scale3, shift3, wf=None, bf=None):

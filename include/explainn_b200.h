@@ -142,6 +142,25 @@ int xnn_head_fwd(const float* opre, const float* scale3, const float* shift3,
                  const float* wf, const float* bf, int B, int U, int F,
                  float* o, float* logits, xnn_stream_t s);
 
+/* The same MLP on the tensor cores (tcgen05, kind::tf32 with a hi/lo split of both operands: fp32
+ * round-off level), without ever writing the (B,100U) hidden activations: each pass recomputes its
+ * FC1 tile in TMEM.  Supported for pool widths n <= 96 (xnn_mlp_supported). */
+int xnn_mlp_supported(int n);
+/* train-mode BatchNorm (linears.7) statistics of hpre = FC1(pool): scale2/shift2, stats2[100U][4],
+ * running-stat update -- xnn_fc1_fwd + xnn_bn_train_prepare in one pass over pool. */
+size_t xnn_mlp_bn2_work_bytes(int B, int U);
+int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
+                              const float* gamma, const float* beta, float eps, float momentum,
+                              float* running_mean, float* running_var, float* scale, float* shift,
+                              double* stats, void* work, xnn_stream_t s);
+/* opre[b,u] = b2[u] + sum_m W2[u,m]*drop(relu(scale2*hpre+shift2)) -- xnn_fc1_fwd + xnn_fc2_fwd fused.
+ * Dropout: injected byte mask (B,U,100), else Philox keep-bits from (seed,b,u) when drop_p > 0.
+ * maskbits uint32 [B][U][4] (may be NULL): the keep bits used, for xnn_mlp_bwd. */
+int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
+                const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
+                unsigned long long seed, const uint8_t* mask, uint32_t* maskbits, float* opre,
+                xnn_stream_t s);
+
 /* ---- a6: backward ---------------------------------------------------------
  * autograd of the above (selene/__init__.py:289-292). Gradients are shaped
  * exactly like the reference parameters. */

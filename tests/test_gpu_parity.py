@@ -153,6 +153,58 @@ def _check_grads(named_grads, ref_grads, rtol, atol_scale):
             U.assert_close(got, ref, rtol=rtol, atol_scale=atol_scale, what="grad " + k)
 
 
+@pytest.mark.parametrize("cfg", [(300, 83, 300), (100, 26, 257), (7, 6, 130), (3, 96, 5), (33, 9, 1000)])
+def test_mlp_forward_tensor_core_vs_fp64(cfg):
+    """FC1 -> BN2 statistics -> ReLU -> dropout -> FC2 on tcgen05 (3xTF32) against an fp64 evaluation and
+    against the FP32 FMA kernels"""
+    from explainn_b200 import ops
+    Uu, n, B = cfg
+    g = torch.Generator().manual_seed(n * 1000 + Uu)
+    pool = torch.exp(torch.randn(B, Uu, n, generator=g) * 0.7)
+    w1 = torch.randn(Uu * 100, n, generator=g) / np.sqrt(n)
+    b1 = torch.randn(Uu * 100, generator=g) * 0.1
+    gamma = torch.rand(Uu * 100, generator=g) + 0.5
+    beta = torch.randn(Uu * 100, generator=g) * 0.1
+    w2 = torch.randn(Uu, 100, generator=g) * 0.1
+    b2 = torch.randn(Uu, generator=g) * 0.1
+    mask = (torch.rand(B, Uu, 100, generator=g) >= 0.3).to(torch.uint8)
+    d = lambda t: t.to(DEV)
+    rm, rv = torch.zeros(Uu * 100, device=DEV), torch.ones(Uu * 100, device=DEV)
+    sc, sh, st = ops.mlp_bn2_train_prepare(d(pool), d(w1), d(b1), d(gamma), d(beta), 1e-5, 0.1, rm, rv)
+    # fp64 reference
+    h = torch.einsum("buq,umq->bum", pool.double(), w1.double().view(Uu, 100, n)) + b1.double().view(Uu, 100)
+    mean, var = h.mean(0), h.var(0, unbiased=False)
+    U.assert_close(st[:, 0].cpu().numpy(), mean.reshape(-1).numpy(), rtol=2e-6, atol_scale=2e-6, what="BN2 mean")
+    U.assert_close(st[:, 1].cpu().numpy(), var.reshape(-1).numpy(), rtol=1e-5, what="BN2 var")
+    U.assert_close(rm.cpu().numpy(), 0.1 * mean.reshape(-1).numpy(), rtol=2e-6, atol_scale=2e-6, what="running mean")
+    U.assert_close(rv.cpu().numpy(), (0.9 + 0.1 * var * B / (B - 1)).reshape(-1).numpy(), what="running var")
+    hn = (h - mean) / torch.sqrt(var + 1e-5) * gamma.double().view(Uu, 100) + beta.double().view(Uu, 100)
+    act = torch.relu(hn) * mask.double() / 0.7
+    ref = (act * w2.double()).sum(-1) + b2.double()
+    opre, bits = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 0, d(mask), want_bits=True)
+    U.assert_close(opre.cpu().numpy(), ref.numpy(), rtol=1e-5, what="opre vs fp64")
+    # the keep bits written for the backward pass are the injected mask
+    bn = bits.cpu().numpy().view(np.uint32)
+    got = ((bn[:, :, np.arange(100) // 32] >> (np.arange(100) % 32).astype(np.uint32)) & 1).astype(np.uint8)
+    assert np.array_equal(got, mask.numpy())
+    # FP32 FMA path, same statistics
+    hpre = ops.fc1_fwd(d(pool), d(w1), d(b1))
+    opre2 = ops.fc2_fwd(hpre, sc, sh, d(w2), d(b2), 0.3, 0, d(mask))
+    U.assert_close(opre.cpu().numpy(), opre2.cpu().numpy(), rtol=1e-5, what="opre tc vs fma")
+    # Philox dropout: deterministic in the seed, keep rate ~ 1 - p, backward bits = forward decisions
+    o1, k1 = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 11, None, want_bits=True)
+    o2, k2 = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 11, None, want_bits=True)
+    o3, _ = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 12, None, want_bits=True)
+    assert torch.equal(o1, o2) and torch.equal(k1, k2) and not torch.equal(o1, o3)
+    kn = k1.cpu().numpy().view(np.uint32)
+    keep = ((kn[:, :, np.arange(100) // 32] >> (np.arange(100) % 32).astype(np.uint32)) & 1)
+    if keep.size > 20000:
+        assert abs(keep.mean() - 0.7) < 0.02
+    mk = torch.tensor(np.ascontiguousarray(keep.astype(np.uint8)), device=DEV)
+    o4, _ = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 0, mk)
+    assert torch.equal(o1, o4)
+
+
 @pytest.mark.parametrize("cfg", [(300, 19, 600, 9), (100, 19, 200, 33), (37, 11, 95, 5), (130, 32, 120, 7),
                                  (5, 3, 40, 3)])
 def test_frontend_bwd_tensor_core_vs_brute_force(cfg):
