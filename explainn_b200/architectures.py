@@ -93,36 +93,52 @@ class _UnitBankFn(torch.autograd.Function):
                 cnt1, cnt2, n_pos, conv_w, conv_b, g1, be1, bn1.eps, _bn_momentum(bn1),
                 bn1.running_mean, bn1.running_var)
             pool, zmax, arg = ops.frontend_fwd(planes, L, conv_w, scale1, shift1, need_argmax=True)
-            hpre = ops.fc1_fwd(pool, w1, b1)
-            scale2, shift2, stats2 = ops.bn_train_prepare(
-                hpre.view(B, U * ops.HIDDEN), g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean, bn2.running_var)
             p = float(drop.p) if drop.training else 0.0
             seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and drop_mask is None) else 0
-            opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, drop_mask)
+            tc = ops.mlp_supported(pool.shape[2])
+            if tc:
+                # tensor-core path: the (B,100U) hidden activations are never materialised
+                scale2, shift2, stats2 = ops.mlp_bn2_train_prepare(
+                    pool, w1, b1, g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean, bn2.running_var)
+                want_bits = p > 0.0 or drop_mask is not None
+                opre, bits = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, drop_mask, want_bits)
+                hpre = None
+            else:
+                hpre = ops.fc1_fwd(pool, w1, b1)
+                scale2, shift2, stats2 = ops.bn_train_prepare(
+                    hpre.view(B, U * ops.HIDDEN), g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean,
+                    bn2.running_var)
+                opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, drop_mask)
+                bits = None
             scale3, shift3, stats3 = ops.bn_train_prepare(
                 opre, g3, be3, bn3.eps, _bn_momentum(bn3), bn3.running_mean, bn3.running_var)
             o, _ = ops.head_fwd(opre, scale3, shift3)
             for bn in (bn1, bn2, bn3):
                 if bn.num_batches_tracked is not None:
                     bn.num_batches_tracked += 1
-        ctx.save_for_backward(planes, conv_w, g1, w1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
-                              scale2, shift2, stats1, stats2, stats3, cov_w, cnt1)
-        ctx.meta = (L, k, n_pos, p, seed, drop_mask)
+        ctx.save_for_backward(planes, conv_w, g1, w1, b1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
+                              scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, bits)
+        ctx.meta = (L, k, n_pos, p, seed, drop_mask, tc)
         return o
 
     @staticmethod
     def backward(ctx, do):
-        (planes, conv_w, g1, w1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
-         scale2, shift2, stats1, stats2, stats3, cov_w, cnt1) = ctx.saved_tensors
-        L, k, n_pos, p, seed, drop_mask = ctx.meta
+        (planes, conv_w, g1, w1, b1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
+         scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, bits) = ctx.saved_tensors
+        L, k, n_pos, p, seed, drop_mask, tc = ctx.meta
         B, U = o.shape
         n = pool.shape[2]
         with torch.no_grad():
             g = do.contiguous().clone()
             dg3, dbe3, dopre = ops.bn_bwd(g, o, opre, stats3, g3)
-            dw2, db2, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, p, seed, drop_mask)
-            dg2, dbe2, dhpre = ops.bn_bwd(gh.view(B, U * ops.HIDDEN), None, hpre.view(B, U * ops.HIDDEN), stats2, g2)
-            dw1, db1, dy = ops.fc1_bwd(dhpre.view(B, U, ops.HIDDEN), pool, w1)
+            if tc:
+                dw1, db1, dg2, dbe2, dw2, db2, dy = ops.mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, g2, w2,
+                                                                bits, p)
+            else:
+                dw2, db2, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, p, seed, drop_mask)
+                dg2, dbe2, dhpre = ops.bn_bwd(gh.view(B, U * ops.HIDDEN), None, hpre.view(B, U * ops.HIDDEN), stats2,
+                                              g2)
+                dw1, db1, dy = ops.fc1_bwd(dhpre.view(B, U, ops.HIDDEN), pool, w1)
             dcw, dcb, dg1, dbe1 = ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos)
         return (None, None, None, None, dcw, dcb, dg1, dbe1, dw1.view(U * ops.HIDDEN, n, 1), db1,
                 dg2, dbe2, dw2.view(U, ops.HIDDEN, 1), db2, dg3, dbe3)
@@ -243,11 +259,14 @@ class UnitBank(nn.Sequential):
             cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = [p.detach() for p in params]
             scale1, shift1 = ops.bn_fold_eval(g1, be1, bn1.running_mean, bn1.running_var, cb, bn1.eps)
             pool, _, _ = ops.frontend_fwd(planes, L, cw, scale1, shift1, need_argmax=False)
-            hpre = ops.fc1_fwd(pool, w1, b1)
             scale2, shift2 = ops.bn_fold_eval(g2, be2, bn2.running_mean, bn2.running_var, None, bn2.eps)
             p = float(drop.p) if drop.training else 0.0
             seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and dropout_mask is None) else 0
-            opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, dropout_mask)
+            if ops.mlp_supported(pool.shape[2]):
+                opre, _ = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, dropout_mask)
+            else:
+                hpre = ops.fc1_fwd(pool, w1, b1)
+                opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, dropout_mask)
             scale3, shift3 = ops.bn_fold_eval(g3, be3, bn3.running_mean, bn3.running_var, None, bn3.eps)
             o, _ = ops.head_fwd(opre, scale3, shift3)
             return o

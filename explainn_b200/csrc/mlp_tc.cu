@@ -18,6 +18,7 @@
 // is how the backward pass gets W1^T, pool^T and dhpre^T without a second copy.
 #include "common.cuh"
 #include "umma.cuh"
+#include <cuda_bf16.h>
 using namespace xnn;
 
 #define MT_THREADS 128
@@ -374,5 +375,413 @@ extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, 
     a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = 0;
     a.drop_p = drop_p; a.seed = seed; a.mask_u8 = mask; a.maskbits = maskbits; a.opre = opre;
     if (mt_launch<MLP_APPLY>(a, to_stream(s))) { set_error("xnn_mlp_fwd: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    return XNN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// backward, pass B1: reductions of the BatchNorm (linears.7) backward and dW2 / db2
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U, const double* __restrict__ stats,
+                        float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2,
+                        float* __restrict__ db2, float2* __restrict__ coef) {
+    const int C = U * MT_H;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+    for (int t = 0; t < slots; ++t) {
+        const double* p = part + (long long)t * 4 * C + c;
+        s1 += p[0]; s2 += p[(long long)C]; s3 += p[2LL * C]; s4 += p[3LL * C];
+    }
+    const double mean = stats[4LL * c], invstd = stats[4LL * c + 2];
+    const double dg = invstd * (s2 - mean * s1);       // sum g * xhat
+    dgamma[c] = (float)dg;
+    dbeta[c] = (float)s1;
+    dw2[c] = (float)s3;
+    if (c % MT_H == 0) db2[c / MT_H] = (float)s4;
+    coef[c] = make_float2((float)(s1 / B), (float)(dg / B));
+}
+
+// ---------------------------------------------------------------------------
+// backward, pass B2 (thread = hidden channel, 64 batch rows per tile):
+//   D1[m][b]  = W1 . pool^T                 -> dh[m][b] = gamma*invstd*(g2 - c1 - xhat*c2)   (registers -> smem)
+//   D2[q][b]  = W1^T . dh                   -> dy[b,u,q] = pool[b,u,q] * D2[q][b]
+//   D3[m][q] += dh . pool                   (accumulated in TMEM over the CTA's tiles of the unit) -> dW1
+// The transposed operands are MN-major views of the same staging buffers, which tcgen05 offers without
+// swizzle only for 16-bit types: this pass therefore runs kind::f16 with a THREE-way bf16 split of both
+// operands (x = x1+x2+x3, 8 mantissa bits each) and the six products x1y1 x1y2 x2y1 x1y3 x2y2 x3y1 --
+// the same fp32-level accuracy as 3xTF32 at the same tensor time, and 6 instead of 8 bytes per element.
+// Staging: an [R rows][K] matrix as uint4 [K/8][R] (8 bf16 per 16 bytes), one buffer per piece.
+// ---------------------------------------------------------------------------
+#define MB_ROWS 64
+
+struct MlpBwdArgs {
+    const float* pool; const float* w1; const float* b1; const float* scale2; const float* shift2;
+    const float* w2; const float* gamma2; const double* stats2; const float2* coef;
+    const float* dopre; const uint32_t* maskbits;
+    float* dy;            // (B,U,n)
+    float* part_w1;       // [slots][100U][n]
+    double* part_db1;     // [slots][100U]
+    int B, U, n, T, slots;
+    float drop_p;
+};
+
+// 8 floats -> three uint4 of packed bf16 pieces (hi, mid, lo)
+__device__ __forceinline__ void split8_bf16x3(const float* v, uint4& p0, uint4& p1, uint4& p2) {
+    uint32_t w0[4], w1[4], w2[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        uint32_t h[2], m[2], l[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const float x = v[2 * i + e];
+            const __nv_bfloat16 a = __float2bfloat16_rn(x);
+            const float r1 = x - __bfloat162float(a);
+            const __nv_bfloat16 b = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 c = __float2bfloat16_rn(r1 - __bfloat162float(b));
+            h[e] = __bfloat16_as_ushort(a); m[e] = __bfloat16_as_ushort(b); l[e] = __bfloat16_as_ushort(c);
+        }
+        w0[i] = h[0] | (h[1] << 16); w1[i] = m[0] | (m[1] << 16); w2[i] = l[0] | (l[1] << 16);
+    }
+    p0 = make_uint4(w0[0], w0[1], w0[2], w0[3]);
+    p1 = make_uint4(w1[0], w1[1], w1[2], w1[3]);
+    p2 = make_uint4(w2[0], w2[1], w2[2], w2[3]);
+}
+
+// stage chunks [cb, ce) of one fp32 row (n values, zero beyond) into the three piece buffers
+__device__ __forceinline__ void stage_row_bf16x3(const float* __restrict__ src, int n, int cb, int ce, int R, int row,
+                                                 uint4* __restrict__ d0, uint32_t piece_u4) {
+#pragma unroll 2
+    for (int c = cb; c < ce; ++c) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int q = 8 * c + e;
+            v[e] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
+        }
+        uint4 p0, p1, p2;
+        split8_bf16x3(v, p0, p1, p2);
+        d0[c * R + row] = p0;
+        d0[piece_u4 + c * R + row] = p1;
+        d0[2 * piece_u4 + c * R + row] = p2;
+    }
+}
+
+__global__ void __launch_bounds__(MT_THREADS)
+mlp_bwd_kernel(MlpBwdArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
+    const uint32_t wpiece = (uint32_t)chunksQ * 2048u;     // [chunksQ][128 rows] uint4
+    const uint32_t ppiece = (uint32_t)chunksQ * 1024u;     // [chunksQ][64 rows] uint4
+    const uint32_t tpiece = 8u * 2048u;                    // [8][128 rows] uint4 (K = 64 batch rows)
+    uint4* w1s = reinterpret_cast<uint4*>(smem_raw);
+    uint4* ps = reinterpret_cast<uint4*>(smem_raw + 3 * wpiece);
+    uint4* ts = reinterpret_cast<uint4*>(smem_raw + 3 * wpiece + 3 * ppiece);
+    // the MN-major view of W1 with M = 128 reads 16 chunks from each piece: keep that inside the allocation
+    const uint32_t body = 3 * wpiece + 3 * ppiece + 3 * tpiece;
+    const uint32_t need = 2 * wpiece + 16u * 2048u;
+    unsigned char* tail = smem_raw + (body > need ? body : need);
+    float* s_dopre = reinterpret_cast<float*>(tail);                 // [64]
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 256);      // [64][4]
+    MtShared* sh = reinterpret_cast<MtShared*>(tail + 256 + 1024);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw);
+        const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
+        for (uint32_t i = tid; i < tot; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 256);
+    if (tid == 0) umma::mbar_init(&sh->bar, 1);
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t w_addr = umma::smem_u32(w1s), p_addr = umma::smem_u32(ps), t_addr = umma::smem_u32(ts);
+    const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);                          // W1 x pool, both K-major
+    const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16); // W1^T x dh^T (MN views)
+    const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);                  // dh x pool^T (MN view)
+    const uint32_t D1 = tmem, D2 = tmem + 64, D3 = tmem + 128;
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+    const uint32_t trow = (uint32_t)(warp * 32) << 16;
+
+    int cur_u = -1;
+    uint32_t phase = 0, d3_started = 0;
+    float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
+    double sdb1 = 0.0;
+
+    auto flush = [&](int u) {
+        // every MMA into D3 has completed (the tile loop waits on each commit)
+        int j = blockIdx.x;
+        const long long start = (long long)u * T;
+        while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+        const int slot = blockIdx.x - j;
+        const bool ok = tid < MT_H && slot < a.slots;
+        float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + tid) * n;
+        for (int c0 = 0; c0 < Nq; c0 += 16) {
+            uint32_t v[16];
+            umma::tmem_ld16(D3 + trow + c0, v);
+            umma::tmem_ld_wait();
+            if (ok) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (c0 + i < n) o[c0 + i] = d3_started ? __uint_as_float(v[i]) : 0.0f;
+            }
+        }
+        if (ok) a.part_db1[(long long)slot * C + (long long)u * MT_H + tid] = sdb1;
+        sdb1 = 0.0;
+        d3_started = 0;
+        umma::fence_before_sync();
+        __syncthreads();
+    };
+
+    // the six products of the 3-way split, smallest first: (piece of A, piece of B), 0 = hi, 1 = mid, 2 = lo
+    auto pa = [](int pass) { return pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u; };
+    auto pb = [](int pass) { return pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u; };
+
+    for (long long tile = lo; tile < hi; ++tile) {
+        const int u = (int)(tile / T), t = (int)(tile % T);
+        const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
+        if (u != cur_u) {
+            if (cur_u >= 0) flush(cur_u);
+            cur_u = u;
+            if (tid < MT_H)
+                stage_row_bf16x3(a.w1 + ((long long)u * MT_H + tid) * n, n, 0, chunksQ, 128, tid, w1s, wpiece / 16);
+            const int ch = u * MT_H + tid;
+            const bool ok = tid < MT_H;
+            b1m = ok ? a.b1[ch] : 0.f; scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f;
+            w2m = ok ? a.w2[ch] : 0.f;
+            meanm = ok ? (float)a.stats2[4LL * ch] : 0.f; invstdm = ok ? (float)a.stats2[4LL * ch + 2] : 0.f;
+            gism = ok ? (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]) : 0.f;
+            const float2 cf = ok ? a.coef[ch] : make_float2(0.f, 0.f);
+            c1m = cf.x; c2m = cf.y;
+        }
+        // pool tile: 64 rows, two threads per row (each stages half of the chunks)
+        {
+            const int r = tid & 63, half = tid >> 6;
+            const int cb = half ? (chunksQ >> 1) : 0, ce = half ? chunksQ : (chunksQ >> 1);
+            const float* src = (r < rows) ? a.pool + ((long long)(b0 + r) * U + u) * n : nullptr;
+            stage_row_bf16x3(src, n, cb, ce, 64, r, ps, ppiece / 16);
+        }
+        if (tid < MB_ROWS) {
+            const long long bu = (long long)(b0 + tid) * U + u;
+            s_dopre[tid] = (tid < rows) ? a.dopre[bu] : 0.f;
+            uint4 kb = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFu);
+            if (a.maskbits && tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
+            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = kb;
+        }
+        umma::fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            umma::fence_after_sync();
+            uint32_t acc = 0;
+#pragma unroll 1
+            for (int pass = 0; pass < 6; ++pass) {
+#pragma unroll 1
+                for (int ks = 0; ks < kstepsQ; ++ks) {
+                    const uint64_t ad = umma::smem_desc(w_addr + pa(pass) * wpiece + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
+                    const uint64_t bd = umma::smem_desc(p_addr + pb(pass) * ppiece + (uint32_t)(2 * ks) * 1024u, 1024u, 128u);
+                    umma::mma_bf16(D1, ad, bd, idesc1, acc);
+                    acc = 1;
+                }
+            }
+            umma::commit(&sh->bar);
+        }
+        umma::mbar_wait(&sh->bar, phase);
+        phase ^= 1u;
+        umma::fence_after_sync();
+
+        // ---- epilogue 1: dh for this thread's channel, 8 batch rows per 16-byte chunk
+#pragma unroll 1
+        for (int c0 = 0; c0 < MB_ROWS; c0 += 16) {
+            uint32_t v[16];
+            umma::tmem_ld16(D1 + trow + c0, v);
+            umma::tmem_ld_wait();
+            float dh[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int c = c0 + i;
+                const float x = __uint_as_float(v[i]) + b1m;
+                const float pre = fmaf(x, scm, shm);
+                const uint32_t keep = (s_mask[4 * c + (tid >> 5)] >> (tid & 31)) & 1u;
+                const float ds = keep ? inv_keep : 0.0f;
+                const float g2 = (pre > 0.0f) ? s_dopre[c] * w2m * ds : 0.0f;
+                const float xhat = (x - meanm) * invstdm;
+                float d = gism * (g2 - c1m - xhat * c2m);
+                if (c >= rows || tid >= MT_H) d = 0.0f;
+                dh[i] = d;
+                sdb1 += (double)d;
+            }
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                uint4 p0, p1, p2;
+                split8_bf16x3(dh + 8 * g, p0, p1, p2);
+                const int chunk = (c0 >> 3) + g;
+                ts[chunk * 128 + tid] = p0;
+                ts[tpiece / 16 + chunk * 128 + tid] = p1;
+                ts[2 * (tpiece / 16) + chunk * 128 + tid] = p2;
+            }
+        }
+        umma::fence_proxy_async();
+        umma::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            umma::fence_after_sync();
+            // D2[q][b] = sum_m W1[m][q] * dh[m][b]: both operands are MN-major views, K = hidden rows (16 per MMA)
+            uint32_t acc = 0;
+#pragma unroll 1
+            for (int pass = 0; pass < 6; ++pass) {
+#pragma unroll 1
+                for (int ks = 0; ks < 7; ++ks) {
+                    const uint64_t ad = umma::smem_desc(w_addr + pa(pass) * wpiece + (uint32_t)ks * 256u, 128u, 2048u);
+                    const uint64_t bd = umma::smem_desc(t_addr + pb(pass) * tpiece + (uint32_t)ks * 256u, 128u, 2048u);
+                    umma::mma_bf16(D2, ad, bd, idesc2, acc);
+                    acc = 1;
+                }
+            }
+            // D3[m][q] += sum_b dh[m][b] * pool[b][q]: A = dh K-major (K = batch rows), B = pool^T (MN view)
+#pragma unroll 1
+            for (int pass = 0; pass < 6; ++pass) {
+#pragma unroll 1
+                for (int ks = 0; ks < MB_ROWS / 16; ++ks) {
+                    const uint64_t ad = umma::smem_desc(t_addr + pa(pass) * tpiece + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
+                    const uint64_t bd = umma::smem_desc(p_addr + pb(pass) * ppiece + (uint32_t)ks * 256u, 128u, 1024u);
+                    umma::mma_bf16(D3, ad, bd, idesc3, d3_started);
+                    d3_started = 1;
+                }
+            }
+            umma::commit(&sh->bar);
+        }
+        d3_started = 1;
+        umma::mbar_wait(&sh->bar, phase);
+        phase ^= 1u;
+        umma::fence_after_sync();
+
+        // ---- epilogue 2: thread = pool column q; dy[b,u,q] = pool[b,u,q] * D2[q][b]  (coalesced over q)
+#pragma unroll 1
+        for (int c0 = 0; c0 < rows; c0 += 16) {
+            uint32_t v[16];
+            umma::tmem_ld16(D2 + trow + c0, v);
+            umma::tmem_ld_wait();
+            if (tid < n) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    if (c0 + i < rows) {
+                        const long long g = ((long long)(b0 + c0 + i) * U + u) * n + tid;
+                        a.dy[g] = __ldg(a.pool + g) * __uint_as_float(v[i]);
+                    }
+                }
+            }
+        }
+        umma::fence_before_sync();
+        __syncthreads();
+    }
+    if (cur_u >= 0) flush(cur_u);
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+}
+
+__global__ void __launch_bounds__(256)
+mlp_bwd_reduce_kernel(const float* __restrict__ part_w1, const double* __restrict__ part_db1, int slots,
+                      long long nw, int C, float* __restrict__ dw1, float* __restrict__ db1) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nw;
+         i += (long long)gridDim.x * blockDim.x) {
+        float v = 0.0f;
+        for (int s = 0; s < slots; ++s) v += part_w1[(long long)s * nw + i];
+        dw1[i] = v;
+        if (i < C) {
+            double d = 0.0;
+            for (int s = 0; s < slots; ++s) d += part_db1[(long long)s * C + i];
+            db1[i] = (float)d;
+        }
+    }
+}
+
+static int mb_tiles(int B) { return (B + MB_ROWS - 1) / MB_ROWS; }
+static int mb_grid(int B, int U) {
+    const long long tiles = (long long)U * mb_tiles(B);
+    const int sms = num_sms();
+    return (int)(tiles < sms ? tiles : sms);
+}
+static int mb_slots(int B, int U) {
+    const int T = mb_tiles(B), G = mb_grid(B, U);
+    const long long per = ((long long)U * T) / G;
+    return (int)((T + per - 1) / per) + 1;
+}
+static size_t mb_smem(int n) {
+    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
+    const size_t body = 3 * chunksQ * 2048 + 3 * chunksQ * 1024 + 3 * 8 * 2048;
+    const size_t need = 2 * chunksQ * 2048 + 16 * 2048;
+    return (body > need ? body : need) + 256 + 1024 + sizeof(MtShared) + 16;
+}
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct MbWork { size_t part1, coef, part_w1, part_db1, total; };
+static MbWork mb_work(int B, int U, int n) {
+    const size_t C = (size_t)U * MT_H;
+    MbWork w;
+    w.part1 = 0;
+    w.coef = align256((size_t)mt_slots(B, U) * 4 * C * sizeof(double));
+    w.part_w1 = w.coef + align256(C * sizeof(float2));
+    w.part_db1 = w.part_w1 + align256((size_t)mb_slots(B, U) * C * n * sizeof(float));
+    w.total = w.part_db1 + align256((size_t)mb_slots(B, U) * C * sizeof(double));
+    return w;
+}
+
+extern "C" size_t xnn_mlp_bwd_work_bytes(int B, int U, int n) {
+    if (B < 1 || U < 1 || n < 1) return 0;
+    return mb_work(B, U, n).total;
+}
+
+extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w1, const float* b1,
+                           const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
+                           const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
+                           float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
+                           float* dy, void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(dopre && pool && w1 && b1 && scale2 && shift2 && stats2 && gamma2 && w2 && dw1 && db1 && dgamma2 &&
+                  dbeta2 && dw2 && db2 && dy && work, "NULL pointer");
+    XNN_CHECK_ARG(B >= 2 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
+    XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
+    XNN_CHECK_ARG(((uintptr_t)work & 255) == 0, "work must be 256-byte aligned");
+    XNN_CHECK_ARG(maskbits == nullptr || ((uintptr_t)maskbits & 15) == 0, "maskbits must be 16-byte aligned");
+    cudaStream_t st = to_stream(s);
+    const MbWork w = mb_work(B, U, n);
+    const int C = U * MT_H;
+    char* base = (char*)work;
+    XNN_CUDA(cudaMemsetAsync(work, 0, w.total, st));
+    // B1: reductions
+    MlpArgs a{};
+    a.pool = pool; a.w1 = w1; a.b1 = b1; a.scale2 = scale2; a.shift2 = shift2; a.w2 = w2; a.dopre = dopre;
+    a.maskbits = const_cast<uint32_t*>(maskbits);
+    a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U); a.drop_p = drop_p;
+    a.part = (double*)(base + w.part1);
+    if (mt_launch<MLP_BWD_STATS>(a, st)) { set_error("xnn_mlp_bwd: B1 launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    float2* coef = (float2*)(base + w.coef);
+    mlp_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, st>>>(a.part, a.slots, B, U, stats2, dgamma2, dbeta2, dw2, db2,
+                                                              coef);
+    XNN_CHECK_LAUNCH();
+    // B2: dh -> dW1, dy
+    MlpBwdArgs g{};
+    g.pool = pool; g.w1 = w1; g.b1 = b1; g.scale2 = scale2; g.shift2 = shift2; g.w2 = w2; g.gamma2 = gamma2;
+    g.stats2 = stats2; g.coef = coef; g.dopre = dopre; g.maskbits = maskbits; g.dy = dy;
+    g.part_w1 = (float*)(base + w.part_w1); g.part_db1 = (double*)(base + w.part_db1);
+    g.B = B; g.U = U; g.n = n; g.T = mb_tiles(B); g.slots = mb_slots(B, U); g.drop_p = drop_p;
+    const size_t smem = mb_smem(n);
+    XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mlp_bwd_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g);
+    XNN_CHECK_LAUNCH();
+    const long long nw = (long long)C * n;
+    long long blocks = (nw + 255) / 256;
+    if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
+    mlp_bwd_reduce_kernel<<<(int)blocks, 256, 0, st>>>(g.part_w1, g.part_db1, g.slots, nw, C, dw1, db1);
+    XNN_CHECK_LAUNCH();
     return XNN_OK;
 }

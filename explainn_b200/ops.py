@@ -249,6 +249,29 @@ def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None,
     return opre, bits
 
 
+def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p):
+    """Backward of FC1 -> BN2 -> ReLU -> dropout -> FC2 from dopre (B,U); see xnn_mlp_bwd."""
+    B, U, n = pool.shape
+    dev = pool.device
+    lib = _lib.load()
+    C = U * HIDDEN
+    dw1 = torch.empty((C, n), dtype=torch.float32, device=dev)
+    db1 = torch.empty(C, dtype=torch.float32, device=dev)
+    dg2 = torch.empty(C, dtype=torch.float32, device=dev)
+    dbe2 = torch.empty(C, dtype=torch.float32, device=dev)
+    dw2 = torch.empty((U, HIDDEN), dtype=torch.float32, device=dev)
+    db2 = torch.empty(U, dtype=torch.float32, device=dev)
+    dy = torch.empty_like(pool)
+    nbytes = int(lib.xnn_mlp_bwd_work_bytes(B, U, n))
+    work = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+    off = (-work.data_ptr()) % 256
+    _call("xnn_mlp_bwd", _p(_req(dopre, torch.float32, "dopre")), _p(_req(pool, torch.float32, "pool")),
+          _p(_req(w1, torch.float32, "w1")), _p(b1), _p(scale2), _p(shift2), _p(_req(stats2, torch.float64, "stats2")),
+          _p(gamma2), _p(_req(w2, torch.float32, "w2")), _p(bits), float(drop_p), B, U, n, _p(dw1), _p(db1), _p(dg2),
+          _p(dbe2), _p(dw2), _p(db2), _p(dy), ctypes.c_void_p(work.data_ptr() + off), _stream())
+    return dw1, db1, dg2, dbe2, dw2, db2, dy
+
+
 def head_fwd(opre, scale3, shift3, wf=None, bf=None):
     B, U = opre.shape
     o = torch.empty((B, U), dtype=torch.float32, device=opre.device)

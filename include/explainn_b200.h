@@ -172,6 +172,18 @@ int xnn_linear_fwd(const float* x, const float* w, const float* b, int B, int U,
 size_t xnn_linear_bwd_work_bytes(int B, int U, int F);
 int xnn_linear_bwd(const float* dy, const float* w, const float* x, int B, int U, int F,
                    float* dx, float* dw, float* db, void* work, xnn_stream_t s);
+/* Backward of the whole per-unit MLP on the tensor cores, from dopre = dL/d(opre) (B,U):
+ * xnn_fc2_bwd + xnn_bn_bwd (linears.7) + xnn_fc1_bwd fused; hpre is recomputed from pool, neither it
+ * nor its gradient is written.  maskbits: the keep bits xnn_mlp_fwd wrote (NULL = no dropout).
+ *   dw1 (100U,n), db1 (100U), dgamma2/dbeta2 (100U), dw2 (U,100), db2 (U),
+ *   dy[b,u,q] = pool * sum_m dhpre*W1 (gradient at the arg-max conv output through exp).
+ * work: xnn_mlp_bwd_work_bytes, 256-byte aligned. */
+size_t xnn_mlp_bwd_work_bytes(int B, int U, int n);
+int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w1, const float* b1,
+                const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
+                const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
+                float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
+                float* dy, void* work, xnn_stream_t s);
 /* Train-mode BatchNorm backward over the batch dimension, C channels:
  *   given g = dL/d(out) (B,C), xpre (B,C), stats (mean,var,invstd), gamma; when
  *   relu_out != NULL the BatchNorm is followed by a ReLU whose output it is and
