@@ -100,8 +100,7 @@ class _UnitBankFn(torch.autograd.Function):
                 # tensor-core path: the (B,100U) hidden activations are never materialised
                 scale2, shift2, stats2 = ops.mlp_bn2_train_prepare(
                     pool, w1, b1, g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean, bn2.running_var)
-                want_bits = p > 0.0 or drop_mask is not None
-                opre, bits = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, drop_mask, want_bits)
+                opre, bits = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, drop_mask, want_bits=True)
                 hpre = None
             else:
                 hpre = ops.fc1_fwd(pool, w1, b1)

@@ -21,7 +21,7 @@
 #include <cuda_bf16.h>
 using namespace xnn;
 
-#define MT_THREADS 128
+#define MT_THREADS 512
 #define MT_ROWS 128
 #define MT_H XNN_HIDDEN          // 100
 #define MT_NMAX 96               // largest pool width n handled on this path
@@ -101,7 +101,7 @@ struct MlpArgs {
     const float* b2;        // (U)      F2
     const float* dopre;     // (B,U)    B1
     const uint8_t* mask_u8; // (B,U,100) injected dropout mask (F2) or NULL
-    uint32_t* maskbits;     // (B,U,4)  keep bits: written by F2, read by B1 (may be NULL when p == 0 and no mask)
+    uint32_t* maskbits;     // (B,U,4)  active bits (kept by dropout AND BN2 output > 0): written by F2, read by B1/B2
     float* opre;            // (B,U)    F2
     double* part;           // [slots][nstat][C] partial sums (F1: 2, B1: 4)
     int B, U, n, T, slots;
@@ -120,9 +120,46 @@ struct MtShared {
 // ---------------------------------------------------------------------------
 // FC1 tile on tcgen05 + fused epilogue.  One CTA per SM walks a contiguous range of the flattened
 // (unit, batch tile) space, so W1 of a unit is staged once per CTA (at most ~3 units per CTA).
+// 512 threads = 16 warps: warp w owns TMEM lanes 32*(w%4).. and the column group cg = w/4 (a quarter of
+// the accumulator columns); the same (row, cg) pair stages a quarter of row `row` of the operand tiles.
+// The next tile's pool rows are prefetched into registers while the tensor core works on this one.
 // ---------------------------------------------------------------------------
+#define MT_CPP 6   // staging chunks (of 4 floats) per thread: ceil(24 / 4)
+
+// keep-bit word `w` (hidden channels 32w .. 32w+31) of one (sequence, unit) row
+__device__ __forceinline__ uint32_t dropout_keep_word(float p, unsigned long long seed, long long bu,
+                                                      const uint8_t* __restrict__ mask_u8, int w) {
+    uint32_t kb = 0u;
+    if (mask_u8) {
+        const uint8_t* mr = mask_u8 + bu * MT_H;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int m = 32 * w + j;
+            if (m < MT_H) kb |= (mr[m] ? 1u : 0u) << j;
+        }
+    } else if (p > 0.0f) {
+        const uint32_t thr = (uint32_t)(p * 65536.0f + 0.5f);
+#pragma unroll
+        for (int ii = 0; ii < 4; ++ii) {
+            const int i = 4 * w + ii;                      // Philox call index: channels 8i .. 8i+7
+            if (i < MT_PHILOX_CALLS) {
+                const uint4 r = philox4(seed, (unsigned long long)bu * 16ull + (unsigned long long)i);
+                const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int s = 0; s < 8; ++s) {
+                    const uint32_t d16 = (wd[s >> 1] >> (16 * (s & 1))) & 0xFFFFu;
+                    if (8 * i + s < MT_H) kb |= (d16 >= thr ? 1u : 0u) << (8 * ii + s);
+                }
+            }
+        }
+    } else {
+        kb = (w < 3) ? 0xFFFFFFFFu : 0xFu;
+    }
+    return kb;
+}
+
 template <int MODE>
-__global__ void __launch_bounds__(MT_THREADS)
+__global__ void __launch_bounds__(MT_THREADS, 1)
 mlp_fc1_kernel(MlpArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int n = a.n, U = a.U, B = a.B, T = a.T;
@@ -134,9 +171,12 @@ mlp_fc1_kernel(MlpArgs a) {
     float4* s_c4 = reinterpret_cast<float4*>(tail);                  // [128] (b1, scale2, shift2, w2) per channel
     float* s_dopre = reinterpret_cast<float*>(tail + 2048);          // [128]
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 2048 + 512);   // [128][4]
-    MtShared* sh = reinterpret_cast<MtShared*>(tail + 2048 + 512 + 2048);
+    float* s_acc = reinterpret_cast<float*>(tail + 2048 + 512 + 2048);   // [4][128]
+    MtShared* sh = reinterpret_cast<MtShared*>(tail + 2048 + 512 + 2048 + 2048);
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row = (warp & 3) * 32 + lane;   // TMEM lane = staging row
+    const int cg = warp >> 2;                 // column group / staging quarter
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw);
         for (uint32_t i = tid; i < 4 * piece_bytes / 16; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -160,20 +200,51 @@ mlp_fc1_kernel(MlpArgs a) {
     const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
     const float inv_keep = 1.0f / (1.0f - a.drop_p);
     const int C = U * MT_H;
+    const int cpp = (chunks + 3) >> 2;                    // chunks per staging quarter (<= MT_CPP)
+    const int cbeg = cg * cpp, cend = min(chunks, cbeg + cpp);
 
     int cur_u = -1;
     uint32_t phase = 0;
     float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f;   // per-channel constants (thread = channel modes)
     double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+    float pv[MT_CPP][4];
 
+    auto prefetch = [&](long long tile) {
+        const bool live = tile < hi;
+        const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
+        const int b0 = t * MT_ROWS;
+        const float* src = (live && b0 + row < B) ? a.pool + ((long long)(b0 + row) * U + u) * n : nullptr;
+#pragma unroll
+        for (int i = 0; i < MT_CPP; ++i) {
+            const int c = cbeg + i;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int q = 4 * c + e;
+                pv[i][e] = (src != nullptr && c < cend && q < n) ? __ldg(src + q) : 0.0f;
+            }
+        }
+    };
+    auto store_tile = [&]() {
+#pragma unroll
+        for (int i = 0; i < MT_CPP; ++i) {
+            const int c = cbeg + i;
+            if (c < cend) {
+                float h[4], l[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) umma::split_tf32(pv[i][e], h[e], l[e]);
+                ps[c * 128 + row] = make_float4(h[0], h[1], h[2], h[3]);
+                ps[chunks * 128 + c * 128 + row] = make_float4(l[0], l[1], l[2], l[3]);
+            }
+        }
+    };
     auto flush = [&](int u) {
         if (MODE == MLP_APPLY) return;
         int j = blockIdx.x;
         const long long start = (long long)u * T;
         while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
-        const int slot = blockIdx.x - j;
-        if (tid < MT_H && slot < a.slots) {
-            const int c = u * MT_H + tid;
+        const int slot = (blockIdx.x - j) * 4 + cg;
+        if (row < MT_H && slot < a.slots) {
+            const int c = u * MT_H + row;
             constexpr int NS = (MODE == MLP_STATS) ? 2 : 4;
             double* o = a.part + (long long)slot * NS * C + c;
             o[0] = s1; o[(long long)C] = s2;
@@ -182,34 +253,43 @@ mlp_fc1_kernel(MlpArgs a) {
         s1 = s2 = s3 = s4 = 0.0;
     };
 
+    prefetch(lo);
     for (long long tile = lo; tile < hi; ++tile) {
         const int u = (int)(tile / T), t = (int)(tile % T);
         const int b0 = t * MT_ROWS, rows = min(MT_ROWS, B - b0);
         if (u != cur_u) {
             if (cur_u >= 0) flush(cur_u);
             cur_u = u;
-            // W1 of this unit: thread m stages row m (rows >= 100 stay zero)
-            if (tid < MT_H)
-                stage_row_split(a.w1 + ((long long)u * MT_H + tid) * n, n, chunks, 128, tid, w1s, w1s + chunks * 128);
-            const int ch = u * MT_H + tid;
-            const bool ok = tid < MT_H;
+            // W1 of this unit: (row, quarter) stages its chunks of row `row` (rows >= 100 stay zero)
+            if (row < MT_H) {
+                const float* src = a.w1 + ((long long)u * MT_H + row) * n;
+#pragma unroll 2
+                for (int c = cbeg; c < cend; ++c) {
+                    float h[4], l[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int q = 4 * c + e;
+                        umma::split_tf32(q < n ? __ldg(src + q) : 0.0f, h[e], l[e]);
+                    }
+                    w1s[c * 128 + row] = make_float4(h[0], h[1], h[2], h[3]);
+                    w1s[chunks * 128 + c * 128 + row] = make_float4(l[0], l[1], l[2], l[3]);
+                }
+            }
+            const int ch = u * MT_H + row;
+            const bool ok = row < MT_H;
             b1m = ok ? a.b1[ch] : 0.f;
             if (MODE != MLP_STATS) {
                 scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f; w2m = ok ? a.w2[ch] : 0.f;
-                if (MODE == MLP_APPLY) s_c4[tid] = make_float4(b1m, scm, shm, w2m);
+                if (MODE == MLP_APPLY && cg == 0) s_c4[row] = make_float4(b1m, scm, shm, w2m);
             }
         }
-        // pool tile: thread r stages batch row b0 + r (zeros past the batch)
-        {
-            const float* src = (tid < rows) ? a.pool + ((long long)(b0 + tid) * U + u) * n : nullptr;
-            stage_row_split(src, n, chunks, 128, tid, ps, ps + chunks * 128);
-        }
-        if (MODE == MLP_BWD_STATS) {
-            const long long bu = (long long)(b0 + tid) * U + u;
-            s_dopre[tid] = (tid < rows) ? a.dopre[bu] : 0.f;
-            uint4 kb = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFu);
-            if (a.maskbits && tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
-            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = kb;
+        store_tile();
+        if (MODE == MLP_BWD_STATS && cg == 0) {
+            const long long bu = (long long)(b0 + row) * U + u;
+            s_dopre[row] = (row < rows) ? a.dopre[bu] : 0.f;
+            uint4 kb = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
+            *reinterpret_cast<uint4*>(s_mask + 4 * row) = kb;
         }
         umma::fence_proxy_async();
         __syncthreads();
@@ -230,66 +310,75 @@ mlp_fc1_kernel(MlpArgs a) {
             }
             umma::commit(&sh->bar);
         }
+        prefetch(tile + 1);                 // global loads of the next tile fly under the MMAs
         umma::mbar_wait(&sh->bar, phase);
         phase ^= 1u;
         umma::fence_after_sync();
-        const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+        const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
 
         if (MODE == MLP_STATS || MODE == MLP_BWD_STATS) {
-            // thread = hidden channel (TMEM lane), columns = batch rows of the tile
-            for (int c0 = 0; c0 < rows; c0 += 16) {
-                uint32_t v[16];
-                umma::tmem_ld16(trow + c0, v);
-                umma::tmem_ld_wait();
+            // thread = (hidden channel, quarter of the tile's batch rows)
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    if (c0 + i < rows) {
-                        const float x = __uint_as_float(v[i]) + b1m;
-                        if (MODE == MLP_STATS) {
-                            s1 += (double)x;
-                            s2 += (double)x * (double)x;
-                        } else {
-                            const float pre = fmaf(x, scm, shm);
-                            const uint32_t keep = (s_mask[4 * (c0 + i) + (tid >> 5)] >> (tid & 31)) & 1u;
-                            const float ds = keep ? inv_keep : 0.0f;
-                            const float d = s_dopre[c0 + i];
-                            const float hact = fmaxf(pre, 0.0f) * ds;
-                            const float g2 = (pre > 0.0f) ? d * w2m * ds : 0.0f;
-                            s1 += (double)g2;
-                            s2 += (double)g2 * (double)x;
-                            s3 += (double)d * (double)hact;
-                            s4 += (double)d;
+            for (int hh = 0; hh < 2; ++hh) {
+                const int c0 = 32 * cg + 16 * hh;
+                if (c0 < rows) {
+                    uint32_t v[16];
+                    umma::tmem_ld16(trow + c0, v);
+                    umma::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        if (c0 + i < rows) {
+                            const float x = __uint_as_float(v[i]) + b1m;
+                            if (MODE == MLP_STATS) {
+                                s1 += (double)x;
+                                s2 += (double)x * (double)x;
+                            } else {
+                                const float pre = fmaf(x, scm, shm);
+                                const uint32_t act = (s_mask[4 * (c0 + i) + (row >> 5)] >> (row & 31)) & 1u;
+                                const float d = s_dopre[c0 + i];
+                                const float hact = act ? pre * inv_keep : 0.0f;
+                                const float g2 = act ? d * w2m * inv_keep : 0.0f;
+                                s1 += (double)g2;
+                                s2 += (double)g2 * (double)x;
+                                s3 += (double)d * (double)hact;
+                                s4 += (double)d;
+                            }
                         }
                     }
                 }
             }
         } else {
-            // thread = batch row, columns = hidden channels
-            const long long bu = (long long)(b0 + tid) * U + u;
-            uint32_t kb[4];
-            if (tid < rows) dropout_keep_bits(a.drop_p, a.seed, bu, a.mask_u8, kb);
-            else { kb[0] = kb[1] = kb[2] = kb[3] = 0u; }
+            // thread = (batch row, 32 hidden channels = keep-bit word cg)
+            const long long bu = (long long)(b0 + row) * U + u;
+            const uint32_t kbw = (row < rows) ? dropout_keep_word(a.drop_p, a.seed, bu, a.mask_u8, cg) : 0u;
+            uint32_t actw = 0u;   // keep AND (BN2 output > 0): the backward passes reuse THIS decision
             float accv = 0.0f;
 #pragma unroll
-            for (int c0 = 0; c0 < 112; c0 += 16) {
-                uint32_t v[16];
-                umma::tmem_ld16(trow + c0, v);
-                umma::tmem_ld_wait();
+            for (int hh = 0; hh < 2; ++hh) {
+                const int c0 = 32 * cg + 16 * hh;
+                if (c0 < 112) {
+                    uint32_t v[16];
+                    umma::tmem_ld16(trow + c0, v);
+                    umma::tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int m = c0 + i;
-                    if (m < MT_H) {
-                        const float4 c4 = s_c4[m];
-                        float h = fmaxf(fmaf(__uint_as_float(v[i]) + c4.x, c4.y, c4.z), 0.0f);
-                        h = ((kb[m >> 5] >> (m & 31)) & 1u) ? h * inv_keep : 0.0f;
-                        accv = fmaf(h, c4.w, accv);
+                    for (int i = 0; i < 16; ++i) {
+                        const int m = c0 + i;
+                        if (m < MT_H) {
+                            const float4 c4 = s_c4[m];
+                            const float pre = fmaf(__uint_as_float(v[i]) + c4.x, c4.y, c4.z);
+                            const uint32_t act = ((kbw >> (16 * hh + i)) & 1u) & (pre > 0.0f ? 1u : 0u);
+                            actw |= act << (16 * hh + i);
+                            const float h = act ? pre * inv_keep : 0.0f;
+                            accv = fmaf(h, c4.w, accv);
+                        }
                     }
                 }
             }
-            if (tid < rows) {
-                a.opre[bu] = accv + a.b2[u];
-                if (a.maskbits) *reinterpret_cast<uint4*>(a.maskbits + bu * 4) = make_uint4(kb[0], kb[1], kb[2], kb[3]);
-            }
+            s_acc[cg * 128 + row] = accv;
+            if (row < rows && a.maskbits) a.maskbits[bu * 4 + cg] = actw;
+            __syncthreads();
+            if (cg == 0 && row < rows)
+                a.opre[bu] = ((s_acc[row] + s_acc[128 + row]) + (s_acc[256 + row] + s_acc[384 + row])) + a.b2[u];
         }
         umma::fence_before_sync();
         __syncthreads();   // accumulator drained, staging buffers free
@@ -317,11 +406,11 @@ static int mt_grid(int B, int U) {
 static int mt_slots(int B, int U) {
     const int T = mt_tiles(B), G = mt_grid(B, U);
     const long long per = ((long long)U * T) / G;   // >= 1
-    return (int)((T + per - 1) / per) + 1;
+    return 4 * ((int)((T + per - 1) / per) + 1);    // x4: one partial per column group of the CTA
 }
 static size_t mt_smem(int n) {
     const int chunks = ((n + 7) & ~7) >> 2;
-    return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + sizeof(MtShared) + 16;
+    return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + 2048 + sizeof(MtShared) + 16;
 }
 
 template <int MODE>
@@ -467,7 +556,7 @@ __device__ __forceinline__ void stage_row_bf16x3(const float* __restrict__ src, 
     }
 }
 
-__global__ void __launch_bounds__(MT_THREADS)
+__global__ void __launch_bounds__(MT_THREADS, 1)
 mlp_bwd_kernel(MlpBwdArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int n = a.n, U = a.U, B = a.B, T = a.T;
@@ -486,7 +575,9 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 256);      // [64][4]
     MtShared* sh = reinterpret_cast<MtShared*>(tail + 256 + 1024);
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row = (warp & 3) * 32 + lane;   // TMEM lane: hidden channel m (D1, D3) / pool column q (D2)
+    const int cg = warp >> 2;                 // column group: 16 of the tile's 64 batch rows
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw);
         const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
@@ -510,22 +601,58 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
     const float inv_keep = 1.0f / (1.0f - a.drop_p);
     const int C = U * MT_H;
-    const uint32_t trow = (uint32_t)(warp * 32) << 16;
+    const uint32_t trow = (uint32_t)((warp & 3) * 32) << 16;
+    // pool tile staging: 8 threads per row, <= 2 chunks (of 8 floats) each
+    const int srow = tid & 63, spart = tid >> 6;
+    const int cpp8 = (chunksQ + 7) >> 3;
+    const int sbeg = spart * cpp8, send = min(chunksQ, sbeg + cpp8);
+    // W1 staging: 4 threads per row
+    const int cpp4 = (chunksQ + 3) >> 2;
+    const int wbeg = cg * cpp4, wend = min(chunksQ, wbeg + cpp4);
 
     int cur_u = -1;
     uint32_t phase = 0, d3_started = 0;
     float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
     double sdb1 = 0.0;
+    float pv[2][8];
 
+    auto prefetch = [&](long long tile) {
+        const bool live = tile < hi;
+        const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
+        const int b0 = t * MB_ROWS;
+        const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int c = sbeg + i;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int q = 8 * c + e;
+                pv[i][e] = (src != nullptr && c < send && q < n) ? __ldg(src + q) : 0.0f;
+            }
+        }
+    };
+    auto store_tile = [&]() {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int c = sbeg + i;
+            if (c < send) {
+                uint4 p0, p1, p2;
+                split8_bf16x3(pv[i], p0, p1, p2);
+                ps[c * 64 + srow] = p0;
+                ps[ppiece / 16 + c * 64 + srow] = p1;
+                ps[2 * (ppiece / 16) + c * 64 + srow] = p2;
+            }
+        }
+    };
     auto flush = [&](int u) {
         // every MMA into D3 has completed (the tile loop waits on each commit)
         int j = blockIdx.x;
         const long long start = (long long)u * T;
         while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
         const int slot = blockIdx.x - j;
-        const bool ok = tid < MT_H && slot < a.slots;
-        float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + tid) * n;
-        for (int c0 = 0; c0 < Nq; c0 += 16) {
+        const bool ok = row < MT_H && slot < a.slots;
+        float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + row) * n;
+        for (int c0 = 16 * cg; c0 < Nq; c0 += 64) {
             uint32_t v[16];
             umma::tmem_ld16(D3 + trow + c0, v);
             umma::tmem_ld_wait();
@@ -535,7 +662,7 @@ mlp_bwd_kernel(MlpBwdArgs a) {
                     if (c0 + i < n) o[c0 + i] = d3_started ? __uint_as_float(v[i]) : 0.0f;
             }
         }
-        if (ok) a.part_db1[(long long)slot * C + (long long)u * MT_H + tid] = sdb1;
+        if (ok) a.part_db1[((long long)slot * 4 + cg) * C + (long long)u * MT_H + row] = sdb1;
         sdb1 = 0.0;
         d3_started = 0;
         umma::fence_before_sync();
@@ -546,16 +673,17 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     auto pa = [](int pass) { return pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u; };
     auto pb = [](int pass) { return pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u; };
 
+    prefetch(lo);
     for (long long tile = lo; tile < hi; ++tile) {
         const int u = (int)(tile / T), t = (int)(tile % T);
         const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
         if (u != cur_u) {
             if (cur_u >= 0) flush(cur_u);
             cur_u = u;
-            if (tid < MT_H)
-                stage_row_bf16x3(a.w1 + ((long long)u * MT_H + tid) * n, n, 0, chunksQ, 128, tid, w1s, wpiece / 16);
-            const int ch = u * MT_H + tid;
-            const bool ok = tid < MT_H;
+            if (row < MT_H)
+                stage_row_bf16x3(a.w1 + ((long long)u * MT_H + row) * n, n, wbeg, wend, 128, row, w1s, wpiece / 16);
+            const int ch = u * MT_H + row;
+            const bool ok = row < MT_H;
             b1m = ok ? a.b1[ch] : 0.f; scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f;
             w2m = ok ? a.w2[ch] : 0.f;
             meanm = ok ? (float)a.stats2[4LL * ch] : 0.f; invstdm = ok ? (float)a.stats2[4LL * ch + 2] : 0.f;
@@ -563,18 +691,12 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             const float2 cf = ok ? a.coef[ch] : make_float2(0.f, 0.f);
             c1m = cf.x; c2m = cf.y;
         }
-        // pool tile: 64 rows, two threads per row (each stages half of the chunks)
-        {
-            const int r = tid & 63, half = tid >> 6;
-            const int cb = half ? (chunksQ >> 1) : 0, ce = half ? chunksQ : (chunksQ >> 1);
-            const float* src = (r < rows) ? a.pool + ((long long)(b0 + r) * U + u) * n : nullptr;
-            stage_row_bf16x3(src, n, cb, ce, 64, r, ps, ppiece / 16);
-        }
+        store_tile();
         if (tid < MB_ROWS) {
             const long long bu = (long long)(b0 + tid) * U + u;
             s_dopre[tid] = (tid < rows) ? a.dopre[bu] : 0.f;
-            uint4 kb = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFu);
-            if (a.maskbits && tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
+            uint4 kb = make_uint4(0u, 0u, 0u, 0u);
+            if (tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
             *reinterpret_cast<uint4*>(s_mask + 4 * tid) = kb;
         }
         umma::fence_proxy_async();
@@ -598,9 +720,9 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         phase ^= 1u;
         umma::fence_after_sync();
 
-        // ---- epilogue 1: dh for this thread's channel, 8 batch rows per 16-byte chunk
-#pragma unroll 1
-        for (int c0 = 0; c0 < MB_ROWS; c0 += 16) {
+        // ---- epilogue 1: dh for (channel row, batch rows 16cg..16cg+15) -> two 16-byte chunks per piece
+        {
+            const int c0 = 16 * cg;
             uint32_t v[16];
             umma::tmem_ld16(D1 + trow + c0, v);
             umma::tmem_ld_wait();
@@ -609,13 +731,11 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             for (int i = 0; i < 16; ++i) {
                 const int c = c0 + i;
                 const float x = __uint_as_float(v[i]) + b1m;
-                const float pre = fmaf(x, scm, shm);
-                const uint32_t keep = (s_mask[4 * c + (tid >> 5)] >> (tid & 31)) & 1u;
-                const float ds = keep ? inv_keep : 0.0f;
-                const float g2 = (pre > 0.0f) ? s_dopre[c] * w2m * ds : 0.0f;
+                const uint32_t act = (s_mask[4 * c + (row >> 5)] >> (row & 31)) & 1u;
+                const float g2 = act ? s_dopre[c] * w2m * inv_keep : 0.0f;
                 const float xhat = (x - meanm) * invstdm;
                 float d = gism * (g2 - c1m - xhat * c2m);
-                if (c >= rows || tid >= MT_H) d = 0.0f;
+                if (c >= rows || row >= MT_H) d = 0.0f;
                 dh[i] = d;
                 sdb1 += (double)d;
             }
@@ -623,10 +743,10 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             for (int g = 0; g < 2; ++g) {
                 uint4 p0, p1, p2;
                 split8_bf16x3(dh + 8 * g, p0, p1, p2);
-                const int chunk = (c0 >> 3) + g;
-                ts[chunk * 128 + tid] = p0;
-                ts[tpiece / 16 + chunk * 128 + tid] = p1;
-                ts[2 * (tpiece / 16) + chunk * 128 + tid] = p2;
+                const int chunk = 2 * cg + g;
+                ts[chunk * 128 + row] = p0;
+                ts[tpiece / 16 + chunk * 128 + row] = p1;
+                ts[2 * (tpiece / 16) + chunk * 128 + row] = p2;
             }
         }
         umma::fence_proxy_async();
@@ -660,23 +780,33 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             umma::commit(&sh->bar);
         }
         d3_started = 1;
+        // loads that fly under the MMAs: this tile's pool values for dy, and the next tile's staging rows
+        float pq[16];
+        {
+            const int c0 = 16 * cg;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const bool ok = row < n && c0 + i < rows;
+                pq[i] = ok ? __ldg(a.pool + ((long long)(b0 + c0 + i) * U + u) * n + row) : 0.0f;
+            }
+        }
+        prefetch(tile + 1);
         umma::mbar_wait(&sh->bar, phase);
         phase ^= 1u;
         umma::fence_after_sync();
 
-        // ---- epilogue 2: thread = pool column q; dy[b,u,q] = pool[b,u,q] * D2[q][b]  (coalesced over q)
-#pragma unroll 1
-        for (int c0 = 0; c0 < rows; c0 += 16) {
-            uint32_t v[16];
-            umma::tmem_ld16(D2 + trow + c0, v);
-            umma::tmem_ld_wait();
-            if (tid < n) {
+        // ---- epilogue 2: thread = (pool column q, 16 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b]
+        {
+            const int c0 = 16 * cg;
+            if (c0 < rows) {
+                uint32_t v[16];
+                umma::tmem_ld16(D2 + trow + c0, v);
+                umma::tmem_ld_wait();
+                if (row < n) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    if (c0 + i < rows) {
-                        const long long g = ((long long)(b0 + c0 + i) * U + u) * n + tid;
-                        a.dy[g] = __ldg(a.pool + g) * __uint_as_float(v[i]);
-                    }
+                    for (int i = 0; i < 16; ++i)
+                        if (c0 + i < rows)
+                            a.dy[((long long)(b0 + c0 + i) * U + u) * n + row] = pq[i] * __uint_as_float(v[i]);
                 }
             }
         }
@@ -699,7 +829,7 @@ mlp_bwd_reduce_kernel(const float* __restrict__ part_w1, const double* __restric
         dw1[i] = v;
         if (i < C) {
             double d = 0.0;
-            for (int s = 0; s < slots; ++s) d += part_db1[(long long)s * C + i];
+            for (int s = 0; s < 4 * slots; ++s) d += part_db1[(long long)s * C + i];
             db1[i] = (float)d;
         }
     }
@@ -732,7 +862,7 @@ static MbWork mb_work(int B, int U, int n) {
     w.coef = align256((size_t)mt_slots(B, U) * 4 * C * sizeof(double));
     w.part_w1 = w.coef + align256(C * sizeof(float2));
     w.part_db1 = w.part_w1 + align256((size_t)mb_slots(B, U) * C * n * sizeof(float));
-    w.total = w.part_db1 + align256((size_t)mb_slots(B, U) * C * sizeof(double));
+    w.total = w.part_db1 + align256((size_t)4 * mb_slots(B, U) * C * sizeof(double));
     return w;
 }
 
@@ -751,7 +881,7 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     XNN_CHECK_ARG(B >= 2 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
     XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
     XNN_CHECK_ARG(((uintptr_t)work & 255) == 0, "work must be 256-byte aligned");
-    XNN_CHECK_ARG(maskbits == nullptr || ((uintptr_t)maskbits & 15) == 0, "maskbits must be 16-byte aligned");
+    XNN_CHECK_ARG(maskbits != nullptr && ((uintptr_t)maskbits & 15) == 0, "maskbits: required, 16-byte aligned");
     cudaStream_t st = to_stream(s);
     const MbWork w = mb_work(B, U, n);
     const int C = U * MT_H;

@@ -155,7 +155,9 @@ int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b
                               double* stats, void* work, xnn_stream_t s);
 /* opre[b,u] = b2[u] + sum_m W2[u,m]*drop(relu(scale2*hpre+shift2)) -- xnn_fc1_fwd + xnn_fc2_fwd fused.
  * Dropout: injected byte mask (B,U,100), else Philox keep-bits from (seed,b,u) when drop_p > 0.
- * maskbits uint32 [B][U][4] (may be NULL): the keep bits used, for xnn_mlp_bwd. */
+ * maskbits uint32 [B][U][4] (NULL in inference): bit m of a (b,u) row = hidden channel m is ACTIVE (kept by
+ * dropout and BN2 output > 0).  xnn_mlp_bwd reuses exactly this decision, so the gradient is the one of
+ * the forward that was computed even where a recomputed pre-activation rounds to the other side of 0. */
 int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
                 const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
                 unsigned long long seed, const uint8_t* mask, uint32_t* maskbits, float* opre,
@@ -174,7 +176,7 @@ int xnn_linear_bwd(const float* dy, const float* w, const float* x, int B, int U
                    float* dx, float* dw, float* db, void* work, xnn_stream_t s);
 /* Backward of the whole per-unit MLP on the tensor cores, from dopre = dL/d(opre) (B,U):
  * xnn_fc2_bwd + xnn_bn_bwd (linears.7) + xnn_fc1_bwd fused; hpre is recomputed from pool, neither it
- * nor its gradient is written.  maskbits: the keep bits xnn_mlp_fwd wrote (NULL = no dropout).
+ * nor its gradient is written.  maskbits: the active bits xnn_mlp_fwd wrote (required).
  *   dw1 (100U,n), db1 (100U), dgamma2/dbeta2 (100U), dw2 (U,100), db2 (U),
  *   dy[b,u,q] = pool * sum_m dhpre*W1 (gradient at the arg-max conv output through exp).
  * work: xnn_mlp_bwd_work_bytes, 256-byte aligned. */

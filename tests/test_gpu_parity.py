@@ -183,10 +183,12 @@ def test_mlp_forward_tensor_core_vs_fp64(cfg):
     ref = (act * w2.double()).sum(-1) + b2.double()
     opre, bits = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 0, d(mask), want_bits=True)
     U.assert_close(opre.cpu().numpy(), ref.numpy(), rtol=1e-5, what="opre vs fp64")
-    # the keep bits written for the backward pass are the injected mask
+    # the active bits written for the backward pass: injected mask AND BN2 output > 0 (knife-edge elements,
+    # |hn| < 1e-5 in fp64, may fall on either side)
     bn = bits.cpu().numpy().view(np.uint32)
     got = ((bn[:, :, np.arange(100) // 32] >> (np.arange(100) % 32).astype(np.uint32)) & 1).astype(np.uint8)
-    assert np.array_equal(got, mask.numpy())
+    want = (mask.numpy() != 0) & (hn.numpy() > 0)
+    assert ((got != want) & (np.abs(hn.numpy()) > 1e-5)).sum() == 0
     # FP32 FMA path, same statistics
     hpre = ops.fc1_fwd(d(pool), d(w1), d(b1))
     opre2 = ops.fc2_fwd(hpre, sc, sh, d(w2), d(b2), 0.3, 0, d(mask))
@@ -197,10 +199,12 @@ def test_mlp_forward_tensor_core_vs_fp64(cfg):
     o3, _ = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 12, None, want_bits=True)
     assert torch.equal(o1, o2) and torch.equal(k1, k2) and not torch.equal(o1, o3)
     kn = k1.cpu().numpy().view(np.uint32)
-    keep = ((kn[:, :, np.arange(100) // 32] >> (np.arange(100) % 32).astype(np.uint32)) & 1)
-    if keep.size > 20000:
-        assert abs(keep.mean() - 0.7) < 0.02
-    mk = torch.tensor(np.ascontiguousarray(keep.astype(np.uint8)), device=DEV)
+    active = ((kn[:, :, np.arange(100) // 32] >> (np.arange(100) % 32).astype(np.uint32)) & 1)
+    pos = hn.numpy() > 1e-5
+    if pos.sum() > 20000:
+        assert abs(active[pos].mean() - 0.7) < 0.02      # keep rate among the ReLU-active channels
+    # feeding the active bits back as an injected mask reproduces the Philox forward exactly
+    mk = torch.tensor(np.ascontiguousarray(active.astype(np.uint8)), device=DEV)
     o4, _ = ops.mlp_fwd(d(pool), d(w1), d(b1), sc, sh, d(w2), d(b2), 0.3, 0, mk)
     assert torch.equal(o1, o4)
 
