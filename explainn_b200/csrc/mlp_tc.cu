@@ -124,7 +124,7 @@ struct MtShared {
 // the accumulator columns); the same (row, cg) pair stages a quarter of row `row` of the operand tiles.
 // The next tile's pool rows are prefetched into registers while the tensor core works on this one.
 // ---------------------------------------------------------------------------
-#define MT_CPP 6   // staging chunks (of 4 floats) per thread: ceil(24 / 4)
+#define MT_CMAX 24   // staging chunks (of 4 floats) per row: MT_NMAX / 4
 
 // keep-bit word `w` (hidden channels 32w .. 32w+31) of one (sequence, unit) row
 __device__ __forceinline__ uint32_t dropout_keep_word(float p, unsigned long long seed, long long bu,
@@ -173,6 +173,7 @@ mlp_fc1_kernel(MlpArgs a) {
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 2048 + 512);   // [128][4]
     float* s_acc = reinterpret_cast<float*>(tail + 2048 + 512 + 2048);   // [4][128]
     MtShared* sh = reinterpret_cast<MtShared*>(tail + 2048 + 512 + 2048 + 2048);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 2048 + 512 + 2048 + 2048 + 32);   // [3 * ksteps] descriptor words
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int row = (warp & 3) * 32 + lane;   // TMEM lane = staging row
@@ -194,47 +195,64 @@ mlp_fc1_kernel(MlpArgs a) {
     const uint32_t idesc = umma::idesc_tf32_f32(128, NDIM, 0, 0);
     const uint32_t a_addr = (MODE == MLP_APPLY) ? p_addr : w_addr;
     const uint32_t b_addr = (MODE == MLP_APPLY) ? w_addr : p_addr;
+    // MMA sequence of a tile (the operand buffers never move): small terms first, lo*hi, hi*lo, then hi*hi
+    if (tid < 3 * ksteps) {
+        const int pass = tid / ksteps, ks = tid - pass * ksteps;
+        const uint32_t ap = (pass == 0) ? 1u : 0u, bp = (pass == 1) ? 1u : 0u;   // piece 0 = hi, 1 = lo
+        s_tab[tid] = make_uint2(umma::desc_lo(a_addr + ap * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u),
+                                umma::desc_lo(b_addr + bp * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u));
+    }
+    __syncthreads();
 
     const long long tiles_total = (long long)U * T;
     const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
     const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
     const float inv_keep = 1.0f / (1.0f - a.drop_p);
     const int C = U * MT_H;
-    const int cpp = (chunks + 3) >> 2;                    // chunks per staging quarter (<= MT_CPP)
-    const int cbeg = cg * cpp, cend = min(chunks, cbeg + cpp);
+    // staging map (coalesced): warp w stages rows 8w..8w+7, lane = (row & 7) * 4 + element of the 4-float chunk,
+    // so one warp-wide access covers 8 rows x 16 B in global memory and 32 distinct banks in shared memory
+    const int srow = warp * 8 + (lane >> 2), se = lane & 3;
 
     int cur_u = -1;
     uint32_t phase = 0;
     float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f;   // per-channel constants (thread = channel modes)
     double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
-    float pv[MT_CPP][4];
+    float pv[MT_CMAX];
+    float pd = 0.0f;                                     // B1: prefetched dopre / active bits of row `row`
+    uint4 pm = make_uint4(0u, 0u, 0u, 0u);
 
     auto prefetch = [&](long long tile) {
         const bool live = tile < hi;
         const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
         const int b0 = t * MT_ROWS;
-        const float* src = (live && b0 + row < B) ? a.pool + ((long long)(b0 + row) * U + u) * n : nullptr;
+        const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
 #pragma unroll
-        for (int i = 0; i < MT_CPP; ++i) {
-            const int c = cbeg + i;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int q = 4 * c + e;
-                pv[i][e] = (src != nullptr && c < cend && q < n) ? __ldg(src + q) : 0.0f;
-            }
+        for (int c = 0; c < MT_CMAX; ++c) {
+            const int q = 4 * c + se;
+            pv[c] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
+        }
+        if (MODE == MLP_BWD_STATS && cg == 0) {
+            const bool ok = live && b0 + row < B;
+            const long long bu = (long long)(b0 + row) * U + u;
+            pd = ok ? __ldg(a.dopre + bu) : 0.0f;
+            pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
         }
     };
     auto store_tile = [&]() {
+        float* hi_p = reinterpret_cast<float*>(ps) + srow * 4 + se;
+        float* lo_p = hi_p + chunks * 512;
 #pragma unroll
-        for (int i = 0; i < MT_CPP; ++i) {
-            const int c = cbeg + i;
-            if (c < cend) {
-                float h[4], l[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) umma::split_tf32(pv[i][e], h[e], l[e]);
-                ps[c * 128 + row] = make_float4(h[0], h[1], h[2], h[3]);
-                ps[chunks * 128 + c * 128 + row] = make_float4(l[0], l[1], l[2], l[3]);
+        for (int c = 0; c < MT_CMAX; ++c) {
+            if (c < chunks) {
+                float h, l;
+                umma::split_tf32(pv[c], h, l);
+                hi_p[c * 512] = h;
+                lo_p[c * 512] = l;
             }
+        }
+        if (MODE == MLP_BWD_STATS && cg == 0) {
+            s_dopre[row] = pd;
+            *reinterpret_cast<uint4*>(s_mask + 4 * row) = pm;
         }
     };
     auto flush = [&](int u) {
@@ -260,19 +278,18 @@ mlp_fc1_kernel(MlpArgs a) {
         if (u != cur_u) {
             if (cur_u >= 0) flush(cur_u);
             cur_u = u;
-            // W1 of this unit: (row, quarter) stages its chunks of row `row` (rows >= 100 stay zero)
-            if (row < MT_H) {
-                const float* src = a.w1 + ((long long)u * MT_H + row) * n;
-#pragma unroll 2
-                for (int c = cbeg; c < cend; ++c) {
-                    float h[4], l[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int q = 4 * c + e;
-                        umma::split_tf32(q < n ? __ldg(src + q) : 0.0f, h[e], l[e]);
-                    }
-                    w1s[c * 128 + row] = make_float4(h[0], h[1], h[2], h[3]);
-                    w1s[chunks * 128 + c * 128 + row] = make_float4(l[0], l[1], l[2], l[3]);
+            // W1 of this unit, same coalesced map (rows >= 100 stay zero)
+            if (srow < MT_H) {
+                const float* src = a.w1 + ((long long)u * MT_H + srow) * n;
+                float* hi_p = reinterpret_cast<float*>(w1s) + srow * 4 + se;
+                float* lo_p = hi_p + chunks * 512;
+#pragma unroll 8
+                for (int c = 0; c < chunks; ++c) {
+                    const int q = 4 * c + se;
+                    float h, l;
+                    umma::split_tf32(q < n ? __ldg(src + q) : 0.0f, h, l);
+                    hi_p[c * 512] = h;
+                    lo_p[c * 512] = l;
                 }
             }
             const int ch = u * MT_H + row;
@@ -284,30 +301,11 @@ mlp_fc1_kernel(MlpArgs a) {
             }
         }
         store_tile();
-        if (MODE == MLP_BWD_STATS && cg == 0) {
-            const long long bu = (long long)(b0 + row) * U + u;
-            s_dopre[row] = (row < rows) ? a.dopre[bu] : 0.f;
-            uint4 kb = make_uint4(0u, 0u, 0u, 0u);
-            if (row < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
-            *reinterpret_cast<uint4*>(s_mask + 4 * row) = kb;
-        }
         umma::fence_proxy_async();
         __syncthreads();
         if (tid == 0) {
             umma::fence_after_sync();
-            uint32_t acc = 0;
-#pragma unroll 1
-            for (int pass = 0; pass < 3; ++pass) {
-                // small terms first: lo*hi, hi*lo, then hi*hi   (piece 0 = hi, 1 = lo)
-                const uint32_t ap = (pass == 0) ? 1u : 0u, bp = (pass == 1) ? 1u : 0u;
-#pragma unroll 1
-                for (int ks = 0; ks < ksteps; ++ks) {
-                    const uint64_t ad = umma::smem_desc(a_addr + ap * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
-                    const uint64_t bd = umma::smem_desc(b_addr + bp * piece_bytes + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
-                    umma::mma_tf32(tmem, ad, bd, idesc, acc);
-                    acc = 1;
-                }
-            }
+            umma::issue_table<true>(s_tab, 3 * ksteps, umma::desc_hi(128u), umma::desc_hi(128u), 0u, tmem, idesc, 0u);
             umma::commit(&sh->bar);
         }
         prefetch(tile + 1);                 // global loads of the next tile fly under the MMAs
@@ -410,7 +408,7 @@ static int mt_slots(int B, int U) {
 }
 static size_t mt_smem(int n) {
     const int chunks = ((n + 7) & ~7) >> 2;
-    return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + 2048 + sizeof(MtShared) + 16;
+    return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + 2048 + 32 + 3 * 12 * 8 + 16;
 }
 
 template <int MODE>
@@ -574,6 +572,9 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     float* s_dopre = reinterpret_cast<float*>(tail);                 // [64]
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 256);      // [64][4]
     MtShared* sh = reinterpret_cast<MtShared*>(tail + 256 + 1024);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 256 + 1024 + 32);  // [36 + 42 + 24] descriptor words
+    float* s_raw = reinterpret_cast<float*>(tail + 256 + 1024 + 32 + 1024);  // [64][n|1] fp32 pool tile (for dy)
+    const int S = n | 1;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int row = (warp & 3) * 32 + lane;   // TMEM lane: hidden channel m (D1, D3) / pool column q (D2)
@@ -595,6 +596,32 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16); // W1^T x dh^T (MN views)
     const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);                  // dh x pool^T (MN view)
     const uint32_t D1 = tmem, D2 = tmem + 64, D3 = tmem + 128;
+    // the six products of the 3-way split, smallest first: (piece of A, piece of B), 0 = hi, 1 = mid, 2 = lo
+    // MMA sequences of a tile (the operand buffers never move):
+    //   T1 [6*kstepsQ]  D1 = W1 (K-major) x pool (K-major)
+    //   T3 [42]         D2 = W1^T (MN view) x dh^T (MN view), K = hidden rows, 16 per MMA
+    //   T4 [24]         D3 += dh (K-major, K = batch rows) x pool^T (MN view)
+    const int n1 = 6 * kstepsQ;
+    if (tid < n1 + 42 + 24) {
+        const int seq = tid < n1 ? 0 : (tid < n1 + 42 ? 1 : 2);
+        const int i = tid - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + 42));
+        const int per = seq == 0 ? kstepsQ : (seq == 1 ? 7 : MB_ROWS / 16);
+        const int pass = i / per, ks = i - pass * per;
+        const uint32_t pa = pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u;
+        const uint32_t pb = pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u;
+        uint2 e;
+        if (seq == 0)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * 2048u, 2048u),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * 1024u, 1024u));
+        else if (seq == 1)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)ks * 256u, 128u),
+                           umma::desc_lo(t_addr + pb * tpiece + (uint32_t)ks * 256u, 128u));
+        else
+            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * 2048u, 2048u),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)ks * 256u, 128u));
+        s_tab[tid] = e;
+    }
+    __syncthreads();
 
     const long long tiles_total = (long long)U * T;
     const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
@@ -602,19 +629,18 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     const float inv_keep = 1.0f / (1.0f - a.drop_p);
     const int C = U * MT_H;
     const uint32_t trow = (uint32_t)((warp & 3) * 32) << 16;
-    // pool tile staging: 8 threads per row, <= 2 chunks (of 8 floats) each
-    const int srow = tid & 63, spart = tid >> 6;
-    const int cpp8 = (chunksQ + 7) >> 3;
-    const int sbeg = spart * cpp8, send = min(chunksQ, sbeg + cpp8);
-    // W1 staging: 4 threads per row
-    const int cpp4 = (chunksQ + 3) >> 2;
-    const int wbeg = cg * cpp4, wend = min(chunksQ, wbeg + cpp4);
+    // staging map (coalesced): a warp-wide access covers 8 rows x 32 B of global memory and 32 distinct banks:
+    // lane = (row & 7) * 4 + word, word = two consecutive pool columns of a 16-byte (8 x bf16) chunk.
+    // pool tile: warp w -> rows 8(w&7).., chunks (w>>3), (w>>3)+2, ...  (<= 6 chunks per warp)
+    const int srow = (warp & 7) * 8 + (lane >> 2), swd = lane & 3, sc0 = warp >> 3;
 
     int cur_u = -1;
     uint32_t phase = 0, d3_started = 0;
-    float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
+    float b1m = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
     double sdb1 = 0.0;
-    float pv[2][8];
+    float pv[6][2];
+    float pd = 0.0f;                                   // prefetched dopre / active bits of batch row tid (< 64)
+    uint4 pm = make_uint4(0u, 0u, 0u, 0u);
 
     auto prefetch = [&](long long tile) {
         const bool live = tile < hi;
@@ -622,26 +648,49 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         const int b0 = t * MB_ROWS;
         const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const int c = sbeg + i;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int q = 8 * c + e;
-                pv[i][e] = (src != nullptr && c < send && q < n) ? __ldg(src + q) : 0.0f;
-            }
+        for (int i = 0; i < 6; ++i) {
+            const int q = 8 * (sc0 + 2 * i) + 2 * swd;
+            pv[i][0] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
+            pv[i][1] = (src != nullptr && q + 1 < n) ? __ldg(src + q + 1) : 0.0f;
+        }
+        if (tid < MB_ROWS) {
+            const bool ok = live && b0 + tid < B;
+            const long long bu = (long long)(b0 + tid) * U + u;
+            pd = ok ? __ldg(a.dopre + bu) : 0.0f;
+            pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
         }
     };
-    auto store_tile = [&]() {
+    auto split2 = [](float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
+        uint32_t h[2], m[2], l[2];
+        const float xs[2] = {x0, x1};
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const int c = sbeg + i;
-            if (c < send) {
-                uint4 p0, p1, p2;
-                split8_bf16x3(pv[i], p0, p1, p2);
-                ps[c * 64 + srow] = p0;
-                ps[ppiece / 16 + c * 64 + srow] = p1;
-                ps[2 * (ppiece / 16) + c * 64 + srow] = p2;
+        for (int e = 0; e < 2; ++e) {
+            const __nv_bfloat16 aa = __float2bfloat16_rn(xs[e]);
+            const float r1 = xs[e] - __bfloat162float(aa);
+            const __nv_bfloat16 bb = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 cc = __float2bfloat16_rn(r1 - __bfloat162float(bb));
+            h[e] = __bfloat16_as_ushort(aa); m[e] = __bfloat16_as_ushort(bb); l[e] = __bfloat16_as_ushort(cc);
+        }
+        w0 = h[0] | (h[1] << 16); w1 = m[0] | (m[1] << 16); w2 = l[0] | (l[1] << 16);
+    };
+    auto store_tile = [&]() {
+        uint32_t* pw = reinterpret_cast<uint32_t*>(ps);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const int c = sc0 + 2 * i;
+            if (c < chunksQ) {
+                uint32_t w0, w1, w2;
+                split2(pv[i][0], pv[i][1], w0, w1, w2);
+                const int o = (c * 64 + srow) * 4 + swd;
+                pw[o] = w0; pw[ppiece / 4 + o] = w1; pw[2 * (ppiece / 4) + o] = w2;
+                const int q = 8 * c + 2 * swd;
+                if (q < n) s_raw[srow * S + q] = pv[i][0];
+                if (q + 1 < n) s_raw[srow * S + q + 1] = pv[i][1];
             }
+        }
+        if (tid < MB_ROWS) {
+            s_dopre[tid] = pd;
+            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = pm;
         }
     };
     auto flush = [&](int u) {
@@ -669,10 +718,6 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         __syncthreads();
     };
 
-    // the six products of the 3-way split, smallest first: (piece of A, piece of B), 0 = hi, 1 = mid, 2 = lo
-    auto pa = [](int pass) { return pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u; };
-    auto pb = [](int pass) { return pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u; };
-
     prefetch(lo);
     for (long long tile = lo; tile < hi; ++tile) {
         const int u = (int)(tile / T), t = (int)(tile % T);
@@ -680,11 +725,25 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         if (u != cur_u) {
             if (cur_u >= 0) flush(cur_u);
             cur_u = u;
-            if (row < MT_H)
-                stage_row_bf16x3(a.w1 + ((long long)u * MT_H + row) * n, n, wbeg, wend, 128, row, w1s, wpiece / 16);
+            {
+                // W1 of this unit, same coalesced map: items (row group of 8, chunk) dealt round-robin to the warps
+                uint32_t* ww = reinterpret_cast<uint32_t*>(w1s);
+                for (int it = warp; it < 13 * chunksQ; it += MT_THREADS / 32) {
+                    const int g = it / chunksQ, c = it - g * chunksQ;
+                    const int r = g * 8 + (lane >> 2);
+                    if (r < MT_H) {
+                        const float* src = a.w1 + ((long long)u * MT_H + r) * n;
+                        const int q = 8 * c + 2 * swd;
+                        uint32_t w0, w1v, w2v;
+                        split2(q < n ? __ldg(src + q) : 0.0f, q + 1 < n ? __ldg(src + q + 1) : 0.0f, w0, w1v, w2v);
+                        const int o = (c * 128 + r) * 4 + swd;
+                        ww[o] = w0; ww[wpiece / 4 + o] = w1v; ww[2 * (wpiece / 4) + o] = w2v;
+                    }
+                }
+            }
             const int ch = u * MT_H + row;
             const bool ok = row < MT_H;
-            b1m = ok ? a.b1[ch] : 0.f; scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f;
+            b1m = ok ? a.b1[ch] : 0.f;
             w2m = ok ? a.w2[ch] : 0.f;
             meanm = ok ? (float)a.stats2[4LL * ch] : 0.f; invstdm = ok ? (float)a.stats2[4LL * ch + 2] : 0.f;
             gism = ok ? (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]) : 0.f;
@@ -692,28 +751,12 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             c1m = cf.x; c2m = cf.y;
         }
         store_tile();
-        if (tid < MB_ROWS) {
-            const long long bu = (long long)(b0 + tid) * U + u;
-            s_dopre[tid] = (tid < rows) ? a.dopre[bu] : 0.f;
-            uint4 kb = make_uint4(0u, 0u, 0u, 0u);
-            if (tid < rows) kb = *reinterpret_cast<const uint4*>(a.maskbits + bu * 4);
-            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = kb;
-        }
+        prefetch(tile + 1);      // a whole tile of tensor + epilogue work hides these loads
         umma::fence_proxy_async();
         __syncthreads();
         if (tid == 0) {
             umma::fence_after_sync();
-            uint32_t acc = 0;
-#pragma unroll 1
-            for (int pass = 0; pass < 6; ++pass) {
-#pragma unroll 1
-                for (int ks = 0; ks < kstepsQ; ++ks) {
-                    const uint64_t ad = umma::smem_desc(w_addr + pa(pass) * wpiece + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
-                    const uint64_t bd = umma::smem_desc(p_addr + pb(pass) * ppiece + (uint32_t)(2 * ks) * 1024u, 1024u, 128u);
-                    umma::mma_bf16(D1, ad, bd, idesc1, acc);
-                    acc = 1;
-                }
-            }
+            umma::issue_table<false>(s_tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), 0u, D1, idesc1, 0u);
             umma::commit(&sh->bar);
         }
         umma::mbar_wait(&sh->bar, phase);
@@ -754,43 +797,12 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         __syncthreads();
         if (tid == 0) {
             umma::fence_after_sync();
-            // D2[q][b] = sum_m W1[m][q] * dh[m][b]: both operands are MN-major views, K = hidden rows (16 per MMA)
-            uint32_t acc = 0;
-#pragma unroll 1
-            for (int pass = 0; pass < 6; ++pass) {
-#pragma unroll 1
-                for (int ks = 0; ks < 7; ++ks) {
-                    const uint64_t ad = umma::smem_desc(w_addr + pa(pass) * wpiece + (uint32_t)ks * 256u, 128u, 2048u);
-                    const uint64_t bd = umma::smem_desc(t_addr + pb(pass) * tpiece + (uint32_t)ks * 256u, 128u, 2048u);
-                    umma::mma_bf16(D2, ad, bd, idesc2, acc);
-                    acc = 1;
-                }
-            }
-            // D3[m][q] += sum_b dh[m][b] * pool[b][q]: A = dh K-major (K = batch rows), B = pool^T (MN view)
-#pragma unroll 1
-            for (int pass = 0; pass < 6; ++pass) {
-#pragma unroll 1
-                for (int ks = 0; ks < MB_ROWS / 16; ++ks) {
-                    const uint64_t ad = umma::smem_desc(t_addr + pa(pass) * tpiece + (uint32_t)(2 * ks) * 2048u, 2048u, 128u);
-                    const uint64_t bd = umma::smem_desc(p_addr + pb(pass) * ppiece + (uint32_t)ks * 256u, 128u, 1024u);
-                    umma::mma_bf16(D3, ad, bd, idesc3, d3_started);
-                    d3_started = 1;
-                }
-            }
+            umma::issue_table<false>(s_tab + n1, 42, umma::desc_hi(2048u), umma::desc_hi(2048u), 0u, D2, idesc2, 0u);
+            umma::issue_table<false>(s_tab + n1 + 42, 24, umma::desc_hi(128u), umma::desc_hi(1024u), 0u, D3, idesc3,
+                                     d3_started);
             umma::commit(&sh->bar);
         }
         d3_started = 1;
-        // loads that fly under the MMAs: this tile's pool values for dy, and the next tile's staging rows
-        float pq[16];
-        {
-            const int c0 = 16 * cg;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const bool ok = row < n && c0 + i < rows;
-                pq[i] = ok ? __ldg(a.pool + ((long long)(b0 + c0 + i) * U + u) * n + row) : 0.0f;
-            }
-        }
-        prefetch(tile + 1);
         umma::mbar_wait(&sh->bar, phase);
         phase ^= 1u;
         umma::fence_after_sync();
@@ -806,7 +818,8 @@ mlp_bwd_kernel(MlpBwdArgs a) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
                         if (c0 + i < rows)
-                            a.dy[((long long)(b0 + c0 + i) * U + u) * n + row] = pq[i] * __uint_as_float(v[i]);
+                            a.dy[((long long)(b0 + c0 + i) * U + u) * n + row] =
+                                s_raw[(c0 + i) * S + row] * __uint_as_float(v[i]);
                 }
             }
         }
@@ -850,7 +863,7 @@ static size_t mb_smem(int n) {
     const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
     const size_t body = 3 * chunksQ * 2048 + 3 * chunksQ * 1024 + 3 * 8 * 2048;
     const size_t need = 2 * chunksQ * 2048 + 16 * 2048;
-    return (body > need ? body : need) + 256 + 1024 + sizeof(MtShared) + 16;
+    return (body > need ? body : need) + 256 + 1024 + 32 + 1024 + (size_t)MB_ROWS * (n | 1) * 4 + 16;
 }
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 

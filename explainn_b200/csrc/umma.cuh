@@ -71,6 +71,40 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
     lo = __uint_as_float(l);
 }
 
+// ---- descriptor tables ---------------------------------------------------------------------------
+// The issuing thread is a single lane: every integer instruction it spends building descriptors sits on
+// the tensor core's critical path (a K = 16 step of a 128 x 64 tile is only 32 cycles of math).  The
+// operand addresses of a tile are known up front, so each kernel precomputes the low descriptor words
+// (start address >> 4 | LBO << 16) of its MMA sequence into shared memory once; the issue loop is then
+// one 8-byte load per MMA.  The high word (SBO | version) is a per-operand constant.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+    return ((saddr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+
+// issue `count` MMAs D (+)= A_i . B_i from a table of (A low word, B low word); add_b is added to every
+// B low word (a per-tile start offset >> 4); the first MMA uses `first_acc`, the rest accumulate.
+template <bool TF32>
+__device__ __forceinline__ void issue_table(const uint2* __restrict__ tab, int count, uint32_t hi_a, uint32_t hi_b,
+                                            uint32_t add_b, uint32_t d_tmem, uint32_t idesc, uint32_t first_acc) {
+    // batches of 6: the table loads of a batch are issued together, ahead of its MMAs
+    for (int i0 = 0; i0 < count; i0 += 6) {
+        uint2 e[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) e[j] = tab[min(i0 + j, count - 1)];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            if (i0 + j < count) {
+                const uint64_t ad = ((uint64_t)hi_a << 32) | (uint64_t)e[j].x;
+                const uint64_t bd = ((uint64_t)hi_b << 32) | (uint64_t)(e[j].y + add_b);
+                const uint32_t acc = (i0 + j == 0) ? first_acc : 1u;
+                if (TF32) mma_tf32(d_tmem, ad, bd, idesc, acc);
+                else mma_bf16(d_tmem, ad, bd, idesc, acc);
+            }
+        }
+    }
+}
+
 // arrive on an mbarrier when every previously issued tcgen05.mma of this thread has completed
 __device__ __forceinline__ void commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
