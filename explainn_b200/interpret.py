@@ -58,11 +58,34 @@ def act_thresholds(model, seqs, idxs=None, rev_complement=False):
     return (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
 
 
+def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=65536):
+    """Pass 2a alone: uncapped number of above-threshold positions per (strand, unit) -> int64 (S,U)
+    device tensor.  A sequence shard needs the totals of the shards before it (parallel.exclusive_carry)
+    to place the reference's 1e6 cap (interpret.py:414-417) on the same global prefix."""
+    packed = _as_packed(seqs)
+    cw, scale, shift = _front_eval_affine(model)
+    U = cw.shape[0]
+    N = len(packed)
+    dev = packed.planes.device
+    half = N // 2 if rev_complement else N
+    idx_all = np.arange(half) if idxs is None else np.asarray(idxs)
+    thr = torch.as_tensor(np.asarray(thresholds, dtype=np.float16).astype(np.float32), device=dev)
+    strands = (0, 1) if rev_complement else (0,)
+    tot = torch.zeros((len(strands), U), dtype=torch.int64, device=dev)
+    for strand in strands:
+        for c0 in range(0, len(idx_all), chunk):
+            idx_dev = torch.as_tensor(idx_all[c0:c0 + chunk] + strand * half, dtype=torch.int32, device=dev)
+            counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
+            tot[strand] += counts.sum(dim=1, dtype=torch.int64)
+    return tot
+
+
 def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap=SITE_CAP,
-                   return_sites=False, site_capacity=None, chunk=65536):
+                   return_sites=False, site_capacity=None, chunk=65536, carry0=None):
     """interpret.py:375-454.  Returns dict(counts (U,) int64 sites emitted per unit,
     pfms (U,4,k) int64, sites: list per unit of int32 arrays (m,3) = (sequence index, strand 0/1, start)
-    when return_sites)."""
+    when return_sites).  carry0 (S,U) int64: global rank of this shard's first site per strand and unit
+    (sequence-sharded runs, parallel.interpret_sharded); counts are then the ranks reached, capped."""
     packed = _as_packed(seqs)
     cw, scale, shift = _front_eval_affine(model)
     U, _, k = cw.shape
@@ -77,6 +100,8 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
     if return_sites and site_capacity is None:
         site_capacity = cap
     for strand in ((0, 1) if rev_complement else (0,)):
+        if carry0 is not None:
+            carry = torch.as_tensor(carry0[strand], dtype=torch.int64, device=dev).clone()
         for c0 in range(0, len(idx_all), chunk):
             ids = idx_all[c0:c0 + chunk]
             idx_dev = torch.as_tensor(ids + strand * half, dtype=torch.int32, device=dev)
@@ -113,7 +138,7 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
             else:
                 ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm, None)
             carry = carry + csum[:, -1]
-            if bool((carry >= cap).all()):
+            if carry0 is None and bool((carry >= cap).all()):
                 break
     out = {
         "counts": torch.clamp(carry, max=cap).cpu().numpy(),

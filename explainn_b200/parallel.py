@@ -86,3 +86,64 @@ def gather_rows(local, n_total, rank, world):
     out = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(out, pad)
     return torch.cat([o[:hi - lo] for o, (lo, hi) in zip(out, sizes)])
+
+
+def exclusive_carry(local_totals, group=None):
+    """Exchange step of the sharded interpret pass 2.  local_totals int64 (S,U): this
+    shard's uncapped site totals per strand and unit.  The reference counts sites strand by strand, then
+    by ascending sequence (interpret.py:388-417), and shards are contiguous ascending ranges, so the
+    global rank of this shard's first site on strand s is
+        sum over all shards of strands < s  +  sum over lower ranks of strand s.
+    Returns (carry0 (S,U), grand total (U,)), both int64 on local_totals' device."""
+    if not (dist.is_initialized() and dist.get_world_size(group) > 1):
+        before = torch.cumsum(local_totals, dim=0) - local_totals
+        return before, local_totals.sum(dim=0)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    allt = [torch.empty_like(local_totals) for _ in range(world)]
+    dist.all_gather(allt, local_totals.contiguous(), group=group)
+    allt = torch.stack(allt)                                   # (world, S, U)
+    per_strand = allt.sum(dim=0)                               # (S, U)
+    strands_before = torch.cumsum(per_strand, dim=0) - per_strand
+    ranks_before = allt[:rank].sum(dim=0) if rank > 0 else torch.zeros_like(local_totals)
+    return strands_before + ranks_before, per_strand.sum(dim=0)
+
+
+def allreduce_max_(t, group=None):
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return t
+
+
+def allreduce_sum_(t, group=None):
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+def interpret_sharded(model, local_seqs, rev_complement=False, cap=None, group=None):
+    """The interpret path (a7-a10) over a contiguous, ascending shard of the sequences per rank.
+    local_seqs: this rank's PackedDNA / float one-hot (both halves when rev_complement).
+    pass 1: local per-unit maxima -> all-reduce(max) -> the same fp16 thresholds on every rank;
+    pass 2: local totals -> exclusive_carry -> capped local emission -> all-reduce(sum) of the PFMs.
+    Returns dict(thresholds (U,) float16, counts (U,) int64, pfms (U,4,k) int64), identical on all ranks
+    and identical to the single-process result."""
+    import numpy as np
+    from . import interpret as I
+    cap = I.SITE_CAP if cap is None else cap
+    packed = I._as_packed(local_seqs)
+    cw, scale, shift = I._front_eval_affine(model)
+    from . import ops
+    N = len(packed)
+    half = N // 2 if rev_complement else N
+    idx = torch.arange(half, dtype=torch.int32, device=packed.planes.device)
+    amax = ops.act_max(packed.planes, packed.length, cw, scale, shift, idx)
+    if rev_complement:
+        amax = torch.maximum(amax, ops.act_max(packed.planes, packed.length, cw, scale, shift, idx + half))
+    allreduce_max_(amax, group)
+    thr = (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
+    tot = I.site_totals(model, packed, thr, None, rev_complement)
+    carry0, grand = exclusive_carry(tot, group)
+    res = I.sites_and_pfms(model, packed, thr, None, rev_complement, cap=cap, carry0=carry0)
+    pfm = torch.as_tensor(res["pfms"], device=packed.planes.device)
+    allreduce_sum_(pfm, group)
+    return {"thresholds": thr, "counts": torch.clamp(grand, max=cap).cpu().numpy(), "pfms": pfm.cpu().numpy()}

@@ -460,6 +460,40 @@ def test_interpret_vs_oracle_with_cap():
     assert mismatched_units <= 2
 
 
+def test_interpret_sequence_shards_reproduce_the_unsharded_result():
+    """contiguous shards + exclusive carries place the site cap on the same global prefix
+    (both strands); the two-shard exchange is emulated in-process, the collective itself is covered by
+    tests/test_parallel_gloo.py."""
+    from explainn_b200 import interpret as I, parallel
+    from explainn_b200.architectures import PackedDNA
+    m = _random_model(24, 19, 120, 1).eval().to(DEV)
+    N = 90
+    fwd = O.random_onehot(N, 120, seed=21, n_frac=0.01).to(DEV)
+    pk = PackedDNA.from_onehot(fwd)
+    both = PackedDNA(torch.cat([pk.planes, pk.revcomp().planes]), 120)
+    thr = I.act_thresholds(m, both, None, rev_complement=True)
+    cap = 400
+    ref = I.sites_and_pfms(m, both, thr, None, rev_complement=True, cap=cap)
+    assert (ref["counts"] == cap).any() and (ref["counts"] < cap).any()   # the cap bites for some units only
+    shards, tots = [], []
+    for r in range(3):
+        lo, hi = parallel.shard_range(N, r, 3)
+        sh = PackedDNA(torch.cat([pk.planes[lo:hi], pk.revcomp().planes[lo:hi]]).contiguous(), 120)
+        shards.append(sh)
+        tots.append(I.site_totals(m, sh, thr, None, True))
+    allt = torch.stack(tots)
+    per_strand = allt.sum(0)
+    pfm = np.zeros_like(ref["pfms"])
+    for r, sh in enumerate(shards):
+        carry0 = (torch.cumsum(per_strand, 0) - per_strand) + allt[:r].sum(0)
+        pfm += I.sites_and_pfms(m, sh, thr, None, True, cap=cap, carry0=carry0)["pfms"]
+    assert np.array_equal(pfm, ref["pfms"])
+    assert np.array_equal(np.minimum(per_strand.sum(0).cpu().numpy(), cap), ref["counts"])
+    one = parallel.interpret_sharded(m, both, rev_complement=True, cap=cap)   # world size 1 path
+    assert np.array_equal(one["pfms"], ref["pfms"]) and np.array_equal(one["counts"], ref["counts"])
+    assert np.array_equal(one["thresholds"], thr)
+
+
 def test_acts_outs_preds_dropin():
     from explainn_b200 import interpret as I
     d = U.load_npz("interpret_small.npz")
