@@ -9,10 +9,11 @@ on synthetic one-hot DNA.  Default workload = cfg3, the configuration the metric
 (weak scaling; one rank per GPU, per-rank BatchNorm statistics, one flat gradient all-reduce per step).
 
 `value`   : K steps with the float one-hot batches already resident in HBM.
-`e2e`     : the same step through the reference-facing API with HOST buffers: pinned one-hot floats are
-            copied to the device every step and the loss is read back (`loss.item()`), as
-            selene/__init__.py:283-295 does.
-`roofline`: the dominant kernel (frontend_fwd_kernel) timed with CUDA events inside the timed region.
+`e2e`     : the same step through the host-facing API (explainn_b200/trainer.py StepPipeline, the step of
+            selene/__init__.py:283-295) with HOST buffers: every step copies its pinned float one-hot batch
+            to the device and reads its loss back; the copy of batch i+1 runs on a copy stream under step i.
+`roofline`: every C-ABI call of the timed region is bracketed by CUDA events on the launching stream; the
+            entry point with the largest share is reported against its bound.
 `cpu_baseline` / `--impl reference`: the oracle port (oracle/explainn_oracle.py, torch CPU, the reference's
             own arithmetic) timed on the host cores on a bounded sample of the same workload.
 """
@@ -29,6 +30,10 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
+# `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
+NCU_TRAFFIC = {}
 
 WORKLOADS = {
     # name: (cnn_units, kernel, length, features, loss kind, per-GPU batch)
@@ -175,26 +180,25 @@ def main():
     xs_d = [x.to(dev) for x in xs_h]
     ys_d = [y.to(dev) for y in ys_h]
 
-    # event pairs around the dominant kernel (launched on torch's current stream)
-    fe_events = []
-    orig_frontend = ops.frontend_fwd
+    # event pairs around every C-ABI call (all launched on torch's current stream): the dominant entry point
+    # of the timed region is found from these, not assumed
+    call_events = {}
+    orig_call = ops._call
 
-    def timed_frontend(*a, **kw):
+    def timed_call(name, *a):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        out = orig_frontend(*a, **kw)
+        orig_call(name, *a)
         e1.record()
-        fe_events.append((e0, e1))
-        return out
+        call_events.setdefault(name, []).append((e0, e1))
 
-    def step(x, y, read_loss):
+    def step(x, y):
         pred = model(x)
         loss = crit(pred, y)
         opt.zero_grad()
         loss.backward()
         bucket.allreduce_mean()
         opt.step()
-        return loss.item() if read_loss else None
 
     def barrier():
         if world > 1:
@@ -215,25 +219,33 @@ def main():
         return float(ms.item())
 
     for i in range(args.warmup):
-        step(xs_d[i % NB], ys_d[i % NB], False)
+        step(xs_d[i % NB], ys_d[i % NB])
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ops.frontend_fwd = timed_frontend
+    ops._call = timed_call
     k0 = ops.kernel_launches
-    ms_dev = timed(lambda i: step(xs_d[i % NB], ys_d[i % NB], False), args.steps)
+    ms_dev = timed(lambda i: step(xs_d[i % NB], ys_d[i % NB]), args.steps)
     launches = ops.kernel_launches - k0
-    ops.frontend_fwd = orig_frontend
-    fe_ms = sum(a.elapsed_time(b) for a, b in fe_events) / max(1, len(fe_events))
+    ops._call = orig_call
+    call_ms = {nme: sum(a.elapsed_time(b) for a, b in ev) / args.steps for nme, ev in call_events.items()}
 
-    def e2e_step(i):
-        x = xs_pin[i % NB].to(dev, non_blocking=True)
-        y = ys_pin[i % NB].to(dev, non_blocking=True)
-        step(x, y, True)
+    # end to end through the host-facing step (explainn_b200/trainer.py): every step copies its batch from
+    # pinned host memory and reads its loss back; copies of batch i+1 overlap step i, losses arrive one call late
+    from explainn_b200.trainer import StepPipeline
+    pipe = StepPipeline(model, crit, opt, bucket, dev)
+    for i in range(3):
+        pipe.step(xs_pin[i % NB], ys_pin[i % NB])
+    pipe.flush()
+    h0, d0 = pipe.h2d_bytes, pipe.d2h_bytes
 
-    for i in range(2):
-        e2e_step(i)
-    ms_e2e = timed(e2e_step, args.steps)
+    def e2e_all(_):
+        for i in range(args.steps):
+            pipe.step(xs_pin[i % NB], ys_pin[i % NB])
+        pipe.flush()
+
+    ms_e2e = timed(e2e_all, 1)
+    h2d_step, d2h_step = (pipe.h2d_bytes - h0) // args.steps, (pipe.d2h_bytes - d0) // args.steps
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -242,8 +254,27 @@ def main():
     e2e = world * B * args.steps / (ms_e2e / 1e3)
     hbm, tf_sus, tf_burst, which = peaks()
     Lc = L - k + 1
-    flops_per_seq = 2.0 * U * Lc * 4 * k          # dense-equivalent conv flops
-    achieved = flops_per_seq * B / (fe_ms / 1e3) / 1e12
+    n = Lc // 7
+    # algorithmic work per sequence of each entry point
+    conv_flops = 2.0 * U * Lc * 4 * k                       # dense-equivalent conv
+    pool_bytes = 4.0 * U * n
+    ALG = {
+        "xnn_frontend_fwd": ("tensor", conv_flops, "conv+BN+exp+maxpool forward, dense-equivalent 2*U*Lc*4k flop"),
+        "xnn_frontend_bwd": ("hbm", 9.0 * U * n + 12.0 * ((L + 31) // 32),
+                             "conv weight gradient: dy+zmax (fp32) + argmax (u8) + planes read"),
+        "xnn_mlp_bwd": ("hbm", 2 * pool_bytes + 24.0 * U, "MLP backward: pool read, dy written, maskbits+dopre read"),
+        "xnn_mlp_fwd": ("hbm", pool_bytes + 20.0 * U, "MLP forward: pool read, opre+maskbits written"),
+        "xnn_mlp_bn2_train_prepare": ("hbm", pool_bytes, "BN2 batch statistics: pool read"),
+        "xnn_pack_onehot_f32": ("hbm", 16.0 * L + 12.0 * ((L + 31) // 32), "float one-hot read, planes written"),
+    }
+    top = max(call_ms, key=call_ms.get)
+    top_ms = call_ms[top]
+    bound, per_seq, what = ALG.get(top, ("hbm", 0.0, "unlisted"))
+    if bound == "tensor":
+        achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e12, tf_sus, "TFLOP/s", "bf16_tflops_sustained"
+    else:
+        achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e9, hbm, "GB/s", "hbm_gbs"
+    fe_ms = call_ms.get("xnn_frontend_fwd", 0.0)
     cpu_rate, cpu_ms, cores = cpu_reference_rate(cfg, 4, 1, args.cpu_sample)
     print(json.dumps({
         "metric": "sequences/sec ExplaiNN fwd+bwd training step", "value": value, "unit": "sequences/s",
@@ -254,13 +285,18 @@ def main():
                    "l2": f"inputs rotate over {NB} distinct batches ({NB * B * 16 * L / 1e6:.0f} MB > 126 MB L2); "
                          f"intermediates exceed L2"},
         "e2e": {"value": e2e, "unit": "sequences/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": B * 4 * L * 4 + B * F * 4, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step,
+                "api": "explainn_b200.trainer.StepPipeline.step(pinned float one-hot, pinned targets): H2D of batch "
+                       "i+1 on a copy stream under step i, loss read back every step one call late"},
         "gpu_launches": launches,
-        "roofline": {"kernel": "frontend_fwd_kernel (conv+BN+exp+maxpool)", "bound": "tensor", "achieved": achieved,
-                     "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": None,
-                     "peak_source": f"bf16_tflops_sustained, {which}", "kernel_ms": fe_ms,
-                     "kernel_share_of_step": fe_ms / (ms_dev / args.steps),
-                     "algorithmic_flops_per_seq": flops_per_seq},
+        "roofline": {"kernel": top, "what": what, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
+                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(top), "peak_source": f"{src}, {which}",
+                     "kernel_ms": top_ms, "kernel_share_of_step": top_ms / (ms_dev / args.steps),
+                     "algorithmic_per_seq": per_seq,
+                     "frontend_fwd": {"bound": "tensor", "kernel_ms": fe_ms,
+                                      "achieved": conv_flops * B / (fe_ms / 1e3) / 1e12 if fe_ms else None,
+                                      "peak": tf_sus, "unit": "TFLOP/s"},
+                     "per_call_ms": {k_: round(v, 4) for k_, v in sorted(call_ms.items(), key=lambda kv: -kv[1])}},
         "cpu_baseline": {"value": cpu_rate, "unit": "sequences/s", "cores": cores, "kind": "port",
                          "sample": f"4 train steps of {args.cpu_sample} sequences, oracle port (torch CPU)"},
         "clocks": clocks,
