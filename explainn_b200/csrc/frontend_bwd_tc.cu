@@ -7,16 +7,26 @@
 //
 //   D[unit, f = 4j+c] (fp32, TMEM) = A[unit, p] (g, bf16 x3 split) . B[p, f] (one-hot window)
 //
-// B is never built: with the sequence position-major in shared memory as bf16 one-hot
-// (8 bytes per position, the forward kernel's layout) element (p, f) sits at byte 8p + 2f.
-// An MN-major UMMA operand without swizzle addresses
-//   K row r, 16-byte N chunk c  ->  start + 16*(r%8) + LBO*(r/8) + SBO*c
-// so LBO = 128, SBO = 16 is the Toeplitz view with K row r <-> position P + 2r; odd
-// positions are a second MMA on a copy of the buffer shifted by one position.
+// B is never built.  The sequence sits in shared memory as bf16 one-hot PAIRS, 16 bytes per
+// position: P2[p] = (x[.,p], x[.,p+1]).  Element (p, f) of the im2col matrix is then at byte
+// 16p + 2f, and an MN-major UMMA operand without swizzle, which addresses
+//   K row r, 16-byte N chunk c  ->  start + 16*(r%8) + LBO*(r/8) + SBO*c,
+// is the Toeplitz view with SBO = 32 (chunk c = taps 2c, 2c+1 = P2[p+2c]).  LBO = 112 = 7*16
+// makes every group of 8 K rows start at a pool window: K rows 8g..8g+7 <-> positions
+// 7g..7g+7, so ONE 16-byte K chunk of A per pool window holds that window's single non-zero
+// at slot arg (slot 7, the next window's first position, is always zero).
+//
+// A (K-major): each producer lane owns one (unit row, window): it loads dy / zmax / argmax
+// coalesced from HBM, splits dy into three bf16 pieces and writes one 16-byte chunk per
+// piece -- no transposition through shared memory, no cross-thread scatter.  Chunk
+// pitch LBO_A = 144 B (128 + 16) keeps those stores bank-conflict free.
 // The accumulator stays in TMEM for the CTA's whole slice of the batch and is read once.
 //
-// A is the sparse g (one non-zero per pool window) scattered into a zeroed K-major tile of
-// 4 windows = 28 positions = 14 (padded to 16) K rows per parity, three bf16 pieces each.
+// Roles (one CTA of 18 warps per SM): two producer groups of 8 warps convert alternate tiles (a warp's
+// serial path per tile is ~1000 cycles, twice the tensor time of a tile); warp 16 lane 0 issues every
+// tcgen05.mma; warp 17 expands the next sequence's planes into the pair buffer.  Stages of 8 windows x 128
+// rows cycle through full[] (one arrival per producer warp) / empty[] (tcgen05.commit) mbarriers; there is
+// no CTA-wide barrier in the loop, and each producer prefetches its next tile while it converts this one.
 #include "common.cuh"
 #include "umma.cuh"
 #include <cuda_bf16.h>
@@ -24,222 +34,293 @@ using namespace xnn;
 
 #define BT_KMAX 32
 #define BT_ROWS 128                 // units per CTA = UMMA M
-#define BT_WIN 4                    // pool windows per tile
-#define BT_TILE_POS (BT_WIN * XNN_POOL)   // 28 positions
+#define BT_WIN 8                    // pool windows per tile (stage)
 #define BT_SPLITS 3
-#define BT_BLOCK_BYTES 4096         // one (piece, parity) A block: K = 16 -> 2 chunks of 2048 B
-#define BT_STAGE_BYTES (BT_SPLITS * 2 * BT_BLOCK_BYTES)
-#define BT_THREADS 128
-#define BT_RG 4                     // rows per staging group (loads in flight)
+#define BT_LBO_A 144                // bytes between K chunks (windows) of one row group
+#define BT_SBO_A (BT_WIN * BT_LBO_A)         // bytes between 8-row groups (1152)
+#define BT_PIECE_BYTES (16 * BT_SBO_A)       // one bf16 piece of a stage (18432)
+#define BT_STAGE_BYTES (BT_SPLITS * BT_PIECE_BYTES)   // 55296
+#define BT_MAX_STAGES 3
+#define BT_GROUPS 2                 // producer groups; group g converts the tiles with global index = g mod 2
+#define BT_GROUP_WARPS 8
+#define BT_PRODUCERS (BT_GROUPS * BT_GROUP_WARPS * 32)   // 512
+#define BT_THREADS (BT_PRODUCERS + 64)                   // + issuer warp + one-hot warp
+#define BT_RGS 4                    // row groups of 4 rows per producer warp (16 rows per warp)
 
 static inline int bt_npad(int k) { return ((4 * k + 15) / 16) * 16; }
 static inline int bt_mtiles(int U) { return (U + BT_ROWS - 1) / BT_ROWS; }
 
-static int bt_slices(int B, int U) {
-    int s = (num_sms() * 2) / bt_mtiles(U);
+// batch slices (CTAs) per M tile: the cost of a tile is the same for every M tile (UMMA M = 128)
+static int bt_slices(int U, int B) {
+    int s = num_sms() / bt_mtiles(U);
     if (s < 1) s = 1;
     if (s > B) s = B;
     return s;
 }
 
 struct BtShared {
-    uint64_t bar[2];
+    uint64_t full[BT_MAX_STAGES];    // producer group -> issuer: stage written and fenced (8 warp arrivals)
+    uint64_t empty[BT_MAX_STAGES];   // issuer -> producers: the MMAs that read the stage completed
+    uint64_t oh_full[2];             // one-hot warp -> issuer: pair buffer of a sequence written
+    uint64_t oh_empty[2];            // issuer -> one-hot warp: the MMAs of the sequence completed
     uint32_t tmem_slot;
     uint32_t pad;
 };
 
-__device__ __forceinline__ uint2 bt_onehot_bf16x4(const uint32_t* __restrict__ sp, int Wp, int L, int i) {
-    uint2 v = make_uint2(0u, 0u);
-    if (i < L) {
-        const int w = i >> 5, b = i & 31;
-        const uint32_t lo = (sp[w] >> b) & 1u, hi = (sp[Wp + w] >> b) & 1u, nm = (sp[2 * Wp + w] >> b) & 1u;
-        if (!nm) {
-            const uint32_t half = lo ? 0x3F800000u : 0x00003F80u;
-            if (hi) v.y = half; else v.x = half;
-        }
-    }
-    return v;
-}
+__device__ __forceinline__ void bt_producer_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 
-__global__ void __launch_bounds__(BT_THREADS)
+struct BtVals {   // one tile's values of a producer lane: 4 row groups
+    float d[BT_RGS], z[BT_RGS];
+    int a[BT_RGS];
+};
+
+__global__ void __launch_bounds__(BT_THREADS, 1)
 frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int U, int k, int n, int npad,
-                       int Lbuf, int dstride, int astride,
+                       int Lbuf, int nstages,
                        const float* __restrict__ dy, const float* __restrict__ zmax,
                        const uint8_t* __restrict__ argmax, const double* __restrict__ stats,
                        uint32_t b_lbo, uint32_t b_sbo,
-                       double* __restrict__ part /* [slices][U][4k+2] */) {
+                       double* __restrict__ part /* [gridDim.y][U][4k+2] */) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* g_smem = smem_raw;                                              // [2 stages][pieces][2][4096]
-    uint2* buf0 = reinterpret_cast<uint2*>(smem_raw + 2 * BT_STAGE_BYTES);         // [Lbuf]
-    uint2* buf1 = buf0 + Lbuf;                                                     // [Lbuf] shifted by one
-    float* s_d = reinterpret_cast<float*>(buf1 + Lbuf);                            // [128][dstride]
-    float* s_sb = s_d + BT_ROWS * dstride;                                         // [128]
-    float* s_sg = s_sb + BT_ROWS;                                                  // [128]
-    float* s_ws = s_sg + BT_ROWS;                                                  // [128]
-    uint8_t* s_arg = reinterpret_cast<uint8_t*>(s_ws + BT_ROWS);                   // [128][astride]
-    BtShared* sh = reinterpret_cast<BtShared*>(s_arg + ((BT_ROWS * astride + 15) & ~15));
+    unsigned char* g_smem = smem_raw;                                                  // [nstages][3][16][8][144]
+    uint2* oh = reinterpret_cast<uint2*>(smem_raw + (size_t)nstages * BT_STAGE_BYTES); // [2][Lbuf] pairs (16 B)
+    double* s_red = reinterpret_cast<double*>(oh + 4 * (size_t)Lbuf);                  // [2 groups][128][2]
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(s_red + 2 * 2 * BT_ROWS);             // [3 * Wp] plane words
+    BtShared* sh = reinterpret_cast<BtShared*>(s_pl + ((3 * Wp + 3) & ~3));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int u0 = blockIdx.x * BT_ROWS;
     const int nu = min(BT_ROWS, U - u0);
-    const int u = u0 + tid;
-    const bool row_ok = tid < nu;
+    const int K4 = 4 * k, pstride = K4 + 2;
+    const int ns = gridDim.y;
 
     // ---- one-time setup
-    {
-        uint4* z = reinterpret_cast<uint4*>(g_smem);
-        for (int i = tid; i < 2 * BT_STAGE_BYTES / 16; i += BT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
-    }
-    s_ws[tid] = row_ok ? (float)stats[4 * u + 3] : 0.0f;
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 128);
-    if (tid == 0) { umma::mbar_init(&sh->bar[0], 1); umma::mbar_init(&sh->bar[1], 1); }
+    if (tid == 0) {
+        for (int s = 0; s < BT_MAX_STAGES; ++s) {
+            umma::mbar_init(&sh->full[s], BT_GROUP_WARPS);
+            umma::mbar_init(&sh->empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) { umma::mbar_init(&sh->oh_full[s], 1); umma::mbar_init(&sh->oh_empty[s], 1); }
+    }
     umma::fence_proxy_async();
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
     const uint32_t tmem = sh->tmem_slot;
-    const uint32_t g_addr = umma::smem_u32(g_smem);
-    const uint32_t b0_addr = umma::smem_u32(buf0), b1_addr = umma::smem_u32(buf1);
-    const uint32_t idesc = umma::idesc_bf16_f32(BT_ROWS, npad) | (1u << 16);   // B is MN-major
-
     const int ntiles = (n + BT_WIN - 1) / BT_WIN;
-    uint32_t uses0 = 0, uses1 = 0, waited0 = 0, waited1 = 0;   // commits issued / completions observed per stage
-    uint32_t any_mma = 0;
-    double sb = 0.0, sg = 0.0;
-    const double invstd = row_ok ? stats[4 * u + 2] : 0.0;
+    const int nseq = (B - 1 - (int)blockIdx.y) / ns + 1;
+    const int gtotal = nseq * ntiles;
 
-    for (int b = blockIdx.y; b < B; b += gridDim.y) {
-        // every MMA of the previous sequence must be done before its one-hot buffers are rewritten
-        while (waited0 < uses0) { umma::mbar_wait(&sh->bar[0], waited0 & 1u); ++waited0; }
-        while (waited1 < uses1) { umma::mbar_wait(&sh->bar[1], waited1 & 1u); ++waited1; }
-        umma::fence_after_sync();
-        __syncthreads();   // all threads finished reading s_d / s_arg of the previous sequence
-
-        const uint32_t* sp = planes + (long long)b * 3 * Wp;
-        for (int i = tid; i < Lbuf; i += BT_THREADS) {
-            const uint2 v = bt_onehot_bf16x4(sp, Wp, L, i);
-            buf0[i] = v;
-            if (i > 0) buf1[i - 1] = v;
-            if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
-        }
-        // stage dy / argmax rows (a warp per row, BT_RG rows of loads in flight), and the per-row
-        // BatchNorm reductions  sum dy  and  sum dy * (z - mean_nobias)
-        for (int row0 = warp * BT_RG; row0 < nu; row0 += 4 * BT_RG) {
-            float a_d[BT_RG], a_dz[BT_RG];
+    if (warp == BT_PRODUCERS / 32) {
+        // ================= issuer warp: lane 0 issues every MMA =================
+        if (lane == 0) {
+            const uint32_t idesc = umma::idesc_bf16_f32(BT_ROWS, npad) | (1u << 16);   // B is MN-major
+            const uint32_t a_lo = umma::desc_lo(umma::smem_u32(g_smem), BT_LBO_A);
+            const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), b_lbo);
+            const uint32_t a_hi = umma::desc_hi(BT_SBO_A), b_hi = umma::desc_hi(b_sbo);
+            uint32_t stage = 0, use = 0, any_mma = 0;
+            for (int sq = 0; sq < nseq; ++sq) {
+                const uint32_t b_sq = b_lo + (uint32_t)(sq & 1) * (uint32_t)Lbuf;      // Lbuf * 16 B >> 4
+                umma::mbar_wait(&sh->oh_full[sq & 1], (uint32_t)(sq >> 1) & 1u);
+                for (int t = 0; t < ntiles; ++t) {
+                    umma::mbar_wait(&sh->full[stage], use & 1u);
+                    umma::fence_after_sync();
+                    const uint32_t a_st = a_lo + stage * (BT_STAGE_BYTES >> 4);
+                    const uint32_t b_t = b_sq + 56u * (uint32_t)t;                     // 8 windows * 7 positions
+                    const int ksteps = (min(BT_WIN, n - t * BT_WIN) + 1) >> 1;
 #pragma unroll
-            for (int r = 0; r < BT_RG; ++r) { a_d[r] = 0.0f; a_dz[r] = 0.0f; }
-            for (int q0 = 0; q0 < n; q0 += 96) {
-                float d[BT_RG][3], z[BT_RG][3];
-                uint8_t a[BT_RG][3];
+                    for (int s3 = 0; s3 < BT_SPLITS; ++s3) {
 #pragma unroll
-                for (int r = 0; r < BT_RG; ++r) {
-                    const long long g = ((long long)b * U + u0 + row0 + r) * n;
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const int q = q0 + 32 * c + lane;
-                        const bool ok = (row0 + r < nu) && (q < n);
-                        d[r][c] = ok ? __ldg(dy + g + q) : 0.0f;
-                        z[r][c] = ok ? __ldg(zmax + g + q) : 0.0f;
-                        a[r][c] = ok ? __ldg(argmax + g + q) : (uint8_t)0;
-                    }
-                }
-#pragma unroll
-                for (int r = 0; r < BT_RG; ++r) {
-                    const float wsr = s_ws[min(row0 + r, BT_ROWS - 1)];
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const int q = q0 + 32 * c + lane;
-                        if ((row0 + r < nu) && (q < n)) {
-                            s_d[(row0 + r) * dstride + q] = d[r][c];
-                            s_arg[(row0 + r) * astride + q] = a[r][c];
-                            a_d[r] += d[r][c];
-                            a_dz[r] = fmaf(d[r][c], z[r][c] - wsr, a_dz[r]);
+                        for (int ks = 0; ks < BT_WIN / 2; ++ks) {
+                            if (ks < ksteps) {
+                                const uint64_t ad = ((uint64_t)a_hi << 32) |
+                                                    (uint64_t)(a_st + (uint32_t)(s3 * BT_PIECE_BYTES + ks * 2 * BT_LBO_A) / 16u);
+                                const uint64_t bd = ((uint64_t)b_hi << 32) | (uint64_t)(b_t + 14u * ks);
+                                umma::mma_bf16(tmem, ad, bd, idesc, any_mma);
+                                any_mma = 1;
+                            }
                         }
                     }
+                    umma::commit(&sh->empty[stage]);
+                    if (++stage == (uint32_t)nstages) { stage = 0; ++use; }
                 }
-            }
-#pragma unroll
-            for (int r = 0; r < BT_RG; ++r) {
-                const float t1 = warp_sum(a_d[r]), t2 = warp_sum(a_dz[r]);
-                if (lane == 0 && row0 + r < nu) { s_sb[row0 + r] = t1; s_sg[row0 + r] = t2; }
+                umma::commit(&sh->oh_empty[sq & 1]);      // the pair buffer of this sequence may be rewritten
             }
         }
-        umma::fence_proxy_async();
-        __syncthreads();
-        if (row_ok) { sb += (double)s_sb[tid]; sg += (double)s_sg[tid] * invstd; }
-
-        for (int t = 0; t < ntiles; ++t) {
-            const int stage = t & 1;
-            if (stage == 0) { while (waited0 < uses0) { umma::mbar_wait(&sh->bar[0], waited0 & 1u); ++waited0; } }
-            else            { while (waited1 < uses1) { umma::mbar_wait(&sh->bar[1], waited1 & 1u); ++waited1; } }
-            umma::fence_after_sync();
-            unsigned char* st = g_smem + stage * BT_STAGE_BYTES;
-            // clear this thread's row of the stage, then scatter its (up to) 4 windows
-#pragma unroll
-            for (int c = 0; c < BT_SPLITS * 2 * 2; ++c)
-                *reinterpret_cast<uint4*>(st + c * 2048 + 16 * tid) = make_uint4(0u, 0u, 0u, 0u);
-            if (row_ok) {
-#pragma unroll
-                for (int w = 0; w < BT_WIN; ++w) {
-                    const int q = t * BT_WIN + w;
-                    if (q < n) {
-                        const float dv = s_d[tid * dstride + q];
-                        const int pl = w * XNN_POOL + (int)s_arg[tid * astride + q];
-                        const int par = pl & 1, kk = pl >> 1;
-                        const __nv_bfloat16 hi = __float2bfloat16_rn(dv);
-                        const float r1 = dv - __bfloat162float(hi);
-                        const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
-                        const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
-                        unsigned char* e = st + par * BT_BLOCK_BYTES + (kk >> 3) * 2048 + 16 * tid + (kk & 7) * 2;
-                        *reinterpret_cast<__nv_bfloat16*>(e + 0 * 2 * BT_BLOCK_BYTES) = lo;
-                        *reinterpret_cast<__nv_bfloat16*>(e + 1 * 2 * BT_BLOCK_BYTES) = mid;
-                        *reinterpret_cast<__nv_bfloat16*>(e + 2 * 2 * BT_BLOCK_BYTES) = hi;
-                    }
+    } else if (warp == BT_PRODUCERS / 32 + 1) {
+        // ================= one-hot warp: planes -> bf16 pair buffer of each sequence =================
+        for (int sq = 0; sq < nseq; ++sq) {
+            const int b = blockIdx.y + sq * ns;
+            const uint32_t* sp = planes + (long long)b * 3 * Wp;
+            for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
+            if (sq >= 2) {
+                if (lane == 0) umma::mbar_wait(&sh->oh_empty[sq & 1], (uint32_t)((sq >> 1) - 1) & 1u);
+            }
+            __syncwarp();
+            uint2* o = oh + (size_t)(sq & 1) * 2 * Lbuf;
+            for (int i = lane; i <= Lbuf; i += 32) {
+                uint2 v = make_uint2(0u, 0u);
+                if (i < L) {
+                    const int w = i >> 5, bt = i & 31;
+                    const uint32_t lo = (s_pl[w] >> bt) & 1u, hi = (s_pl[Wp + w] >> bt) & 1u,
+                                   nm = (s_pl[2 * Wp + w] >> bt) & 1u;
+                    const uint32_t half = nm ? 0u : (lo ? 0x3F800000u : 0x00003F80u);
+                    if (hi) v.y = half; else v.x = half;
                 }
+                if (i < Lbuf) o[2 * i] = v;
+                if (i > 0) o[2 * i - 1] = v;
             }
             umma::fence_proxy_async();
-            __syncthreads();
-            if (tid == 0) {
-                umma::fence_after_sync();
-                const uint32_t boff = 8u * (uint32_t)(t * BT_TILE_POS);
-#pragma unroll 1
-                for (int s3 = 0; s3 < BT_SPLITS; ++s3) {
-#pragma unroll 1
-                    for (int par = 0; par < 2; ++par) {
-                        const uint64_t ad = umma::smem_desc(
-                            g_addr + (uint32_t)(stage * BT_STAGE_BYTES + (s3 * 2 + par) * BT_BLOCK_BYTES), 2048u, 128u);
-                        const uint64_t bd = umma::smem_desc((par ? b1_addr : b0_addr) + boff, b_lbo, b_sbo);
-                        umma::mma_bf16(tmem, ad, bd, idesc, any_mma);
-                        any_mma = 1;
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->oh_full[sq & 1]);
+        }
+    } else {
+        // ================= producers =================
+        // group grp converts the tiles whose global index (sequence-major) is = grp mod 2; inside a group warp
+        // wg owns unit rows 16wg..16wg+15; lane = (rsub = lane/8, qsub = lane%8); row group rg -> row 16wg+4rg+rsub
+        const int grp = warp / BT_GROUP_WARPS, wg = warp % BT_GROUP_WARPS;
+        const int rsub = lane >> 3, qsub = lane & 7;
+        int row[BT_RGS];
+        long long rowoff[BT_RGS];
+        float wsr[BT_RGS];
+        uint32_t soff[BT_RGS];
+#pragma unroll
+        for (int rg = 0; rg < BT_RGS; ++rg) {
+            row[rg] = 16 * wg + 4 * rg + rsub;
+            const int lrow = min(row[rg], nu - 1);       // rows past the tile load a valid row, then zero it
+            rowoff[rg] = ((long long)blockIdx.y * U + u0 + lrow) * n;
+            wsr[rg] = (float)stats[4 * (u0 + lrow) + 3];
+            soff[rg] = (uint32_t)((row[rg] >> 3) * BT_SBO_A + (row[rg] & 7) * 16 + qsub * BT_LBO_A);
+        }
+        double sbd[BT_RGS], sgd[BT_RGS];
+        float a_d[BT_RGS], a_dz[BT_RGS];
+#pragma unroll
+        for (int rg = 0; rg < BT_RGS; ++rg) { sbd[rg] = 0.0; sgd[rg] = 0.0; a_d[rg] = 0.0f; a_dz[rg] = 0.0f; }
+        const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+        const long long seq_step = (long long)ns * U * n;
+
+        // 8 lanes share a row: fold the per-lane float partial sums of one sequence into the fp64 row sums
+        auto flush = [&]() {
+#pragma unroll
+            for (int rg = 0; rg < BT_RGS; ++rg) {
+                float t1 = a_d[rg], t2 = a_dz[rg];
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, o);
+                    t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+                }
+                sbd[rg] += (double)t1;
+                sgd[rg] += (double)t2;
+                a_d[rg] = 0.0f; a_dz[rg] = 0.0f;
+            }
+        };
+
+        // this group's tile list: g = grp, grp + 2, ...;  (f_sq, f_t) runs one tile ahead of (c_sq, c_t)
+        int f_sq = 0, f_t = grp;
+        while (f_t >= ntiles) { f_t -= ntiles; ++f_sq; }
+        long long f_seq = (long long)f_sq * seq_step;
+        auto fetch = [&](BtVals& v) {
+            if (f_sq < nseq) {
+                const int q = min(f_t * BT_WIN + qsub, n - 1);     // windows past n load a valid one, then zero it
+#pragma unroll
+                for (int rg = 0; rg < BT_RGS; ++rg) {
+                    const long long g = rowoff[rg] + f_seq + q;
+                    v.d[rg] = __ldg(dy + g);
+                    v.z[rg] = __ldg(zmax + g);
+                    v.a[rg] = (int)__ldg(argmax + g);
+                }
+            }
+            f_t += BT_GROUPS;
+            while (f_t >= ntiles) { f_t -= ntiles; ++f_sq; f_seq += seq_step; }
+        };
+
+        BtVals cur, nxt;
+#pragma unroll
+        for (int rg = 0; rg < BT_RGS; ++rg) { cur.d[rg] = nxt.d[rg] = 0.0f; cur.z[rg] = nxt.z[rg] = 0.0f; cur.a[rg] = nxt.a[rg] = 0; }
+        int c_sq = f_sq, c_t = f_t;
+        fetch(cur);
+        uint32_t stage = (uint32_t)grp % (uint32_t)nstages, use = (uint32_t)grp / (uint32_t)nstages;
+        for (int g = grp; g < gtotal; g += BT_GROUPS) {
+            const int n_sq = f_sq, n_t = f_t;               // coordinates of the tile fetched next
+            fetch(nxt);                                     // its loads fly under this tile's conversion
+            if (use) {                                      // lane 0 polls, the warp follows
+                if (lane == 0) umma::mbar_wait(&sh->empty[stage], (use - 1) & 1u);
+                __syncwarp();
+            }
+            unsigned char* st = g_smem + (size_t)stage * BT_STAGE_BYTES;
+            const bool q_ok = (c_t * BT_WIN + qsub) < n;
+#pragma unroll
+            for (int rg = 0; rg < BT_RGS; ++rg) {
+                const float dv = (q_ok && row[rg] < nu) ? cur.d[rg] : 0.0f;
+                const __nv_bfloat16 hi = __float2bfloat16_rn(dv);
+                const float r1 = dv - __bfloat162float(hi);
+                const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+                const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+                unsigned char* e = st + soff[rg];
+                // zero the window's 16-byte chunk of each piece, then drop the value at slot arg (same thread,
+                // program order); piece order lo, mid, hi: the small pieces enter the fp32 accumulator first
+                *reinterpret_cast<uint4*>(e + 0 * BT_PIECE_BYTES) = zero4;
+                *reinterpret_cast<uint4*>(e + 1 * BT_PIECE_BYTES) = zero4;
+                *reinterpret_cast<uint4*>(e + 2 * BT_PIECE_BYTES) = zero4;
+                unsigned char* e2 = e + 2 * cur.a[rg];
+                *reinterpret_cast<__nv_bfloat16*>(e2 + 0 * BT_PIECE_BYTES) = lo;
+                *reinterpret_cast<__nv_bfloat16*>(e2 + 1 * BT_PIECE_BYTES) = mid;
+                *reinterpret_cast<__nv_bfloat16*>(e2 + 2 * BT_PIECE_BYTES) = hi;
+                a_d[rg] += dv;
+                a_dz[rg] = fmaf(dv, cur.z[rg] - wsr[rg], a_dz[rg]);
+            }
+            umma::fence_proxy_async();                      // this thread's stage writes -> async proxy
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->full[stage]);
+            stage += BT_GROUPS;
+            while (stage >= (uint32_t)nstages) { stage -= (uint32_t)nstages; ++use; }
+            if (n_sq != c_sq) flush();                      // sequence boundary: float partials -> fp64
+            c_sq = n_sq; c_t = n_t;
+            cur = nxt;
+        }
+        flush();
+        // all MMAs complete (they finish in order: wait for the last tile)
+        {
+            const int g2 = gtotal - 1;
+            umma::mbar_wait(&sh->empty[g2 % nstages], (uint32_t)(g2 / nstages) & 1u);
+        }
+        umma::fence_after_sync();
+        if (qsub == 0) {
+#pragma unroll
+            for (int rg = 0; rg < BT_RGS; ++rg) {
+                if (row[rg] < nu) {
+                    s_red[(grp * BT_ROWS + row[rg]) * 2] = sbd[rg];
+                    s_red[(grp * BT_ROWS + row[rg]) * 2 + 1] = sgd[rg] * stats[4 * (u0 + row[rg]) + 2];   // * invstd
+                }
+            }
+        }
+        bt_producer_sync();
+
+        // ---- read the accumulator once: warps 0-3, thread = unit (TMEM lane), columns f = 4j + c
+        if (warp < 4) {
+            const int r = tid;                      // TMEM lane = unit row
+            const bool row_ok = r < nu;
+            double* o = part + ((long long)blockIdx.y * U + u0 + r) * pstride;
+            const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+            for (int c0 = 0; c0 < npad; c0 += 16) {
+                uint32_t v[16];
+                umma::tmem_ld16(trow + c0, v);
+                umma::tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int f = c0 + i;
+                        if (f < K4) o[(f & 3) * k + (f >> 2)] = (double)__uint_as_float(v[i]);
                     }
                 }
-                umma::commit(&sh->bar[stage]);
             }
-            if (stage == 0) ++uses0; else ++uses1;
-        }
-    }
-    while (waited0 < uses0) { umma::mbar_wait(&sh->bar[0], waited0 & 1u); ++waited0; }
-    while (waited1 < uses1) { umma::mbar_wait(&sh->bar[1], waited1 & 1u); ++waited1; }
-    umma::fence_after_sync();
-
-    // ---- read the accumulator once: thread = unit (TMEM lane), columns f = 4j + c
-    const int K4 = 4 * k, stride = K4 + 2;
-    double* o = part + ((long long)blockIdx.y * U + u) * stride;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-    const bool have = (uses0 + uses1) > 0;
-    for (int c0 = 0; c0 < npad; c0 += 16) {
-        uint32_t v[16];
-        umma::tmem_ld16(trow + c0, v);
-        umma::tmem_ld_wait();
-        if (row_ok) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int f = c0 + i;
-                if (f < K4) o[(f & 3) * k + (f >> 2)] = have ? (double)__uint_as_float(v[i]) : 0.0;
+            if (row_ok) {
+                o[K4] = s_red[r * 2] + s_red[(BT_ROWS + r) * 2];
+                o[K4 + 1] = s_red[r * 2 + 1] + s_red[(BT_ROWS + r) * 2 + 1];
             }
         }
     }
-    if (row_ok) { o[K4] = sb; o[K4 + 1] = sg; }
     umma::fence_before_sync();
     __syncthreads();
     if (warp == 0) umma::tmem_dealloc(tmem, 128);
@@ -252,23 +333,23 @@ int launch_frontend_bwd_finalize(const double* part, int slices, int U, int k, c
 int frontend_bwd_simt_slices(int B);
 }
 
-static size_t bt_smem_bytes(int n, int* Lbuf_out, int* dstride_out, int* astride_out) {
+// shared memory of one CTA; picks the number of A stages (3, or 2 for long sequences)
+static size_t bt_smem_bytes(int n, int* Lbuf_out, int* nstages_out) {
     const int ntiles = (n + BT_WIN - 1) / BT_WIN;
-    const int Lbuf = ntiles * BT_TILE_POS + 64;            // even; last tile reads < P0 + 64 positions
-    const int dstride = n | 1;
-    int a4 = (n + 3) / 4;
-    if ((a4 & 1) == 0) ++a4;
-    const int astride = 4 * a4;
+    const int Lbuf = 56 * ntiles + 24;     // last tile reads P2 up to 56*ntiles + 18
+    // pair buffers, fp64 row sums of both groups, plane words (<= 3 * ceil(L/32), L <= 7n + 38), barriers
+    const size_t fixed = (size_t)2 * Lbuf * 16 + (size_t)2 * 2 * BT_ROWS * 8 + (size_t)3 * 4 * ((7 * n + 38 + 31) / 32 + 2) +
+                         sizeof(BtShared) + 32;
+    int nstages = BT_MAX_STAGES;
+    if ((size_t)nstages * BT_STAGE_BYTES + fixed > (size_t)227 * 1024) nstages = 2;
     if (Lbuf_out) *Lbuf_out = Lbuf;
-    if (dstride_out) *dstride_out = dstride;
-    if (astride_out) *astride_out = astride;
-    return (size_t)2 * BT_STAGE_BYTES + (size_t)2 * Lbuf * 8 + (size_t)BT_ROWS * dstride * 4 + 3 * BT_ROWS * 4 +
-           (((size_t)BT_ROWS * astride + 15) & ~(size_t)15) + sizeof(BtShared) + 16;
+    if (nstages_out) *nstages_out = nstages;
+    return (size_t)nstages * BT_STAGE_BYTES + fixed;
 }
 
 extern "C" size_t xnn_frontend_bwd_work_bytes(int B, int U, int k) {
     if (B < 1 || U < 1 || k < 1) return 0;
-    int slices = bt_slices(B, U);
+    int slices = bt_slices(U, B);
     const int s2 = frontend_bwd_simt_slices(B);
     if (s2 > slices) slices = s2;
     return (size_t)slices * U * (4 * k + 2) * sizeof(double);
@@ -284,19 +365,19 @@ extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int
     XNN_CHECK_ARG(k >= 1 && k <= BT_KMAX && L >= k && U >= 1 && B >= 1 && n_pos >= 1, "bad sizes (kernel_size <= 32)");
     const int n = (L - k + 1) / XNN_POOL;
     XNN_CHECK_ARG(n >= 1, "sequence shorter than one pool window");
-    int Lbuf = 0, dstride = 0, astride = 0;
-    const size_t smem = bt_smem_bytes(n, &Lbuf, &dstride, &astride);
+    int Lbuf = 0, nstages = 0;
+    const size_t smem = bt_smem_bytes(n, &Lbuf, &nstages);
     XNN_CHECK_ARG(smem <= 227 * 1024, "sequence too long for the front-end backward staging buffers");
     cudaStream_t st = to_stream(s);
-    const int slices = bt_slices(B, U);
-    // MN-major Toeplitz view of the one-hot buffer: K-group stride 128 B, N-chunk stride 16 B.
-    // XNN_BWD_DESC_SWAP=1 exchanges the two fields (bring-up aid for the descriptor convention).
+    const int slices = bt_slices(U, B);
+    // MN-major Toeplitz view of the one-hot pair buffer: K-group (pool window) stride 112 B, N-chunk
+    // stride 32 B.  XNN_BWD_DESC_SWAP=1 exchanges the two fields (bring-up aid for the descriptor convention).
     static const int swap = [] { const char* e = getenv("XNN_BWD_DESC_SWAP"); return e && e[0] == '1'; }();
-    const uint32_t lbo = swap ? 16u : 128u, sbo = swap ? 128u : 16u;
+    const uint32_t lbo = swap ? 32u : 112u, sbo = swap ? 112u : 32u;
     XNN_CUDA(cudaFuncSetAttribute(frontend_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(bt_mtiles(U), slices);
     frontend_bwd_tc_kernel<<<grid, BT_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, k, n, bt_npad(k), Lbuf,
-                                                          dstride, astride, dy, zmax, argmax, stats, lbo, sbo,
+                                                          nstages, dy, zmax, argmax, stats, lbo, sbo,
                                                           (double*)work);
     XNN_CHECK_LAUNCH();
     if (launch_frontend_bwd_finalize((const double*)work, slices, U, k, gamma, stats, cov_w, cnt1, n_pos, dconv_w,
