@@ -23,8 +23,8 @@
 // The accumulator stays in TMEM for the CTA's whole slice of the batch and is read once.
 //
 // Roles (one CTA of 18 warps per SM): two producer groups of 8 warps convert alternate tiles (a warp's
-// serial path per tile is ~1000 cycles, twice the tensor time of a tile); warp 16 lane 0 issues every
-// tcgen05.mma; warp 17 expands the next sequence's planes into the pair buffer.  Stages of 8 windows x 128
+// serial path per tile is longer than the tensor time of a tile); warp 16 issues every tcgen05.mma
+// (elect.sync, uniform descriptors); warp 17 expands the next sequence's planes into the pair buffer.  Stages of 8 windows x 128
 // rows cycle through full[] (one arrival per producer warp) / empty[] (tcgen05.commit) mbarriers; there is
 // no CTA-wide barrier in the loop, and each producer prefetches its next tile while it converts this one.
 #include "common.cuh"
@@ -113,21 +113,24 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
     const int gtotal = nseq * ntiles;
 
     if (warp == BT_PRODUCERS / 32) {
-        // ================= issuer warp: lane 0 issues every MMA =================
-        if (lane == 0) {
-            const uint32_t idesc = umma::idesc_bf16_f32(BT_ROWS, npad) | (1u << 16);   // B is MN-major
-            const uint32_t a_lo = umma::desc_lo(umma::smem_u32(g_smem), BT_LBO_A);
-            const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), b_lbo);
-            const uint32_t a_hi = umma::desc_hi(BT_SBO_A), b_hi = umma::desc_hi(b_sbo);
-            uint32_t stage = 0, use = 0, any_mma = 0;
-            for (int sq = 0; sq < nseq; ++sq) {
-                const uint32_t b_sq = b_lo + (uint32_t)(sq & 1) * (uint32_t)Lbuf;      // Lbuf * 16 B >> 4
-                umma::mbar_wait(&sh->oh_full[sq & 1], (uint32_t)(sq >> 1) & 1u);
-                for (int t = 0; t < ntiles; ++t) {
-                    umma::mbar_wait(&sh->full[stage], use & 1u);
-                    umma::fence_after_sync();
+        // ================= issuer warp =================
+        // every lane runs the loop and waits on the barriers (a lone lane spinning while its 31 siblings sit
+        // at the closing __syncthreads is a divergent warp, and MMAs issued under `if (lane == 0)` are wrapped by
+        // the compiler in ~25-instruction election/waterfall sequences each); elect.sync picks the issuing lane.
+        const uint32_t idesc = umma::idesc_bf16_f32(BT_ROWS, npad) | (1u << 16);   // B is MN-major
+        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(g_smem), BT_LBO_A);
+        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), b_lbo);
+        const uint32_t a_hi = umma::desc_hi(BT_SBO_A), b_hi = umma::desc_hi(b_sbo);
+        uint32_t stage = 0, use = 0, any_mma = 0;
+        for (int sq = 0; sq < nseq; ++sq) {
+            const uint32_t b_sq = b_lo + (uint32_t)(sq & 1) * (uint32_t)Lbuf;      // Lbuf * 16 B >> 4
+            umma::mbar_wait(&sh->oh_full[sq & 1], (uint32_t)(sq >> 1) & 1u);
+            for (int t = 0; t < ntiles; ++t) {
+                umma::mbar_wait(&sh->full[stage], use & 1u);
+                umma::fence_after_sync();
+                {
                     const uint32_t a_st = a_lo + stage * (BT_STAGE_BYTES >> 4);
-                    const uint32_t b_t = b_sq + 56u * (uint32_t)t;                     // 8 windows * 7 positions
+                    const uint32_t b_t = b_sq + 56u * (uint32_t)t;                 // 8 windows * 7 positions
                     const int ksteps = (min(BT_WIN, n - t * BT_WIN) + 1) >> 1;
 #pragma unroll
                     for (int s3 = 0; s3 < BT_SPLITS; ++s3) {
@@ -137,15 +140,16 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
                                 const uint64_t ad = ((uint64_t)a_hi << 32) |
                                                     (uint64_t)(a_st + (uint32_t)(s3 * BT_PIECE_BYTES + ks * 2 * BT_LBO_A) / 16u);
                                 const uint64_t bd = ((uint64_t)b_hi << 32) | (uint64_t)(b_t + 14u * ks);
-                                umma::mma_bf16(tmem, ad, bd, idesc, any_mma);
+                                umma::mma_bf16_elect(tmem, ad, bd, idesc, any_mma);
                                 any_mma = 1;
                             }
                         }
                     }
-                    umma::commit(&sh->empty[stage]);
-                    if (++stage == (uint32_t)nstages) { stage = 0; ++use; }
+                    umma::commit_elect(&sh->empty[stage]);
+                    if (t == ntiles - 1) umma::commit_elect(&sh->oh_empty[sq & 1]);   // pair buffer may be rewritten
                 }
-                umma::commit(&sh->oh_empty[sq & 1]);      // the pair buffer of this sequence may be rewritten
+                __syncwarp();
+                if (++stage == (uint32_t)nstages) { stage = 0; ++use; }
             }
         }
     } else if (warp == BT_PRODUCERS / 32 + 1) {
@@ -235,19 +239,44 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
             while (f_t >= ntiles) { f_t -= ntiles; ++f_sq; f_seq += seq_step; }
         };
 
+        // L2 prefetch of the NEXT sequence's rows of this warp (16 rows are one contiguous block of each array):
+        // the register prefetch below runs only one tile ahead, far less than the HBM latency under load
+        auto prefetch_seq = [&](int sq) {
+            if (sq >= nseq) return;
+            const int r0 = 16 * wg;
+            if (r0 >= nu) return;
+            const long long e0 = ((long long)(blockIdx.y + (long long)sq * ns) * U + u0 + r0) * n;
+            const long long ne = (long long)min(16, nu - r0) * n;
+            if (grp == 0) {
+                const char* p = reinterpret_cast<const char*>(dy + e0);
+                for (long long o = (long long)lane * 128; o < ne * 4; o += 32 * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+            } else {
+                const char* p = reinterpret_cast<const char*>(zmax + e0);
+                for (long long o = (long long)lane * 128; o < ne * 4; o += 32 * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+                const char* pa = reinterpret_cast<const char*>(argmax + e0);
+                for (long long o = (long long)lane * 128; o < ne; o += 32 * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + o));
+            }
+        };
+
         BtVals cur, nxt;
 #pragma unroll
         for (int rg = 0; rg < BT_RGS; ++rg) { cur.d[rg] = nxt.d[rg] = 0.0f; cur.z[rg] = nxt.z[rg] = 0.0f; cur.a[rg] = nxt.a[rg] = 0; }
         int c_sq = f_sq, c_t = f_t;
         fetch(cur);
+        prefetch_seq(c_sq + 1);
         uint32_t stage = (uint32_t)grp % (uint32_t)nstages, use = (uint32_t)grp / (uint32_t)nstages;
         for (int g = grp; g < gtotal; g += BT_GROUPS) {
             const int n_sq = f_sq, n_t = f_t;               // coordinates of the tile fetched next
-            fetch(nxt);                                     // its loads fly under this tile's conversion
             if (use) {                                      // lane 0 polls, the warp follows
                 if (lane == 0) umma::mbar_wait(&sh->empty[stage], (use - 1) & 1u);
                 __syncwarp();
             }
+            // the next tile's loads fly under this tile's conversion (issued after the wait loop: before it,
+            // the register allocator copies the first loaded value at once and the warp stalls on the load)
+            fetch(nxt);
             unsigned char* st = g_smem + (size_t)stage * BT_STAGE_BYTES;
             const bool q_ok = (c_t * BT_WIN + qsub) < n;
 #pragma unroll
@@ -275,7 +304,7 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
             if (lane == 0) umma::mbar_arrive(&sh->full[stage]);
             stage += BT_GROUPS;
             while (stage >= (uint32_t)nstages) { stage -= (uint32_t)nstages; ++use; }
-            if (n_sq != c_sq) flush();                      // sequence boundary: float partials -> fp64
+            if (n_sq != c_sq) { flush(); prefetch_seq(n_sq + 1); }   // sequence boundary: float partials -> fp64
             c_sq = n_sq; c_t = n_t;
             cur = nxt;
         }
