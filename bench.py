@@ -2,6 +2,7 @@
 """bench.py -- headline benchmark of the ExplaiNN hot path on B200.
 
     python bench.py [--gpus N --steps K --warmup W] [--workload cfg3|cfg2|cfg1] [--impl reference]
+    python bench.py --workload cfg1_fwd|cfg3_fwd|cfg4|cfg5     (inference / interpret / PWM scan: bench_paths.py)
 
 Metric (BASELINE.json): sequences/s of the ExplaiNN training step (forward + loss + backward + Adam)
 on synthetic one-hot DNA.  Default workload = cfg3, the configuration the metric is quoted on at
@@ -33,7 +34,10 @@ import torch  # noqa: E402
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
 # `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
-NCU_TRAFFIC = {}
+NCU_TRAFFIC = {
+    "xnn_mlp_bwd": 1123.1e6,        # mlp_bwd_kernel 698.7 MB read + 424.5 MB written (profiles/r01_ncu_full_s18.txt)
+    "xnn_frontend_fwd": 986.3e6,    # frontend_tc_kernel<1> 66.6 MB read + 919.7 MB written (same capture)
+}
 
 WORKLOADS = {
     # name: (cnn_units, kernel, length, features, loss kind, per-GPU batch)
@@ -127,11 +131,17 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS))
+    import bench_paths
+    ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS) + list(bench_paths.AUX))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: workload's)")
     ap.add_argument("--cpu-sample", type=int, default=128, help="sequences per CPU-baseline step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.workload in bench_paths.AUX:
+        assert args.impl == "ours" and torch.cuda.is_available(), "secondary workloads run on the GPU arm only"
+        lr = int(os.environ.get("LOCAL_RANK", "0"))
+        return bench_paths.run(args.workload, args, int(os.environ.get("RANK", "0")),
+                               int(os.environ.get("WORLD_SIZE", "1")), lr, peaks, ClockSampler(lr))
     cfg = WORKLOADS[args.workload]
     U, k, L, F, kind, B = cfg
     if args.batch:
