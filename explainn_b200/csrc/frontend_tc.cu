@@ -26,7 +26,7 @@
 #include <cuda_bf16.h>
 using namespace xnn;
 
-#define TC_KMAX 32          // largest kernel_size
+#define TC_KMAX 48          // largest kernel_size / PWM width
 #define TC_ROWS 128         // units per CTA = UMMA M
 #define TC_WIN 32           // pool windows per tile
 #define TC_TILE_POS (TC_WIN * XNN_POOL)   // 224 positions per tile
@@ -34,8 +34,8 @@ using namespace xnn;
 #define TC_ODD_COL 128      // TMEM column of the odd-position accumulator
 #define TC_STAGE_COLS 256   // TMEM columns of one accumulator stage (even + odd)
 #define TC_TMEM_COLS 512    // two accumulator stages
-#define TC_GROUP_WARPS 8
-#define TC_THREADS (32 * (2 * TC_GROUP_WARPS + 2))   // two epilogue groups + issuer warp + one-hot warp
+#define TC_EPI_WARPS 16
+#define TC_THREADS (32 * (TC_EPI_WARPS + 3))   // epilogue warps + two issuer warps + one-hot warp
 
 static inline int tc_kpad(int k) { return ((4 * k + 15) / 16) * 16; }
 static inline int tc_mtiles(int U) { return (U + TC_ROWS - 1) / TC_ROWS; }
@@ -66,7 +66,7 @@ tc_split_weights_kernel(const float* __restrict__ conv_w, const float* __restric
         float w = 0.0f;
         if (u < U && j < k) {
             w = conv_w[((long long)u * 4 + c) * k + j];
-            if (scale[u] < 0.0f) w = -w;
+            if (scale != nullptr && scale[u] < 0.0f) w = -w;
         }
         const __nv_bfloat16 hi = __float2bfloat16_rn(w);
         const float r1 = w - __bfloat162float(hi);
@@ -105,36 +105,67 @@ struct TcShared {
     uint32_t pad;
 };
 
-__device__ __forceinline__ void group_barrier(int grp) {
-    asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(32 * TC_GROUP_WARPS) : "memory");
+__device__ __forceinline__ void epi_barrier() {
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
 }
+
+// contiguous copy shared -> global of `cnt` elements by ONE warp, asynchronously: the shared copy starts at the
+// same 16-byte phase as the global destination (sbase is 16-byte aligned, element i sits at sbase[phase + i]),
+// so everything between a scalar head and tail (< 16 bytes each, written by the lanes) is one bulk-async
+// store (cp.async.bulk.global.shared::cta) issued by lane 0; the caller commits the group.
+template <typename T>
+__device__ __forceinline__ void bulk_copy_out(T* __restrict__ gdst, const T* __restrict__ sbase, int phase, int cnt,
+                                              int lane) {
+    constexpr int V = 16 / (int)sizeof(T);
+    const T* src = sbase + phase;
+    const int head = min((V - phase) & (V - 1), cnt);
+    const int nvec = (cnt - head) / V;
+    const int tail0 = head + nvec * V;
+    if (lane < head) gdst[lane] = src[lane];
+    if (tail0 + lane < cnt) gdst[tail0 + lane] = src[tail0 + lane];
+    if (lane == 0 && nvec > 0)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst + head),
+                     "r"(umma::smem_u32(src + head)), "r"(nvec * 16)
+                     : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------
 // fused forward: conv (tcgen05) + BN affine + max over 7 (+ exp on the maximum).
 // One CTA per SM, grid (M tiles, batch slices), warp-specialised over mbarriers:
-//   warps 0-15  two epilogue groups of 8; group g drains TMEM accumulator stage g (tiles alternate).
-//               Inside a group warp wi owns TMEM lanes 32(wi%4).. (one thread = one unit) and the
-//               window half wi/4 of the tile; 8 windows (28 even + 28 odd columns) are read at a time,
-//               max-of-7 is a tree, one expf per window; results are transposed through shared memory
-//               so that each global store is 32 consecutive windows of one unit.
-//   warp 16     issuer: every lane runs the loop, elect.sync issues the MMAs (uniform descriptors)
-//   warp 17     expands the next sequence's planes into the bf16 one-hot buffers (double buffered)
-// The tensor core works on tile g+1 while group g%2 is still in the epilogue of tile g.
+//   warps 0-15  epilogue: warp w owns TMEM lanes 32(w%4).. (one thread = one unit) and windows 8(w/4)..+7 of
+//               the tile (28 even + 28 odd accumulator columns), max-of-7 as a tree, one expf per window.
+//               Results are staged in shared memory in the layout of the output itself: the (units of this
+//               M tile) x n block of one sequence is ONE contiguous range of pool / zmax / argmax, so the
+//               copy-out is one bulk-async store per array and sequence (`linear`); sequences too long for
+//               that (or n a multiple of 4, whose row stride would serialise the staging stores on a few
+//               banks) are staged and written tile by tile, one 32-window row segment per store.
+//   warps 16-17 issuers (even / odd positions): every lane runs the loop, elect.sync issues the MMAs
+//   warp 18     expands the next sequence's planes into the bf16 one-hot buffers (double buffered)
+// Two TMEM accumulator stages: the tensor core works on tile g+1 during the epilogue of tile g.
 // ---------------------------------------------------------------------------
 template <bool TRAIN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int U, int n, int kpad, int Lbuf,
-                   int noh, const __nv_bfloat16* __restrict__ wsplit, const float* __restrict__ scale,
+                   int noh, int linear, const __nv_bfloat16* __restrict__ wsplit, const float* __restrict__ scale,
                    const float* __restrict__ shift, float* __restrict__ pool, float* __restrict__ zmax,
                    uint8_t* __restrict__ argmax) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int chunks = kpad >> 3, ksteps = kpad >> 4;
     const uint32_t a_bytes = 3u * chunks * 2048u;
-    constexpr uint32_t STG = TRAIN ? (2u * TC_ROWS * 33u * 4u + TC_ROWS * 36u) : (TC_ROWS * 33u * 4u);
+    // staging: floats [rows][sstride] (+ 4 elements of phase slack), bytes [rows][bstride] (+ 16)
+    const int sstride = linear ? n : 33, bstride = linear ? n : 36;
+    const uint32_t f_bytes = (uint32_t)((TC_ROWS * sstride + 4) * 4 + 15) & ~15u;
+    const uint32_t b_bytes = (uint32_t)(TC_ROWS * bstride + 16 + 15) & ~15u;
     unsigned char* a_smem = smem_raw;                                        // [3][chunks][16][8][8] bf16
     uint2* oh = reinterpret_cast<uint2*>(smem_raw + a_bytes);                // [noh][2][Lbuf]: position i / i+1
-    unsigned char* stg = reinterpret_cast<unsigned char*>(oh + (size_t)noh * 2 * Lbuf);   // [2 groups][STG]
-    uint32_t* s_pl = reinterpret_cast<uint32_t*>(stg + 2 * STG);             // [3 * Wp] planes of one sequence
+    unsigned char* stg = reinterpret_cast<unsigned char*>(oh + (size_t)noh * 2 * Lbuf);
+    float* s_pool = reinterpret_cast<float*>(stg);
+    float* s_z = reinterpret_cast<float*>(stg + f_bytes);                    // (train)
+    uint8_t* s_arg = stg + 2 * f_bytes;                                      // (train)
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(stg + (TRAIN ? 2 * f_bytes + b_bytes : f_bytes));
     TcShared* sh = reinterpret_cast<TcShared*>(reinterpret_cast<unsigned char*>(s_pl) + ((3 * Wp * 4 + 15) & ~15));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -152,10 +183,10 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
         for (int s = 0; s < 2; ++s) {
-            umma::mbar_init(&sh->acc_full[s], 1);
-            umma::mbar_init(&sh->acc_empty[s], TC_GROUP_WARPS);
+            umma::mbar_init(&sh->acc_full[s], 2);       // one commit per issuer warp
+            umma::mbar_init(&sh->acc_empty[s], TC_EPI_WARPS);
             umma::mbar_init(&sh->oh_full[s], 1);
-            umma::mbar_init(&sh->oh_empty[s], 1);
+            umma::mbar_init(&sh->oh_empty[s], 2);
         }
     }
     umma::fence_proxy_async();
@@ -165,10 +196,13 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
     const uint32_t tmem = sh->tmem_slot;
     const int ntiles = (n + TC_WIN - 1) / TC_WIN;
     const int nseq = (B - 1 - (int)blockIdx.y) / ns + 1;
-    const int gtotal = nseq * ntiles;
 
-    if (warp == 2 * TC_GROUP_WARPS) {
-        // ================= issuer warp =================
+    if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
+        // ================= issuer warps =================
+        // issuing one MMA costs ~20 instructions (elect, R2UR of the descriptors) against 56 cycles of tensor
+        // time: one warp cannot keep the pipe fed.  The even- and odd-position accumulators are independent
+        // chains, so each gets its own issuer warp (on different schedulers); both commit to acc_full.
+        const int par = warp - TC_EPI_WARPS;
         const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
         const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
         const uint32_t hi128 = umma::desc_hi(128u);
@@ -184,8 +218,7 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
                 const int wins = min(TC_WIN, n - t * TC_WIN);
                 const int N = ((((wins * XNN_POOL + 1) >> 1) + 15) & ~15);
                 const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
-#pragma unroll
-                for (int par = 0; par < 2; ++par) {
+                {
                     const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
                     const uint32_t d = tmem + stage * TC_STAGE_COLS + (par ? TC_ODD_COL : 0);
                     uint32_t acc = 0;
@@ -208,13 +241,29 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
                 __syncwarp();
             }
         }
-    } else if (warp == 2 * TC_GROUP_WARPS + 1) {
+    } else if (warp == TC_EPI_WARPS + 2) {
         // ================= one-hot warp =================
+        // the planes of sequence sq+1 are loaded into registers before sequence sq is expanded, so the global
+        // latency never sits between two sequences (up to 128 words; longer sequences load the rest directly)
+        uint32_t nx[4];
+        auto load_planes = [&](int sq) {
+            const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)sq * ns) * 3 * Wp;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int i = lane + 32 * j;
+                nx[j] = (sq < nseq && i < 3 * Wp) ? __ldg(sp + i) : 0u;
+            }
+        };
+        load_planes(0);
         for (int sq = 0; sq < nseq; ++sq) {
             const int so = sq % noh;
             const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)sq * ns) * 3 * Wp;
             __syncwarp();
-            for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (lane + 32 * j < 3 * Wp) s_pl[lane + 32 * j] = nx[j];
+            for (int i = lane + 128; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
+            load_planes(sq + 1);
             if (sq >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(sq / noh - 1) & 1u);
             __syncwarp();
             uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
@@ -230,9 +279,8 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
             if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
         }
     } else {
-        // ================= epilogue groups =================
-        const int grp = warp / TC_GROUP_WARPS, wi = warp % TC_GROUP_WARPS;
-        const int quarter = wi & 3, half = wi >> 2;
+        // ================= epilogue warps =================
+        const int quarter = warp & 3, wq = warp >> 2;
         const int row = quarter * 32 + lane;
         const int u = u0 + row;
         const bool rows_live = quarter * 32 < nu;
@@ -241,34 +289,39 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
             const float sc = scale[u];
             asc = fabsf(sc); shf = shift[u]; sgn = (sc < 0.0f) ? -1.0f : 1.0f;
         }
-        float* s_pool = reinterpret_cast<float*>(stg + (size_t)grp * STG);            // [128][33]
-        float* s_z = s_pool + TC_ROWS * 33;                                           // [128][33] (train)
-        uint8_t* s_arg = reinterpret_cast<uint8_t*>(s_pool + 2 * TC_ROWS * 33);       // [128][36] (train)
-        const uint32_t trow = tmem + (uint32_t)grp * TC_STAGE_COLS + ((uint32_t)(quarter * 32) << 16);
-        int sq = 0, t = grp;
-        while (t >= ntiles) { t -= ntiles; ++sq; }
-        for (int g = grp; g < gtotal; g += 2) {
-            const int q0 = t * TC_WIN;
-            const int wins = min(TC_WIN, n - q0);
-            umma::mbar_wait(&sh->acc_full[grp], ((uint32_t)g >> 1) & 1u);
-            umma::fence_after_sync();
-#pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                const int c = 2 * half + cc;                       // 8 windows = columns 28c .. 28c+27
-                const bool live = rows_live && 8 * c < wins;
+        const uint32_t tlane = tmem + ((uint32_t)(quarter * 32) << 16);
+        int g = 0;
+        for (int sq = 0; sq < nseq; ++sq) {
+            const long long b = blockIdx.y + (long long)sq * ns;
+            const long long gbase = (b * U + u0) * n;              // first element of this CTA's block
+            const int ph4 = linear ? (int)(gbase & 3) : 0, ph16 = linear ? (int)(gbase & 15) : 0;
+            for (int t = 0; t < ntiles; ++t, ++g) {
+                const int q0 = t * TC_WIN;
+                const int wins = min(TC_WIN, n - q0);
+                const uint32_t stage = (uint32_t)g & 1u;
+                umma::mbar_wait(&sh->acc_full[stage], ((uint32_t)g >> 1) & 1u);
+                umma::fence_after_sync();
+                const bool live = rows_live && 8 * wq < wins;
                 uint32_t E[28], O[28];
                 if (live) {
-                    umma::tmem_ld28(trow + 28 * c, E);
-                    umma::tmem_ld28(trow + TC_ODD_COL + 28 * c, O);
+                    const uint32_t trow = tlane + stage * TC_STAGE_COLS + 28u * wq;
+                    umma::tmem_ld28(trow, E);
+                    umma::tmem_ld28(trow + TC_ODD_COL, O);
                     umma::tmem_ld_wait();
                 }
-                if (cc == 1) {
-                    // this warp's share of the accumulator is in registers: hand the stage back
-                    umma::fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) umma::mbar_arrive(&sh->acc_empty[grp]);
+                // this warp's share of the accumulator is in registers: hand the stage back
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
+                if (linear && t == 0 && sq > 0) {                  // previous sequence read out of the staging
+                    if (warp == 0 && lane == 0) bulk_wait_read();
+                    epi_barrier();
                 }
                 if (live) {
+                    const int qs = (linear ? q0 : 0) + 8 * wq;
+                    float* pp = s_pool + ph4 + row * sstride + qs;
+                    float* pz = s_z + ph4 + row * sstride + qs;
+                    uint8_t* pa = s_arg + ph16 + row * bstride + qs;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         float z[7];
@@ -279,49 +332,67 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
                         }
                         const float best = fmaxf(fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3])),
                                                  fmaxf(fmaxf(z[4], z[5]), z[6]));
-                        const int q = 8 * c + j;
-                        s_pool[row * 33 + q] = expf(fmaf(asc, best, shf));
-                        if (TRAIN) {
-                            int arg = 6;                           // first maximum wins
+                        if (8 * wq + j < wins) {                   // windows past the tile are never staged
+                            pp[j] = expf(fmaf(asc, best, shf));
+                            if (TRAIN) {
+                                int arg = 6;                       // first maximum wins
 #pragma unroll
-                            for (int r = 5; r >= 0; --r) arg = (z[r] == best) ? r : arg;
-                            s_z[row * 33 + q] = sgn * best;
-                            s_arg[row * 36 + q] = (uint8_t)arg;
+                                for (int r = 5; r >= 0; --r) arg = (z[r] == best) ? r : arg;
+                                pz[j] = sgn * best;
+                                pa[j] = (uint8_t)arg;
+                            }
                         }
                     }
                 }
-            }
-            group_barrier(grp);                                    // tile staged
-            {
-                const long long b = blockIdx.y + (long long)sq * ns;
-                const bool lq = lane < wins;
-#pragma unroll 4
-                for (int rr = 0; rr < 16; ++rr) {
-                    const int r = 16 * wi + rr;
-                    if (r < nu && lq) {
-                        const long long gi = (b * U + u0 + r) * n + q0 + lane;
-                        pool[gi] = s_pool[r * 33 + lane];
-                        if (TRAIN) { zmax[gi] = s_z[r * 33 + lane]; argmax[gi] = s_arg[r * 36 + lane]; }
+                if (!linear) {
+                    epi_barrier();                                 // tile staged
+                    float* gp = pool + gbase + (long long)(8 * warp) * n + q0 + lane;
+                    float* gz = TRAIN ? zmax + gbase + (long long)(8 * warp) * n + q0 + lane : nullptr;
+                    uint8_t* ga = TRAIN ? argmax + gbase + (long long)(8 * warp) * n + q0 + lane : nullptr;
+                    if (lane < wins) {
+#pragma unroll
+                        for (int rr = 0; rr < 8; ++rr) {
+                            const int r = 8 * warp + rr;
+                            if (r < nu) {
+                                gp[rr * n] = s_pool[r * 33 + lane];
+                                if (TRAIN) { gz[rr * n] = s_z[r * 33 + lane]; ga[rr * n] = s_arg[r * 36 + lane]; }
+                            }
+                        }
                     }
+                    epi_barrier();                                 // staging free again
                 }
             }
-            group_barrier(grp);                                    // staging free again
-            t += 2;
-            while (t >= ntiles) { t -= ntiles; ++sq; }
+            if (linear) {
+                umma::fence_proxy_async();                         // staging stores -> visible to the bulk copy
+                epi_barrier();                                     // sequence staged
+                if (warp == 0) {
+                    const int cnt = nu * n;
+                    bulk_copy_out<float>(pool + gbase, s_pool, ph4, cnt, lane);
+                    if (TRAIN) {
+                        bulk_copy_out<float>(zmax + gbase, s_z, ph4, cnt, lane);
+                        bulk_copy_out<uint8_t>(argmax + gbase, s_arg, ph16, cnt, lane);
+                    }
+                    if (lane == 0) bulk_commit();
+                }
+            }
         }
+        if (linear && warp == 0 && lane == 0) bulk_wait_all();
     }
     umma::fence_before_sync();
     __syncthreads();
     if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
 }
 
-static size_t tc_smem_bytes(int k, int L, int n, bool train, int noh, int* Lbuf_out) {
+static size_t tc_smem_bytes(int k, int L, int n, bool train, int noh, bool linear, int* Lbuf_out) {
     const int ntiles = (n + TC_WIN - 1) / TC_WIN;
     const int Lbuf = ntiles * TC_TILE_POS + 64;   // last tile reads <= P + 2*112 + 2*chunks + 2 positions
     if (Lbuf_out) *Lbuf_out = Lbuf;
-    const size_t stg = train ? (size_t)2 * TC_ROWS * 33 * 4 + (size_t)TC_ROWS * 36 : (size_t)TC_ROWS * 33 * 4;
+    const size_t sstride = linear ? n : 33, bstride = linear ? n : 36;
+    const size_t f_bytes = ((TC_ROWS * sstride + 4) * 4 + 15) & ~(size_t)15;
+    const size_t b_bytes = (TC_ROWS * bstride + 16 + 15) & ~(size_t)15;
+    const size_t stg = train ? 2 * f_bytes + b_bytes : f_bytes;
     const int Wp = (L + 31) / 32;
-    return tc_split_bytes(k) + (size_t)noh * 2 * Lbuf * 8 + 2 * stg + (size_t)((3 * Wp * 4 + 15) & ~15) +
+    return tc_split_bytes(k) + (size_t)noh * 2 * Lbuf * 8 + stg + (size_t)((3 * Wp * 4 + 15) & ~15) +
            sizeof(TcShared) + 16;
 }
 
@@ -330,15 +401,20 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
                                 uint8_t* argmax, void* work, xnn_stream_t s) {
     XNN_CHECK_ARG(planes && conv_w && scale && shift && pool && work, "NULL pointer");
     XNN_CHECK_ARG((zmax == nullptr) == (argmax == nullptr), "zmax and argmax go together");
-    XNN_CHECK_ARG(k >= 1 && k <= TC_KMAX && L >= k && U >= 1 && B >= 0, "bad sizes (kernel_size <= 32)");
+    XNN_CHECK_ARG(k >= 1 && k <= TC_KMAX && L >= k && U >= 1 && B >= 0, "bad sizes (kernel_size <= 48)");
     XNN_CHECK_ARG(((uintptr_t)work & 15) == 0, "work must be 16-byte aligned");
     const int n = (L - k + 1) / XNN_POOL;
     if (B == 0 || n == 0) return XNN_OK;
     const int kpad = tc_kpad(k), mt = tc_mtiles(U);
     const bool train = (zmax != nullptr);
+    // staging choice: whole sequence in output layout (one vector memcpy per sequence) when it fits and the row
+    // stride n keeps the staging stores off a handful of banks; else tile by tile.  One-hot buffers: 2, else 1.
     int Lbuf = 0, noh = 2;
-    size_t smem = tc_smem_bytes(k, L, n, train, noh, &Lbuf);
-    if (smem > 227 * 1024) { noh = 1; smem = tc_smem_bytes(k, L, n, train, noh, &Lbuf); }
+    bool linear = (n % 4) != 0;
+    size_t smem = tc_smem_bytes(k, L, n, train, noh, linear, &Lbuf);
+    if (smem > 227 * 1024 && linear) { noh = 1; smem = tc_smem_bytes(k, L, n, train, noh, linear, &Lbuf); }
+    if (smem > 227 * 1024) { noh = 2; linear = false; smem = tc_smem_bytes(k, L, n, train, noh, linear, &Lbuf); }
+    if (smem > 227 * 1024) { noh = 1; smem = tc_smem_bytes(k, L, n, train, noh, linear, &Lbuf); }
     XNN_CHECK_ARG(smem <= 227 * 1024, "sequence too long for the front-end staging buffers");
     cudaStream_t st = to_stream(s);
     tc_split_weights_kernel<<<dim3(ceil_div((long long)TC_ROWS * kpad, 256), mt), 256, 0, st>>>(
@@ -350,15 +426,291 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
     dim3 grid(mt, slices);
     if (train) {
         XNN_CUDA(cudaFuncSetAttribute(frontend_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        frontend_tc_kernel<true><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh,
+        frontend_tc_kernel<true><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh, (int)linear,
                                                                  reinterpret_cast<const __nv_bfloat16*>(work), scale,
                                                                  shift, pool, zmax, argmax);
     } else {
         XNN_CUDA(cudaFuncSetAttribute(frontend_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        frontend_tc_kernel<false><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh,
+        frontend_tc_kernel<false><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh, (int)linear,
                                                                   reinterpret_cast<const __nv_bfloat16*>(work), scale,
                                                                   shift, pool, zmax, argmax);
     }
     XNN_CHECK_LAUNCH();
+    return XNN_OK;
+}
+
+
+// ===========================================================================
+// a11 on the tensor cores: the `PWM` module (architectures/__init__.py:116-170) as the same Toeplitz GEMM.
+//   o[b, g, :] = [ conv(x_b, W_g) | conv(flip(x_b), W_g) ],  out[b, g] = max / sum over that axis
+// flip(x) (channel and position reversed, :387-404) is the reverse complement, so every sequence is run as
+// two "strands" with the SAME A operand (the G matrices) and the one-hot of x, then of RC(x), as B: the rev
+// half is by construction bit-identical to the forward half of the reverse-complemented input.  Rows of an
+// M tile are 128 matrices, columns are window starts; each epilogue thread keeps the running maximum (and
+// its index on the concatenated axis, first maximum wins) or the running sum of its 56-column share of
+// every tile, and the four column shares of a row are merged through shared memory once per sequence.
+// ===========================================================================
+struct PwShared {
+    uint64_t acc_full[2], acc_empty[2], oh_full[2], oh_empty[2];
+    uint32_t tmem_slot, pad;
+    float val[2][4][TC_ROWS];      // [sequence parity][column share][row]
+    int idx[2][4][TC_ROWS];
+};
+
+// one-hot bf16 x4 of position i of the reverse complement of a sequence held as planes
+__device__ __forceinline__ uint2 onehot_rc_bf16x4(const uint32_t* __restrict__ sp, int Wp, int L, int i) {
+    uint2 v = make_uint2(0u, 0u);
+    if (i < L) {
+        const int s = L - 1 - i, w = s >> 5, b = s & 31;
+        const uint32_t lo = ((sp[w] >> b) & 1u) ^ 1u, hi = ((sp[Wp + w] >> b) & 1u) ^ 1u, nm = (sp[2 * Wp + w] >> b) & 1u;
+        if (!nm) {
+            const uint32_t half = lo ? 0x3F800000u : 0x00003F80u;
+            if (hi) v.y = half; else v.x = half;
+        }
+    }
+    return v;
+}
+
+template <bool WANT_ARG>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, int Lw, int kpad, int Lbuf, int noh,
+              int mode, const __nv_bfloat16* __restrict__ wsplit, float* __restrict__ out,
+              int32_t* __restrict__ argmax) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int chunks = kpad >> 3, ksteps = kpad >> 4;
+    const uint32_t a_bytes = 3u * chunks * 2048u;
+    unsigned char* a_smem = smem_raw;
+    uint2* oh = reinterpret_cast<uint2*>(smem_raw + a_bytes);                // [noh][2][Lbuf]
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);
+    PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + ((3 * Wp * 4 + 15) & ~15));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g0 = blockIdx.x * TC_ROWS;
+    const int ng = min(TC_ROWS, G - g0);
+    const int ns = gridDim.y;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(wsplit) +
+                                                          (size_t)blockIdx.x * a_bytes);
+        uint4* dst = reinterpret_cast<uint4*>(a_smem);
+        for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            umma::mbar_init(&sh->acc_full[s], 2);
+            umma::mbar_init(&sh->acc_empty[s], TC_EPI_WARPS);
+            umma::mbar_init(&sh->oh_full[s], 1);
+            umma::mbar_init(&sh->oh_empty[s], 2);
+        }
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
+    const int nseq = (B - 1 - (int)blockIdx.y) / ns + 1;
+    const int nvs = 2 * nseq;                                   // (sequence, strand) pairs of this CTA
+
+    if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
+        // ================= issuer warps (even / odd window starts) =================
+        const int par = warp - TC_EPI_WARPS;
+        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
+        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
+        const uint32_t hi128 = umma::desc_hi(128u);
+        int g = 0;
+        for (int v = 0; v < nvs; ++v) {
+            const int so = v % noh;
+            umma::mbar_wait(&sh->oh_full[so], (uint32_t)(v / noh) & 1u);
+            const uint32_t b_sq = b_lo + (uint32_t)so * (uint32_t)Lbuf;
+            for (int t = 0; t < ntiles; ++t, ++g) {
+                const uint32_t stage = (uint32_t)g & 1u;
+                umma::mbar_wait(&sh->acc_empty[stage], (((uint32_t)g >> 1) & 1u) ^ 1u);
+                umma::fence_after_sync();
+                const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
+                const int N = (((cnt + 1) >> 1) + 15) & ~15;
+                const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
+                const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
+                const uint32_t d = tmem + stage * TC_STAGE_COLS + (par ? TC_ODD_COL : 0);
+                uint32_t acc = 0;
+#pragma unroll
+                for (int s3 = 0; s3 < 3; ++s3) {
+#pragma unroll
+                    for (int ks = 0; ks < TC_KMAX / 4; ++ks) {
+                        if (ks < ksteps) {
+                            const uint64_t ad = ((uint64_t)hi128 << 32) |
+                                                (uint64_t)(a_lo + (uint32_t)(s3 * chunks + 2 * ks) * 128u);
+                            const uint64_t bd = ((uint64_t)hi128 << 32) | (uint64_t)(b_t + 2u * ks);
+                            umma::mma_bf16_elect(d, ad, bd, idesc, acc);
+                            acc = 1;
+                        }
+                    }
+                }
+                umma::commit_elect(&sh->acc_full[stage]);
+                if (t == ntiles - 1) umma::commit_elect(&sh->oh_empty[so]);
+                __syncwarp();
+            }
+        }
+    } else if (warp == TC_EPI_WARPS + 2) {
+        // ================= one-hot warp: x, then RC(x), of every sequence =================
+        for (int v = 0; v < nvs; ++v) {
+            const int so = v % noh, strand = v & 1;
+            if (!strand) {
+                const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)(v >> 1) * ns) * 3 * Wp;
+                __syncwarp();
+                for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
+            }
+            if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
+            __syncwarp();
+            uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
+            uint2* buf1 = buf0 + Lbuf;
+            for (int i = lane; i < Lbuf; i += 32) {
+                const uint2 x = strand ? onehot_rc_bf16x4(s_pl, Wp, L, i) : onehot_bf16x4(s_pl, Wp, L, i);
+                buf0[i] = x;
+                if (i > 0) buf1[i - 1] = x;
+                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
+            }
+            umma::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
+        }
+    } else {
+        // ================= epilogue warps =================
+        const int quarter = warp & 3, wq = warp >> 2;
+        const int row = quarter * 32 + lane;
+        const bool rows_live = quarter * 32 < ng;
+        const uint32_t tlane = tmem + ((uint32_t)(quarter * 32) << 16) + 28u * wq;
+        float best = -INFINITY, acc = 0.0f;
+        int bidx = 0x7fffffff;
+        int g = 0;
+        for (int sq = 0; sq < nseq; ++sq) {
+            for (int strand = 0; strand < 2; ++strand) {
+                for (int t = 0; t < ntiles; ++t, ++g) {
+                    const uint32_t stage = (uint32_t)g & 1u;
+                    umma::mbar_wait(&sh->acc_full[stage], ((uint32_t)g >> 1) & 1u);
+                    umma::fence_after_sync();
+                    const int p0 = t * TC_TILE_POS + 56 * wq;      // first window start of this warp's share
+                    const int limit = Lw - p0;                     // local starts 0 .. limit-1 exist
+                    const bool live = rows_live && limit > 0;
+                    uint32_t E[28], O[28];
+                    if (live) {
+                        umma::tmem_ld28(tlane + stage * TC_STAGE_COLS, E);
+                        umma::tmem_ld28(tlane + stage * TC_STAGE_COLS + TC_ODD_COL, O);
+                        umma::tmem_ld_wait();
+                    }
+                    umma::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
+                    if (live) {
+                        const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
+                        if (limit >= 56) {
+#pragma unroll
+                            for (int pl = 0; pl < 56; ++pl) {
+                                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+                                if (mode == 0) acc += z;
+                                else if (WANT_ARG) { if (z > best) { best = z; bidx = base + pl; } }
+                                else best = fmaxf(best, z);
+                            }
+                        } else {
+#pragma unroll
+                            for (int pl = 0; pl < 56; ++pl) {
+                                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+                                if (pl < limit) {
+                                    if (mode == 0) acc += z;
+                                    else if (z > best) { best = z; bidx = base + pl; }
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            // merge the four column shares of every row (first maximum wins: smaller index on ties)
+            const int par = sq & 1;
+            sh->val[par][wq][row] = mode == 0 ? acc : best;
+            sh->idx[par][wq][row] = bidx;
+            epi_barrier();
+            if (wq == 0 && row < ng) {
+                float bv = sh->val[par][0][row];
+                int bi = sh->idx[par][0][row];
+#pragma unroll
+                for (int s = 1; s < 4; ++s) {
+                    const float v = sh->val[par][s][row];
+                    const int i = sh->idx[par][s][row];
+                    if (mode == 0) bv += v;
+                    else if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+                }
+                const long long o = (long long)(blockIdx.y + (long long)sq * ns) * G + g0 + row;
+                out[o] = bv;
+                if (WANT_ARG) argmax[o] = bi;
+            }
+            best = -INFINITY; acc = 0.0f; bidx = 0x7fffffff;
+        }
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
+}
+
+static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_out) {
+    if (w < 1 || w > TC_KMAX || L < w) return false;
+    const int Lw = L - w + 1, kpad = tc_kpad(w);
+    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
+    const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;   // last tile reads up to start + 224 + kpad/4 + 2
+    const int Wp = (L + 31) / 32;
+    for (int noh = 2; noh >= 1; --noh) {
+        const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + (size_t)((3 * Wp * 4 + 15) & ~15) +
+                            sizeof(PwShared) + 16;
+        if (smem <= 227 * 1024) {
+            if (noh_out) *noh_out = noh;
+            if (Lbuf_out) *Lbuf_out = Lbuf;
+            if (smem_out) *smem_out = smem;
+            return true;
+        }
+    }
+    return false;
+}
+
+extern "C" int xnn_pwm_scan_tc_supported(int L, int w) { return pwm_tc_fits(L, w, nullptr, nullptr, nullptr) ? 1 : 0; }
+extern "C" size_t xnn_pwm_scan_tc_work_bytes(int G, int w) {
+    if (G < 1 || w < 1 || w > TC_KMAX) return 0;
+    return (size_t)tc_mtiles(G) * tc_split_bytes(w);
+}
+
+static int launch_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w, const float* pwm_w, int mode, float* out,
+                       int32_t* argmax, void* work, cudaStream_t st) {
+    int noh = 0, Lbuf = 0;
+    size_t smem = 0;
+    if (!pwm_tc_fits(L, w, &noh, &Lbuf, &smem)) return 1;
+    const int Lw = L - w + 1, Wp = (L + 31) / 32;
+    const int kpad = tc_kpad(w), mt = tc_mtiles(G);
+    tc_split_weights_kernel<<<dim3(ceil_div((long long)TC_ROWS * kpad, 256), mt), 256, 0, st>>>(
+        pwm_w, nullptr, G, w, kpad, reinterpret_cast<__nv_bfloat16*>(work));
+    if (cudaGetLastError() != cudaSuccess) return -1;
+    int slices = num_sms() / mt;
+    if (slices < 1) slices = 1;
+    if (slices > B) slices = B;
+    dim3 grid(mt, slices);
+    if (argmax) {
+        if (cudaFuncSetAttribute(pwm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        pwm_tc_kernel<true><<<grid, TC_THREADS, smem, st>>>(planes, B, L, Wp, G, Lw, kpad, Lbuf, noh, mode,
+                                                            reinterpret_cast<const __nv_bfloat16*>(work), out, argmax);
+    } else {
+        if (cudaFuncSetAttribute(pwm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        pwm_tc_kernel<false><<<grid, TC_THREADS, smem, st>>>(planes, B, L, Wp, G, Lw, kpad, Lbuf, noh, mode,
+                                                             reinterpret_cast<const __nv_bfloat16*>(work), out, argmax);
+    }
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+extern "C" int xnn_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w, const float* pwm_w, int mode,
+                               float* out, int32_t* argmax, void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(planes && pwm_w && out && work, "NULL pointer");
+    XNN_CHECK_ARG(w >= 1 && L >= w && G >= 1 && B >= 0 && (mode == 0 || mode == 1), "bad sizes");
+    XNN_CHECK_ARG(((uintptr_t)work & 15) == 0, "work must be 16-byte aligned");
+    XNN_CHECK_ARG(argmax == nullptr || mode == 1, "argmax goes with mode 1 (max)");
+    if (B == 0) return XNN_OK;
+    const int r = launch_pwm_scan_tc(planes, B, L, G, w, pwm_w, mode, out, argmax, work, to_stream(s));
+    if (r == 1) { set_error("xnn_pwm_scan_tc: shape outside the tensor-core path (see xnn_pwm_scan_tc_supported)"); return XNN_ERR_ARG; }
+    if (r != 0) { set_error("xnn_pwm_scan_tc: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
     return XNN_OK;
 }

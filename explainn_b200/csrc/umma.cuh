@@ -173,6 +173,20 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t* r) {
                  : "r"(taddr)
                  : "memory");
 }
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
+}
+// 14 consecutive columns (4 pool windows of one position parity) as 8 + 4 + 2; asynchronous until tmem_ld_wait
+__device__ __forceinline__ void tmem_ld14(uint32_t taddr, uint32_t (&r)[14]) {
+    tmem_ld8(taddr, &r[0]);
+    tmem_ld4(taddr + 8, &r[8]);
+    tmem_ld2(taddr + 12, &r[12]);
+}
+// wait for the outstanding tcgen05.ld's; the loaded registers are tied to the statement so that no use of them
+// can be scheduled above the wait
+__device__ __forceinline__ void tmem_ld_wait14(uint32_t (&a)[14], uint32_t (&b)[14]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]), "+r"(a[8]), "+r"(a[9]), "+r"(a[10]), "+r"(a[11]), "+r"(a[12]), "+r"(a[13]), "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]), "+r"(b[8]), "+r"(b[9]), "+r"(b[10]), "+r"(b[11]), "+r"(b[12]), "+r"(b[13]) : : "memory");
+}
 // 28 consecutive columns (a quarter of a 112-column pool tile) as 16 + 8 + 4
 __device__ __forceinline__ void tmem_ld28(uint32_t taddr, uint32_t (&r)[28]) {
     asm volatile(
@@ -194,7 +208,7 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t hint = 0x989680u) {
     const uint32_t a = smem_u32(bar);
     uint32_t done = 0, spins = 0;
     while (!done) {
@@ -202,11 +216,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t"
             "}\n"
             : "=r"(done)
-            : "r"(a), "r"(parity)
+            : "r"(a), "r"(parity), "r"(hint)   // suspend-time hint: a waiting warp sleeps instead of spinning
             : "memory");
     }
 }

@@ -408,11 +408,18 @@ def site_emit(planes, L, conv_w, scale, shift, thr, offsets, cap, idx=None, pfm=
 
 
 # ---- a11: PWM module ---------------------------------------------------------------------------
-def pwm_scan(planes, L, pwm_w, mode, want_argmax=False):
+def pwm_scan(planes, L, pwm_w, mode, want_argmax=False, tensor_cores=True):
+    """The PWM module's scan.  tensor_cores: the tcgen05 Toeplitz kernel (xnn_pwm_scan_tc) whenever the shape
+    fits it; False (or a width above 48 / a sequence too long for shared memory) runs the FP32 gather-add scan."""
     B = planes.shape[0]
     G, _, w = pwm_w.shape
     out = torch.empty((B, G), dtype=torch.float32, device=planes.device)
     arg = torch.empty((B, G), dtype=torch.int32, device=planes.device) if want_argmax else None
+    if tensor_cores and _lib.load().xnn_pwm_scan_tc_supported(int(L), int(w)):
+        work = _work(_lib.load().xnn_pwm_scan_tc_work_bytes(int(G), int(w)), planes.device)
+        _call("xnn_pwm_scan_tc", _p(_req(planes, torch.int32, "planes")), B, L, G, w,
+              _p(_req(pwm_w, torch.float32, "pwm_w")), 1 if mode == "max" else 0, _p(out), _p(arg), _p(work), _stream())
+        return out, arg
     _call("xnn_pwm_scan", _p(_req(planes, torch.int32, "planes")), B, L, G, w,
           _p(_req(pwm_w, torch.float32, "pwm_w")), 1 if mode == "max" else 0, _p(out), _p(arg), _stream())
     return out, arg

@@ -269,6 +269,21 @@ int xnn_pwm_scan(const uint32_t* planes, int B, int L, int G, int w,
                  const float* pwm_w /* (G,4,w) */, int mode,
                  float* out, int32_t* argmax, xnn_stream_t s);
 
+/* The same scan on the tensor cores (tcgen05): the G matrices are the A operand
+ * of a Toeplitz GEMM over the bf16 one-hot of x, then of its reverse complement
+ * (flip(x), architectures/__init__.py:387-404); weights are split in three bf16
+ * pieces so every product is exact and accumulation is fp32.  Same arguments
+ * and results as xnn_pwm_scan (scores to fp32 rounding, argmax with the same
+ * first-maximum rule) plus a work buffer of xnn_pwm_scan_tc_work_bytes(G, w)
+ * bytes, 16-byte aligned.  xnn_pwm_scan_tc_supported: 1 when (L, w) fit this
+ * path (w <= 48 and the one-hot buffers fit in shared memory), else 0 -- use
+ * xnn_pwm_scan then. */
+int xnn_pwm_scan_tc_supported(int L, int w);
+size_t xnn_pwm_scan_tc_work_bytes(int G, int w);
+int xnn_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w,
+                    const float* pwm_w /* (G,4,w) */, int mode,
+                    float* out, int32_t* argmax, void* work, xnn_stream_t s);
+
 /* ---- a13/a14: PWMScan pwm_scoring semantics, pwmscan/pwm_scoring.c ---------
  * Sequences are int8 codes 0..4 (A C G T N) as pwm_scoring.c:627-655, one
  * record per row of `offsets` (int64 [R+1], start of each record in codes).

@@ -113,7 +113,10 @@ def test_eval_forward_golden(name):
 
 
 @pytest.mark.parametrize("cfg", [(300, 19, 60, 66, 64), (300, 19, 600, 50, 6), (33, 24, 100, 2, 17),
-                                 (100, 19, 200, 1, 300)])
+                                 (100, 19, 200, 1, 300),
+                                 # front-end staging modes: n % 4 == 0 -> tile-by-tile copy-out (one and two
+                                 # tiles, two M tiles); odd U*n -> every 16-byte phase of the linear copy-out
+                                 (130, 19, 74, 3, 21), (20, 19, 270, 2, 9), (37, 19, 124, 2, 33)])
 def test_eval_forward_vs_oracle(cfg):
     Uu, k, L, F, B = cfg
     m = _random_model(Uu, k, L, F).eval()
@@ -333,7 +336,7 @@ def test_train_step_golden(name, kind):
 
 
 @pytest.mark.parametrize("cfg", [(40, 19, 200, 5, 64, "linear"), (300, 19, 60, 66, 32, "linear"),
-                                 (17, 11, 95, 1, 48, "binary")])
+                                 (17, 11, 95, 1, 48, "binary"), (37, 19, 124, 2, 33, "linear")])
 def test_train_step_vs_fp64_oracle(cfg):
     """gradients against the fp64 evaluation of the oracle, with an injected dropout mask (p = 0.3)"""
     from explainn_b200.architectures import get_loss
@@ -535,6 +538,32 @@ def test_pwm_module_vs_oracle_wide():
     m = PWM(pw, 300, "max").to(DEV)
     p = PackedDNA.from_onehot(x.to(DEV))
     assert torch.equal(m(p), m(p.revcomp()))
+
+
+@pytest.mark.parametrize("cfg", [(5, 6, 40, 3), (70, 35, 300, 9), (300, 19, 1000, 5), (130, 48, 230, 33),
+                                 (17, 24, 24, 7)])
+def test_pwm_scan_tensor_core_vs_fp32_scan_and_oracle(cfg):
+    """xnn_pwm_scan_tc against the FP32 gather-add scan and the oracle: one and several M tiles, one and several
+    position tiles, partial last tile, a single window (L == w), N bases, argmax on the [fwd | rev] axis"""
+    from explainn_b200 import ops
+    G, w, L, B = cfg
+    rng = np.random.default_rng(G + w)
+    pw = np.ascontiguousarray(np.log(np.maximum(rng.dirichlet([0.5] * 4, size=(G, w)).transpose(0, 2, 1), 1e-4)))
+    x = O.random_onehot(B, L, seed=G, n_frac=0.01)
+    planes = ops.pack_onehot(x.to(DEV))
+    wd = torch.tensor(pw, dtype=torch.float32, device=DEV)
+    for mode in ("max", "sum"):
+        ref, ref_i = O.pwm_module_scores(pw, x.numpy(), mode)
+        tc, tc_i = ops.pwm_scan(planes, L, wd, mode, want_argmax=(mode == "max"), tensor_cores=True)
+        fp, fp_i = ops.pwm_scan(planes, L, wd, mode, want_argmax=(mode == "max"), tensor_cores=False)
+        U.assert_close(tc.cpu().numpy(), ref, what="tensor-core " + mode)
+        U.assert_close(tc.cpu().numpy(), fp.cpu().numpy(), what="tensor-core vs fp32 scan " + mode)
+        if mode == "max":
+            assert np.array_equal(tc_i.cpu().numpy(), ref_i)
+            assert np.array_equal(tc_i.cpu().numpy(), fp_i.cpu().numpy())
+            # without the index the running maximum is an fmax chain: same values
+            tc2, _ = ops.pwm_scan(planes, L, wd, mode, want_argmax=False, tensor_cores=True)
+            assert torch.equal(tc2, tc)
 
 
 # ---------------------------------------------------------------------------------------------------
