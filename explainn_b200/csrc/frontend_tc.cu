@@ -471,25 +471,66 @@ __device__ __forceinline__ uint2 onehot_rc_bf16x4(const uint32_t* __restrict__ s
     return v;
 }
 
-template <bool WANT_ARG>
+// The same pipeline serves the interpret passes 1 and 2a (test.py:128-166, interpret.py:363-421): rows are
+// units (sign of the BatchNorm scale folded into A), one strand, and the epilogue keeps per unit
+//   SCAN_ACT_MAX    the maximum of D = sgn(s) z over every listed sequence; the activation
+//                   fp16(exp(|s| D + t)) is monotone in D, so its maximum is the activation of max D;
+//   SCAN_SITE_COUNT the number of starts whose fp16 activation exceeds thr_u, per listed sequence.  The
+//                   predicate is monotone in D as well: each thread bisects (on the float order) the first D
+//                   for which it holds and afterwards evaluates exp only for D within 64 ulps of that
+//                   point -- one or two compares per position instead of an exp and two conversions;
+//   SCAN_SITE_EMIT  pass 2b: the same predicate; every site gets its rank (caller's exclusive offset of the
+//                   (unit, sequence) pair + sites at earlier starts of the sequence), and while rank < cap its
+//                   k-mer is counted into the unit's PFM (shared-memory atomics, flushed once per CTA) and,
+//                   optionally, (list position, start) is written to sites[unit][rank].
+enum { SCAN_SUM = 0, SCAN_MAX = 1, SCAN_MAX_ARG = 2, SCAN_ACT_MAX = 3, SCAN_SITE_COUNT = 4, SCAN_SITE_EMIT = 5 };
+
+struct ScanArgs {
+    const uint32_t* planes;
+    int n_items, L, Wp, R, Lw, kpad, Lbuf, noh, nstr;
+    const int32_t* idx;            // listed sequences (interpret) or NULL
+    const __nv_bfloat16* wsplit;
+    const float* scale; const float* shift; const float* thr;   // interpret
+    float* out; int32_t* argmax;                                // PWM
+    uint32_t* amax_bits; int32_t* counts;                       // interpret
+    const long long* offsets; long long cap; int32_t* pfm; int32_t* sites; long long site_cap; int k;   // emit
+};
+
+__device__ __forceinline__ float act16_of(float asc, float D, float shf) {
+    return __half2float(__float2half_rn(expf(fmaf(asc, D, shf))));
+}
+__device__ __forceinline__ uint32_t float_key(float x) {
+    const uint32_t b = __float_as_uint(x);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, int Lw, int kpad, int Lbuf, int noh,
-              int mode, const __nv_bfloat16* __restrict__ wsplit, float* __restrict__ out,
-              int32_t* __restrict__ argmax) {
+scan_tc_kernel(ScanArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t* __restrict__ planes = a.planes;
+    const int L = a.L, Wp = a.Wp, Lw = a.Lw, kpad = a.kpad, Lbuf = a.Lbuf, noh = a.noh, nstr = a.nstr;
     const int chunks = kpad >> 3, ksteps = kpad >> 4;
     const uint32_t a_bytes = 3u * chunks * 2048u;
     unsigned char* a_smem = smem_raw;
     uint2* oh = reinterpret_cast<uint2*>(smem_raw + a_bytes);                // [noh][2][Lbuf]
     uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);
-    PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + ((3 * Wp * 4 + 15) & ~15));
+    const int pl_bytes = (3 * Wp * 4 + 15) & ~15;
+    PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + pl_bytes);
+    uint32_t* s_pl2 = reinterpret_cast<uint32_t*>(sh + 1);                   // [2][3 * Wp] (emit): planes of the
+    int* s_pfm = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(s_pl2) + 2 * pl_bytes);   // sequence in the epilogue; [128][4][k]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g0 = blockIdx.x * TC_ROWS;
-    const int ng = min(TC_ROWS, G - g0);
+    const int ng = min(TC_ROWS, a.R - g0);
+    if (MODE == SCAN_SITE_EMIT)
+        for (int i = tid; i < TC_ROWS * 4 * a.k; i += TC_THREADS) s_pfm[i] = 0;
     const int ns = gridDim.y;
     {
-        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(wsplit) +
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(a.wsplit) +
                                                           (size_t)blockIdx.x * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
         for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
@@ -509,8 +550,8 @@ pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, 
     umma::fence_after_sync();
     const uint32_t tmem = sh->tmem_slot;
     const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
-    const int nseq = (B - 1 - (int)blockIdx.y) / ns + 1;
-    const int nvs = 2 * nseq;                                   // (sequence, strand) pairs of this CTA
+    const int nseq = (a.n_items - 1 - (int)blockIdx.y) / ns + 1;
+    const int nvs = nstr * nseq;                                // (sequence, strand) pairs of this CTA
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps (even / odd window starts) =================
@@ -554,9 +595,11 @@ pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, 
     } else if (warp == TC_EPI_WARPS + 2) {
         // ================= one-hot warp: x, then RC(x), of every sequence =================
         for (int v = 0; v < nvs; ++v) {
-            const int so = v % noh, strand = v & 1;
+            const int so = v % noh, strand = (nstr == 2) ? (v & 1) : 0;
             if (!strand) {
-                const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)(v >> 1) * ns) * 3 * Wp;
+                const int item = blockIdx.y + (nstr == 2 ? (v >> 1) : v) * ns;
+                const long long b = a.idx ? (long long)a.idx[item] : (long long)item;
+                const uint32_t* sp = planes + b * 3 * Wp;
                 __syncwarp();
                 for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
             }
@@ -580,11 +623,33 @@ pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, 
         const int row = quarter * 32 + lane;
         const bool rows_live = quarter * 32 < ng;
         const uint32_t tlane = tmem + ((uint32_t)(quarter * 32) << 16) + 28u * wq;
+        constexpr bool INTERP = (MODE >= SCAN_ACT_MAX);
+        float asc = 0.0f, shf = 0.0f, thr = 0.0f;
+        float Dlo = INFINITY, Dhi = INFINITY;      // SITE_COUNT: D >= Dhi is a site, D <= Dlo is not, between: evaluate
+        if (INTERP && row < ng) {
+            asc = fabsf(a.scale[g0 + row]);
+            shf = a.shift[g0 + row];
+            if (MODE == SCAN_SITE_COUNT || MODE == SCAN_SITE_EMIT) {
+                thr = a.thr[g0 + row];
+                if (act16_of(asc, -INFINITY, shf) > thr) {
+                    Dlo = -INFINITY; Dhi = -INFINITY;                      // every start is a site
+                } else if (act16_of(asc, INFINITY, shf) > thr) {
+                    uint32_t lo = float_key(-INFINITY), hi = float_key(INFINITY);   // predicate false at lo, true at hi
+                    while (hi - lo > 1u) {
+                        const uint32_t mid = lo + ((hi - lo) >> 1);
+                        if (act16_of(asc, key_float(mid), shf) > thr) hi = mid; else lo = mid;
+                    }
+                    const uint32_t kmin = float_key(-INFINITY), kmax = float_key(INFINITY);
+                    Dlo = key_float(hi - kmin > 64u ? hi - 64u : kmin);
+                    Dhi = key_float(kmax - hi > 64u ? hi + 64u : kmax);
+                }
+            }
+        }
         float best = -INFINITY, acc = 0.0f;
-        int bidx = 0x7fffffff;
+        int bidx = 0x7fffffff, cnt = 0;
         int g = 0;
         for (int sq = 0; sq < nseq; ++sq) {
-            for (int strand = 0; strand < 2; ++strand) {
+            for (int strand = 0; strand < nstr; ++strand) {
                 for (int t = 0; t < ntiles; ++t, ++g) {
                     const uint32_t stage = (uint32_t)g & 1u;
                     umma::mbar_wait(&sh->acc_full[stage], ((uint32_t)g >> 1) & 1u);
@@ -601,33 +666,81 @@ pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, 
                     umma::fence_before_sync();
                     __syncwarp();
                     if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
-                    if (live) {
-                        const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
-                        if (limit >= 56) {
+                    if (MODE == SCAN_SITE_EMIT) {
+                        // hit mask of this thread's 56 starts, ascending
+                        unsigned long long mask = 0ull;
+                        if (live) {
 #pragma unroll
                             for (int pl = 0; pl < 56; ++pl) {
                                 const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
-                                if (mode == 0) acc += z;
-                                else if (WANT_ARG) { if (z > best) { best = z; bidx = base + pl; } }
-                                else best = fmaxf(best, z);
+                                bool hit = z >= Dhi;
+                                if (!hit && z > Dlo) hit = act16_of(asc, z, shf) > thr;
+                                if (hit && pl < limit) mask |= 1ull << pl;
                             }
-                        } else {
+                        }
+                        const int tp = g & 1;
+                        const int item = blockIdx.y + sq * ns;
+                        uint32_t* pl2 = s_pl2 + (sq & 1) * (pl_bytes >> 2);
+                        sh->idx[tp][wq][row] = __popcll(mask);
+                        if (t == 0 && warp == 0) {                 // planes of this sequence for the k-mer counts
+                            const long long b = a.idx ? (long long)a.idx[item] : (long long)item;
+                            for (int i = lane; i < 3 * Wp; i += 32) pl2[i] = __ldg(planes + b * 3 * Wp + i);
+                        }
+                        epi_barrier();
+                        int before = 0, total = 0;
 #pragma unroll
-                            for (int pl = 0; pl < 56; ++pl) {
-                                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
-                                if (pl < limit) {
-                                    if (mode == 0) acc += z;
-                                    else if (z > best) { best = z; bidx = base + pl; }
+                        for (int s2 = 0; s2 < 4; ++s2) {
+                            const int c2 = sh->idx[tp][s2][row];
+                            total += c2;
+                            if (s2 < wq) before += c2;
+                        }
+                        if (mask != 0ull && row < ng) {
+                            const int u = g0 + row, k = a.k;
+                            long long rank = a.offsets[(long long)u * a.n_items + item] + cnt + before;
+                            while (mask != 0ull && rank < a.cap) {
+                                const int pl = __ffsll((long long)mask) - 1;
+                                mask &= mask - 1ull;
+                                const int p = p0 + pl;
+                                if (a.sites && rank < a.site_cap) {
+                                    a.sites[((long long)u * a.site_cap + rank) * 2 + 0] = item;
+                                    a.sites[((long long)u * a.site_cap + rank) * 2 + 1] = p;
+                                }
+                                for (int j = 0; j < k; ++j) {
+                                    const int q = p + j, w = q >> 5, bt = q & 31;
+                                    if (!((pl2[2 * Wp + w] >> bt) & 1u)) {
+                                        const int c = (int)((pl2[w] >> bt) & 1u) | ((int)((pl2[Wp + w] >> bt) & 1u) << 1);
+                                        atomicAdd(&s_pfm[(row * 4 + c) * k + j], 1);
+                                    }
+                                }
+                                ++rank;
+                            }
+                        }
+                        cnt += total;                              // sites at earlier starts of this sequence
+                    } else if (live) {
+                        const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
+                        const bool full = limit >= 56;
+#pragma unroll
+                        for (int pl = 0; pl < 56; ++pl) {
+                            const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+                            if (full || pl < limit) {
+                                if (MODE == SCAN_SUM) acc += z;
+                                else if (MODE == SCAN_MAX_ARG) { if (z > best) { best = z; bidx = base + pl; } }
+                                else if (MODE == SCAN_MAX || MODE == SCAN_ACT_MAX) best = fmaxf(best, z);
+                                else {
+                                    if (z >= Dhi) ++cnt;
+                                    else if (z > Dlo) cnt += (act16_of(asc, z, shf) > thr) ? 1 : 0;
                                 }
                             }
                         }
                     }
                 }
             }
+            if (MODE == SCAN_ACT_MAX) continue;                    // one maximum per unit over the whole list
+            if (MODE == SCAN_SITE_EMIT) { cnt = 0; continue; }
             // merge the four column shares of every row (first maximum wins: smaller index on ties)
             const int par = sq & 1;
-            sh->val[par][wq][row] = mode == 0 ? acc : best;
-            sh->idx[par][wq][row] = bidx;
+            sh->val[par][wq][row] = MODE == SCAN_SUM ? acc : best;
+            sh->idx[par][wq][row] = MODE == SCAN_SITE_COUNT ? cnt : bidx;
             epi_barrier();
             if (wq == 0 && row < ng) {
                 float bv = sh->val[par][0][row];
@@ -636,30 +749,49 @@ pwm_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int G, 
                 for (int s = 1; s < 4; ++s) {
                     const float v = sh->val[par][s][row];
                     const int i = sh->idx[par][s][row];
-                    if (mode == 0) bv += v;
+                    if (MODE == SCAN_SUM) bv += v;
+                    else if (MODE == SCAN_SITE_COUNT) bi += i;
                     else if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
                 }
-                const long long o = (long long)(blockIdx.y + (long long)sq * ns) * G + g0 + row;
-                out[o] = bv;
-                if (WANT_ARG) argmax[o] = bi;
+                const long long item = blockIdx.y + (long long)sq * ns;
+                if (MODE == SCAN_SITE_COUNT) {
+                    a.counts[(long long)(g0 + row) * a.n_items + item] = bi;
+                } else {
+                    a.out[item * a.R + g0 + row] = bv;
+                    if (MODE == SCAN_MAX_ARG) a.argmax[item * a.R + g0 + row] = bi;
+                }
             }
-            best = -INFINITY; acc = 0.0f; bidx = 0x7fffffff;
+            best = -INFINITY; acc = 0.0f; bidx = 0x7fffffff; cnt = 0;
+        }
+        if (MODE == SCAN_ACT_MAX) {
+            sh->val[0][wq][row] = best;
+            epi_barrier();
+            if (wq == 0 && row < ng) {
+                const float m = fmaxf(fmaxf(sh->val[0][0][row], sh->val[0][1][row]),
+                                      fmaxf(sh->val[0][2][row], sh->val[0][3][row]));
+                // activations are >= 0 (or +inf): uint order == float order for non-negative floats
+                if (m > -INFINITY) atomicMax(&a.amax_bits[g0 + row], __float_as_uint(act16_of(asc, m, shf)));
+            }
         }
     }
     umma::fence_before_sync();
     __syncthreads();
     if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
+    if (MODE == SCAN_SITE_EMIT)
+        for (int i = tid; i < ng * 4 * a.k; i += TC_THREADS)
+            if (s_pfm[i]) atomicAdd(&a.pfm[(long long)g0 * 4 * a.k + i], s_pfm[i]);
 }
 
-static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_out) {
+static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_out, bool emit = false) {
     if (w < 1 || w > TC_KMAX || L < w) return false;
     const int Lw = L - w + 1, kpad = tc_kpad(w);
     const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
     const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;   // last tile reads up to start + 224 + kpad/4 + 2
     const int Wp = (L + 31) / 32;
     for (int noh = 2; noh >= 1; --noh) {
-        const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + (size_t)((3 * Wp * 4 + 15) & ~15) +
-                            sizeof(PwShared) + 16;
+        const size_t plb = (size_t)((3 * Wp * 4 + 15) & ~15);
+        const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + plb + sizeof(PwShared) + 16 +
+                            (emit ? 2 * plb + (size_t)TC_ROWS * 4 * w * 4 : 0);
         if (smem <= 227 * 1024) {
             if (noh_out) *noh_out = noh;
             if (Lbuf_out) *Lbuf_out = Lbuf;
@@ -676,30 +808,45 @@ extern "C" size_t xnn_pwm_scan_tc_work_bytes(int G, int w) {
     return (size_t)tc_mtiles(G) * tc_split_bytes(w);
 }
 
-static int launch_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w, const float* pwm_w, int mode, float* out,
-                       int32_t* argmax, void* work, cudaStream_t st) {
+template <int MODE>
+static int launch_scan(const ScanArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
+    if (cudaFuncSetAttribute(scan_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return -1;
+    scan_tc_kernel<MODE><<<grid, TC_THREADS, smem, st>>>(a);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// mode: SCAN_*; returns 0 when launched, 1 when the shape is outside this path, -1 on a CUDA error
+static int launch_scan_tc(int mode, const uint32_t* planes, int n_items, const int32_t* idx, int L, int R, int w,
+                          const float* weights, const float* scale, const float* shift, const float* thr, float* out,
+                          int32_t* argmax, uint32_t* amax_bits, int32_t* counts, void* work, cudaStream_t st,
+                          const long long* offsets = nullptr, long long cap = 0, int32_t* pfm = nullptr,
+                          int32_t* sites = nullptr, long long site_cap = 0) {
     int noh = 0, Lbuf = 0;
     size_t smem = 0;
-    if (!pwm_tc_fits(L, w, &noh, &Lbuf, &smem)) return 1;
-    const int Lw = L - w + 1, Wp = (L + 31) / 32;
-    const int kpad = tc_kpad(w), mt = tc_mtiles(G);
+    if (!pwm_tc_fits(L, w, &noh, &Lbuf, &smem, mode == SCAN_SITE_EMIT)) return 1;
+    const int kpad = tc_kpad(w), mt = tc_mtiles(R);
     tc_split_weights_kernel<<<dim3(ceil_div((long long)TC_ROWS * kpad, 256), mt), 256, 0, st>>>(
-        pwm_w, nullptr, G, w, kpad, reinterpret_cast<__nv_bfloat16*>(work));
+        weights, scale, R, w, kpad, reinterpret_cast<__nv_bfloat16*>(work));
     if (cudaGetLastError() != cudaSuccess) return -1;
     int slices = num_sms() / mt;
     if (slices < 1) slices = 1;
-    if (slices > B) slices = B;
+    if (slices > n_items) slices = n_items;
     dim3 grid(mt, slices);
-    if (argmax) {
-        if (cudaFuncSetAttribute(pwm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
-        pwm_tc_kernel<true><<<grid, TC_THREADS, smem, st>>>(planes, B, L, Wp, G, Lw, kpad, Lbuf, noh, mode,
-                                                            reinterpret_cast<const __nv_bfloat16*>(work), out, argmax);
-    } else {
-        if (cudaFuncSetAttribute(pwm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
-        pwm_tc_kernel<false><<<grid, TC_THREADS, smem, st>>>(planes, B, L, Wp, G, Lw, kpad, Lbuf, noh, mode,
-                                                             reinterpret_cast<const __nv_bfloat16*>(work), out, argmax);
+    ScanArgs a{};
+    a.planes = planes; a.n_items = n_items; a.L = L; a.Wp = (L + 31) / 32; a.R = R; a.Lw = L - w + 1; a.kpad = kpad;
+    a.Lbuf = Lbuf; a.noh = noh; a.nstr = (mode <= SCAN_MAX_ARG) ? 2 : 1; a.idx = idx;
+    a.wsplit = reinterpret_cast<const __nv_bfloat16*>(work); a.scale = scale; a.shift = shift; a.thr = thr;
+    a.out = out; a.argmax = argmax; a.amax_bits = amax_bits; a.counts = counts;
+    a.offsets = offsets; a.cap = cap; a.pfm = pfm; a.sites = sites; a.site_cap = site_cap; a.k = w;
+    switch (mode) {
+        case SCAN_SUM: return launch_scan<SCAN_SUM>(a, grid, smem, st);
+        case SCAN_MAX: return launch_scan<SCAN_MAX>(a, grid, smem, st);
+        case SCAN_MAX_ARG: return launch_scan<SCAN_MAX_ARG>(a, grid, smem, st);
+        case SCAN_ACT_MAX: return launch_scan<SCAN_ACT_MAX>(a, grid, smem, st);
+        case SCAN_SITE_EMIT: return launch_scan<SCAN_SITE_EMIT>(a, grid, smem, st);
+        default: return launch_scan<SCAN_SITE_COUNT>(a, grid, smem, st);
     }
-    return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 extern "C" int xnn_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w, const float* pwm_w, int mode,
@@ -709,8 +856,54 @@ extern "C" int xnn_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int 
     XNN_CHECK_ARG(((uintptr_t)work & 15) == 0, "work must be 16-byte aligned");
     XNN_CHECK_ARG(argmax == nullptr || mode == 1, "argmax goes with mode 1 (max)");
     if (B == 0) return XNN_OK;
-    const int r = launch_pwm_scan_tc(planes, B, L, G, w, pwm_w, mode, out, argmax, work, to_stream(s));
+    const int m = mode == 0 ? SCAN_SUM : (argmax ? SCAN_MAX_ARG : SCAN_MAX);
+    const int r = launch_scan_tc(m, planes, B, nullptr, L, G, w, pwm_w, nullptr, nullptr, nullptr, out, argmax, nullptr,
+                                 nullptr, work, to_stream(s));
     if (r == 1) { set_error("xnn_pwm_scan_tc: shape outside the tensor-core path (see xnn_pwm_scan_tc_supported)"); return XNN_ERR_ARG; }
     if (r != 0) { set_error("xnn_pwm_scan_tc: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    return XNN_OK;
+}
+
+#define INTERP_TC_CHECKS(fn)                                                                               \
+    XNN_CHECK_ARG(planes && conv_w && scale && shift && work, "NULL pointer");                             \
+    XNN_CHECK_ARG(k >= 1 && L >= k && U >= 1 && B >= 0 && n_idx >= 0, "bad sizes");                        \
+    XNN_CHECK_ARG(idx != nullptr || n_idx == B, "idx == NULL means all B sequences (n_idx must equal B)"); \
+    XNN_CHECK_ARG(((uintptr_t)work & 15) == 0, "work must be 16-byte aligned");                            \
+    if (n_idx == 0) return XNN_OK;
+
+extern "C" int xnn_act_max_tc(const uint32_t* planes, int B, int L, int U, int k, const float* conv_w,
+                              const float* scale, const float* shift, const int32_t* idx, int n_idx,
+                              uint32_t* amax_bits, void* work, xnn_stream_t s) {
+    INTERP_TC_CHECKS();
+    XNN_CHECK_ARG(amax_bits, "NULL pointer");
+    const int r = launch_scan_tc(SCAN_ACT_MAX, planes, n_idx, idx, L, U, k, conv_w, scale, shift, nullptr, nullptr,
+                                 nullptr, amax_bits, nullptr, work, to_stream(s));
+    if (r) { set_error("xnn_act_max_tc: %s", r == 1 ? "shape outside the tensor-core path" : "launch failed"); return r == 1 ? XNN_ERR_ARG : XNN_ERR_CUDA; }
+    return XNN_OK;
+}
+
+extern "C" int xnn_site_counts_tc(const uint32_t* planes, int B, int L, int U, int k, const float* conv_w,
+                                  const float* scale, const float* shift, const float* thr, const int32_t* idx,
+                                  int n_idx, int32_t* counts, void* work, xnn_stream_t s) {
+    INTERP_TC_CHECKS();
+    XNN_CHECK_ARG(thr && counts, "NULL pointer");
+    const int r = launch_scan_tc(SCAN_SITE_COUNT, planes, n_idx, idx, L, U, k, conv_w, scale, shift, thr, nullptr,
+                                 nullptr, nullptr, counts, work, to_stream(s));
+    if (r) { set_error("xnn_site_counts_tc: %s", r == 1 ? "shape outside the tensor-core path" : "launch failed"); return r == 1 ? XNN_ERR_ARG : XNN_ERR_CUDA; }
+    return XNN_OK;
+}
+
+extern "C" int xnn_interpret_tc_supported(int L, int k) { return pwm_tc_fits(L, k, nullptr, nullptr, nullptr, true) ? 1 : 0; }
+
+extern "C" int xnn_site_emit_tc(const uint32_t* planes, int B, int L, int U, int k, const float* conv_w,
+                                const float* scale, const float* shift, const float* thr, const int32_t* idx,
+                                int n_idx, const long long* offsets, long long cap, int32_t* pfm, int32_t* sites,
+                                long long site_cap, void* work, xnn_stream_t s) {
+    INTERP_TC_CHECKS();
+    XNN_CHECK_ARG(thr && offsets && pfm, "NULL pointer");
+    XNN_CHECK_ARG(cap >= 0 && (sites == nullptr || site_cap >= 0), "bad cap");
+    const int r = launch_scan_tc(SCAN_SITE_EMIT, planes, n_idx, idx, L, U, k, conv_w, scale, shift, thr, nullptr,
+                                 nullptr, nullptr, nullptr, work, to_stream(s), offsets, cap, pfm, sites, site_cap);
+    if (r) { set_error("xnn_site_emit_tc: %s", r == 1 ? "shape outside the tensor-core path" : "launch failed"); return r == 1 ? XNN_ERR_ARG : XNN_ERR_CUDA; }
     return XNN_OK;
 }

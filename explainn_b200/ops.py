@@ -22,7 +22,7 @@ KERNELS_PER_CALL = {
     "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
-    "xnn_pwm_scan": 1, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
+    "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
 }
 kernel_launches = 0
 
@@ -372,7 +372,16 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_de
 
 
 # ---- a7-a10: interpret ----------------------------------------------------------------------
-def act_max(planes, L, conv_w, scale, shift, idx=None):
+def _scan_tc_work(L, rows, width, dev, tensor_cores):
+    """work buffer of the tcgen05 interpret kernels, or None when the shape is outside that path (the three
+    passes switch together: counts and emission must classify every start identically)"""
+    lib = _lib.load()
+    if not tensor_cores or not lib.xnn_interpret_tc_supported(int(L), int(width)):
+        return None
+    return _work(lib.xnn_pwm_scan_tc_work_bytes(int(rows), int(width)), dev)
+
+
+def act_max(planes, L, conv_w, scale, shift, idx=None, tensor_cores=True):
     """fp16-rounded per-unit maximum activation over the listed sequences -> float32 (U,)."""
     B = planes.shape[0]
     U, _, k = conv_w.shape
@@ -380,28 +389,44 @@ def act_max(planes, L, conv_w, scale, shift, idx=None):
     bits = torch.zeros(U, dtype=torch.int32, device=planes.device)
     if idx is not None:
         _req(idx, torch.int32, "idx")
-    _call("xnn_act_max", _p(_req(planes, torch.int32, "planes")), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
-          _p(idx), n_idx, _p(bits), _stream())
+    work = _scan_tc_work(L, U, k, planes.device, tensor_cores)
+    if work is not None:
+        _call("xnn_act_max_tc", _p(_req(planes, torch.int32, "planes")), B, L, U, k, _p(conv_w), _p(scale),
+              _p(shift), _p(idx), n_idx, _p(bits), _p(work), _stream())
+    else:
+        _call("xnn_act_max", _p(_req(planes, torch.int32, "planes")), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
+              _p(idx), n_idx, _p(bits), _stream())
     return bits.view(torch.float32)
 
 
-def site_counts(planes, L, conv_w, scale, shift, thr, idx=None):
+def site_counts(planes, L, conv_w, scale, shift, thr, idx=None, tensor_cores=True):
     B = planes.shape[0]
     U, _, k = conv_w.shape
     n_idx = B if idx is None else idx.numel()
     counts = torch.zeros((U, n_idx), dtype=torch.int32, device=planes.device)
-    _call("xnn_site_counts", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
-          _p(_req(thr, torch.float32, "thr")), _p(idx), n_idx, _p(counts), _stream())
+    work = _scan_tc_work(L, U, k, planes.device, tensor_cores)
+    if work is not None:
+        _call("xnn_site_counts_tc", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
+              _p(_req(thr, torch.float32, "thr")), _p(idx), n_idx, _p(counts), _p(work), _stream())
+    else:
+        _call("xnn_site_counts", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift),
+              _p(_req(thr, torch.float32, "thr")), _p(idx), n_idx, _p(counts), _stream())
     return counts
 
 
-def site_emit(planes, L, conv_w, scale, shift, thr, offsets, cap, idx=None, pfm=None, sites=None):
+def site_emit(planes, L, conv_w, scale, shift, thr, offsets, cap, idx=None, pfm=None, sites=None, tensor_cores=True):
     B = planes.shape[0]
     U, _, k = conv_w.shape
     n_idx = B if idx is None else idx.numel()
     if pfm is None:
         pfm = torch.zeros((U, 4, k), dtype=torch.int32, device=planes.device)
     site_cap = 0 if sites is None else sites.shape[1]
+    work = _scan_tc_work(L, U, k, planes.device, tensor_cores)
+    if work is not None:
+        _call("xnn_site_emit_tc", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(thr), _p(idx), n_idx,
+              _p(_req(offsets, torch.int64, "offsets")), int(cap), _p(pfm), _p(sites), int(site_cap), _p(work),
+              _stream())
+        return pfm
     _call("xnn_site_emit", _p(planes), B, L, U, k, _p(conv_w), _p(scale), _p(shift), _p(thr), _p(idx), n_idx,
           _p(_req(offsets, torch.int64, "offsets")), int(cap), _p(pfm), _p(sites), int(site_cap), _stream())
     return pfm

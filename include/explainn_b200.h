@@ -260,6 +260,36 @@ int xnn_site_emit(const uint32_t* planes, int B, int L, int U, int k,
                   const long long* offsets, long long cap,
                   int32_t* pfm, int32_t* sites, long long site_cap, xnn_stream_t s);
 
+/* Passes 1 and 2a on the tensor cores (tcgen05): the Toeplitz GEMM of the conv
+ * front end with a per-unit running maximum / site count in the epilogue.  The
+ * fp16-rounded activation is monotone in the conv output, so the maximum is
+ * taken before the exp and the threshold test is a compare against a per-unit
+ * bisected conv value (exp evaluated only within 64 ulps of it).  Same arguments
+ * and results as xnn_act_max / xnn_site_counts, plus a 16-byte aligned work
+ * buffer of xnn_pwm_scan_tc_work_bytes(U, k) bytes; shapes must satisfy
+ * xnn_interpret_tc_supported(L, k). */
+int xnn_act_max_tc(const uint32_t* planes, int B, int L, int U, int k,
+                   const float* conv_w, const float* scale, const float* shift,
+                   const int32_t* idx, int n_idx, uint32_t* amax_bits,
+                   void* work, xnn_stream_t s);
+int xnn_site_counts_tc(const uint32_t* planes, int B, int L, int U, int k,
+                       const float* conv_w, const float* scale, const float* shift,
+                       const float* thr, const int32_t* idx, int n_idx,
+                       int32_t* counts, void* work, xnn_stream_t s);
+/* Pass 2b on the same kernel: identical predicate (so counts and emission
+ * always agree), rank = offsets[u][i] + sites at earlier starts; PFM counted
+ * with shared-memory atomics.  Arguments as xnn_site_emit plus `work`.
+ * xnn_interpret_tc_supported(L, k): 1 when all three *_tc interpret passes fit
+ * (use the three of them together, or none: the conv summation order differs
+ * from the gather-add passes in the last bit). */
+int xnn_interpret_tc_supported(int L, int k);
+int xnn_site_emit_tc(const uint32_t* planes, int B, int L, int U, int k,
+                     const float* conv_w, const float* scale, const float* shift,
+                     const float* thr, const int32_t* idx, int n_idx,
+                     const long long* offsets, long long cap,
+                     int32_t* pfm, int32_t* sites, long long site_cap,
+                     void* work, xnn_stream_t s);
+
 /* ---- a11: PWM module, architectures/__init__.py:119-170 -------------------
  * score+[b,g,p] = sum_j W[g,base(p+j),j]; score- the same on the reverse
  * complement; out[b,g] = max or sum over both strands and all p (fp32).

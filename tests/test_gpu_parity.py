@@ -463,6 +463,58 @@ def test_interpret_vs_oracle_with_cap():
     assert mismatched_units <= 2
 
 
+@pytest.mark.parametrize("cfg", [(100, 19, 200, 257), (300, 19, 600, 40), (37, 11, 95, 64), (130, 24, 24, 9)])
+def test_interpret_tensor_core_passes_vs_fp32_passes(cfg):
+    """xnn_act_max_tc / xnn_site_counts_tc against the FP32 gather-add passes (same fp16 rule; the two conv
+    summation orders may differ in the last fp32 bit, so a start sitting exactly on an fp16 rounding boundary
+    may flip: at most a 1e-4 fraction of the starts, and maxima within one fp16 ulp)"""
+    from explainn_b200 import ops
+    Uu, k, L, B = cfg
+    g = torch.Generator().manual_seed(Uu)
+    cw = (torch.randn(Uu, 4, k, generator=g) * 0.3).to(DEV)
+    scale = ((torch.rand(Uu, generator=g) + 0.5) * torch.where(torch.rand(Uu, generator=g) < 0.15, -1.0, 1.0)).to(DEV)
+    shift = (torch.randn(Uu, generator=g) * 0.3).to(DEV)
+    planes = ops.pack_onehot(O.random_onehot(B, L, seed=7, n_frac=0.01).to(DEV))
+    idx = torch.arange(0, B, 2, dtype=torch.int32, device=DEV)
+    for sel in (None, idx):
+        m_tc = ops.act_max(planes, L, cw, scale, shift, sel, tensor_cores=True).cpu().numpy()
+        m_fp = ops.act_max(planes, L, cw, scale, shift, sel, tensor_cores=False).cpu().numpy()
+        assert np.all(np.abs(m_tc - m_fp) <= np.spacing(m_fp.astype(np.float16)).astype(np.float32))
+        thr = torch.tensor((0.5 * m_fp.astype(np.float16)).astype(np.float32), device=DEV)
+        c_tc = ops.site_counts(planes, L, cw, scale, shift, thr, sel, tensor_cores=True).cpu().numpy()
+        c_fp = ops.site_counts(planes, L, cw, scale, shift, thr, sel, tensor_cores=False).cpu().numpy()
+        assert c_tc.shape == c_fp.shape and c_fp.sum() > 0
+        assert np.abs(c_tc - c_fp).sum() <= max(1, int(1e-4 * c_fp.size * (L - k + 1)))
+        # pass 2b: PFM and site list of the tensor-core emission are consistent with its own counts, and equal to
+        # the FP32 passes' wherever the two agree on every start of a unit
+        n_idx = c_tc.shape[1]
+        for tcflag, cnts in ((True, c_tc), (False, c_fp)):
+            ct = torch.tensor(cnts, device=DEV)
+            csum = torch.cumsum(ct.to(torch.int64), dim=1)
+            offs = (csum - ct).contiguous()
+            cap = 300
+            sites = torch.full((Uu, cap, 2), -1, dtype=torch.int32, device=DEV)
+            pfm = ops.site_emit(planes, L, cw, scale, shift, thr, offs, cap, sel, None, sites, tensor_cores=tcflag)
+            tot = np.minimum(cnts.sum(1), cap)
+            assert np.array_equal(pfm.cpu().numpy().sum(1).max(1) <= tot, np.ones(Uu, bool))
+            sh_ = sites.cpu().numpy()
+            for uu in range(Uu):
+                assert (sh_[uu, :tot[uu], 0] >= 0).all() and (sh_[uu, tot[uu]:, 0] == -1).all()
+                rec = sh_[uu, :tot[uu]].astype(np.int64)
+                assert (np.diff(rec[:, 0] * 100000 + rec[:, 1]) > 0).all()          # (sequence, start) ascending
+            if tcflag:
+                pfm_tc, sites_tc = pfm.cpu().numpy(), sh_
+            else:
+                same = (c_tc == c_fp).all(1)
+                assert same.sum() >= Uu - 2
+                assert np.array_equal(pfm_tc[same], pfm.cpu().numpy()[same])
+                assert np.array_equal(sites_tc[same], sh_[same])
+    # thresholds no activation reaches / every activation exceeds
+    none = ops.site_counts(planes, L, cw, scale, shift, torch.full((Uu,), 6.0e4, device=DEV), None)
+    every = ops.site_counts(planes, L, cw, scale, shift, torch.full((Uu,), -1.0, device=DEV), None)
+    assert int(none.sum()) == 0 and bool((every == L - k + 1).all())
+
+
 def test_interpret_sequence_shards_reproduce_the_unsharded_result():
     """contiguous shards + exclusive carries place the site cap on the same global prefix
     (both strands); the two-shard exchange is emulated in-process, the collective itself is covered by
