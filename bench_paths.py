@@ -273,17 +273,16 @@ def run_interpret(name, args, rank, world, local, peaks, sampler):
     Lc = L - k + 1
     top = max(call_ms, key=call_ms.get)
     passes = sum(len(ev) for ev in events.values() if ev) / args.steps
-    # one-hot-aware work of one pass over one sequence: k gather-adds + 1 exp (~8 FP32 ops) per (unit, position)
-    ops_per_seq = float(U) * Lc * (k + 8)
-    n_top = len(events[top]) / args.steps
-    fp32_peak = 148 * 128 * 1.965e9 / 1e12            # FP32 instruction issue, Tinstr/s (no FMA doubling: adds)
-    achieved = ops_per_seq * N * n_top / (call_ms[top] / 1e3) / 1e12
-    roof = {"kernel": top, "bound": "fp32-issue", "achieved": achieved, "peak": fp32_peak, "unit": "Tinstr/s",
-            "frac": achieved / fp32_peak, "traffic": None,
-            "peak_source": "nominal 148 SM x 128 lanes x 1.965 GHz (FP32 add issue; not in MEASURED_PEAKS.json)",
-            "what": "U*Lc*(k+8) FP32 operations per sequence per pass (gather-add formulation)",
+    # every pass is the conv front end on the tensor cores: dense-equivalent 2*U*Lc*4k flop per sequence and pass
+    # (SURVEY.md 8d); the bf16x3 weight split issues 3x that.  call_ms[top] sums the chunked calls of one step.
+    conv_flops = 2.0 * U * Lc * 4 * k
+    n_pass = 2.0 if top == "xnn_site_counts_tc" else 1.0       # totals pass + offsets pass
+    achieved = conv_flops * N * n_pass / (call_ms[top] / 1e3) / 1e12
+    roof = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s",
+            "frac": achieved / tf_sus, "traffic": None, "peak_source": "bf16_tflops_sustained, " + which,
+            "what": "dense-equivalent 2*U*Lc*4k flop per sequence and pass (3x issued: bf16x3 weight split)",
             "kernel_ms": call_ms[top], "kernel_share_of_step": call_ms[top] / (ms_dev / args.steps),
-            "hbm_input_gbs": 12.0 * ((L + 31) // 32) * N * n_top / (call_ms[top] / 1e3) / 1e9, "hbm_peak": hbm,
+            "hbm_input_gbs": 12.0 * ((L + 31) // 32) * N * n_pass / (call_ms[top] / 1e3) / 1e9, "hbm_peak": hbm,
             "per_call_ms": {k_: round(v, 4) for k_, v in sorted(call_ms.items(), key=lambda kv: -kv[1])}}
     sample = max(64, args.cpu_sample * 4)
     cpu = _cpu_interpret_rate(U, k, L, sample)
@@ -398,15 +397,15 @@ def run_scan(name, args, rank, world, local, peaks, sampler):
         return
     hbm, tf_sus, _, which = peaks()
     top = max(call_ms, key=call_ms.get)
-    adds = 2.0 * G * w * (L - w + 1)                  # gather-adds per sequence, both strands
-    fp32_peak = 148 * 128 * 1.965e9 / 1e12
-    achieved = adds * N / (call_ms[top] / 1e3) / 1e12
-    roof = {"kernel": top, "bound": "fp32-issue", "achieved": achieved, "peak": fp32_peak, "unit": "Tinstr/s",
-            "frac": achieved / fp32_peak, "traffic": None,
-            "peak_source": "nominal 148 SM x 128 lanes x 1.965 GHz (FP32 add issue; not in MEASURED_PEAKS.json)",
-            "what": "2*G*w*(L-w+1) gather-adds per sequence", "kernel_ms": call_ms[top],
-            "kernel_share_of_step": call_ms[top] / (ms_dev / args.steps),
-            "dense_equivalent_tflops": 2 * 4 * adds * N / (call_ms[top] / 1e3) / 1e12, "tensor_peak": tf_sus,
+    adds = 2.0 * G * w * (L - w + 1)                  # one-hot-aware gather-adds per sequence, both strands
+    dense = 2.0 * 4.0 * adds                           # dense-equivalent flop (2 flop per MAC, 4 channels)
+    achieved = dense * N / (call_ms[top] / 1e3) / 1e12
+    roof = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s",
+            "frac": achieved / tf_sus, "traffic": None, "peak_source": "bf16_tflops_sustained, " + which,
+            "what": "dense-equivalent 2*2*G*4w*(L-w+1) flop per sequence (3x issued: bf16x3 weight split, "
+                    "plus padding of 4w to 16 and of G to 128)",
+            "kernel_ms": call_ms[top], "kernel_share_of_step": call_ms[top] / (ms_dev / args.steps),
+            "gather_adds_per_s": adds * N / (call_ms[top] / 1e3),
             "per_call_ms": {k_: round(v, 4) for k_, v in sorted(call_ms.items(), key=lambda kv: -kv[1])}}
     torch.set_num_threads(os.cpu_count() or 1)
     sample = max(16, args.cpu_sample // 4)
@@ -423,7 +422,7 @@ def run_scan(name, args, rank, world, local, peaks, sampler):
         "config": {"workload": f"pwm_scoring: {G} PWMs (width {w} after resize) over {N} x {L}-bp packed sequences "
                                f"per GPU ({N * L / 1e6:.1f} Mbp; 8 GPUs = 100 Mbp)",
                    "parallelism": f"sequences sharded over {world} rank(s), no collective",
-                   "l2": "input 0.4 MB per Mbp: compute-bound; weights in shared memory",
+                   "l2": "input 0.4 MB per Mbp: tensor-bound; weights resident in shared memory",
                    "mbp_per_s": rate * L / 1e6, "mbp_pwm_per_s": rate * L * G / 1e6},
         "e2e": {"value": world * N / (ms_e2e / 1e3), "unit": "sequences/s", "h2d_bytes_per_step": planes_h.numel() * 4,
                 "d2h_bytes_per_step": N * G * 4, "api": "PWM.forward(PackedDNA from pinned host planes) -> host scores"},

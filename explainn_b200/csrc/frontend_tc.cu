@@ -520,8 +520,9 @@ scan_tc_kernel(ScanArgs a) {
     uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);
     const int pl_bytes = (3 * Wp * 4 + 15) & ~15;
     PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + pl_bytes);
-    uint32_t* s_pl2 = reinterpret_cast<uint32_t*>(sh + 1);                   // [2][3 * Wp] (emit): planes of the
-    int* s_pfm = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(s_pl2) + 2 * pl_bytes);   // sequence in the epilogue; [128][4][k]
+    const int code_bytes = (L + 15) & ~15;
+    uint8_t* s_codes = reinterpret_cast<uint8_t*>(sh + 1);                   // [2][L] (emit): base codes 0..3 / 4 of the
+    int* s_pfm = reinterpret_cast<int*>(s_codes + 2 * code_bytes);           // sequence in the epilogue; [128][4][k]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g0 = blockIdx.x * TC_ROWS;
@@ -680,11 +681,17 @@ scan_tc_kernel(ScanArgs a) {
                         }
                         const int tp = g & 1;
                         const int item = blockIdx.y + sq * ns;
-                        uint32_t* pl2 = s_pl2 + (sq & 1) * (pl_bytes >> 2);
+                        uint8_t* codes = s_codes + (sq & 1) * code_bytes;
                         sh->idx[tp][wq][row] = __popcll(mask);
-                        if (t == 0 && warp == 0) {                 // planes of this sequence for the k-mer counts
+                        if (t == 0 && warp == 0) {                 // base codes of this sequence for the k-mer counts
                             const long long b = a.idx ? (long long)a.idx[item] : (long long)item;
-                            for (int i = lane; i < 3 * Wp; i += 32) pl2[i] = __ldg(planes + b * 3 * Wp + i);
+                            const uint32_t* sp = planes + b * 3 * Wp;
+                            for (int i = lane; i < L; i += 32) {
+                                const int w = i >> 5;
+                                const uint32_t lo = (__ldg(sp + w) >> lane) & 1u, hi = (__ldg(sp + Wp + w) >> lane) & 1u,
+                                               nm = (__ldg(sp + 2 * Wp + w) >> lane) & 1u;
+                                codes[i] = (uint8_t)(nm ? 4u : (lo | (hi << 1)));
+                            }
                         }
                         epi_barrier();
                         int before = 0, total = 0;
@@ -705,12 +712,11 @@ scan_tc_kernel(ScanArgs a) {
                                     a.sites[((long long)u * a.site_cap + rank) * 2 + 0] = item;
                                     a.sites[((long long)u * a.site_cap + rank) * 2 + 1] = p;
                                 }
+                                const uint8_t* cp = codes + p;
+                                int* pr = s_pfm + row * 4 * k;
                                 for (int j = 0; j < k; ++j) {
-                                    const int q = p + j, w = q >> 5, bt = q & 31;
-                                    if (!((pl2[2 * Wp + w] >> bt) & 1u)) {
-                                        const int c = (int)((pl2[w] >> bt) & 1u) | ((int)((pl2[Wp + w] >> bt) & 1u) << 1);
-                                        atomicAdd(&s_pfm[(row * 4 + c) * k + j], 1);
-                                    }
+                                    const int c = cp[j];
+                                    if (c < 4) atomicAdd(&pr[c * k + j], 1);
                                 }
                                 ++rank;
                             }
@@ -791,7 +797,7 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
     for (int noh = 2; noh >= 1; --noh) {
         const size_t plb = (size_t)((3 * Wp * 4 + 15) & ~15);
         const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + plb + sizeof(PwShared) + 16 +
-                            (emit ? 2 * plb + (size_t)TC_ROWS * 4 * w * 4 : 0);
+                            (emit ? 2 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * 4 * w * 4 : 0);
         if (smem <= 227 * 1024) {
             if (noh_out) *noh_out = noh;
             if (Lbuf_out) *Lbuf_out = Lbuf;
