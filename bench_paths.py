@@ -276,7 +276,7 @@ def run_interpret(name, args, rank, world, local, peaks, sampler):
     # every pass is the conv front end on the tensor cores: dense-equivalent 2*U*Lc*4k flop per sequence and pass
     # (SURVEY.md 8d); the bf16x3 weight split issues 3x that.  call_ms[top] sums the chunked calls of one step.
     conv_flops = 2.0 * U * Lc * 4 * k
-    n_pass = 2.0 if top == "xnn_site_counts_tc" else 1.0       # totals pass + offsets pass
+    n_pass = 1.0                                               # each pass runs once (pass 2a counts are reused)
     achieved = conv_flops * N * n_pass / (call_ms[top] / 1e3) / 1e12
     roof = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s",
             "frac": achieved / tf_sus, "traffic": None, "peak_source": "bf16_tflops_sustained, " + which,

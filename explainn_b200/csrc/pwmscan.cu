@@ -352,3 +352,176 @@ extern "C" int xnn_ipwm_scan_best(const int8_t* codes, const long long* offsets,
     XNN_CHECK_LAUNCH();
     return XNN_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Long records (a chromosome is ONE FASTA record): the kernels above give a record to one block.  The
+// `_parts` entry points split every record's windows into P contiguous parts (P depends on R only, so the
+// summation order is fixed), one block per (record, part), partial results in a caller-provided work buffer,
+// and a second kernel combines the parts in ascending order: sums are deterministic, the integer best hit keeps
+// the tool's first-maximum rule.
+// ---------------------------------------------------------------------------
+static int scan_parts(int R) {
+    const int want = num_sms() * 8;
+    if (R >= want) return 1;
+    int P = (want + R - 1) / R;
+    return P > 1024 ? 1024 : P;
+}
+extern "C" int xnn_scan_parts(int R) { return R < 1 ? 1 : scan_parts(R); }
+extern "C" size_t xnn_scan_work_bytes(int R) { return R < 1 ? 0 : (size_t)R * scan_parts(R) * 24; }
+
+__global__ void __launch_bounds__(256)
+lpm_sum_parts_kernel(const int8_t* __restrict__ codes, const long long* __restrict__ offsets, int R, int w, int P,
+                     const double* __restrict__ lpm, const double* __restrict__ bg, int bg_per_record, int fwd_only,
+                     double* __restrict__ part_sum) {
+    __shared__ LpmTab T;
+    __shared__ double red[8];
+    for (int i = threadIdx.x; i < 5 * w; i += blockDim.x) T.l[i / w][i % w] = lpm[i];
+    if (threadIdx.x < 5) T.bg[threadIdx.x] = bg[threadIdx.x];
+    __syncthreads();
+    const int part = blockIdx.y;
+    for (int r = blockIdx.x; r < R; r += gridDim.x) {
+        if (bg_per_record) {
+            if (threadIdx.x < 5) T.bg[threadIdx.x] = bg[(long long)r * 5 + threadIdx.x];
+            __syncthreads();
+        }
+        const long long beg = offsets[r], len = offsets[r + 1] - beg;
+        const long long nwin = len - w + 1;
+        const long long per = nwin > 0 ? (nwin + P - 1) / P : 0;
+        const long long i0 = (long long)part * per, i1 = min(nwin, i0 + per);
+        double acc = 0.0;
+        for (long long i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+            double p, pr;
+            lpm_window(codes + beg + i, w, T, fwd_only != 0, p, pr);
+            acc += fwd_only ? p : (p + pr);
+        }
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int i = 0; i < 8; ++i) t += red[i];
+            part_sum[(long long)r * P + part] = t;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+lpm_sum_combine_kernel(const double* __restrict__ part_sum, int R, int P, double* __restrict__ out_sum) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    double t = 0.0;
+    for (int p = 0; p < P; ++p) t += part_sum[(long long)r * P + p];
+    out_sum[r] = t;
+}
+
+extern "C" int xnn_lpm_scan_sum_parts(const int8_t* codes, const long long* offsets, int R, int w, const double* lpm,
+                                      const double* bg, int bg_per_record, int forward_only, double* out_sum,
+                                      void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(codes && offsets && lpm && bg && out_sum && work, "NULL pointer");
+    XNN_CHECK_ARG(R >= 0 && w >= 1 && w <= LPM_WMAX, "bad sizes (matrix length <= 64)");
+    if (R == 0) return XNN_OK;
+    const int P = scan_parts(R);
+    cudaStream_t st = to_stream(s);
+    dim3 grid(R < 65535 ? R : 65535, P);
+    if ((long long)grid.x * P > (long long)num_sms() * 64) grid.x = (unsigned)max(1, num_sms() * 64 / P);
+    lpm_sum_parts_kernel<<<grid, 256, 0, st>>>(codes, offsets, R, w, P, lpm, bg, bg_per_record, forward_only,
+                                               (double*)work);
+    XNN_CHECK_LAUNCH();
+    lpm_sum_combine_kernel<<<ceil_div(R, 256), 256, 0, st>>>((const double*)work, R, P, out_sum);
+    XNN_CHECK_LAUNCH();
+    return XNN_OK;
+}
+
+struct IpwmPart { int v; int st; long long ix; };
+
+__global__ void __launch_bounds__(256)
+ipwm_best_parts_kernel(const int8_t* __restrict__ codes, const long long* __restrict__ offsets, int R, int w, int P,
+                       const int32_t* __restrict__ pwm, int fwd_only, IpwmPart* __restrict__ parts) {
+    __shared__ int32_t Tm[5][LPM_WMAX];
+    __shared__ int s_val[8];
+    __shared__ long long s_idx[8];
+    __shared__ int s_str[8];
+    for (int i = threadIdx.x; i < 5 * w; i += blockDim.x) Tm[i / w][i % w] = pwm[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, part = blockIdx.y;
+    for (int r = blockIdx.x; r < R; r += gridDim.x) {
+        const long long beg = offsets[r], len = offsets[r + 1] - beg;
+        const long long nwin = len - w + 1;
+        const long long per = nwin > 0 ? (nwin + P - 1) / P : 0;
+        const long long i0 = (long long)part * per, i1 = min(nwin, i0 + per);
+        int bv = INT_MIN, bs = 0;
+        long long bi = LLONG_MAX;
+        for (long long i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+            const int8_t* sq = codes + beg + i;
+            uint32_t sc = 0, rv = 0;
+            for (int j = 0; j < w; ++j) {
+                const int c = sq[j];
+                sc += (uint32_t)Tm[c][j];
+                if (!fwd_only) rv += (uint32_t)Tm[(c == 4) ? 4 : 3 - c][w - j - 1];
+            }
+            int m, kk = 0;
+            if (fwd_only) {
+                m = (int)sc;
+            } else {
+                const uint32_t cdiff = sc - rv;
+                kk = (int)(cdiff >> 31);
+                m = (int)(sc - (uint32_t)kk * cdiff);
+            }
+            if (m > bv || (m == bv && bi != LLONG_MAX && i < bi)) { bv = m; bi = i; bs = kk; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const int ov = __shfl_xor_sync(0xffffffffu, bv, off);
+            const long long oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            const int os = __shfl_xor_sync(0xffffffffu, bs, off);
+            if (oi != LLONG_MAX && (ov > bv || bi == LLONG_MAX || (ov == bv && oi < bi))) { bv = ov; bi = oi; bs = os; }
+        }
+        if (lane == 0) { s_val[warp] = bv; s_idx[warp] = bi; s_str[warp] = bs; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int v = INT_MIN, st = 0; long long ix = LLONG_MAX;
+            for (int i = 0; i < 8; ++i)
+                if (s_idx[i] != LLONG_MAX && (ix == LLONG_MAX || s_val[i] > v || (s_val[i] == v && s_idx[i] < ix))) {
+                    v = s_val[i]; ix = s_idx[i]; st = s_str[i];
+                }
+            IpwmPart o; o.v = v; o.st = st; o.ix = ix;
+            parts[(long long)r * P + part] = o;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+ipwm_best_combine_kernel(const IpwmPart* __restrict__ parts, const long long* __restrict__ offsets, int R, int w, int P,
+                         int32_t* __restrict__ best_out, int32_t* __restrict__ pos_out, int8_t* __restrict__ strand_out) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    const long long nwin = offsets[r + 1] - offsets[r] - w + 1;
+    int v = INT_MIN, st = 0; long long ix = LLONG_MAX;
+    for (int p = 0; p < P; ++p) {
+        const IpwmPart q = parts[(long long)r * P + p];
+        if (q.ix != LLONG_MAX && (ix == LLONG_MAX || q.v > v || (q.v == v && q.ix < ix))) { v = q.v; ix = q.ix; st = q.st; }
+    }
+    if (nwin <= 0) { best_out[r] = INT_MIN; pos_out[r] = -1; strand_out[r] = 0; }        // "NOTAG"
+    else if (ix == LLONG_MAX) { best_out[r] = INT_MIN; pos_out[r] = 0; strand_out[r] = 0; }  // nothing > INT_MIN
+    else { best_out[r] = v; pos_out[r] = (int32_t)ix; strand_out[r] = (int8_t)st; }
+}
+
+extern "C" int xnn_ipwm_scan_best_parts(const int8_t* codes, const long long* offsets, int R, int w,
+                                        const int32_t* pwm, int forward_only, int32_t* best, int32_t* pos,
+                                        int8_t* strand, void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(codes && offsets && pwm && best && pos && strand && work, "NULL pointer");
+    XNN_CHECK_ARG(R >= 0 && w >= 1 && w <= LPM_WMAX, "bad sizes (matrix length <= 64)");
+    XNN_CHECK_ARG(((uintptr_t)work & 7) == 0, "work must be 8-byte aligned");
+    if (R == 0) return XNN_OK;
+    const int P = scan_parts(R);
+    cudaStream_t st = to_stream(s);
+    dim3 grid(R < 65535 ? R : 65535, P);
+    if ((long long)grid.x * P > (long long)num_sms() * 64) grid.x = (unsigned)max(1, num_sms() * 64 / P);
+    ipwm_best_parts_kernel<<<grid, 256, 0, st>>>(codes, offsets, R, w, P, pwm, forward_only, (IpwmPart*)work);
+    XNN_CHECK_LAUNCH();
+    ipwm_best_combine_kernel<<<ceil_div(R, 256), 256, 0, st>>>((const IpwmPart*)work, offsets, R, w, P, best, pos, strand);
+    XNN_CHECK_LAUNCH();
+    return XNN_OK;
+}

@@ -58,10 +58,11 @@ def act_thresholds(model, seqs, idxs=None, rev_complement=False):
     return (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
 
 
-def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=65536):
+def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=65536, keep_counts=None):
     """Pass 2a alone: uncapped number of above-threshold positions per (strand, unit) -> int64 (S,U)
     device tensor.  A sequence shard needs the totals of the shards before it (parallel.exclusive_carry)
-    to place the reference's 1e6 cap (interpret.py:414-417) on the same global prefix."""
+    to place the reference's 1e6 cap (interpret.py:414-417) on the same global prefix.  keep_counts: a dict that
+    receives the per-chunk count matrices, to be handed to sites_and_pfms(counts_cache=...) with the same chunk."""
     packed = _as_packed(seqs)
     cw, scale, shift = _front_eval_affine(model)
     U = cw.shape[0]
@@ -76,12 +77,14 @@ def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=
         for c0 in range(0, len(idx_all), chunk):
             idx_dev = torch.as_tensor(idx_all[c0:c0 + chunk] + strand * half, dtype=torch.int32, device=dev)
             counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
+            if keep_counts is not None:
+                keep_counts[(strand, c0)] = counts         # (U, chunk) int32: 4*U bytes per listed sequence
             tot[strand] += counts.sum(dim=1, dtype=torch.int64)
     return tot
 
 
 def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap=SITE_CAP,
-                   return_sites=False, site_capacity=None, chunk=65536, carry0=None):
+                   return_sites=False, site_capacity=None, chunk=65536, carry0=None, counts_cache=None):
     """interpret.py:375-454.  Returns dict(counts (U,) int64 sites emitted per unit,
     pfms (U,4,k) int64, sites: list per unit of int32 arrays (m,3) = (sequence index, strand 0/1, start)
     when return_sites).  carry0 (S,U) int64: global rank of this shard's first site per strand and unit
@@ -105,7 +108,9 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
         for c0 in range(0, len(idx_all), chunk):
             ids = idx_all[c0:c0 + chunk]
             idx_dev = torch.as_tensor(ids + strand * half, dtype=torch.int32, device=dev)
-            counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
+            counts = counts_cache.get((strand, c0)) if counts_cache is not None else None
+            if counts is None:
+                counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
             csum = torch.cumsum(counts.to(torch.int64), dim=1)
             offsets = (csum - counts + carry[:, None]).contiguous()
             sites = None

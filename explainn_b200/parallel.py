@@ -141,9 +141,10 @@ def interpret_sharded(model, local_seqs, rev_complement=False, cap=None, group=N
         amax = torch.maximum(amax, ops.act_max(packed.planes, packed.length, cw, scale, shift, idx + half))
     allreduce_max_(amax, group)
     thr = (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
-    tot = I.site_totals(model, packed, thr, None, rev_complement)
+    cache = {}                                                  # pass 2a's counts, reused by pass 2b
+    tot = I.site_totals(model, packed, thr, None, rev_complement, keep_counts=cache)
     carry0, grand = exclusive_carry(tot, group)
-    res = I.sites_and_pfms(model, packed, thr, None, rev_complement, cap=cap, carry0=carry0)
+    res = I.sites_and_pfms(model, packed, thr, None, rev_complement, cap=cap, carry0=carry0, counts_cache=cache)
     pfm = torch.as_tensor(res["pfms"], device=packed.planes.device)
     allreduce_sum_(pfm, group)
     return {"thresholds": thr, "counts": torch.clamp(grand, max=cap).cpu().numpy(), "pfms": pfm.cpu().numpy()}

@@ -643,10 +643,12 @@ def test_pwmscan_reproduces_reference_tool_output():
         assert lines == run["stdout"].splitlines(), name
 
 
-def test_pwmscan_vs_c_oracle_random():
+@pytest.mark.parametrize("lengths", [[40] * 50 + [7, 19, 20, 1000, 5003], [200003], [90001, 12, 30000]])
+def test_pwmscan_vs_c_oracle_random(lengths):
+    """many short records (one part each would do; R = 55 gives 22 parts per record, most of them empty) and
+    chromosome-like single records split over 1024 blocks"""
     from explainn_b200 import ops
     rng = np.random.default_rng(11)
-    lengths = [0 + 40] * 50 + [7, 19, 20, 1000, 5003]
     codes, offsets = U.random_codes(rng, lengths, n_frac=0.02)
     for w in (6, 19, 33):
         lpm = rng.dirichlet([0.6] * 4, size=w).T
