@@ -35,8 +35,12 @@ import torch  # noqa: E402
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
 # `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
 NCU_TRAFFIC = {
-    "xnn_mlp_bwd": 1123.1e6,        # mlp_bwd_kernel 698.7 MB read + 424.5 MB written (profiles/r01_ncu_full_s18.txt)
-    "xnn_frontend_fwd": 986.3e6,    # frontend_tc_kernel<1> 66.6 MB read + 919.7 MB written (same capture)
+    # profiles/r01_ncu_full_s41.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
+    "xnn_mlp_bwd": 1758.3e6,        # mlp_fc1_kernel<2> 629.2 + 7.1 MB, mlp_bwd_kernel 698.6 MB read + 423.4 MB written
+    "xnn_frontend_bwd": 923.4e6,    # frontend_bwd_tc_kernel 918.9 MB read + 4.5 MB written
+    "xnn_frontend_fwd": 860.4e6,    # frontend_tc_kernel<1> 2.2 MB read + 858.2 MB written
+    "xnn_mlp_fwd": 663.8e6,         # mlp_fc1_kernel<1> 617.1 MB read + 46.7 MB written
+    "xnn_mlp_bn2_train_prepare": 580.7e6,
 }
 
 WORKLOADS = {
@@ -272,7 +276,9 @@ def main():
         "xnn_frontend_fwd": ("tensor", conv_flops, "conv+BN+exp+maxpool forward, dense-equivalent 2*U*Lc*4k flop"),
         "xnn_frontend_bwd": ("hbm", 9.0 * U * n + 12.0 * ((L + 31) // 32),
                              "conv weight gradient: dy+zmax (fp32) + argmax (u8) + planes read"),
-        "xnn_mlp_bwd": ("hbm", 2 * pool_bytes + 24.0 * U, "MLP backward: pool read, dy written, maskbits+dopre read"),
+        "xnn_mlp_bwd": ("hbm", 3 * pool_bytes + 48.0 * U,
+                        "MLP backward, two passes (BN2-backward reductions; dW1/dy): pool read twice, dy written, "
+                        "maskbits+dopre read twice"),
         "xnn_mlp_fwd": ("hbm", pool_bytes + 20.0 * U, "MLP forward: pool read, opre+maskbits written"),
         "xnn_mlp_bn2_train_prepare": ("hbm", pool_bytes, "BN2 batch statistics: pool read"),
         "xnn_pack_onehot_f32": ("hbm", 16.0 * L + 12.0 * ((L + 31) // 32), "float one-hot read, planes written"),

@@ -528,7 +528,7 @@ scan_tc_kernel(ScanArgs a) {
     const int g0 = blockIdx.x * TC_ROWS;
     const int ng = min(TC_ROWS, a.R - g0);
     if (MODE == SCAN_SITE_EMIT)
-        for (int i = tid; i < TC_ROWS * 4 * a.k; i += TC_THREADS) s_pfm[i] = 0;
+        for (int i = tid; i < TC_ROWS * (4 * a.k + 1); i += TC_THREADS) s_pfm[i] = 0;
     const int ns = gridDim.y;
     {
         const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(a.wsplit) +
@@ -713,7 +713,8 @@ scan_tc_kernel(ScanArgs a) {
                                     a.sites[((long long)u * a.site_cap + rank) * 2 + 1] = p;
                                 }
                                 const uint8_t* cp = codes + p;
-                                int* pr = s_pfm + row * 4 * k;
+                                int* pr = s_pfm + row * (4 * k + 1);           // odd row pitch: rows on distinct banks
+#pragma unroll 4
                                 for (int j = 0; j < k; ++j) {
                                     const int c = cp[j];
                                     if (c < 4) atomicAdd(&pr[c * k + j], 1);
@@ -784,8 +785,11 @@ scan_tc_kernel(ScanArgs a) {
     __syncthreads();
     if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
     if (MODE == SCAN_SITE_EMIT)
-        for (int i = tid; i < ng * 4 * a.k; i += TC_THREADS)
-            if (s_pfm[i]) atomicAdd(&a.pfm[(long long)g0 * 4 * a.k + i], s_pfm[i]);
+        for (int i = tid; i < ng * 4 * a.k; i += TC_THREADS) {
+            const int r = i / (4 * a.k), e = i - r * 4 * a.k;
+            const int v = s_pfm[r * (4 * a.k + 1) + e];
+            if (v) atomicAdd(&a.pfm[(long long)g0 * 4 * a.k + i], v);
+        }
 }
 
 static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_out, bool emit = false) {
@@ -797,7 +801,7 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
     for (int noh = 2; noh >= 1; --noh) {
         const size_t plb = (size_t)((3 * Wp * 4 + 15) & ~15);
         const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + plb + sizeof(PwShared) + 16 +
-                            (emit ? 2 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * 4 * w * 4 : 0);
+                            (emit ? 2 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * (4 * w + 1) * 4 : 0);
         if (smem <= 227 * 1024) {
             if (noh_out) *noh_out = noh;
             if (Lbuf_out) *Lbuf_out = Lbuf;
