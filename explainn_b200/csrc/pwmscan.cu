@@ -525,3 +525,179 @@ extern "C" int xnn_ipwm_scan_best_parts(const int8_t* codes, const long long* of
     XNN_CHECK_LAUNCH();
     return XNN_OK;
 }
+
+// ---- LPM best-hit mode over record parts --------------------------------------------------------------
+// A: per (record, part) best value and first window;  B: per record best / first (kept in the record's part 0);
+// C: per part, the number of later windows equal to the best (and the hit itself: position, strand);
+// D: per record, exclusive prefix of those counts;  E: per part, the tied positions in ascending order.
+struct LpmPart { double bv; long long bi; int ties; int off; };
+
+__device__ __forceinline__ void lpm_load_tab(LpmTab& T, const double* lpm, const double* bg, int w) {
+    for (int i = threadIdx.x; i < 5 * w; i += blockDim.x) T.l[i / w][i % w] = lpm[i];
+    if (threadIdx.x < 5) T.bg[threadIdx.x] = bg[threadIdx.x];
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+lpm_best_partsA_kernel(const int8_t* __restrict__ codes, const long long* __restrict__ offsets, int R, int w, int P,
+                       const double* __restrict__ lpm, const double* __restrict__ bg, int bg_per_record, int fwd_only,
+                       LpmPart* __restrict__ parts) {
+    __shared__ LpmTab T;
+    __shared__ double s_val[8];
+    __shared__ long long s_idx[8];
+    lpm_load_tab(T, lpm, bg, w);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, part = blockIdx.y;
+    for (int r = blockIdx.x; r < R; r += gridDim.x) {
+        if (bg_per_record) {
+            if (threadIdx.x < 5) T.bg[threadIdx.x] = bg[(long long)r * 5 + threadIdx.x];
+            __syncthreads();
+        }
+        const long long beg = offsets[r], nwin = offsets[r + 1] - beg - w + 1;
+        const long long per = nwin > 0 ? (nwin + P - 1) / P : 0;
+        const long long i0 = (long long)part * per, i1 = min(nwin, i0 + per);
+        double bv = 0.0;                 // the reference starts from best_score = 0.0 and needs max > best
+        long long bi = LLONG_MAX;
+        for (long long i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+            double p, pr;
+            lpm_window(codes + beg + i, w, T, fwd_only != 0, p, pr);
+            const double m = fwd_only ? p : (p > pr ? p : pr);
+            if (m > bv || (m == bv && m != 0.0 && i < bi)) { bv = m; bi = i; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bv, off);
+            const long long oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { s_val[warp] = bv; s_idx[warp] = bi; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double v = s_val[0]; long long ix = s_idx[0];
+            for (int i = 1; i < 8; ++i)
+                if (s_val[i] > v || (s_val[i] == v && s_idx[i] < ix)) { v = s_val[i]; ix = s_idx[i]; }
+            LpmPart o; o.bv = v; o.bi = ix; o.ties = 0; o.off = 0;
+            parts[(long long)r * P + part] = o;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+lpm_best_partsB_kernel(LpmPart* __restrict__ parts, int R, int P, double* __restrict__ best_out,
+                       int32_t* __restrict__ pos_out, int8_t* __restrict__ strand_out, int32_t* __restrict__ nties_out) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    double v = 0.0; long long ix = LLONG_MAX;
+    for (int p = 0; p < P; ++p) {
+        const LpmPart q = parts[(long long)r * P + p];
+        if (q.bv > v || (q.bv == v && q.bi < ix)) { v = q.bv; ix = q.bi; }
+    }
+    parts[(long long)r * P].bv = v;
+    parts[(long long)r * P].bi = ix;
+    if (v == 0.0 || ix == LLONG_MAX) {
+        // nothing beat 0.0: the reference prints position "0", strand '+'
+        best_out[r] = 0.0; pos_out[r] = 0; strand_out[r] = '+'; nties_out[r] = 0;
+        parts[(long long)r * P].bi = LLONG_MAX;
+    }
+}
+
+// MODE 0: count ties per part (and write the hit); MODE 1: list them at the part's offset
+template <int MODE>
+__global__ void __launch_bounds__(256)
+lpm_best_partsC_kernel(const int8_t* __restrict__ codes, const long long* __restrict__ offsets, int R, int w, int P,
+                       const double* __restrict__ lpm, const double* __restrict__ bg, int bg_per_record, int fwd_only,
+                       LpmPart* __restrict__ parts, double* __restrict__ best_out, int32_t* __restrict__ pos_out,
+                       int8_t* __restrict__ strand_out, int32_t* __restrict__ tie_pos, int tie_cap) {
+    __shared__ LpmTab T;
+    __shared__ int s_cnt[8];
+    lpm_load_tab(T, lpm, bg, w);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, part = blockIdx.y;
+    for (int r = blockIdx.x; r < R; r += gridDim.x) {
+        const double best = parts[(long long)r * P].bv;
+        const long long first = parts[(long long)r * P].bi;
+        if (first == LLONG_MAX) continue;
+        LpmPart* me = parts + (long long)r * P + part;
+        if (MODE == 1 && me->ties == 0) continue;
+        if (bg_per_record) {
+            __syncthreads();
+            if (threadIdx.x < 5) T.bg[threadIdx.x] = bg[(long long)r * 5 + threadIdx.x];
+            __syncthreads();
+        }
+        const long long beg = offsets[r], nwin = offsets[r + 1] - beg - w + 1;
+        const long long per = nwin > 0 ? (nwin + P - 1) / P : 0;
+        const long long i0 = max((long long)part * per, first), i1 = min(nwin, (long long)part * per + per);
+        int total = 0;
+        const int base0 = MODE == 1 ? me->off : 0;
+        for (long long ib = i0; ib < i1; ib += blockDim.x) {
+            const long long i = ib + threadIdx.x;
+            bool hit = false; int enc = 0;
+            if (i < i1) {
+                double p, pr;
+                lpm_window(codes + beg + i, w, T, fwd_only != 0, p, pr);
+                const double m = fwd_only ? p : (p > pr ? p : pr);
+                const bool plus = fwd_only ? true : (m == p);
+                enc = plus ? (int)i : (int)(i + w);
+                hit = (m == best);
+                if (i == first) {
+                    hit = false;
+                    if (MODE == 0) { best_out[r] = best; pos_out[r] = enc; strand_out[r] = plus ? '+' : '-'; }
+                }
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+            __syncthreads();
+            if (lane == 0) s_cnt[warp] = __popc(bal);
+            __syncthreads();
+            int before = 0, tile_total = 0;
+            for (int i2 = 0; i2 < 8; ++i2) { if (i2 < warp) before += s_cnt[i2]; tile_total += s_cnt[i2]; }
+            if (MODE == 1 && hit) {
+                const int my = base0 + total + before + __popc(bal & ((1u << lane) - 1u));
+                if (my < tie_cap) tie_pos[(long long)r * tie_cap + my] = enc;
+            }
+            total += tile_total;
+        }
+        if (MODE == 0 && threadIdx.x == 0) me->ties = total;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+lpm_best_partsD_kernel(LpmPart* __restrict__ parts, int R, int P, int32_t* __restrict__ nties_out) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R || parts[(long long)r * P].bi == LLONG_MAX) return;
+    int run = 0;
+    for (int p = 0; p < P; ++p) {
+        LpmPart* q = parts + (long long)r * P + p;
+        q->off = run;
+        run += q->ties;
+    }
+    nties_out[r] = run;
+}
+
+extern "C" int xnn_lpm_scan_best_parts(const int8_t* codes, const long long* offsets, int R, int w, const double* lpm,
+                                       const double* bg, int bg_per_record, int forward_only, double* best,
+                                       int32_t* best_pos, int8_t* best_strand, int32_t* n_ties, int32_t* tie_pos,
+                                       int tie_cap, void* work, xnn_stream_t s) {
+    XNN_CHECK_ARG(codes && offsets && lpm && bg && best && best_pos && best_strand && n_ties && work, "NULL pointer");
+    XNN_CHECK_ARG(R >= 0 && w >= 1 && w <= LPM_WMAX && tie_cap >= 0, "bad sizes (matrix length <= 64)");
+    XNN_CHECK_ARG(((uintptr_t)work & 7) == 0, "work must be 8-byte aligned");
+    if (R == 0) return XNN_OK;
+    const int P = scan_parts(R);
+    cudaStream_t st = to_stream(s);
+    dim3 grid(R < 65535 ? R : 65535, P);
+    if ((long long)grid.x * P > (long long)num_sms() * 64) grid.x = (unsigned)max(1, num_sms() * 64 / P);
+    LpmPart* parts = (LpmPart*)work;
+    lpm_best_partsA_kernel<<<grid, 256, 0, st>>>(codes, offsets, R, w, P, lpm, bg, bg_per_record, forward_only, parts);
+    XNN_CHECK_LAUNCH();
+    lpm_best_partsB_kernel<<<ceil_div(R, 256), 256, 0, st>>>(parts, R, P, best, best_pos, best_strand, n_ties);
+    XNN_CHECK_LAUNCH();
+    lpm_best_partsC_kernel<0><<<grid, 256, 0, st>>>(codes, offsets, R, w, P, lpm, bg, bg_per_record, forward_only,
+                                                    parts, best, best_pos, best_strand, tie_pos, tie_cap);
+    XNN_CHECK_LAUNCH();
+    lpm_best_partsD_kernel<<<ceil_div(R, 256), 256, 0, st>>>(parts, R, P, n_ties);
+    XNN_CHECK_LAUNCH();
+    if (tie_pos && tie_cap > 0) {
+        lpm_best_partsC_kernel<1><<<grid, 256, 0, st>>>(codes, offsets, R, w, P, lpm, bg, bg_per_record, forward_only,
+                                                        parts, best, best_pos, best_strand, tie_pos, tie_cap);
+        XNN_CHECK_LAUNCH();
+    }
+    return XNN_OK;
+}

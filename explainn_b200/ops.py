@@ -22,7 +22,7 @@ KERNELS_PER_CALL = {
     "xnn_frontend_acts": 1, "xnn_fc1_fwd": 1, "xnn_bn_train_prepare": 2, "xnn_fc2_fwd": 1, "xnn_head_fwd": 2,
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
-    "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
+    "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_lpm_scan_best_parts": 5, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
 }
 kernel_launches = 0
 
@@ -473,9 +473,10 @@ def lpm_scan_best(codes, offsets, lpm, bg, forward_only=False, tie_cap=16):
     strand = torch.empty(R, dtype=torch.int8, device=dev)
     nties = torch.empty(R, dtype=torch.int32, device=dev)
     ties = torch.full((R, max(tie_cap, 1)), -1, dtype=torch.int32, device=dev)
-    _call("xnn_lpm_scan_best", _p(_req(codes, torch.int8, "codes")), _p(_req(offsets, torch.int64, "offsets")), R, w,
-          _p(_req(lpm, torch.float64, "lpm")), _p(_req(bg, torch.float64, "bg")), per_rec, int(forward_only), _p(best),
-          _p(pos), _p(strand), _p(nties), _p(ties), int(tie_cap), _stream())
+    work = _work(_lib.load().xnn_scan_work_bytes(int(R)), dev)
+    _call("xnn_lpm_scan_best_parts", _p(_req(codes, torch.int8, "codes")), _p(_req(offsets, torch.int64, "offsets")),
+          R, w, _p(_req(lpm, torch.float64, "lpm")), _p(_req(bg, torch.float64, "bg")), per_rec, int(forward_only),
+          _p(best), _p(pos), _p(strand), _p(nties), _p(ties), int(tie_cap), _p(work), _stream())
     return best, pos, strand, nties, ties
 
 

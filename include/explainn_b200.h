@@ -341,14 +341,19 @@ int xnn_ipwm_scan_best(const int8_t* codes, const long long* offsets, int R, int
 /* The same two scans with every record's windows split into xnn_scan_parts(R)
  * contiguous parts, one block per (record, part) -- a chromosome is ONE record --
  * and the parts combined in ascending order by a second kernel (deterministic
- * sums; first-maximum rule kept).  work: xnn_scan_work_bytes(R) bytes, 8-byte
- * aligned.  Results as xnn_lpm_scan_sum (sum order differs: 1e-12 relative) and
- * xnn_ipwm_scan_best (bit-exact). */
+ * sums; first-maximum rule and the ascending tie list kept).  work:
+ * xnn_scan_work_bytes(R) bytes, 8-byte aligned.  Results as xnn_lpm_scan_sum (sum
+ * order differs: 1e-12 relative), xnn_lpm_scan_best and xnn_ipwm_scan_best
+ * (bit-exact). */
 int xnn_scan_parts(int R);
 size_t xnn_scan_work_bytes(int R);
 int xnn_lpm_scan_sum_parts(const int8_t* codes, const long long* offsets, int R, int w,
                            const double* lpm, const double* bg, int bg_per_record, int forward_only,
                            double* out_sum, void* work, xnn_stream_t s);
+int xnn_lpm_scan_best_parts(const int8_t* codes, const long long* offsets, int R, int w,
+                            const double* lpm, const double* bg, int bg_per_record, int forward_only,
+                            double* best, int32_t* best_pos, int8_t* best_strand, int32_t* n_ties,
+                            int32_t* tie_pos, int tie_cap, void* work, xnn_stream_t s);
 int xnn_ipwm_scan_best_parts(const int8_t* codes, const long long* offsets, int R, int w,
                              const int32_t* pwm, int forward_only,
                              int32_t* best, int32_t* pos, int8_t* strand, void* work, xnn_stream_t s);

@@ -660,10 +660,13 @@ def test_pwmscan_vs_c_oracle_random(lengths):
             s = ops.lpm_scan_sum(cd, od, l5, bgd, fwd).cpu().numpy()
             U.assert_close(s, U.oracle_lpm_sum(codes, offsets, lpm5, bg, fwd), rtol=1e-12, atol_scale=1e-13,
                            what="lpm sum")
-            best, pos, strand, nties, _ = [t.cpu().numpy() for t in ops.lpm_scan_best(cd, od, l5, bgd, fwd)]
-            rb, rp, rs, rn, _ = U.oracle_lpm_best(codes, offsets, lpm5, bg, fwd)
+            best, pos, strand, nties, ties = [t.cpu().numpy() for t in ops.lpm_scan_best(cd, od, l5, bgd, fwd)]
+            rb, rp, rs, rn, rt = U.oracle_lpm_best(codes, offsets, lpm5, bg, fwd)
             assert np.array_equal(best, rb) and np.array_equal(pos, rp)          # each window product is bit-exact
             assert np.array_equal(strand, rs) and np.array_equal(nties, rn)
+            for r_ in range(len(nties)):                 # the listed ties (the oracle keeps stale entries past n_ties)
+                m_ = min(int(nties[r_]), ties.shape[1], np.asarray(rt).shape[1])
+                assert np.array_equal(ties[r_, :m_], np.asarray(rt)[r_, :m_]) and (ties[r_, m_:] == -1).all()
             ip = np.round(100 * np.log2(lpm / 0.25)).astype(np.int32)
             p5 = np.ascontiguousarray(np.vstack([ip, np.full((1, w), -2 ** 31)]).astype(np.int32))
             b, p, st = [t.cpu().numpy() for t in ops.ipwm_scan_best(cd, od, torch.tensor(p5, device=DEV), fwd)]
