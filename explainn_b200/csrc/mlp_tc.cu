@@ -118,13 +118,38 @@ struct MtShared {
 };
 
 // ---------------------------------------------------------------------------
-// FC1 tile on tcgen05 + fused epilogue.  One CTA per SM walks a contiguous range of the flattened
-// (unit, batch tile) space, so W1 of a unit is staged once per CTA (at most ~3 units per CTA).
-// 512 threads = 16 warps: warp w owns TMEM lanes 32*(w%4).. and the column group cg = w/4 (a quarter of
-// the accumulator columns); the same (row, cg) pair stages a quarter of row `row` of the operand tiles.
-// The next tile's pool rows are prefetched into registers while the tensor core works on this one.
+// FC1 tile on tcgen05 + fused epilogue, warp-specialised.  One CTA per SM walks a contiguous range of the
+// flattened (unit, batch tile) space, so W1 of a unit is staged once per CTA (at most ~3 units per CTA).
+// Measured on the lock-step version (every warp staging, then waiting, then in the epilogue): global loads
+// 0.10 ms + staging stores 0.055 + MMAs 0.065 + epilogue 0.04 (statistics) .. 0.155 (apply) + loop 0.07 were
+// ADDITIVE.  Here three roles run on different tiles at the same time:
+//   warps 0-7   producers: prefetch tile t+1 of `pool` into registers, split it (three bf16 pieces, kind::f16
+//               with the six significant products = fp32-level accuracy at 6 instead of 8 bytes per element)
+//               into pool stage t%2 as soon as the MMAs of tile t-2 released it, restage W1 at a unit
+//               boundary (W1 is kept in a 104-row layout, 60 KB, so that two 74 KB pool stages fit); in the
+//               backward-statistics pass also dopre and the active bits of the tile (four-deep ring)
+//   warp  16    issuer: waits for "staged" and for the accumulator stage, issues the tile's MMAs
+//   warps 8-15  epilogue of tile t out of TMEM stage t%2 while tile t+1 is staged and multiplied:
+//               warp e owns TMEM lanes 32*(e%4).. and the column half e/4
+// mbarriers: staged[2] (8 producer warps -> issuer), mma_done[2] (tcgen05.commit -> epilogue + producers),
+// acc_free[2] (8 epilogue warps -> issuer).
 // ---------------------------------------------------------------------------
 #define MT_CMAX 24   // staging chunks (of 4 floats) per row: MT_NMAX / 4
+#define WS_P_WARPS 8
+#define WS_E_WARPS 8
+#define WS_THREADS (32 * (WS_P_WARPS + WS_E_WARPS + 1))
+
+struct WsShared {
+    uint64_t staged[2];
+    uint64_t mma_done[2];
+    uint64_t acc_free[2];
+    uint32_t tmem_slot;
+    uint32_t pad;
+};
+
+__device__ __forceinline__ void ws_epi_barrier() {
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * WS_E_WARPS) : "memory");
+}
 
 // keep-bit word `w` (hidden channels 32w .. 32w+31) of one (sequence, unit) row
 __device__ __forceinline__ uint32_t dropout_keep_word(float p, unsigned long long seed, long long bu,
@@ -158,9 +183,331 @@ __device__ __forceinline__ uint32_t dropout_keep_word(float p, unsigned long lon
     return kb;
 }
 
+// two floats -> one packed bf16 pair per piece (hi, mid, lo): x = hi + mid + lo to 2^-24 |x|
+__device__ __forceinline__ void split2_bf16x3(float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
+    uint32_t h[2], m[2], l[2];
+    const float xs[2] = {x0, x1};
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+        const __nv_bfloat16 aa = __float2bfloat16_rn(xs[e]);
+        const float r1 = xs[e] - __bfloat162float(aa);
+        const __nv_bfloat16 bb = __float2bfloat16_rn(r1);
+        const __nv_bfloat16 cc = __float2bfloat16_rn(r1 - __bfloat162float(bb));
+        h[e] = __bfloat16_as_ushort(aa); m[e] = __bfloat16_as_ushort(bb); l[e] = __bfloat16_as_ushort(cc);
+    }
+    w0 = h[0] | (h[1] << 16); w1 = m[0] | (m[1] << 16); w2 = l[0] | (l[1] << 16);
+}
+
+#define WS_WROWS 104   // rows of the W1 operand layout (100 hidden channels, padded to a multiple of 8)
+#define WS_QMAX 6      // 16-byte chunks per producer lane: 2 columns of each of <= 12 chunks -> pv[2][12][2]
+
+template <int MODE>
+__global__ void __launch_bounds__(WS_THREADS, 1)
+mlp_fc1_kernel(MlpArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;       // K in 16-byte chunks of 8 bf16
+    const uint32_t wlbo = WS_WROWS * 16u;                                     // W1: [piece][chunk][104 rows] uint4
+    const uint32_t wpiece = (uint32_t)chunksQ * wlbo;
+    const uint32_t ppiece = (uint32_t)chunksQ * 2048u;                        // pool: [stage][piece][chunk][128 rows] uint4
+    const uint32_t pstage = 3u * ppiece;
+    uint4* w1s = reinterpret_cast<uint4*>(smem_raw);
+    uint4* ps = reinterpret_cast<uint4*>(smem_raw + 3 * wpiece);
+    unsigned char* tail = smem_raw + 3 * wpiece + 2 * pstage;
+    float4* s_c4 = reinterpret_cast<float4*>(tail);                  // [128] (b1, scale2, shift2, w2) per channel
+    float* s_dopre_all = reinterpret_cast<float*>(tail + 2048);      // [4][128]
+    uint32_t* s_mask_all = reinterpret_cast<uint32_t*>(tail + 2048 + 2048);   // [4][128][4]
+    float* s_acc = reinterpret_cast<float*>(tail + 2048 + 2048 + 8192);       // [2][2][128]
+    WsShared* sh = reinterpret_cast<WsShared*>(tail + 2048 + 2048 + 8192 + 2048);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 2048 + 2048 + 8192 + 2048 + 64);   // [6 * kstepsQ] descriptor words
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw);
+        for (uint32_t i = tid; i < (3 * wpiece + 2 * pstage) / 16; i += WS_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 256);            // two accumulator stages of 128 columns
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            umma::mbar_init(&sh->staged[s], WS_P_WARPS);
+            umma::mbar_init(&sh->mma_done[s], 1);
+            umma::mbar_init(&sh->acc_free[s], WS_E_WARPS);
+        }
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t w_addr = umma::smem_u32(w1s), p_addr = umma::smem_u32(ps);
+    // F1 / B1: D[hidden][batch] (A = W1, N = 128 batch rows); F2: D[batch][hidden] (A = pool tile, N = 112)
+    constexpr int NDIM = (MODE == MLP_APPLY) ? 112 : 128;
+    const uint32_t idesc = umma::idesc_bf16_f32(128, NDIM);
+    // MMA sequence of a tile: the six significant products of the 3-way split, smallest first
+    // (piece of W1, piece of pool): lo*hi, hi*lo, mid*mid, mid*hi, hi*mid, hi*hi   (0 = hi, 1 = mid, 2 = lo)
+    if (tid < 6 * kstepsQ) {
+        const int pass = tid / kstepsQ, ks = tid - pass * kstepsQ;
+        const uint32_t pw = pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u;
+        const uint32_t pp = pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u;
+        const uint32_t wd = umma::desc_lo(w_addr + pw * wpiece + (uint32_t)(2 * ks) * wlbo, wlbo);
+        const uint32_t pd2 = umma::desc_lo(p_addr + pp * ppiece + (uint32_t)(2 * ks) * 2048u, 2048u);
+        s_tab[tid] = (MODE == MLP_APPLY) ? make_uint2(pd2, wd) : make_uint2(wd, pd2);   // (A, B)
+    }
+    __syncthreads();
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const int ntl = (int)(hi - lo);
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+
+    if (warp < WS_P_WARPS) {
+        // ================= producers =================
+        // staging map (coalesced): lane = (row & 7) * 4 + word, word = two consecutive pool columns of a 16-byte
+        // (8 x bf16) chunk: one warp-wide access covers 8 rows x 32 B of global memory and 32 distinct banks;
+        // warp p stages rows 8p.. and 64+8p.., all chunks
+        const int swd = lane & 3;
+        const int srow0 = warp * 8 + (lane >> 2);
+        float pv[2][12][2];
+        float pd = 0.0f;
+        uint4 pm = make_uint4(0u, 0u, 0u, 0u);
+        auto prefetch = [&](int i) {
+            const bool live = i < ntl;
+            const long long tile = lo + i;
+            const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
+            const int b0 = t * MT_ROWS;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int srow = srow0 + 64 * h;
+                const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
+#pragma unroll
+                for (int c = 0; c < 12; ++c) {
+                    const int q = 8 * c + 2 * swd;
+                    pv[h][c][0] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
+                    pv[h][c][1] = (src != nullptr && q + 1 < n) ? __ldg(src + q + 1) : 0.0f;
+                }
+            }
+            if (MODE == MLP_BWD_STATS && tid < MT_ROWS) {
+                const bool ok = live && b0 + tid < B;
+                const long long bu = (long long)(b0 + tid) * U + u;
+                pd = ok ? __ldg(a.dopre + bu) : 0.0f;
+                pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
+            }
+            // L2 prefetch of the tile after the next two: the register prefetch above runs one tile ahead, far
+            // less than the HBM latency under load; thread (row, half) touches the row's 128-byte lines
+            if (i + 2 < ntl) {
+                const long long tile2 = lo + i + 2;
+                const int u2 = (int)(tile2 / T), r2 = (int)(tile2 % T) * MT_ROWS + (tid & 127);
+                if (r2 < B) {
+                    const char* p2 = reinterpret_cast<const char*>(a.pool + ((long long)r2 * U + u2) * n);
+                    const int o0 = (tid >> 7) ? 256 : 0, o1 = (tid >> 7) ? 4 * n - 1 : 128;
+                    if (o0 < 4 * n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p2 + o0));
+                    if (o1 < 4 * n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p2 + o1));
+                }
+            }
+        };
+        int cur_u = -1;
+        prefetch(0);
+        for (int i = 0; i < ntl; ++i) {
+            const int u = (int)((lo + i) / T);
+            const uint32_t st = (uint32_t)i & 1u;
+            if (i >= 2) umma::mbar_wait(&sh->mma_done[st], (uint32_t)((i >> 1) - 1) & 1u);   // pool stage free
+            if (u != cur_u) {
+                cur_u = u;
+                // every MMA reads W1: wait for the previous tile's too, then restage (rows >= 100 are never read
+                // into a used accumulator lane / column)
+                if (i >= 1) umma::mbar_wait(&sh->mma_done[st ^ 1u], (uint32_t)((i - 1) >> 1) & 1u);
+                uint32_t* ww = reinterpret_cast<uint32_t*>(w1s);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int srow = srow0 + 64 * h;
+                    if (srow < MT_H) {
+                        const float* src = a.w1 + ((long long)u * MT_H + srow) * n;
+                        for (int c = 0; c < chunksQ; ++c) {
+                            const int q = 8 * c + 2 * swd;
+                            uint32_t w0, w1v, w2v;
+                            split2_bf16x3(q < n ? __ldg(src + q) : 0.0f, q + 1 < n ? __ldg(src + q + 1) : 0.0f, w0, w1v, w2v);
+                            const int o = (c * WS_WROWS + srow) * 4 + swd;
+                            ww[o] = w0; ww[wpiece / 4 + o] = w1v; ww[2 * (wpiece / 4) + o] = w2v;
+                        }
+                    }
+                }
+            }
+            uint32_t* pw = reinterpret_cast<uint32_t*>(ps) + st * (pstage / 4);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int srow = srow0 + 64 * h;
+#pragma unroll
+                for (int c = 0; c < 12; ++c) {
+                    if (c < chunksQ) {
+                        uint32_t w0, w1v, w2v;
+                        split2_bf16x3(pv[h][c][0], pv[h][c][1], w0, w1v, w2v);
+                        const int o = (c * 128 + srow) * 4 + swd;
+                        pw[o] = w0; pw[ppiece / 4 + o] = w1v; pw[2 * (ppiece / 4) + o] = w2v;
+                    }
+                }
+            }
+            if (MODE == MLP_BWD_STATS && tid < MT_ROWS) {
+                s_dopre_all[(i & 3) * 128 + tid] = pd;
+                *reinterpret_cast<uint4*>(s_mask_all + (i & 3) * 512 + 4 * tid) = pm;
+            }
+            umma::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->staged[st]);
+            prefetch(i + 1);                    // global loads of the next tile fly under the MMAs
+        }
+    } else if (warp == WS_P_WARPS + WS_E_WARPS) {
+        // ================= issuer =================
+        for (int i = 0; i < ntl; ++i) {
+            const uint32_t st = (uint32_t)i & 1u;
+            umma::mbar_wait(&sh->staged[st], ((uint32_t)i >> 1) & 1u);
+            umma::mbar_wait(&sh->acc_free[st], (((uint32_t)i >> 1) & 1u) ^ 1u);
+            umma::fence_after_sync();
+            if (lane == 0) {
+                const uint32_t poff = st * (pstage >> 4);            // pool stage, in descriptor units
+                umma::issue_table2(s_tab, 6 * kstepsQ, umma::desc_hi(128u), umma::desc_hi(128u),
+                                   MODE == MLP_APPLY ? poff : 0u, MODE == MLP_APPLY ? 0u : poff, tmem + st * 128u, idesc);
+                umma::commit(&sh->mma_done[st]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ================= epilogue =================
+        const int e = warp - WS_P_WARPS;
+        const int quarter = e & 3, cg = e >> 2;      // TMEM lane quarter (= warp % 4) and column half
+        const int row = quarter * 32 + lane;
+        int cur_u = -1;
+        float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f;   // per-channel constants (thread = channel modes)
+        double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+        auto flush = [&](int u) {
+            if (MODE == MLP_APPLY) return;
+            int j = blockIdx.x;
+            const long long start = (long long)u * T;
+            while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+            const int slot = (blockIdx.x - j) * 4 + cg;
+            if (row < MT_H && slot < a.slots) {
+                const int c = u * MT_H + row;
+                constexpr int NS = (MODE == MLP_STATS) ? 2 : 4;
+                double* o = a.part + (long long)slot * NS * C + c;
+                o[0] = s1; o[(long long)C] = s2;
+                if (MODE == MLP_BWD_STATS) { o[2LL * C] = s3; o[3LL * C] = s4; }
+            }
+            s1 = s2 = s3 = s4 = 0.0;
+        };
+        for (int i = 0; i < ntl; ++i) {
+            const long long tile = lo + i;
+            const int u = (int)(tile / T), t = (int)(tile % T);
+            const int b0 = t * MT_ROWS, rows = min(MT_ROWS, B - b0);
+            const uint32_t st = (uint32_t)i & 1u;
+            if (u != cur_u) {
+                if (cur_u >= 0) flush(cur_u);
+                cur_u = u;
+                const int ch = u * MT_H + row;
+                const bool ok = row < MT_H;
+                b1m = ok ? a.b1[ch] : 0.f;
+                if (MODE != MLP_STATS) { scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f; w2m = ok ? a.w2[ch] : 0.f; }
+                if (MODE == MLP_APPLY) {
+                    ws_epi_barrier();           // every epilogue warp is done with the previous unit's constants
+                    if (cg == 0) s_c4[row] = make_float4(b1m, scm, shm, w2m);
+                    ws_epi_barrier();
+                }
+            }
+            umma::mbar_wait(&sh->mma_done[st], ((uint32_t)i >> 1) & 1u);
+            umma::fence_after_sync();
+            const uint32_t trow = tmem + st * 128u + ((uint32_t)(quarter * 32) << 16);
+            if (MODE == MLP_STATS || MODE == MLP_BWD_STATS) {
+                // thread = (hidden channel, half of the tile's batch rows)
+                const float* s_dopre = s_dopre_all + (i & 3) * 128;
+                const uint32_t* s_mask = s_mask_all + (i & 3) * 512;
+#pragma unroll
+                for (int hh = 0; hh < 4; ++hh) {
+                    const int c0 = 64 * cg + 16 * hh;
+                    if (c0 < rows) {
+                        uint32_t v[16];
+                        umma::tmem_ld16(trow + c0, v);
+                        umma::tmem_ld_wait();
+#pragma unroll
+                        for (int k2 = 0; k2 < 16; ++k2) {
+                            if (c0 + k2 < rows) {
+                                const float x = __uint_as_float(v[k2]) + b1m;
+                                if (MODE == MLP_STATS) {
+                                    s1 += (double)x;
+                                    s2 += (double)x * (double)x;
+                                } else {
+                                    const float pre = fmaf(x, scm, shm);
+                                    const uint32_t act = (s_mask[4 * (c0 + k2) + (row >> 5)] >> (row & 31)) & 1u;
+                                    const float d = s_dopre[c0 + k2];
+                                    const float hact = act ? pre * inv_keep : 0.0f;
+                                    const float g2 = act ? d * w2m * inv_keep : 0.0f;
+                                    s1 += (double)g2;
+                                    s2 += (double)g2 * (double)x;
+                                    s3 += (double)d * (double)hact;
+                                    s4 += (double)d;
+                                }
+                            }
+                        }
+                    }
+                }
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_free[st]);
+            } else {
+                // thread = (batch row, 64 hidden channels = keep-bit words 2cg, 2cg+1)
+                const long long bu = (long long)(b0 + row) * U + u;
+                uint32_t kbw[2], actw[2] = {0u, 0u};
+                kbw[0] = (row < rows) ? dropout_keep_word(a.drop_p, a.seed, bu, a.mask_u8, 2 * cg) : 0u;
+                kbw[1] = (row < rows) ? dropout_keep_word(a.drop_p, a.seed, bu, a.mask_u8, 2 * cg + 1) : 0u;
+                float accv = 0.0f;
+#pragma unroll
+                for (int hh = 0; hh < 4; ++hh) {
+                    const int c0 = 64 * cg + 16 * hh;
+                    if (c0 < 112) {
+                        uint32_t v[16];
+                        umma::tmem_ld16(trow + c0, v);
+                        umma::tmem_ld_wait();
+#pragma unroll
+                        for (int k2 = 0; k2 < 16; ++k2) {
+                            const int m = c0 + k2;
+                            if (m < MT_H) {
+                                const float4 c4 = s_c4[m];
+                                const float pre = fmaf(__uint_as_float(v[k2]) + c4.x, c4.y, c4.z);
+                                const int bit = 16 * (hh & 1) + k2;
+                                const uint32_t act = ((kbw[hh >> 1] >> bit) & 1u) & (pre > 0.0f ? 1u : 0u);
+                                actw[hh >> 1] |= act << bit;   // keep AND (BN2 output > 0): the backward reuses THIS decision
+                                const float h = act ? pre * inv_keep : 0.0f;
+                                accv = fmaf(h, c4.w, accv);
+                            }
+                        }
+                    }
+                }
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_free[st]);
+                float* acc2 = s_acc + st * 256;              // [tile parity][column half][row]
+                acc2[cg * 128 + row] = accv;
+                if (row < rows && a.maskbits)
+                    *reinterpret_cast<uint2*>(a.maskbits + bu * 4 + 2 * cg) = make_uint2(actw[0], actw[1]);
+                ws_epi_barrier();
+                if (cg == 0 && row < rows) a.opre[bu] = (acc2[row] + acc2[128 + row]) + a.b2[u];
+            }
+        }
+        if (cur_u >= 0) flush(cur_u);
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+}
+
+
+// ---------------------------------------------------------------------------
+// The lock-step version of the same tile loop (512 threads: every warp stages, waits for the MMAs, then runs
+// the epilogue; kind::tf32 hi/lo split).  Kept for the backward-statistics pass, whose fp64-heavy epilogue is
+// faster on 16 epilogue warps than on the 8 of the warp-specialised kernel (0.43 vs 0.58 ms at cfg3 B=4096).
+// ---------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(MT_THREADS, 1)
-mlp_fc1_kernel(MlpArgs a) {
+mlp_fc1_lockstep_kernel(MlpArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int n = a.n, U = a.U, B = a.B, T = a.T;
     const int Kp = (n + 7) & ~7, chunks = Kp >> 2, ksteps = Kp >> 3;
@@ -407,16 +754,28 @@ static int mt_slots(int B, int U) {
     return 4 * ((int)((T + per - 1) / per) + 1);    // x4: one partial per column group of the CTA
 }
 static size_t mt_smem(int n) {
+    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
+    return 3 * chunksQ * WS_WROWS * 16 + 2 * 3 * chunksQ * 2048 + 2048 + 2048 + 8192 + 2048 + 64 + 6 * 6 * 8 + 16;
+}
+
+static size_t mt_smem_lockstep(int n) {
     const int chunks = ((n + 7) & ~7) >> 2;
     return (size_t)4 * chunks * 2048 + 2048 + 512 + 2048 + 2048 + 32 + 3 * 12 * 8 + 16;
 }
 
 template <int MODE>
 static int mt_launch(const MlpArgs& a, cudaStream_t st) {
+    if (MODE == MLP_BWD_STATS) {
+        const size_t smem = mt_smem_lockstep(a.n);
+        if (cudaFuncSetAttribute(mlp_fc1_lockstep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return 1;
+        mlp_fc1_lockstep_kernel<MODE><<<mt_grid(a.B, a.U), MT_THREADS, smem, st>>>(a);
+        return cudaGetLastError() != cudaSuccess;
+    }
     const size_t smem = mt_smem(a.n);
     if (cudaFuncSetAttribute(mlp_fc1_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return 1;
-    mlp_fc1_kernel<MODE><<<mt_grid(a.B, a.U), MT_THREADS, smem, st>>>(a);
+    mlp_fc1_kernel<MODE><<<mt_grid(a.B, a.U), WS_THREADS, smem, st>>>(a);
     return cudaGetLastError() != cudaSuccess;
 }
 

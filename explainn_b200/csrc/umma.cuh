@@ -130,6 +130,24 @@ __device__ __forceinline__ void issue_table(const uint2* __restrict__ tab, int c
     }
 }
 
+// kind::f16 variant with a per-tile offset for BOTH operands (double-buffered operand stages)
+__device__ __forceinline__ void issue_table2(const uint2* __restrict__ tab, int count, uint32_t hi_a, uint32_t hi_b,
+                                             uint32_t add_a, uint32_t add_b, uint32_t d_tmem, uint32_t idesc) {
+    for (int i0 = 0; i0 < count; i0 += 6) {
+        uint2 e[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) e[j] = tab[min(i0 + j, count - 1)];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            if (i0 + j < count) {
+                const uint64_t ad = ((uint64_t)hi_a << 32) | (uint64_t)(e[j].x + add_a);
+                const uint64_t bd = ((uint64_t)hi_b << 32) | (uint64_t)(e[j].y + add_b);
+                mma_bf16(d_tmem, ad, bd, idesc, (i0 + j == 0) ? 0u : 1u);
+            }
+        }
+    }
+}
+
 // arrive on an mbarrier when every previously issued tcgen05.mma of this thread has completed
 __device__ __forceinline__ void commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
