@@ -123,21 +123,20 @@ struct MtShared {
 // Measured on the lock-step version (every warp staging, then waiting, then in the epilogue): global loads
 // 0.10 ms + staging stores 0.055 + MMAs 0.065 + epilogue 0.04 (statistics) .. 0.155 (apply) + loop 0.07 were
 // ADDITIVE.  Here three roles run on different tiles at the same time:
-//   warps 0-7   producers: prefetch tile t+1 of `pool` into registers, split it (three bf16 pieces, kind::f16
+//   warps 0-15  producers: prefetch tile t+1 of `pool` into registers, split it (three bf16 pieces, kind::f16
 //               with the six significant products = fp32-level accuracy at 6 instead of 8 bytes per element)
 //               into pool stage t%2 as soon as the MMAs of tile t-2 released it, restage W1 at a unit
 //               boundary (W1 is kept in a 104-row layout, 60 KB, so that two 74 KB pool stages fit); in the
 //               backward-statistics pass also dopre and the active bits of the tile (four-deep ring)
-//   warp  16    issuer: waits for "staged" and for the accumulator stage, issues the tile's MMAs
-//   warps 8-15  epilogue of tile t out of TMEM stage t%2 while tile t+1 is staged and multiplied:
+//   warp  24    issuer: waits for "staged" and for the accumulator stage, issues the tile's MMAs
+//   warps 16-23 epilogue of tile t out of TMEM stage t%2 while tile t+1 is staged and multiplied:
 //               warp e owns TMEM lanes 32*(e%4).. and the column half e/4
-// mbarriers: staged[2] (8 producer warps -> issuer), mma_done[2] (tcgen05.commit -> epilogue + producers),
+// mbarriers: staged[2] (16 producer warps -> issuer), mma_done[2] (tcgen05.commit -> epilogue + producers),
 // acc_free[2] (8 epilogue warps -> issuer).
 // ---------------------------------------------------------------------------
 #define MT_CMAX 24   // staging chunks (of 4 floats) per row: MT_NMAX / 4
-#define WS_P_WARPS 8
+#define WS_P_MAX 16     // producer warps: 16 for the statistics pass (one row each), 8 for apply (two rows each)
 #define WS_E_WARPS 8
-#define WS_THREADS (32 * (WS_P_WARPS + WS_E_WARPS + 1))
 
 struct WsShared {
     uint64_t staged[2];
@@ -183,27 +182,27 @@ __device__ __forceinline__ uint32_t dropout_keep_word(float p, unsigned long lon
     return kb;
 }
 
-// two floats -> one packed bf16 pair per piece (hi, mid, lo): x = hi + mid + lo to 2^-24 |x|
+// two floats -> one packed bf16 pair per piece (hi, mid, lo).  Each piece is the TRUNCATED upper half of the
+// running remainder (a mask and an exact subtraction instead of three round-to-nearest conversions):
+// x = hi + mid + lo + e with |e| < 2^-23 |x|, every piece exactly representable in bf16.
 __device__ __forceinline__ void split2_bf16x3(float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
-    uint32_t h[2], m[2], l[2];
-    const float xs[2] = {x0, x1};
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-        const __nv_bfloat16 aa = __float2bfloat16_rn(xs[e]);
-        const float r1 = xs[e] - __bfloat162float(aa);
-        const __nv_bfloat16 bb = __float2bfloat16_rn(r1);
-        const __nv_bfloat16 cc = __float2bfloat16_rn(r1 - __bfloat162float(bb));
-        h[e] = __bfloat16_as_ushort(aa); m[e] = __bfloat16_as_ushort(bb); l[e] = __bfloat16_as_ushort(cc);
-    }
-    w0 = h[0] | (h[1] << 16); w1 = m[0] | (m[1] << 16); w2 = l[0] | (l[1] << 16);
+    const uint32_t h0 = __float_as_uint(x0) & 0xFFFF0000u, h1 = __float_as_uint(x1) & 0xFFFF0000u;
+    const float r0 = x0 - __uint_as_float(h0), r1 = x1 - __uint_as_float(h1);
+    const uint32_t m0 = __float_as_uint(r0) & 0xFFFF0000u, m1 = __float_as_uint(r1) & 0xFFFF0000u;
+    const float q0 = r0 - __uint_as_float(m0), q1 = r1 - __uint_as_float(m1);
+    w0 = __byte_perm(h0, h1, 0x7632);                       // (upper half of x0) | (upper half of x1) << 16
+    w1 = __byte_perm(m0, m1, 0x7632);
+    w2 = __byte_perm(__float_as_uint(q0), __float_as_uint(q1), 0x7632);
 }
 
 #define WS_WROWS 104   // rows of the W1 operand layout (100 hidden channels, padded to a multiple of 8)
 #define WS_QMAX 6      // 16-byte chunks per producer lane: 2 columns of each of <= 12 chunks -> pv[2][12][2]
 
-template <int MODE>
-__global__ void __launch_bounds__(WS_THREADS, 1)
+template <int MODE, int WS_P_WARPS>
+__global__ void __launch_bounds__(32 * (WS_P_WARPS + WS_E_WARPS + 1), 1)
 mlp_fc1_kernel(MlpArgs a) {
+    constexpr int WS_THREADS = 32 * (WS_P_WARPS + WS_E_WARPS + 1);
+    constexpr int HS = 16 / WS_P_WARPS;          // rows of the tile per producer thread
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int n = a.n, U = a.U, B = a.B, T = a.T;
     const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;       // K in 16-byte chunks of 8 bf16
@@ -266,10 +265,10 @@ mlp_fc1_kernel(MlpArgs a) {
         // ================= producers =================
         // staging map (coalesced): lane = (row & 7) * 4 + word, word = two consecutive pool columns of a 16-byte
         // (8 x bf16) chunk: one warp-wide access covers 8 rows x 32 B of global memory and 32 distinct banks;
-        // warp p stages rows 8p.. and 64+8p.., all chunks
+        // warp p stages rows 8p .. 8p+7 (and 64+8p .. with 8 producer warps), all chunks
         const int swd = lane & 3;
         const int srow0 = warp * 8 + (lane >> 2);
-        float pv[2][12][2];
+        float pv[HS][12][2];
         float pd = 0.0f;
         uint4 pm = make_uint4(0u, 0u, 0u, 0u);
         auto prefetch = [&](int i) {
@@ -278,8 +277,8 @@ mlp_fc1_kernel(MlpArgs a) {
             const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
             const int b0 = t * MT_ROWS;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int srow = srow0 + 64 * h;
+            for (int h = 0; h < HS; ++h) {
+                const int srow = srow0 + 8 * WS_P_WARPS * h;
                 const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
 #pragma unroll
                 for (int c = 0; c < 12; ++c) {
@@ -294,16 +293,16 @@ mlp_fc1_kernel(MlpArgs a) {
                 pd = ok ? __ldg(a.dopre + bu) : 0.0f;
                 pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
             }
-            // L2 prefetch of the tile after the next two: the register prefetch above runs one tile ahead, far
-            // less than the HBM latency under load; thread (row, half) touches the row's 128-byte lines
+            // L2 prefetch of the tile after the next two: the register prefetch above runs one tile ahead;
+            // thread (row, part) touches one 128-byte line of the row
             if (i + 2 < ntl) {
                 const long long tile2 = lo + i + 2;
                 const int u2 = (int)(tile2 / T), r2 = (int)(tile2 % T) * MT_ROWS + (tid & 127);
-                if (r2 < B) {
-                    const char* p2 = reinterpret_cast<const char*>(a.pool + ((long long)r2 * U + u2) * n);
-                    const int o0 = (tid >> 7) ? 256 : 0, o1 = (tid >> 7) ? 4 * n - 1 : 128;
-                    if (o0 < 4 * n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p2 + o0));
-                    if (o1 < 4 * n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p2 + o1));
+                const char* p2 = reinterpret_cast<const char*>(a.pool + ((long long)r2 * U + u2) * n);
+#pragma unroll
+                for (int part = tid >> 7; part < 4; part += WS_P_WARPS / 4) {
+                    const int off = part < 3 ? 128 * part : 4 * n - 1;
+                    if (r2 < B && off < 4 * n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p2 + off));
                 }
             }
         };
@@ -320,8 +319,8 @@ mlp_fc1_kernel(MlpArgs a) {
                 if (i >= 1) umma::mbar_wait(&sh->mma_done[st ^ 1u], (uint32_t)((i - 1) >> 1) & 1u);
                 uint32_t* ww = reinterpret_cast<uint32_t*>(w1s);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int srow = srow0 + 64 * h;
+                for (int h = 0; h < HS; ++h) {
+                    const int srow = srow0 + 8 * WS_P_WARPS * h;
                     if (srow < MT_H) {
                         const float* src = a.w1 + ((long long)u * MT_H + srow) * n;
                         for (int c = 0; c < chunksQ; ++c) {
@@ -336,8 +335,8 @@ mlp_fc1_kernel(MlpArgs a) {
             }
             uint32_t* pw = reinterpret_cast<uint32_t*>(ps) + st * (pstage / 4);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int srow = srow0 + 64 * h;
+            for (int h = 0; h < HS; ++h) {
+                const int srow = srow0 + 8 * WS_P_WARPS * h;
 #pragma unroll
                 for (int c = 0; c < 12; ++c) {
                     if (c < chunksQ) {
@@ -773,9 +772,10 @@ static int mt_launch(const MlpArgs& a, cudaStream_t st) {
         return cudaGetLastError() != cudaSuccess;
     }
     const size_t smem = mt_smem(a.n);
-    if (cudaFuncSetAttribute(mlp_fc1_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    constexpr int PW = (MODE == MLP_APPLY) ? 8 : 16;       // measured: apply 0.34 (8) vs 0.39 ms (16); statistics 0.288 vs 0.278
+    if (cudaFuncSetAttribute(mlp_fc1_kernel<MODE, PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return 1;
-    mlp_fc1_kernel<MODE><<<mt_grid(a.B, a.U), WS_THREADS, smem, st>>>(a);
+    mlp_fc1_kernel<MODE, PW><<<mt_grid(a.B, a.U), 32 * (PW + WS_E_WARPS + 1), smem, st>>>(a);
     return cudaGetLastError() != cudaSuccess;
 }
 
