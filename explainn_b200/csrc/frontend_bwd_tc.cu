@@ -282,10 +282,15 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
 #pragma unroll
             for (int rg = 0; rg < BT_RGS; ++rg) {
                 const float dv = (q_ok && row[rg] < nu) ? cur.d[rg] : 0.0f;
-                const __nv_bfloat16 hi = __float2bfloat16_rn(dv);
-                const float r1 = dv - __bfloat162float(hi);
-                const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
-                const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+                // truncating 3-way split: every piece is the upper half of the running remainder (a mask and an
+                // exact subtraction instead of round-to-nearest conversions); dv = hi + mid + lo to 2^-23 |dv|
+                const uint32_t hb = __float_as_uint(dv) & 0xFFFF0000u;
+                const float r1 = dv - __uint_as_float(hb);
+                const uint32_t mb = __float_as_uint(r1) & 0xFFFF0000u;
+                const uint32_t lb = __float_as_uint(r1 - __uint_as_float(mb));
+                const __nv_bfloat16 hi = __ushort_as_bfloat16((unsigned short)(hb >> 16));
+                const __nv_bfloat16 mid = __ushort_as_bfloat16((unsigned short)(mb >> 16));
+                const __nv_bfloat16 lo = __ushort_as_bfloat16((unsigned short)(lb >> 16));
                 unsigned char* e = st + soff[rg];
                 // zero the window's 16-byte chunk of each piece, then drop the value at slot arg (same thread,
                 // program order); piece order lo, mid, hi: the small pieces enter the fp32 accumulator first

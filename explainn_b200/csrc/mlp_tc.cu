@@ -872,23 +872,11 @@ struct MlpBwdArgs {
     float drop_p;
 };
 
-// 8 floats -> three uint4 of packed bf16 pieces (hi, mid, lo)
+// 8 floats -> three uint4 of packed bf16 pieces (hi, mid, lo), truncating split (split2_bf16x3)
 __device__ __forceinline__ void split8_bf16x3(const float* v, uint4& p0, uint4& p1, uint4& p2) {
     uint32_t w0[4], w1[4], w2[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        uint32_t h[2], m[2], l[2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const float x = v[2 * i + e];
-            const __nv_bfloat16 a = __float2bfloat16_rn(x);
-            const float r1 = x - __bfloat162float(a);
-            const __nv_bfloat16 b = __float2bfloat16_rn(r1);
-            const __nv_bfloat16 c = __float2bfloat16_rn(r1 - __bfloat162float(b));
-            h[e] = __bfloat16_as_ushort(a); m[e] = __bfloat16_as_ushort(b); l[e] = __bfloat16_as_ushort(c);
-        }
-        w0[i] = h[0] | (h[1] << 16); w1[i] = m[0] | (m[1] << 16); w2[i] = l[0] | (l[1] << 16);
-    }
+    for (int i = 0; i < 4; ++i) split2_bf16x3(v[2 * i], v[2 * i + 1], w0[i], w1[i], w2[i]);
     p0 = make_uint4(w0[0], w0[1], w0[2], w0[3]);
     p1 = make_uint4(w1[0], w1[1], w1[2], w1[3]);
     p2 = make_uint4(w2[0], w2[1], w2[2], w2[3]);
@@ -1019,19 +1007,7 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
         }
     };
-    auto split2 = [](float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
-        uint32_t h[2], m[2], l[2];
-        const float xs[2] = {x0, x1};
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const __nv_bfloat16 aa = __float2bfloat16_rn(xs[e]);
-            const float r1 = xs[e] - __bfloat162float(aa);
-            const __nv_bfloat16 bb = __float2bfloat16_rn(r1);
-            const __nv_bfloat16 cc = __float2bfloat16_rn(r1 - __bfloat162float(bb));
-            h[e] = __bfloat16_as_ushort(aa); m[e] = __bfloat16_as_ushort(bb); l[e] = __bfloat16_as_ushort(cc);
-        }
-        w0 = h[0] | (h[1] << 16); w1 = m[0] | (m[1] << 16); w2 = l[0] | (l[1] << 16);
-    };
+    auto split2 = [](float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) { split2_bf16x3(x0, x1, w0, w1, w2); };
     auto store_tile = [&]() {
         uint32_t* pw = reinterpret_cast<uint32_t*>(ps);
 #pragma unroll
