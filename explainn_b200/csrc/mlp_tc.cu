@@ -669,6 +669,9 @@ mlp_fc1_lockstep_kernel(MlpArgs a) {
                     uint32_t v[16];
                     umma::tmem_ld16(trow + c0, v);
                     umma::tmem_ld_wait();
+                    // backward reductions: fp32 partial sums over the 16 columns, folded into the fp64 running sums
+                    // once per chunk (these sums have no large cancelling terms, unlike E[x^2] - mean^2)
+                    float f1 = 0.0f, f2 = 0.0f, f3 = 0.0f, f4 = 0.0f;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
                         if (c0 + i < rows) {
@@ -682,13 +685,14 @@ mlp_fc1_lockstep_kernel(MlpArgs a) {
                                 const float d = s_dopre[c0 + i];
                                 const float hact = act ? pre * inv_keep : 0.0f;
                                 const float g2 = act ? d * w2m * inv_keep : 0.0f;
-                                s1 += (double)g2;
-                                s2 += (double)g2 * (double)x;
-                                s3 += (double)d * (double)hact;
-                                s4 += (double)d;
+                                f1 += g2;
+                                f2 = fmaf(g2, x, f2);
+                                f3 = fmaf(d, hact, f3);
+                                f4 += d;
                             }
                         }
                     }
+                    if (MODE == MLP_BWD_STATS) { s1 += (double)f1; s2 += (double)f2; s3 += (double)f3; s4 += (double)f4; }
                 }
             }
         } else {
