@@ -426,6 +426,7 @@ mlp_fc1_kernel(MlpArgs a) {
                         uint32_t v[16];
                         umma::tmem_ld16(trow + c0, v);
                         umma::tmem_ld_wait();
+                        float f1 = 0.0f, f2 = 0.0f, f3 = 0.0f, f4 = 0.0f;   // backward: fp32 partials per chunk
 #pragma unroll
                         for (int k2 = 0; k2 < 16; ++k2) {
                             if (c0 + k2 < rows) {
@@ -439,13 +440,14 @@ mlp_fc1_kernel(MlpArgs a) {
                                     const float d = s_dopre[c0 + k2];
                                     const float hact = act ? pre * inv_keep : 0.0f;
                                     const float g2 = act ? d * w2m * inv_keep : 0.0f;
-                                    s1 += (double)g2;
-                                    s2 += (double)g2 * (double)x;
-                                    s3 += (double)d * (double)hact;
-                                    s4 += (double)d;
+                                    f1 += g2;
+                                    f2 = fmaf(g2, x, f2);
+                                    f3 = fmaf(d, hact, f3);
+                                    f4 += d;
                                 }
                             }
                         }
+                        if (MODE == MLP_BWD_STATS) { s1 += (double)f1; s2 += (double)f2; s3 += (double)f3; s4 += (double)f4; }
                     }
                 }
                 umma::fence_before_sync();
@@ -768,7 +770,7 @@ static size_t mt_smem_lockstep(int n) {
 
 template <int MODE>
 static int mt_launch(const MlpArgs& a, cudaStream_t st) {
-    if (MODE == MLP_BWD_STATS) {
+    if (MODE == MLP_BWD_STATS) {      // measured with the warp-specialised kernel instead: 1.46 vs 1.40 ms for xnn_mlp_bwd
         const size_t smem = mt_smem_lockstep(a.n);
         if (cudaFuncSetAttribute(mlp_fc1_lockstep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
             return 1;
