@@ -865,7 +865,14 @@ mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U
 // the same fp32-level accuracy as 3xTF32 at the same tensor time, and 6 instead of 8 bytes per element.
 // Staging: an [R rows][K] matrix as uint4 [K/8][R] (8 bf16 per 16 bytes), one buffer per piece.
 // ---------------------------------------------------------------------------
-#define MB_ROWS 64
+#define MB_ROWS 128
+#define MB_WROWS 112      // rows per 16-byte chunk column of the W1 / dh staging: 100 hidden channels, 7 K steps of 16
+
+struct MbShared {
+    uint64_t bar;
+    uint32_t tmem_slot;
+    uint32_t pad[5];
+};
 
 struct MlpBwdArgs {
     const float* pool; const float* w1; const float* b1; const float* scale2; const float* shift2;
@@ -875,6 +882,7 @@ struct MlpBwdArgs {
     float* part_w1;       // [slots][100U][n]
     double* part_db1;     // [slots][100U]
     int B, U, n, T, slots;
+    int P;                // unit interleave (mb_interleave): CTAs that run side by side work on adjacent units
     float drop_p;
 };
 
@@ -912,69 +920,71 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int n = a.n, U = a.U, B = a.B, T = a.T;
     const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
-    const uint32_t wpiece = (uint32_t)chunksQ * 2048u;     // [chunksQ][128 rows] uint4
-    const uint32_t ppiece = (uint32_t)chunksQ * 1024u;     // [chunksQ][64 rows] uint4
-    const uint32_t tpiece = 8u * 2048u;                    // [8][128 rows] uint4 (K = 64 batch rows)
+    const uint32_t wcol = MB_WROWS * 16u;                  // one 16-byte chunk column of W1 / dh: 112 rows
+    const uint32_t wpiece = (uint32_t)chunksQ * wcol;      // [chunksQ][112 rows] uint4
+    const uint32_t pcol = MB_ROWS * 16u;                   // one chunk column of the pool tile: 128 batch rows
+    const uint32_t ppiece = (uint32_t)chunksQ * pcol;      // [chunksQ][128 rows] uint4
+    const uint32_t tpiece = (MB_ROWS / 8) * wcol;          // [16][112 rows] uint4 (K = 128 batch rows)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint4* w1s = reinterpret_cast<uint4*>(smem_raw);
     uint4* ps = reinterpret_cast<uint4*>(smem_raw + 3 * wpiece);
     uint4* ts = reinterpret_cast<uint4*>(smem_raw + 3 * wpiece + 3 * ppiece);
-    // the MN-major view of W1 with M = 128 reads 16 chunks from each piece: keep that inside the allocation
-    const uint32_t body = 3 * wpiece + 3 * ppiece + 3 * tpiece;
-    const uint32_t need = 2 * wpiece + 16u * 2048u;
-    unsigned char* tail = smem_raw + (body > need ? body : need);
-    float* s_dopre = reinterpret_cast<float*>(tail);                 // [64]
-    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 256);      // [64][4]
-    MtShared* sh = reinterpret_cast<MtShared*>(tail + 256 + 1024);
-    uint2* s_tab = reinterpret_cast<uint2*>(tail + 256 + 1024 + 32);  // [36 + 42 + 24] descriptor words
-    float* s_raw = reinterpret_cast<float*>(tail + 256 + 1024 + 32 + 1024);  // [64][n|1] fp32 pool tile (for dy)
-    const int S = n | 1;
+    // (the MN-major view of W1 with M = 128 reads 16 chunk columns from each piece: 2 wpiece + 16 wcol stays
+    //  inside 3 wpiece + 3 ppiece + 3 tpiece for every n)
+    unsigned char* tail = smem_raw + 3 * wpiece + 3 * ppiece + 3 * tpiece;
+    float* s_dopre = reinterpret_cast<float*>(tail);                                     // [128]
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 512);                          // [128][4]
+    MbShared* sh = reinterpret_cast<MbShared*>(tail + 512 + 2048);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 512 + 2048 + 32);                     // [36 + 42 + 48] descriptor words
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int row = (warp & 3) * 32 + lane;   // TMEM lane: hidden channel m (D1, D3) / pool column q (D2)
-    const int cg = warp >> 2;                 // column group: 16 of the tile's 64 batch rows
+    const int cg = warp >> 2;                 // column group: 32 of the tile's 128 batch rows
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw);
         const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
         for (uint32_t i = tid; i < tot; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
-    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 256);
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 512);
     if (tid == 0) umma::mbar_init(&sh->bar, 1);
     umma::fence_proxy_async();
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
     const uint32_t tmem = sh->tmem_slot;
-    const uint32_t w_addr = umma::smem_u32(w1s), p_addr = umma::smem_u32(ps), t_addr = umma::smem_u32(ts);
     const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);                          // W1 x pool, both K-major
     const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16); // W1^T x dh^T (MN views)
     const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);                  // dh x pool^T (MN view)
-    const uint32_t D1 = tmem, D2 = tmem + 64, D3 = tmem + 128;
+    const uint32_t D1 = tmem, D2 = tmem + MB_ROWS, D3 = tmem + 2 * MB_ROWS;
     // the six products of the 3-way split, smallest first: (piece of A, piece of B), 0 = hi, 1 = mid, 2 = lo
     // MMA sequences of a tile (the operand buffers never move):
     //   T1 [6*kstepsQ]  D1 = W1 (K-major) x pool (K-major)
-    //   T3 [42]         D2 = W1^T (MN view) x dh^T (MN view), K = hidden rows, 16 per MMA
-    //   T4 [24]         D3 += dh (K-major, K = batch rows) x pool^T (MN view)
-    const int n1 = 6 * kstepsQ;
-    if (tid < n1 + 42 + 24) {
-        const int seq = tid < n1 ? 0 : (tid < n1 + 42 ? 1 : 2);
-        const int i = tid - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + 42));
+    //   T3 [42]         D2 = W1^T (MN view) x dh^T (MN view), K = hidden rows, 16 per MMA (7 steps = 112 rows)
+    //   T4 [48]         D3 += dh (K-major, K = batch rows) x pool^T (MN view)
+    const int n1 = 6 * kstepsQ, n4 = 6 * (MB_ROWS / 16), ntab = n1 + 42 + n4;
+    if (tid < ntab) {
+        const int ti = tid;
+        const uint32_t w_addr = umma::smem_u32(smem_raw);
+        const uint32_t p_addr = w_addr + 3 * wpiece, t_addr = p_addr + 3 * ppiece;
+        const int seq = ti < n1 ? 0 : (ti < n1 + 42 ? 1 : 2);
+        const int i = ti - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + 42));
         const int per = seq == 0 ? kstepsQ : (seq == 1 ? 7 : MB_ROWS / 16);
         const int pass = i / per, ks = i - pass * per;
         const uint32_t pa = pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u;
         const uint32_t pb = pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u;
         uint2 e;
         if (seq == 0)
-            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * 2048u, 2048u),
-                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * 1024u, 1024u));
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * wcol, wcol),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * pcol, pcol));
         else if (seq == 1)
             e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)ks * 256u, 128u),
                            umma::desc_lo(t_addr + pb * tpiece + (uint32_t)ks * 256u, 128u));
         else
-            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * 2048u, 2048u),
+            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * wcol, wcol),
                            umma::desc_lo(p_addr + pb * ppiece + (uint32_t)ks * 256u, 128u));
-        s_tab[tid] = e;
+        s_tab[ti] = e;
     }
-    __syncthreads();
+    const uint2* tab = s_tab;
+    uint64_t* bar = &sh->bar;
 
     const long long tiles_total = (long long)U * T;
     const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
@@ -984,25 +994,23 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     const uint32_t trow = (uint32_t)((warp & 3) * 32) << 16;
     // staging map (coalesced): a warp-wide access covers 8 rows x 32 B of global memory and 32 distinct banks:
     // lane = (row & 7) * 4 + word, word = two consecutive pool columns of a 16-byte (8 x bf16) chunk.
-    // pool tile: warp w -> rows 8(w&7).., chunks (w>>3), (w>>3)+2, ...  (<= 6 chunks per warp)
-    const int srow = (warp & 7) * 8 + (lane >> 2), swd = lane & 3, sc0 = warp >> 3;
+    // pool tile: warp w -> rows 8 w .. 8 w + 7, every chunk
+    const int srow = warp * 8 + (lane >> 2), swd = lane & 3;
 
-    int cur_u = -1;
     uint32_t phase = 0, d3_started = 0;
     float b1m = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
     double sdb1 = 0.0;
-    float pv[6][2];
-    float pd = 0.0f;                                   // prefetched dopre / active bits of batch row tid (< 64)
+    float pv[MT_NMAX / 8][2];
+    float pd = 0.0f;                                   // prefetched dopre / active bits of batch row tid (< 128)
     uint4 pm = make_uint4(0u, 0u, 0u, 0u);
 
-    auto prefetch = [&](long long tile) {
-        const bool live = tile < hi;
-        const int u = live ? (int)(tile / T) : 0, t = live ? (int)(tile % T) : 0;
+    auto prefetch = [&](long long tile, int u, bool live) {
+        const int t = live ? (int)(tile % T) : 0;
         const int b0 = t * MB_ROWS;
         const float* src = (live && b0 + srow < B) ? a.pool + ((long long)(b0 + srow) * U + u) * n : nullptr;
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const int q = 8 * (sc0 + 2 * i) + 2 * swd;
+        for (int i = 0; i < MT_NMAX / 8; ++i) {
+            const int q = 8 * i + 2 * swd;
             pv[i][0] = (src != nullptr && q < n) ? __ldg(src + q) : 0.0f;
             pv[i][1] = (src != nullptr && q + 1 < n) ? __ldg(src + q + 1) : 0.0f;
         }
@@ -1013,20 +1021,15 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
         }
     };
-    auto split2 = [](float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) { split2_bf16x3(x0, x1, w0, w1, w2); };
     auto store_tile = [&]() {
         uint32_t* pw = reinterpret_cast<uint32_t*>(ps);
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const int c = sc0 + 2 * i;
-            if (c < chunksQ) {
+        for (int i = 0; i < MT_NMAX / 8; ++i) {
+            if (i < chunksQ) {
                 uint32_t w0, w1, w2;
-                split2(pv[i][0], pv[i][1], w0, w1, w2);
-                const int o = (c * 64 + srow) * 4 + swd;
+                split2_bf16x3(pv[i][0], pv[i][1], w0, w1, w2);
+                const int o = (i * MB_ROWS + srow) * 4 + swd;
                 pw[o] = w0; pw[ppiece / 4 + o] = w1; pw[2 * (ppiece / 4) + o] = w2;
-                const int q = 8 * c + 2 * swd;
-                if (q < n) s_raw[srow * S + q] = pv[i][0];
-                if (q + 1 < n) s_raw[srow * S + q + 1] = pv[i][1];
             }
         }
         if (tid < MB_ROWS) {
@@ -1034,10 +1037,10 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             *reinterpret_cast<uint4*>(s_mask + 4 * tid) = pm;
         }
     };
-    auto flush = [&](int u) {
+    auto flush = [&](int v, int u) {
         // every MMA into D3 has completed (the tile loop waits on each commit)
         int j = blockIdx.x;
-        const long long start = (long long)u * T;
+        const long long start = (long long)v * T;
         while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
         const int slot = blockIdx.x - j;
         const bool ok = row < MT_H && slot < a.slots;
@@ -1056,30 +1059,29 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         sdb1 = 0.0;
         d3_started = 0;
         umma::fence_before_sync();
-        __syncthreads();
     };
 
-    prefetch(lo);
-    for (long long tile = lo; tile < hi; ++tile) {
-        const int u = (int)(tile / T), t = (int)(tile % T);
-        const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
-        if (u != cur_u) {
-            if (cur_u >= 0) flush(cur_u);
-            cur_u = u;
-            {
-                // W1 of this unit, same coalesced map: items (row group of 8, chunk) dealt round-robin to the warps
-                uint32_t* ww = reinterpret_cast<uint32_t*>(w1s);
-                for (int it = warp; it < 13 * chunksQ; it += MT_THREADS / 32) {
-                    const int g = it / chunksQ, c = it - g * chunksQ;
-                    const int r = g * 8 + (lane >> 2);
-                    if (r < MT_H) {
-                        const float* src = a.w1 + ((long long)u * MT_H + r) * n;
-                        const int q = 8 * c + 2 * swd;
-                        uint32_t w0, w1v, w2v;
-                        split2(q < n ? __ldg(src + q) : 0.0f, q + 1 < n ? __ldg(src + q + 1) : 0.0f, w0, w1v, w2v);
-                        const int o = (c * 128 + r) * 4 + swd;
-                        ww[o] = w0; ww[wpiece / 4 + o] = w1v; ww[2 * (wpiece / 4) + o] = w2v;
-                    }
+    for (long long seg = lo; seg < hi;) {
+        // position v in the CTA order -> unit u: class v % P holds a contiguous run of units, so the CTAs that are
+        // at the same batch rows at the same time read and write neighbouring 4n-byte segments of those rows
+        const int v = (int)(seg / T);
+        int u = v / a.P;
+        for (int c = 0; c < v % a.P; ++c) u += (U - c + a.P - 1) / a.P;
+        const long long seg_end = min(hi, (long long)(v + 1) * T);
+        __syncthreads();            // the previous unit's flush is done
+        {
+            // W1 of this unit, same coalesced map: items (row group of 8, chunk) dealt round-robin to the warps
+            uint32_t* ww = reinterpret_cast<uint32_t*>(w1s);
+            for (int it = warp; it < 13 * chunksQ; it += MT_THREADS / 32) {
+                const int g8 = it / chunksQ, c = it - g8 * chunksQ;
+                const int r = g8 * 8 + (lane >> 2);
+                if (r < MT_H) {
+                    const float* src = a.w1 + ((long long)u * MT_H + r) * n;
+                    const int q = 8 * c + 2 * swd;
+                    uint32_t w0, w1v, w2v;
+                    split2_bf16x3(q < n ? __ldg(src + q) : 0.0f, q + 1 < n ? __ldg(src + q + 1) : 0.0f, w0, w1v, w2v);
+                    const int o = (c * MB_WROWS + r) * 4 + swd;
+                    ww[o] = w0; ww[wpiece / 4 + o] = w1v; ww[2 * (wpiece / 4) + o] = w2v;
                 }
             }
             const int ch = u * MT_H + row;
@@ -1091,86 +1093,112 @@ mlp_bwd_kernel(MlpBwdArgs a) {
             const float2 cf = ok ? a.coef[ch] : make_float2(0.f, 0.f);
             c1m = cf.x; c2m = cf.y;
         }
-        store_tile();
-        prefetch(tile + 1);      // a whole tile of tensor + epilogue work hides these loads
+        prefetch(seg, u, true);
         umma::fence_proxy_async();
         __syncthreads();
-        if (tid == 0) {
-            umma::fence_after_sync();
-            umma::issue_table<false>(s_tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), 0u, D1, idesc1, 0u);
-            umma::commit(&sh->bar);
-        }
-        umma::mbar_wait(&sh->bar, phase);
-        phase ^= 1u;
-        umma::fence_after_sync();
 
-        // ---- epilogue 1: dh for (channel row, batch rows 16cg..16cg+15) -> two 16-byte chunks per piece
-        {
-            const int c0 = 16 * cg;
-            uint32_t v[16];
-            umma::tmem_ld16(D1 + trow + c0, v);
-            umma::tmem_ld_wait();
-            float dh[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int c = c0 + i;
-                const float x = __uint_as_float(v[i]) + b1m;
-                const uint32_t act = (s_mask[4 * c + (row >> 5)] >> (row & 31)) & 1u;
-                const float g2 = act ? s_dopre[c] * w2m * inv_keep : 0.0f;
-                const float xhat = (x - meanm) * invstdm;
-                float d = gism * (g2 - c1m - xhat * c2m);
-                if (c >= rows || row >= MT_H) d = 0.0f;
-                dh[i] = d;
-                sdb1 += (double)d;
+        for (long long tile = seg; tile < seg_end; ++tile) {
+            const int t = (int)(tile % T);
+            const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
+            store_tile();
+            prefetch(tile + 1, u, tile + 1 < seg_end);
+            umma::fence_proxy_async();
+            __syncthreads();
+            if (tid == 0) {
+                umma::fence_after_sync();
+                umma::issue_table<false>(tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), 0u, D1, idesc1, 0u);
+                umma::commit(bar);
             }
-#pragma unroll
-            for (int g = 0; g < 2; ++g) {
-                uint4 p0, p1, p2;
-                split8_bf16x3(dh + 8 * g, p0, p1, p2);
-                const int chunk = 2 * cg + g;
-                ts[chunk * 128 + row] = p0;
-                ts[tpiece / 16 + chunk * 128 + row] = p1;
-                ts[2 * (tpiece / 16) + chunk * 128 + row] = p2;
-            }
-        }
-        umma::fence_proxy_async();
-        umma::fence_before_sync();
-        __syncthreads();
-        if (tid == 0) {
+            umma::mbar_wait(bar, phase);
+            phase ^= 1u;
             umma::fence_after_sync();
-            umma::issue_table<false>(s_tab + n1, 42, umma::desc_hi(2048u), umma::desc_hi(2048u), 0u, D2, idesc2, 0u);
-            umma::issue_table<false>(s_tab + n1 + 42, 24, umma::desc_hi(128u), umma::desc_hi(1024u), 0u, D3, idesc3,
-                                     d3_started);
-            umma::commit(&sh->bar);
-        }
-        d3_started = 1;
-        umma::mbar_wait(&sh->bar, phase);
-        phase ^= 1u;
-        umma::fence_after_sync();
 
-        // ---- epilogue 2: thread = (pool column q, 16 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b]
-        {
-            const int c0 = 16 * cg;
-            if (c0 < rows) {
-                uint32_t v[16];
-                umma::tmem_ld16(D2 + trow + c0, v);
+            // ---- epilogue 1: dh for (channel row, batch rows 32cg..32cg+31) -> four 16-byte chunks per piece
+            {
+                uint32_t v[2][16];
+                umma::tmem_ld16(D1 + trow + 32 * cg, v[0]);
+                umma::tmem_ld16(D1 + trow + 32 * cg + 16, v[1]);
+                umma::tmem_ld_wait();
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c0 = 32 * cg + 16 * h;
+                    float dh[16];
+                    float part = 0.0f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int c = c0 + i;
+                        const float x = __uint_as_float(v[h][i]) + b1m;
+                        const uint32_t act = (s_mask[4 * c + (row >> 5)] >> (row & 31)) & 1u;
+                        const float g2 = act ? s_dopre[c] * w2m * inv_keep : 0.0f;
+                        const float xhat = (x - meanm) * invstdm;
+                        float d = gism * (g2 - c1m - xhat * c2m);
+                        if (c >= rows || row >= MT_H) d = 0.0f;
+                        dh[i] = d;
+                        part += d;
+                    }
+                    sdb1 += (double)part;
+                    if (row < MB_WROWS) {
+#pragma unroll
+                        for (int gg = 0; gg < 2; ++gg) {
+                            uint4 p0, p1, p2;
+                            split8_bf16x3(dh + 8 * gg, p0, p1, p2);
+                            const int chunk = (c0 >> 3) + gg;
+                            ts[chunk * MB_WROWS + row] = p0;
+                            ts[tpiece / 16 + chunk * MB_WROWS + row] = p1;
+                            ts[2 * (tpiece / 16) + chunk * MB_WROWS + row] = p2;
+                        }
+                    }
+                }
+            }
+            umma::fence_proxy_async();
+            umma::fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                umma::fence_after_sync();
+                umma::issue_table<false>(tab + n1, 42, umma::desc_hi(wcol), umma::desc_hi(wcol), 0u, D2, idesc2, 0u);
+                umma::issue_table<false>(tab + n1 + 42, n4, umma::desc_hi(128u), umma::desc_hi(pcol), 0u, D3, idesc3,
+                                         d3_started);
+                umma::commit(bar);
+            }
+            d3_started = 1;
+            // ---- epilogue 2: thread = (pool column q, 32 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b];
+            //      the pool values come back from L2 (read one tile ago), requested while the MMAs run
+            const long long e2 = ((long long)(b0 + 32 * cg) * U + u) * n + row;
+            const long long bstride = (long long)U * n;
+            float x[2][16];
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int c = 32 * cg + 16 * h + i;
+                    x[h][i] = (row < n && c < rows) ? __ldg(a.pool + e2 + (long long)(16 * h + i) * bstride) : 0.0f;
+                }
+            umma::mbar_wait(bar, phase);
+            phase ^= 1u;
+            umma::fence_after_sync();
+            if (32 * cg < rows) {
+                uint32_t v[2][16];
+                umma::tmem_ld16(D2 + trow + 32 * cg, v[0]);
+                umma::tmem_ld16(D2 + trow + 32 * cg + 16, v[1]);
                 umma::tmem_ld_wait();
                 if (row < n) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c0 + i < rows)
-                            a.dy[((long long)(b0 + c0 + i) * U + u) * n + row] =
-                                s_raw[(c0 + i) * S + row] * __uint_as_float(v[i]);
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (32 * cg + 16 * h + i < rows)
+                                a.dy[e2 + (long long)(16 * h + i) * bstride] = x[h][i] * __uint_as_float(v[h][i]);
                 }
             }
+            // no barrier here: the next tile's two barriers order these TMEM reads before the MMAs that
+            // overwrite D1 / D2, and every MMA that reads the staging buffers has completed
         }
-        umma::fence_before_sync();
-        __syncthreads();
+        flush(v, u);
+        seg = seg_end;
     }
-    if (cur_u >= 0) flush(cur_u);
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+    if (warp == 0) umma::tmem_dealloc(sh->tmem_slot, 512);
 }
 
 __global__ void __launch_bounds__(256)
@@ -1195,16 +1223,22 @@ static int mb_grid(int B, int U) {
     const int sms = num_sms();
     return (int)(tiles < sms ? tiles : sms);
 }
+static int mb_interleave(int B, int U) {
+    const int G = mb_grid(B, U);
+    const int P = (U + G / 2) / G;      // units per CTA, rounded
+    const char* e = getenv("XNN_MB_INTERLEAVE");
+    if (e) return atoi(e) < 1 ? 1 : atoi(e);
+    return P < 1 ? 1 : P;
+}
 static int mb_slots(int B, int U) {
     const int T = mb_tiles(B), G = mb_grid(B, U);
     const long long per = ((long long)U * T) / G;
-    return (int)((T + per - 1) / per) + 1;
+    return (int)((T + per - 1) / per) + 1;      // CTAs that can touch one unit
 }
 static size_t mb_smem(int n) {
     const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
-    const size_t body = 3 * chunksQ * 2048 + 3 * chunksQ * 1024 + 3 * 8 * 2048;
-    const size_t need = 2 * chunksQ * 2048 + 16 * 2048;
-    return (body > need ? body : need) + 256 + 1024 + 32 + 1024 + (size_t)MB_ROWS * (n | 1) * 4 + 16;
+    const size_t wcol = MB_WROWS * 16;
+    return 3 * chunksQ * wcol + 3 * chunksQ * MB_ROWS * 16 + 3 * (MB_ROWS / 8) * wcol + 512 + 2048 + 32 + 126 * 8 + 16;
 }
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -1258,6 +1292,7 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     g.stats2 = stats2; g.coef = coef; g.dopre = dopre; g.maskbits = maskbits; g.dy = dy;
     g.part_w1 = (float*)(base + w.part_w1); g.part_db1 = (double*)(base + w.part_db1);
     g.B = B; g.U = U; g.n = n; g.T = mb_tiles(B); g.slots = mb_slots(B, U); g.drop_p = drop_p;
+    g.P = mb_interleave(B, U);
     const size_t smem = mb_smem(n);
     XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     mlp_bwd_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g);
