@@ -35,12 +35,12 @@ import torch  # noqa: E402
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
 # `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
 NCU_TRAFFIC = {
-    # profiles/r01_ncu_full_s55.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
-    "xnn_mlp_bwd": 1761.3e6,        # mlp_fc1_lockstep_kernel<2> 629.1 + 8.6 MB, mlp_bwd_kernel 699.5 MB read + 424.0 MB written
-    "xnn_frontend_bwd": 923.3e6,    # frontend_bwd_tc_kernel 919.0 MB read + 4.4 MB written
-    "xnn_frontend_fwd": 860.9e6,    # frontend_tc_kernel<1> 2.2 MB read + 858.7 MB written
-    "xnn_mlp_fwd": 662.7e6,         # mlp_fc1_kernel<1,8> 616.9 MB read + 45.8 MB written
-    "xnn_mlp_bn2_train_prepare": 580.4e6,
+    # profiles/r01_ncu_full_s60.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
+    "xnn_mlp_bwd": 1484.2e6,        # mlp_fc1_lockstep_kernel<2> 629.1 + 7.6 MB, mlp_bwd_kernel 464.5 MB read + 383.0 MB written
+    "xnn_frontend_bwd": 923.0e6,    # frontend_bwd_tc_kernel 918.9 MB read + 4.1 MB written
+    "xnn_frontend_fwd": 860.5e6,    # frontend_tc_kernel<1> 2.2 MB read + 858.3 MB written
+    "xnn_mlp_fwd": 661.6e6,         # mlp_fc1_kernel<1,8> 616.9 MB read + 44.7 MB written
+    "xnn_mlp_bn2_train_prepare": 581.4e6,
 }
 
 WORKLOADS = {
