@@ -1,4 +1,4 @@
-"""Secondary workloads of bench.py (`--workload cfg1_fwd | cfg3_fwd | cfg4 | cfg5`): the inference, interpret
+"""Secondary workloads of bench.py (`--workload cfg1_fwd | cfg3_fwd | cfg4 | cfg5 | metrics`): the inference, interpret
 and PWM-scan rows of SURVEY.md section 8(d), each printed as one JSON line in bench.py's format.  The default
 bench line (cfg3 training step) does not come through here.
 
@@ -18,6 +18,7 @@ AUX = {
     "cfg3_fwd": ("fwd", 300, 19, 600, 50, 8192),
     "cfg4": ("interpret", 100, 19, 200, 1, 1000000),
     "cfg5": ("scan", 750, 35, 1000, 0, 12500),
+    "metrics": ("metrics", 750, 0, 0, 0, 100000),
 }
 
 
@@ -432,9 +433,82 @@ def run_scan(name, args, rank, world, local, peaks, sampler):
         "ctool": _ctool_compare(dev), "clocks": clocks}))
 
 
+def run_metrics(name, args, rank, world, local, peaks, sampler):
+    """The per-PWM AUC loop of pwm-scoring.py:115-120 (get_metrics: aucROC + aucPR of every score column against one
+    y_true): G columns x N sequences per GPU, columns sharded across ranks, no collective."""
+    from explainn_b200 import metrics, ops
+    from oracle import metrics_oracle as MO
+    _, G, _, _, _, N = AUX[name]
+    N = args.batch or N
+    dev = torch.device("cuda", local)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    y = (torch.rand(N, device=dev, generator=g) < 0.5).to(torch.uint8)
+    cols = torch.randn((G, N), device=dev, generator=g) + 0.5 * y.float()[None, :] * torch.rand((G, 1), device=dev, generator=g)
+    res = {}
+
+    def step(_):
+        res["m"] = ops.metric_auc(cols, y)
+
+    for i in range(args.warmup):
+        step(i)
+    if rank == 0:
+        sampler.start()
+    events, orig, timed_call = _call_timer(ops)
+    ops._call = timed_call
+    k0 = ops.kernel_launches
+    ms_dev = _timed(step, args.steps, world, dev)
+    launches = ops.kernel_launches - k0
+    ops._call = orig
+    call_ms = {n_: sum(a.elapsed_time(b) for a, b in ev) / args.steps for n_, ev in events.items()}
+    scores_h = cols.t().contiguous().cpu().pin_memory()          # (N,G) as pwm-scoring.py holds it
+    y_h = y.cpu().pin_memory()
+
+    def e2e(_):
+        res["e"] = metrics.column_metrics(y_h.to(dev, non_blocking=True), scores_h.to(dev, non_blocking=True), "binary")
+
+    e2e(0)
+    ms_e2e = _timed(e2e, 1, world, dev)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        return
+    hbm, _, _, which = peaks()
+    top = max(call_ms, key=call_ms.get)
+    alg = 34.0 * N * G              # two passes over (score 4 + perm 8 + gathered label 1 + tp 4) per element
+    achieved = alg / (call_ms[top] / 1e3) / 1e9
+    roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+            "traffic": None, "peak_source": "hbm " + which,
+            "what": "34 B per (column, sequence): sorted score, int64 permutation, gathered label and cumulative "
+                    "positives, read in two passes; torch.sort (library) is outside this call and inside the step",
+            "kernel_ms": call_ms[top], "kernel_share_of_step": call_ms[top] / (ms_dev / args.steps),
+            "per_call_ms": {k_: round(v, 4) for k_, v in sorted(call_ms.items(), key=lambda kv: -kv[1])}}
+    sample = 8
+    sc = scores_h[:, :sample].numpy()
+    yt = y_h.numpy()
+    t0 = time.perf_counter()
+    ref = MO.column_metrics(yt, sc, "binary")
+    cpu = sample / (time.perf_counter() - t0)
+    err = max(float(np.abs(res["e"][k_][:sample] - np.asarray(ref[k_])).max()) for k_ in ref)
+    rate = world * G * args.steps / (ms_dev / 1e3)
+    print(json.dumps({
+        "metric": "score columns/sec aucROC + aucPR (per-PWM metrics)", "value": rate, "unit": "columns/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"pwm-scoring metrics: aucROC + aucPR of {G} score columns x {N} sequences per GPU "
+                               "against one y_true", "parallelism": f"columns sharded over {world} rank(s), no collective",
+                   "l2": f"columns {G * N * 4 / 1e6:.0f} MB + permutation {G * N * 8 / 1e6:.0f} MB per step (> L2)",
+                   "max_abs_err_vs_sklearn_on_sample": err},
+        "e2e": {"value": world * G / (ms_e2e / 1e3), "unit": "columns/s", "h2d_bytes_per_step": N * G * 4 + N,
+                "d2h_bytes_per_step": G * 16, "api": "metrics.column_metrics(pinned host y_true, scores (N,G)) -> host arrays"},
+        "gpu_launches": launches, "roofline": roof,
+        "cpu_baseline": {"value": cpu, "unit": "columns/s", "cores": 1, "kind": "reference",
+                         "sample": f"{sample} columns x {N} sequences through sklearn roc_auc_score + "
+                                   "average_precision_score (the functions the reference calls)"},
+        "clocks": clocks}))
+
+
 def run(name, args, rank, world, local, peaks, sampler):
     from explainn_b200 import parallel
     torch.cuda.set_device(local)
     parallel.init_from_env("nccl")
     kind = AUX[name][0]
-    {"fwd": run_fwd, "interpret": run_interpret, "scan": run_scan}[kind](name, args, rank, world, local, peaks, sampler)
+    {"fwd": run_fwd, "interpret": run_interpret, "scan": run_scan, "metrics": run_metrics}[kind](name, args, rank, world, local, peaks, sampler)

@@ -392,12 +392,10 @@ def get_loss(input_data="binary"):
 
 
 def get_metrics(input_data="binary"):
-    """architectures/__init__.py:458-461 (host-side metrics, imported lazily)"""
-    if input_data == "binary":
-        from sklearn.metrics import average_precision_score, roc_auc_score
-        return dict(aucROC=roc_auc_score, aucPR=average_precision_score)
-    from scipy.stats import pearsonr, spearmanr
-    return dict(Pearson=pearsonr, Spearman=spearmanr)
+    """architectures/__init__.py:458-461: the same keys and `(y_true, y_score)` call signature; the functions are
+    the device versions of explainn_b200/metrics.py (csrc/metrics.cu), not sklearn / scipy on the host."""
+    from . import metrics
+    return metrics.get_metrics(input_data)
 
 
 def get_optimizer(params, lr=1e-03):

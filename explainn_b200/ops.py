@@ -23,6 +23,7 @@ KERNELS_PER_CALL = {
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
     "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_lpm_scan_best_parts": 5, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
+    "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
 }
 kernel_launches = 0
 
@@ -492,3 +493,59 @@ def ipwm_scan_best(codes, offsets, pwm, forward_only=False):
           R, w, _p(_req(pwm, torch.int32, "pwm")), int(forward_only), _p(best), _p(pos), _p(strand), _p(work),
           _stream())
     return best, pos, strand
+
+
+# ---- validation metrics (explainn_b200/metrics.py is the reference-facing surface) ----
+def metric_auc(scores, labels):
+    """scores float32 (G,N) columns contiguous; labels uint8 (N,) shared or (G,N).  Returns (auroc, aupr) float64 (G,).
+    The descending sort is torch.sort (library plumbing); ranks over ties, the cumulative positives and both
+    reductions are xnn_metric_auc."""
+    _req(scores, torch.float32, "scores")
+    _req(labels, torch.uint8, "labels")
+    G, N = scores.shape
+    if labels.dim() == 1:
+        if labels.shape[0] != N:
+            raise ValueError("labels: expected N entries")
+        stride = 0
+    else:
+        if tuple(labels.shape) != (G, N):
+            raise ValueError("labels: expected shape (N,) or (G,N)")
+        stride = N
+    sv, perm = torch.sort(scores, dim=1, descending=True)
+    auroc = torch.empty(G, dtype=torch.float64, device=scores.device)
+    aupr = torch.empty(G, dtype=torch.float64, device=scores.device)
+    lib = _lib.load()
+    work = torch.empty(int(lib.xnn_metric_auc_work_bytes(N, G)), dtype=torch.uint8, device=scores.device)
+    _call("xnn_metric_auc", _p(sv), _p(perm), _p(labels), stride, N, G, _p(auroc), _p(aupr), _p(work), _stream())
+    return auroc, aupr
+
+
+def metric_ranks(vals):
+    """Average 1-based ranks (ties share their mean position) of every row of vals float32 (G,N) -> float64 (G,N)."""
+    _req(vals, torch.float32, "vals")
+    G, N = vals.shape
+    sv, perm = torch.sort(vals, dim=1)
+    ranks = torch.empty((G, N), dtype=torch.float64, device=vals.device)
+    _call("xnn_metric_ranks", _p(sv), _p(perm), N, G, _p(ranks), _stream())
+    return ranks
+
+
+def metric_pearson(x, y):
+    """Pearson r of row g of x (G,N) against y (N,) or row g of y (G,N); float32 or float64 inputs -> float64 (G,)."""
+    if x.dtype not in (torch.float32, torch.float64):
+        raise TypeError("x: expected float32 or float64")
+    _req(x, x.dtype, "x")
+    _req(y, x.dtype, "y")
+    G, N = x.shape
+    if y.dim() == 1:
+        if y.shape[0] != N:
+            raise ValueError("y: expected N entries")
+        stride = 0
+    else:
+        if tuple(y.shape) != (G, N):
+            raise ValueError("y: expected shape (N,) or (G,N)")
+        stride = N
+    r = torch.empty(G, dtype=torch.float64, device=x.device)
+    _call("xnn_metric_pearson_f32" if x.dtype == torch.float32 else "xnn_metric_pearson_f64", _p(x), _p(y), stride, N, G,
+          _p(r), _stream())
+    return r

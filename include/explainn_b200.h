@@ -358,6 +358,34 @@ int xnn_ipwm_scan_best_parts(const int8_t* codes, const long long* offsets, int 
                              const int32_t* pwm, int forward_only,
                              int32_t* best, int32_t* pos, int8_t* strand, void* work, xnn_stream_t s);
 
+/* ---- validation metrics on device-resident columns -----
+ * Replace the host calls of architectures/__init__.py:458-461 (get_metrics:
+ * sklearn roc_auc_score / average_precision_score, scipy pearsonr / spearmanr) as
+ * used by selene/__init__.py:359-366 (one flattened column) and
+ * pwm-scoring.py:115-120 (one call per PWM column).  Columns are contiguous
+ * ([G][N]); the caller sorts them (any stable or unstable sort: ties are handled
+ * by value) and passes sorted values plus the permutation (int64 indices into the
+ * original order).
+ *
+ * xnn_metric_auc: sorted_scores DESCENDING; labels uint8 0/1 in ORIGINAL order,
+ * column g at labels + g*label_stride (label_stride 0 = one label vector shared
+ * by all columns); auroc/aupr double [G] (NaN where a column has one class only /
+ * no positive); work = xnn_metric_auc_work_bytes(N, G) bytes.  N < 2^31.
+ * xnn_metric_ranks: sorted_vals ASCENDING -> average 1-based ranks (scipy rankdata
+ * "average") as double [G][N] in the original order.
+ * xnn_metric_pearson_*: r double [G] of column g of x against column g of y
+ * (y_stride 0 = shared y); fp64 two-pass; NaN for a constant column. */
+size_t xnn_metric_auc_work_bytes(long long N, int G);
+int xnn_metric_auc(const float* sorted_scores, const long long* perm, const uint8_t* labels,
+                   long long label_stride, long long N, int G, double* auroc, double* aupr,
+                   void* work, xnn_stream_t s);
+int xnn_metric_ranks(const float* sorted_vals, const long long* perm, long long N, int G,
+                     double* ranks, xnn_stream_t s);
+int xnn_metric_pearson_f32(const float* x, const float* y, long long y_stride, long long N, int G,
+                           double* r, xnn_stream_t s);
+int xnn_metric_pearson_f64(const double* x, const double* y, long long y_stride, long long N, int G,
+                           double* r, xnn_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,3 +122,25 @@ def test_jaspar_writer_matches_fixture():
         pfm = O.parse_jaspar(pair["jaspar"])
         title = pair["jaspar"].splitlines()[0][1:].split(" ", 1)
         assert pfm_to_jaspar(pfm, title[0], title[1]).strip() == pair["jaspar"].strip(), name
+
+
+def test_metrics_surface_and_no_cpu_fallback():
+    """get_metrics keeps the reference's keys (architectures/__init__.py:458-461); the ops refuse CPU tensors."""
+    import numpy as np
+    import torch
+    from explainn_b200 import metrics, ops
+    from oracle import metrics_oracle as MO
+    assert list(metrics.get_metrics("binary")) == list(MO.get_metrics("binary"))
+    assert list(metrics.get_metrics("other")) == list(MO.get_metrics("other"))
+    with pytest.raises(RuntimeError):
+        ops.metric_auc(torch.zeros((1, 4)), torch.zeros(4, dtype=torch.uint8))
+    with pytest.raises(RuntimeError):
+        ops.metric_pearson(torch.zeros((1, 4)), torch.zeros(4))
+    with pytest.raises(RuntimeError):
+        ops.metric_ranks(torch.zeros((1, 4)))
+    lib = _lib.load()
+    assert lib.xnn_metric_auc_work_bytes(1000, 3) == 12000
+    # sklearn's own answers on the two-threshold example of its documentation pin the oracle wrapper
+    y, s = np.array([0, 0, 1, 1]), np.array([0.1, 0.4, 0.35, 0.8])
+    assert abs(MO.get_metrics()["aucROC"](y, s) - 0.75) < 1e-15
+    assert abs(MO.get_metrics()["aucPR"](y, s) - 0.8333333333333333) < 1e-15
