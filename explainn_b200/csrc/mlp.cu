@@ -119,6 +119,13 @@ static int launch_gemm(const GemmArgs& g, cudaStream_t st) {
     return 0;
 }
 
+// final Linear weight gradient (M = F, N = U are one handful of tiles): split the batch finely enough to fill the SMs
+static int splitk_wide(int K) {
+    int s = (K + 127) / 128;
+    if (s > 32) s = 32;
+    if (s < 1) s = 1;
+    return s;
+}
 static int splitk_for(int K) {
     int s = (K + 511) / 512;
     if (s > 32) s = 32;
@@ -389,7 +396,7 @@ extern "C" int xnn_linear_fwd(const float* x, const float* w, const float* b, in
 }
 
 extern "C" size_t xnn_linear_bwd_work_bytes(int B, int U, int F) {
-    const size_t splitk = (size_t)splitk_for(B) * F * U * sizeof(float);
+    const size_t splitk = (size_t)splitk_wide(B) * F * U * sizeof(float);
     const size_t cs = xnn_bn_work_bytes(B, F);
     return splitk + cs + 256;
 }
@@ -422,7 +429,7 @@ extern "C" int xnn_linear_bwd(const float* dlogits, const float* wf, const float
     h.C = dwf; h.c_bs = 0; h.c_rs = U; h.c_cs = 1;
     h.M = F; h.N = U; h.K = B; h.batch = 1;
     h.bias = nullptr; h.bias_bs = 0; h.mul = nullptr; h.mul_mode = 0;
-    h.splits = splitk_for(B); h.part = (float*)work;
+    h.splits = splitk_wide(B); h.part = (float*)work;
     if (launch_gemm(h, st)) { set_error("xnn_linear_bwd: launch failed"); return XNN_ERR_CUDA; }
     // dbf = column sums of dlogits
     size_t off = ((size_t)h.splits * F * U * sizeof(float) + 255) & ~(size_t)255;
