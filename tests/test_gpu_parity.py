@@ -212,7 +212,7 @@ def test_mlp_forward_tensor_core_vs_fp64(cfg):
     assert torch.equal(o1, o4)
 
 
-@pytest.mark.parametrize("cfg", [(40, 83, 300), (100, 26, 257), (7, 6, 130), (3, 96, 70), (33, 9, 1000)])
+@pytest.mark.parametrize("cfg", [(40, 83, 300), (100, 26, 257), (7, 6, 130), (3, 96, 70), (33, 9, 1000), (300, 83, 512)])
 def test_mlp_backward_tensor_core_vs_fp64_autograd(cfg):
     """gradients of the per-unit MLP on tcgen05 against torch fp64 autograd of the same function"""
     from explainn_b200 import ops
