@@ -587,3 +587,74 @@ extern "C" int xnn_adam_step(float* param, const float* grad, float* exp_avg, fl
     XNN_CHECK_LAUNCH();
     return XNN_OK;
 }
+
+// ---------------------------------------------------------------------------
+// The same update over a LIST of tensors in one launch (the reference's optimizer.step() walks 14 parameters; 14
+// launches of a few microseconds each cost more in gaps than in work).  Element arithmetic is adam_kernel's, so the
+// results are bit-identical to per-tensor calls.
+// ---------------------------------------------------------------------------
+#define ADAM_MAX_TENSORS 32
+#define ADAM_CHUNK 2048              // elements per block
+struct AdamList {
+    float* p[ADAM_MAX_TENSORS];
+    const float* g[ADAM_MAX_TENSORS];
+    float* m[ADAM_MAX_TENSORS];
+    float* v[ADAM_MAX_TENSORS];
+    long long numel[ADAM_MAX_TENSORS];
+    int first_block[ADAM_MAX_TENSORS + 1];
+    int n;
+};
+
+__global__ void __launch_bounds__(256)
+adam_multi_kernel(const __grid_constant__ AdamList L, float lr, float b1, float b2, float eps, float wd, float bc1,
+                  float bc2_sqrt, float grad_scale) {
+    int t = 0;
+    while (t + 1 < L.n && (int)blockIdx.x >= L.first_block[t + 1]) ++t;
+    const long long base = (long long)((int)blockIdx.x - L.first_block[t]) * ADAM_CHUNK;
+    const long long end = min(L.numel[t], base + ADAM_CHUNK);
+    float* __restrict__ p = L.p[t];
+    const float* __restrict__ g = L.g[t];
+    float* __restrict__ m = L.m[t];
+    float* __restrict__ v = L.v[t];
+    for (long long i = base + threadIdx.x; i < end; i += 256) {
+        float gi = g[i] * grad_scale;
+        const float pi = p[i];
+        if (wd != 0.0f) gi = fmaf(wd, pi, gi);
+        const float mi = m[i] + (1.0f - b1) * (gi - m[i]);
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        p[i] = pi - (lr / bc1) * (mi / denom);
+    }
+}
+
+extern "C" int xnn_adam_step_multi(int n_tensors, float* const* params, const float* const* grads,
+                                   float* const* exp_avg, float* const* exp_avg_sq, const long long* numels, float lr,
+                                   float beta1, float beta2, float eps, float weight_decay, long long step,
+                                   float grad_scale, xnn_stream_t s) {
+    XNN_CHECK_ARG(n_tensors >= 0 && step >= 1, "bad sizes");
+    XNN_CHECK_ARG(n_tensors == 0 || (params && grads && exp_avg && exp_avg_sq && numels), "NULL pointer");
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    for (int t0 = 0; t0 < n_tensors; t0 += ADAM_MAX_TENSORS) {
+        AdamList L{};
+        int blocks = 0;
+        for (int t = t0; t < n_tensors && t < t0 + ADAM_MAX_TENSORS; ++t) {
+            XNN_CHECK_ARG(numels[t] >= 0, "negative numel");
+            if (numels[t] == 0) continue;
+            XNN_CHECK_ARG(params[t] && grads[t] && exp_avg[t] && exp_avg_sq[t], "NULL tensor pointer");
+            const long long nb = (numels[t] + ADAM_CHUNK - 1) / ADAM_CHUNK;
+            XNN_CHECK_ARG(nb + blocks < (1LL << 30), "too many elements for one launch");
+            L.p[L.n] = params[t]; L.g[L.n] = grads[t]; L.m[L.n] = exp_avg[t]; L.v[L.n] = exp_avg_sq[t];
+            L.numel[L.n] = numels[t]; L.first_block[L.n] = blocks;
+            blocks += (int)nb;
+            ++L.n;
+        }
+        if (L.n == 0) continue;
+        L.first_block[L.n] = blocks;
+        adam_multi_kernel<<<blocks, 256, 0, to_stream(s)>>>(L, lr, beta1, beta2, eps, weight_decay, (float)bc1,
+                                                            (float)sqrt(bc2), grad_scale);
+        XNN_CHECK_LAUNCH();
+    }
+    return XNN_OK;
+}

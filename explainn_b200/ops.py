@@ -23,7 +23,7 @@ KERNELS_PER_CALL = {
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
     "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_lpm_scan_best_parts": 5, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
-    "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
+    "xnn_adam_step_multi": 1, "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
 }
 kernel_launches = 0
 
@@ -493,6 +493,24 @@ def ipwm_scan_best(codes, offsets, pwm, forward_only=False):
           R, w, _p(_req(pwm, torch.int32, "pwm")), int(forward_only), _p(best), _p(pos), _p(strand), _p(work),
           _stream())
     return best, pos, strand
+
+
+def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
+    """One launch for a list of parameter tensors that share `step` (xnn_adam_step_multi); bit-identical to
+    adam_step per tensor."""
+    n = len(params)
+    if not (len(grads) == len(exp_avgs) == len(exp_avg_sqs) == n):
+        raise ValueError("adam_step_multi: lists of different lengths")
+    for p_, g_, m_, v_ in zip(params, grads, exp_avgs, exp_avg_sqs):
+        _req(p_, torch.float32, "param"); _req(g_, torch.float32, "grad")
+        _req(m_, torch.float32, "exp_avg"); _req(v_, torch.float32, "exp_avg_sq")
+        if not (g_.numel() == m_.numel() == v_.numel() == p_.numel()):
+            raise ValueError("adam_step_multi: tensor sizes differ")
+    arr = ctypes.c_void_p * n
+    ptrs = [arr(*[t.data_ptr() for t in lst]) for lst in (params, grads, exp_avgs, exp_avg_sqs)]
+    numels = (ctypes.c_longlong * n)(*[t.numel() for t in params])
+    _call("xnn_adam_step_multi", n, ptrs[0], ptrs[1], ptrs[2], ptrs[3], numels, float(lr), float(beta1), float(beta2),
+          float(eps), float(weight_decay), int(step), float(grad_scale), _stream())
 
 
 # ---- validation metrics (explainn_b200/metrics.py is the reference-facing surface) ----

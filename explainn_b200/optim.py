@@ -1,4 +1,4 @@
-"""Adam with the update done by the fused xnn_adam_step kernel (K14: architectures/__init__.py:463-464).
+"""Adam with the update done by the fused xnn_adam_step_multi kernel (one launch per parameter group) (K14: architectures/__init__.py:463-464).
 
 State layout is torch.optim.Adam's ({"step", "exp_avg", "exp_avg_sq"} per parameter), so optimizer
 state_dicts inside reference checkpoints (selene/__init__.py:376-384,208-221) load and save unchanged.
@@ -20,6 +20,7 @@ class FusedAdam(torch.optim.Optimizer):
                 loss = closure()
         for group in self.param_groups:
             b1, b2 = group["betas"]
+            by_step = {}            # parameters stepped together share one launch
             for p in group["params"]:
                 if p.grad is None:
                     continue
@@ -30,6 +31,9 @@ class FusedAdam(torch.optim.Optimizer):
                     st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
                 st["step"] += 1
                 g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
-                ops.adam_step(p.data, g, st["exp_avg"], st["exp_avg_sq"], group["lr"], b1, b2, group["eps"],
-                              group["weight_decay"], int(st["step"]), grad_scale)
+                lst = by_step.setdefault(int(st["step"]), ([], [], [], []))
+                lst[0].append(p.data); lst[1].append(g); lst[2].append(st["exp_avg"]); lst[3].append(st["exp_avg_sq"])
+            for step, (ps, gs, ms, vs) in by_step.items():
+                ops.adam_step_multi(ps, gs, ms, vs, group["lr"], b1, b2, group["eps"], group["weight_decay"], step,
+                                    grad_scale)
         return loss

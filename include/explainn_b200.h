@@ -232,6 +232,16 @@ int xnn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
                   long long numel, float lr, float beta1, float beta2, float eps,
                   float weight_decay, long long step, float grad_scale, xnn_stream_t s);
 
+/* The same update over a list of n_tensors parameter tensors in one launch
+ * (optimizer.step() of selene/__init__.py:292 walks every parameter).  The five
+ * arrays are HOST arrays of device pointers / element counts, read before the call
+ * returns; all tensors share step (torch.optim.Adam steps them together).  Results
+ * are bit-identical to n_tensors calls of xnn_adam_step. */
+int xnn_adam_step_multi(int n_tensors, float* const* params, const float* const* grads,
+                        float* const* exp_avg, float* const* exp_avg_sq, const long long* numels,
+                        float lr, float beta1, float beta2, float eps, float weight_decay,
+                        long long step, float grad_scale, xnn_stream_t s);
+
 /* ---- a7-a10: interpret ------------------------------------------------------
  * test.py:128-166 (fp16 activations), interpret.py:363-454. */
 /* pass 1: per-unit maximum activation, rounded to fp16 like test.py:137, over

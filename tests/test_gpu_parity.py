@@ -404,6 +404,40 @@ def test_fused_adam_matches_torch_adam():
         U.assert_close(pd.cpu().numpy(), ref_p.detach().numpy(), rtol=2e-6, what=f"adam step {step}")
 
 
+def test_fused_adam_list_is_bit_identical_to_per_tensor_calls_and_torch_optimizer():
+    """xnn_adam_step_multi (one launch for the parameter list) vs xnn_adam_step per tensor: same bits; FusedAdam vs
+    torch.optim.Adam over several parameters (sizes around the 2048-element block chunk, an empty one, 40 tensors
+    > the 32 of one launch)."""
+    from explainn_b200 import ops
+    from explainn_b200.optim import FusedAdam
+    g = torch.Generator().manual_seed(5)
+    sizes = [1, 2047, 2048, 2049, 0, 100003] + [17 + 3 * i for i in range(34)]
+    ps = [torch.randn(n, generator=g) for n in sizes]
+    a = [[t.to(DEV).clone() for t in ps], [torch.zeros(n, device=DEV) for n in sizes], [torch.zeros(n, device=DEV) for n in sizes]]
+    b = [[t.to(DEV).clone() for t in ps], [torch.zeros(n, device=DEV) for n in sizes], [torch.zeros(n, device=DEV) for n in sizes]]
+    for step in range(1, 4):
+        grads = [torch.randn(n, generator=g).to(DEV) for n in sizes]
+        ops.adam_step_multi(a[0], grads, a[1], a[2], 0.003, 0.9, 0.999, 1e-8, 0.01, step, 0.5)
+        for i in range(len(sizes)):
+            if sizes[i] == 0:
+                continue          # the list entry skips empty tensors; the single-tensor entry wants real pointers
+            ops.adam_step(b[0][i], grads[i], b[1][i], b[2][i], 0.003, 0.9, 0.999, 1e-8, 0.01, step, 0.5)
+        for k in range(3):
+            for x, y in zip(a[k], b[k]):
+                assert torch.equal(x, y)
+    ref = [t.clone().requires_grad_(True) for t in ps if t.numel()]
+    mine = [t.to(DEV).clone().requires_grad_(True) for t in ps if t.numel()]
+    o_ref, o_mine = torch.optim.Adam(ref, lr=0.003), FusedAdam(mine, lr=0.003)
+    for step in range(3):
+        for r, m_ in zip(ref, mine):
+            gr = torch.randn(r.shape, generator=g)
+            r.grad, m_.grad = gr.clone(), gr.to(DEV)
+        o_ref.step(); o_mine.step()
+    for r, m_ in zip(ref, mine):
+        U.assert_close(m_.detach().cpu().numpy(), r.detach().numpy(), rtol=2e-6, what="FusedAdam")
+    assert set(o_mine.state[mine[0]]) == {"step", "exp_avg", "exp_avg_sq"}
+
+
 # ---------------------------------------------------------------------------------------------------
 # a7-a10: interpret
 # ---------------------------------------------------------------------------------------------------
