@@ -855,7 +855,8 @@ mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U
 }
 
 // ---------------------------------------------------------------------------
-// backward, pass B2 (thread = hidden channel, 64 batch rows per tile):
+// backward, pass B2 (thread = hidden channel, 128 batch rows per tile -- N = 128 MMAs: the shared-memory operand
+// fetch of the 126 MMAs per tile bounds this kernel, and 64-row tiles fetched a third more per row):
 //   D1[m][b]  = W1 . pool^T                 -> dh[m][b] = gamma*invstd*(g2 - c1 - xhat*c2)   (registers -> smem)
 //   D2[q][b]  = W1^T . dh                   -> dy[b,u,q] = pool[b,u,q] * D2[q][b]
 //   D3[m][q] += dh . pool                   (accumulated in TMEM over the CTA's tiles of the unit) -> dW1
@@ -863,7 +864,8 @@ mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U
 // swizzle only for 16-bit types: this pass therefore runs kind::f16 with a THREE-way bf16 split of both
 // operands (x = x1+x2+x3, 8 mantissa bits each) and the six products x1y1 x1y2 x2y1 x1y3 x2y2 x3y1 --
 // the same fp32-level accuracy as 3xTF32 at the same tensor time, and 6 instead of 8 bytes per element.
-// Staging: an [R rows][K] matrix as uint4 [K/8][R] (8 bf16 per 16 bytes), one buffer per piece.
+// Staging: an [R rows][K] matrix as uint4 [K/8][R] (8 bf16 per 16 bytes), one buffer per piece; W1 and dh use
+// R = 112 (100 hidden channels, zero rows up to the 7th K step of 16), the pool tile R = 128.
 // ---------------------------------------------------------------------------
 #define MB_ROWS 128
 #define MB_WROWS 112      // rows per 16-byte chunk column of the W1 / dh staging: 100 hidden channels, 7 K steps of 16
