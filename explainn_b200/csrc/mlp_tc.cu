@@ -935,7 +935,7 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     //  inside 3 wpiece + 3 ppiece + 3 tpiece for every n)
     unsigned char* tail = smem_raw + 3 * wpiece + 3 * ppiece + 3 * tpiece;
     float* s_dopre = reinterpret_cast<float*>(tail);                                     // [128]
-    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 512);                          // [128][4]
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 512);                          // [4 words][128 batch rows]
     MbShared* sh = reinterpret_cast<MbShared*>(tail + 512 + 2048);
     uint2* s_tab = reinterpret_cast<uint2*>(tail + 512 + 2048 + 32);                     // [36 + 42 + 48] descriptor words
 
@@ -1036,7 +1036,7 @@ mlp_bwd_kernel(MlpBwdArgs a) {
         }
         if (tid < MB_ROWS) {
             s_dopre[tid] = pd;
-            *reinterpret_cast<uint4*>(s_mask + 4 * tid) = pm;
+            s_mask[tid] = pm.x; s_mask[MB_ROWS + tid] = pm.y; s_mask[2 * MB_ROWS + tid] = pm.z; s_mask[3 * MB_ROWS + tid] = pm.w;
         }
     };
     auto flush = [&](int v, int u) {
@@ -1126,12 +1126,22 @@ mlp_bwd_kernel(MlpBwdArgs a) {
                     const int c0 = 32 * cg + 16 * h;
                     float dh[16];
                     float part = 0.0f;
+                    // mask words of this warp's 32 channels and dopre for 16 batch rows: four 16-byte loads each
+                    uint32_t mk[16];
+                    float dp[16];
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        const uint4 mq = *reinterpret_cast<const uint4*>(s_mask + (row >> 5) * MB_ROWS + c0 + 4 * q4);
+                        const float4 dq = *reinterpret_cast<const float4*>(s_dopre + c0 + 4 * q4);
+                        mk[4 * q4] = mq.x; mk[4 * q4 + 1] = mq.y; mk[4 * q4 + 2] = mq.z; mk[4 * q4 + 3] = mq.w;
+                        dp[4 * q4] = dq.x; dp[4 * q4 + 1] = dq.y; dp[4 * q4 + 2] = dq.z; dp[4 * q4 + 3] = dq.w;
+                    }
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
                         const int c = c0 + i;
                         const float x = __uint_as_float(v[h][i]) + b1m;
-                        const uint32_t act = (s_mask[4 * c + (row >> 5)] >> (row & 31)) & 1u;
-                        const float g2 = act ? s_dopre[c] * w2m * inv_keep : 0.0f;
+                        const uint32_t act = (mk[i] >> (row & 31)) & 1u;
+                        const float g2 = act ? dp[i] * w2m * inv_keep : 0.0f;
                         const float xhat = (x - meanm) * invstdm;
                         float d = gism * (g2 - c1m - xhat * c2m);
                         if (c >= rows || row >= MT_H) d = 0.0f;
