@@ -35,7 +35,7 @@ import torch  # noqa: E402
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
 # `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
 NCU_TRAFFIC = {
-    # profiles/r01_ncu_full_s60.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
+    # profiles/r01_ncu_full_s71.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
     "xnn_mlp_bwd": 1484.2e6,        # mlp_fc1_lockstep_kernel<2> 629.1 + 7.6 MB, mlp_bwd_kernel 464.5 MB read + 383.0 MB written
     "xnn_frontend_bwd": 923.0e6,    # frontend_bwd_tc_kernel 918.9 MB read + 4.1 MB written
     "xnn_frontend_fwd": 860.5e6,    # frontend_tc_kernel<1> 2.2 MB read + 858.3 MB written
