@@ -345,8 +345,72 @@ extern "C" int xnn_fc2_fwd(const float* hpre, const float* scale2, const float* 
     return XNN_OK;
 }
 
+// Final Linear forward for F <= 64 outputs: sgemm_kernel's 64 x 64 tiles give B/64 blocks (64 at B = 4096, on 148
+// SMs) that each waste the columns beyond F.  Here: 32 batch rows per block, W^T and the x tile in shared memory,
+// warp = 4 rows, lane = 2 outputs; per 4 values of u four 16-byte loads of x (broadcast), four 8-byte loads of W^T
+// and 32 FMAs.  Sum over u ascending in one accumulator per output, as sgemm_kernel does.
+#define LF_ROWS 32
+#define LF_FS 64
+__global__ void __launch_bounds__(256)
+linear_fwd_small_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, int B,
+                        int U, int F, float* __restrict__ y) {
+    extern __shared__ __align__(16) float s_lf[];
+    const int Up = (U + 3) & ~3, S = Up + 4;
+    float* s_w = s_lf;                      // [Up][LF_FS]  (W^T, zero beyond U and F)
+    float* s_x = s_lf + (size_t)Up * LF_FS;  // [LF_ROWS][S]
+    const int r0 = blockIdx.x * LF_ROWS, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < Up * LF_FS; i += 256) {
+        const int f = i & (LF_FS - 1), u = i >> 6;             // lanes along f: conflict-free stores
+        s_w[i] = (f < F && u < U) ? __ldg(w + (long long)f * U + u) : 0.0f;
+    }
+    for (int i = threadIdx.x; i < LF_ROWS * Up; i += 256) {
+        const int r = i / Up, u = i - r * Up;
+        s_x[r * S + u] = (r0 + r < B && u < U) ? x[(long long)(r0 + r) * U + u] : 0.0f;
+    }
+    __syncthreads();
+    float acc[4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = 0.0f;
+    const float* xr = s_x + (warp * 4) * S;
+    const float* wc = s_w + 2 * lane;
+    for (int u = 0; u < Up; u += 4) {
+        float4 xv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xv[i] = *reinterpret_cast<const float4*>(xr + i * S + u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 wv = *reinterpret_cast<const float2*>(wc + (u + k) * LF_FS);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float xs = k == 0 ? xv[i].x : k == 1 ? xv[i].y : k == 2 ? xv[i].z : xv[i].w;
+                acc[i][0] = fmaf(xs, wv.x, acc[i][0]);
+                acc[i][1] = fmaf(xs, wv.y, acc[i][1]);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = r0 + warp * 4 + i;
+        if (r >= B) continue;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int f = 2 * lane + j;
+            if (f < F) y[(long long)r * F + f] = acc[i][j] + (b ? b[f] : 0.0f);
+        }
+    }
+}
+
 static int linear_fwd_launch(const float* x, const float* w, const float* b, int B, int U, int F, float* y,
                              cudaStream_t st) {
+    const int Up = (U + 3) & ~3;
+    const size_t lf_smem = ((size_t)Up * LF_FS + (size_t)LF_ROWS * (Up + 4)) * sizeof(float);
+    if (F <= LF_FS && lf_smem <= 200 * 1024) {
+        if (cudaFuncSetAttribute(linear_fwd_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lf_smem) !=
+            cudaSuccess)
+            return 1;
+        linear_fwd_small_kernel<<<ceil_div(B, LF_ROWS), 256, lf_smem, st>>>(x, w, b, B, U, F, y);
+        return cudaGetLastError() != cudaSuccess;
+    }
     GemmArgs g{};
     g.A = x; g.a_bs = 0; g.a_rs = U; g.a_cs = 1;
     g.Bm = w; g.b_bs = 0; g.b_rs = 1; g.b_cs = U;            // B[u][f] = W[f*U + u]
