@@ -351,17 +351,18 @@ extern "C" int xnn_fc2_fwd(const float* hpre, const float* scale2, const float* 
 // and 32 FMAs.  Sum over u ascending in one accumulator per output, as sgemm_kernel does.
 #define LF_ROWS 32
 #define LF_FS 64
+#define LF_WS 66      // row stride of W^T in shared memory (floats)
 __global__ void __launch_bounds__(256)
 linear_fwd_small_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, int B,
                         int U, int F, float* __restrict__ y) {
     extern __shared__ __align__(16) float s_lf[];
     const int Up = (U + 3) & ~3, S = Up + 4;
-    float* s_w = s_lf;                      // [Up][LF_FS]  (W^T, zero beyond U and F)
-    float* s_x = s_lf + (size_t)Up * LF_FS;  // [LF_ROWS][S]
+    float* s_w = s_lf;                      // [Up][LF_WS]  (W^T, zero beyond U and F)
+    float* s_x = s_lf + (size_t)Up * LF_WS;  // [LF_ROWS][S]
     const int r0 = blockIdx.x * LF_ROWS, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < Up * LF_FS; i += 256) {
-        const int f = i & (LF_FS - 1), u = i >> 6;             // lanes along f: conflict-free stores
-        s_w[i] = (f < F && u < U) ? __ldg(w + (long long)f * U + u) : 0.0f;
+    for (int i = threadIdx.x; i < LF_FS * Up; i += 256) {
+        const int f = i / Up, u = i - f * Up;                  // lanes along u: coalesced reads, 2-way conflicts at stride 66
+        s_w[u * LF_WS + f] = (f < F && u < U) ? __ldg(w + (long long)f * U + u) : 0.0f;
     }
     for (int i = threadIdx.x; i < LF_ROWS * Up; i += 256) {
         const int r = i / Up, u = i - r * Up;
@@ -379,7 +380,7 @@ linear_fwd_small_kernel(const float* __restrict__ x, const float* __restrict__ w
         for (int i = 0; i < 4; ++i) xv[i] = *reinterpret_cast<const float4*>(xr + i * S + u);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const float2 wv = *reinterpret_cast<const float2*>(wc + (u + k) * LF_FS);
+            const float2 wv = *reinterpret_cast<const float2*>(wc + (u + k) * LF_WS);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const float xs = k == 0 ? xv[i].x : k == 1 ? xv[i].y : k == 2 ? xv[i].z : xv[i].w;
@@ -403,7 +404,7 @@ linear_fwd_small_kernel(const float* __restrict__ x, const float* __restrict__ w
 static int linear_fwd_launch(const float* x, const float* w, const float* b, int B, int U, int F, float* y,
                              cudaStream_t st) {
     const int Up = (U + 3) & ~3;
-    const size_t lf_smem = ((size_t)Up * LF_FS + (size_t)LF_ROWS * (Up + 4)) * sizeof(float);
+    const size_t lf_smem = ((size_t)Up * LF_WS + (size_t)LF_ROWS * (Up + 4)) * sizeof(float);
     if (F <= LF_FS && lf_smem <= 200 * 1024) {
         if (cudaFuncSetAttribute(linear_fwd_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lf_smem) !=
             cudaSuccess)
