@@ -193,6 +193,27 @@ class UnitBank(nn.Sequential):
         raise NotImplementedError(
             f"slice {keys} of the fused unit bank is not callable; supported: full, [:3], [:4]")
 
+    # What happens to a float input column that is neither one-hot nor all-zero (the packed layout cannot hold
+    # it; the reference's Conv1d would compute on it):
+    #   "strict": raise at once (one device->host read per call) -- the default;
+    #   "lazy"  : count such columns in a device-side flag without a sync; `check_inputs()` raises later
+    #             (StepPipeline reads the flag together with every loss it hands back).
+    input_check = "strict"
+
+    def _bad_flag(self, device):
+        flags = self.__dict__.setdefault("_bad_flags", {})
+        if device not in flags:
+            flags[device] = torch.zeros(1, dtype=torch.int32, device=device)
+        return flags[device]
+
+    def check_inputs(self):
+        """Raise if any float batch packed since the last check had non-one-hot columns ("lazy" mode)."""
+        for dev, flag in self.__dict__.get("_bad_flags", {}).items():
+            if int(flag.item()) != 0:
+                flag.zero_()
+                raise ValueError("input is not one-hot: a batch had columns that are neither one-hot nor all-zero "
+                                 "(explainn_b200 computes on the packed 2-bit layout)")
+
     def _pack(self, x):
         if isinstance(x, PackedDNA):
             return x.planes, x.length
@@ -203,7 +224,18 @@ class UnitBank(nn.Sequential):
         U = self[0].out_channels
         if x.shape[1] not in (4, 4 * U):
             raise ValueError(f"expected 4 or {4 * U} input channels, got {x.shape[1]}")
-        return ops.pack_onehot(x), x.shape[2]
+        if self.input_check == "strict" and not torch.cuda.is_current_stream_capturing():
+            return ops.pack_onehot(x, check=True), x.shape[2]
+        return ops.pack_onehot(x, bad=self._bad_flag(x.device)), x.shape[2]
+
+    def _check_kernel_size(self, training_path):
+        k = self[0].kernel_size[0]
+        lim = ops.kernel_size_limit(1 if training_path else 0)
+        if k > lim:
+            what = ("training (BatchNorm batch statistics, backward) and linears[:3] activations"
+                    if training_path else "the fused front end")
+            raise NotImplementedError(f"kernel_size {k}: {what} support kernel_size <= {lim} "
+                                      f"(eval forward / interpret / PWM scans: <= {ops.kernel_size_limit(0)})")
 
     def _front_affine(self, planes, L):
         """(scale, shift) of BN1 folded with the conv bias; batch statistics in train mode."""
@@ -229,6 +261,7 @@ class UnitBank(nn.Sequential):
         conv = self[0]
         if L < conv.kernel_size[0]:
             raise ValueError("sequence shorter than the kernel")
+        self._check_kernel_size(training_path=(kind == "acts" or self[1].training))
         if kind in ("acts", "pool"):
             with torch.no_grad():
                 cw, scale, shift = self._front_affine(planes, L)
@@ -323,6 +356,9 @@ class ExplaiNN(_Model):
             "n_features": n_features,
             "weights_file": weights_file,
         }
+        if kernel_size > ops.KERNEL_SIZE_MAX:
+            raise NotImplementedError(f"kernel_size {kernel_size}: the fused front end supports kernel_size <= "
+                                      f"{ops.KERNEL_SIZE_MAX} ({ops.KERNEL_SIZE_MAX_TRAIN} for training)")
         n = math.floor((sequence_length - kernel_size + 1) / 7.)
         self._channels_after_maxpool = n
         # same construction order as the reference, so the same seed gives the same initial weights
@@ -351,6 +387,10 @@ class ExplaiNN(_Model):
         """x: float32 one-hot (B,4,L) on CUDA (or PackedDNA) -> logits (B,F).  The reference's
         `x.repeat(1, cnn_units, 1)` (:111) is never materialised."""
         return self.final(self.linears(x, dropout_mask=dropout_mask))
+
+    def check_inputs(self):
+        """see UnitBank.input_check"""
+        self.linears.check_inputs()
 
 
 class PWM(nn.Module):

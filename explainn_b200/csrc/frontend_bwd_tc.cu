@@ -405,9 +405,8 @@ extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int
     cudaStream_t st = to_stream(s);
     const int slices = bt_slices(U, B);
     // MN-major Toeplitz view of the one-hot pair buffer: K-group (pool window) stride 112 B, N-chunk
-    // stride 32 B.  XNN_BWD_DESC_SWAP=1 exchanges the two fields (bring-up aid for the descriptor convention).
-    static const int swap = [] { const char* e = getenv("XNN_BWD_DESC_SWAP"); return e && e[0] == '1'; }();
-    const uint32_t lbo = swap ? 32u : 112u, sbo = swap ? 112u : 32u;
+    // stride 32 B (pinned by test_frontend_bwd_tensor_core_vs_brute_force).
+    const uint32_t lbo = 112u, sbo = 32u;
     XNN_CUDA(cudaFuncSetAttribute(frontend_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(bt_mtiles(U), slices);
     frontend_bwd_tc_kernel<<<grid, BT_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, k, n, bt_npad(k), Lbuf,

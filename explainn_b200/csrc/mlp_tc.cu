@@ -1238,8 +1238,6 @@ static int mb_grid(int B, int U) {
 static int mb_interleave(int B, int U) {
     const int G = mb_grid(B, U);
     const int P = (U + G / 2) / G;      // units per CTA, rounded
-    const char* e = getenv("XNN_MB_INTERLEAVE");
-    if (e) return atoi(e) < 1 ? 1 : atoi(e);
     return P < 1 ? 1 : P;
 }
 static int mb_slots(int B, int U) {

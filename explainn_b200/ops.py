@@ -12,6 +12,8 @@ from . import _lib
 
 HIDDEN = 100  # explainn/architectures/__init__.py:86
 POOL = 7      # explainn/architectures/__init__.py:81
+KERNEL_SIZE_MAX = 48        # xnn_kernel_size_limit(0): eval forward, interpret, PWM scans (tcgen05 Toeplitz kernels)
+KERNEL_SIZE_MAX_TRAIN = 32  # xnn_kernel_size_limit(1): training and linears[:3] activations
 
 _launches = 0  # C-ABI calls issued (bench.py reports kernel launches from the per-call table below)
 
@@ -28,20 +30,42 @@ KERNELS_PER_CALL = {
 kernel_launches = 0
 
 
+_seen_devices = []      # devices of the tensors handed to the C call being assembled (filled by _p)
+_STREAM = object()      # placeholder for "the current stream of those tensors' device", resolved in _call
+
+
 def _call(name, *args):
+    """One C-ABI call.  Every tensor of the call must live on ONE device; the call runs with that device
+    current (the library sizes grids from the current device) on that device's current torch stream."""
     global _launches, kernel_launches
     lib = _lib.load()
+    devs = set(_seen_devices)
+    _seen_devices.clear()
+    if len(devs) > 1:
+        raise RuntimeError(f"{name}: tensors on different devices {sorted(map(str, devs))}")
+    dev = devs.pop() if devs else torch.device("cuda", torch.cuda.current_device())
     _launches += 1
     kernel_launches += KERNELS_PER_CALL.get(name, 1)
-    _lib.check(getattr(lib, name)(*args), name)
+    if dev.index is not None and dev.index != torch.cuda.current_device():
+        with torch.cuda.device(dev):
+            return _call_on(lib, name, dev, args)
+    return _call_on(lib, name, dev, args)
+
+
+def _call_on(lib, name, dev, args):
+    st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(getattr(lib, name)(*[st if a is _STREAM else a for a in args]), name)
 
 
 def _p(t):
-    return None if t is None else ctypes.c_void_p(t.data_ptr())
+    if t is None:
+        return None
+    _seen_devices.append(t.device)
+    return ctypes.c_void_p(t.data_ptr())
 
 
 def _stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return _STREAM
 
 
 def _req(t, dtype, name, contiguous=True):
@@ -61,6 +85,15 @@ def planes_words(L):
     return (L + 31) // 32
 
 
+def kernel_size_limit(path):
+    return int(_lib.load().xnn_kernel_size_limit(int(path)))
+
+
+def set_sm_reserve(n):
+    """leave n SMs out of the persistent grids (for a concurrent NCCL all-reduce); 0 = use every SM"""
+    _lib.check(_lib.load().xnn_set_sm_reserve(int(n)), "xnn_set_sm_reserve")
+
+
 def sm_count():
     out = ctypes.c_int(0)
     _lib.check(_lib.load().xnn_sm_count(ctypes.byref(out)), "xnn_sm_count")
@@ -68,10 +101,13 @@ def sm_count():
 
 
 # ---- a16: encoding -------------------------------------------------------------
-def pack_onehot(x, check=False):
+def pack_onehot(x, check=False, bad=None):
     """float32 one-hot (B,C>=4,L) (channels 0..3 are read) -> planes int32 (B,3,ceil(L/32)).
 
-    Mirrors the input contract of explainn/sequence/__init__.py:8-29 (all-zero column = N)."""
+    Mirrors the input contract of explainn/sequence/__init__.py:8-29 (all-zero column = N).  A column that is
+    neither one-hot nor all-zero (soft encodings, 0.25 for N, perturbed inputs) cannot be expressed in the packed
+    layout: `check=True` raises on it (one device->host read); `bad` (int32 (1,) device tensor) accumulates the
+    number of such columns without a sync, for the caller to read later (UnitBank.check_inputs)."""
     _req(x, torch.float32, "x", contiguous=False)
     if x.dim() != 3 or x.shape[1] < 4:
         raise ValueError("x must be (B, 4*m, L)")
@@ -79,10 +115,13 @@ def pack_onehot(x, check=False):
         x = x.contiguous()
     B, _, L = x.shape
     planes = torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=x.device)
-    bad = torch.zeros(1, dtype=torch.int32, device=x.device) if check else None
+    if bad is None and check:
+        bad = torch.zeros(1, dtype=torch.int32, device=x.device)
     _call("xnn_pack_onehot_f32", _p(x), x.stride(0), x.stride(1), B, L, _p(planes), _p(bad), _stream())
     if check and int(bad.item()) != 0:
-        raise ValueError("input has columns that are neither one-hot nor all-zero")
+        raise ValueError("input is not one-hot: it has columns that are neither one-hot nor all-zero "
+                         "(explainn_b200 computes on the packed 2-bit layout; the reference's Conv1d accepts "
+                         "arbitrary floats)")
     return planes
 
 

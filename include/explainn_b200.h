@@ -47,6 +47,15 @@ int xnn_version(void);
 const char* xnn_last_error(void);
 /* number of SMs of the current device (grids are sized in multiples of it) */
 int xnn_sm_count(int* out);
+/* leave `n` SMs out of every persistent grid launched afterwards (0 = use all): data-parallel training
+ * reserves a few SMs so that the NCCL all-reduce of the MLP gradients (issued right after xnn_mlp_bwd) runs
+ * under xnn_frontend_bwd instead of behind it.  Process-wide; no counterpart in the reference (single device,
+ * explainn/selene/__init__.py:176-180). */
+int xnn_set_sm_reserve(int n);
+/* largest kernel_size: path 0 = eval forward / interpret / PWM scans on tcgen05 (48), path 1 = training
+ * (BatchNorm batch statistics, backward) and `linears[:3]` activations (32).  The reference module has no
+ * limit (explainn/architectures/__init__.py:44-45); explainn_b200.ExplaiNN validates against these. */
+int xnn_kernel_size_limit(int path);
 
 /* ---- a16: input contract, explainn/sequence/__init__.py:8-29,58-60 ------
  * one_hot_encode gives (4,L) rows A,C,G,T, any other letter an all-zero

@@ -157,6 +157,46 @@ def main():
                    opts=np.array([U, k, L, Fo, B]))
         np.savez_compressed(os.path.join(HERE, f"{tag}.npz"), **out)
 
+    # ---- 2b. the headline workload at its own shape (cfg3: U=300, L=600, F=50), B=32, p=0 -------------------
+    # The state dict is 10.6 MB: instead of three copies of it the fixture keeps what regenerates it (seed 0
+    # construction + randomise_bn(11), checked through per-key fp64 checksums), x as base codes, and for the 10 MB
+    # tensor linears.6.weight the gradient / updated rows of SAMPLED units plus per-unit norms of all of them.
+    U, k, L, Fo, B = 300, 19, 600, 50, 32
+    torch.manual_seed(0)
+    model = ExplaiNN(U, k, L, Fo)
+    randomise_bn(model, 11)
+    model.train()
+    model.linears[9].p = 0.0
+    x = random_onehot(B, L, 4321, 0.01)
+    y = torch.randn(B, Fo, generator=torch.Generator().manual_seed(99))
+    before = sd_np(model)
+    import architectures as ref_arch
+    crit, opt = ref_arch.get_loss("linear"), ref_arch.get_optimizer(model.parameters(), 0.003)
+    logits = model(x)
+    loss = crit(logits, y)
+    opt.zero_grad()
+    loss.backward()
+    grads = {k_: p.grad.detach().numpy().copy() for k_, p in model.named_parameters()}
+    opt.step()
+    after = sd_np(model)
+    units = np.array([0, 1, 57, 127, 128, 255, 256, 299])
+    codes = np.where(x.numpy().sum(1) > 0, x.numpy().argmax(1), 4).astype(np.uint8)
+    out = {"opts": np.array([U, k, L, Fo, B]), "codes": codes, "y": y.numpy(), "loss": loss.detach().numpy(),
+           "logits": logits.detach().numpy(), "units": units,
+           "sd_keys": np.array(list(before.keys())),
+           "sd_checksum": np.array([np.asarray(v, dtype=np.float64).sum() for v in before.values()])}
+    big = "linears.6.weight"
+    n_ = before[big].shape[1]
+    for tag_, dct in (("grad.", grads), ("after.", after)):
+        for k_, v in dct.items():
+            if k_ == big:
+                v3 = v.reshape(U, 100, n_)
+                out[tag_ + k_ + ".units"] = v3[units]
+                out[tag_ + k_ + ".unit_norms"] = np.sqrt((v3.astype(np.float64) ** 2).sum(axis=(1, 2)))
+            else:
+                out[tag_ + k_] = v
+    np.savez_compressed(os.path.join(HERE, "train_cfg3.npz"), **out)
+
     # ---- 3. interpret: thresholds + sites from the reference's own functions (a8, a9) -------------
     d = np.load(os.path.join(HERE, "eval_small.npz"))
     U, k, L, Fo, B = d["opts"]
@@ -252,6 +292,20 @@ def main():
         if os.path.exists(sp) and os.path.exists(mp) and os.path.getsize(sp) < 200000:
             fx[f"filter{i}"] = {"sites": open(sp).read(), "jaspar": open(mp).read()}
     json.dump(fx, open(os.path.join(HERE, "sites_jaspar_fixtures.json"), "w"))
+    # all 126 pairs, compact: the emitted k-mers of every sites file as ASCII bytes (N, k) + the JASPAR text
+    allfx, ids_ = {}, []
+    for i in range(1000):
+        sp, mp = os.path.join(cam, "sites", f"filter{i}.fa"), os.path.join(cam, "motifs", f"filter{i}.jaspar")
+        if not (os.path.exists(sp) and os.path.exists(mp)):
+            continue
+        kmers = [ln.strip() for ln in open(sp) if ln.strip() and ln[0] != ">"]
+        w = len(kmers[0]) if kmers else 0
+        assert all(len(s_) == w for s_ in kmers)
+        allfx[f"kmers{i}"] = np.frombuffer("".join(kmers).encode(), dtype=np.uint8).reshape(len(kmers), w)
+        allfx[f"jaspar{i}"] = np.array(open(mp).read())
+        ids_.append(i)
+    allfx["ids"] = np.array(ids_)
+    np.savez_compressed(os.path.join(HERE, "sites_jaspar_all.npz"), **allfx)
     print("golden vectors written to", HERE)
 
 

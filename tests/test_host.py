@@ -54,6 +54,66 @@ def test_module_surface_matches_reference_state_dict():
     assert np.array_equal(m2.final.weight.detach().numpy(), c["sd.final.weight"])
 
 
+def test_kernel_size_limits_agree_with_the_library():
+    from explainn_b200 import ops
+    from explainn_b200.architectures import ExplaiNN
+    assert ops.kernel_size_limit(0) == ops.KERNEL_SIZE_MAX and ops.kernel_size_limit(1) == ops.KERNEL_SIZE_MAX_TRAIN
+    ExplaiNN(3, ops.KERNEL_SIZE_MAX, 120, 1)                        # constructs (eval / interpret paths)
+    with pytest.raises(NotImplementedError, match="kernel_size"):
+        ExplaiNN(3, ops.KERNEL_SIZE_MAX + 1, 120, 1)
+
+
+def test_reference_call_sites_on_the_module_object(tmp_path):
+    """what the reference's trainer does to the model object besides calling it.
+    copy.deepcopy (selene/__init__.py:375), the checkpoint dict (:376-384) and its reload (:208-221),
+    `_Model.load_weights` (architectures/__init__.py:27-39), weight re-assignment (train.py:316-324)."""
+    import copy
+    from explainn_b200.architectures import ExplaiNN, get_optimizer
+    torch.manual_seed(0)
+    m = ExplaiNN(6, 19, 67, 2)
+    m2 = copy.deepcopy(m)
+    assert type(m2) is ExplaiNN and m2._options == m._options and m2._options is not m._options
+    for (k1, v1), (k2, v2) in zip(m.state_dict().items(), m2.state_dict().items()):
+        assert k1 == k2 and torch.equal(v1, v2) and v1.data_ptr() != v2.data_ptr()
+    # checkpoint dict round trip through torch.save / torch.load, optimizer state included
+    opt = get_optimizer(m.parameters(), 0.003)
+    ckpt = {"step": 7, "arch": m.__class__.__name__, "options": m._options, "state_dict": m.state_dict(),
+            "min_loss": 0.5, "optimizer": copy.deepcopy(opt.state_dict())}
+    path = tmp_path / "best_model.pth.tar"
+    torch.save(ckpt, path)
+    back = torch.load(path, weights_only=False)
+    assert back["arch"] == "ExplaiNN" and back["options"] == m._options
+    m3 = ExplaiNN(**{k: v for k, v in back["options"].items() if k != "weights_file"})
+    m3.load_state_dict(back["state_dict"])
+    get_optimizer(m3.parameters(), 0.003).load_state_dict(back["optimizer"])
+    # the same state dict loads into a stock torch.optim.Adam and vice versa (FusedAdam keeps Adam's layout)
+    ref_opt = torch.optim.Adam(m3.parameters(), lr=0.003)
+    ref_opt.load_state_dict(back["optimizer"])
+    assert ref_opt.state_dict()["param_groups"][0]["lr"] == 0.003
+    get_optimizer(m3.parameters(), 0.003).load_state_dict(ref_opt.state_dict())
+    # legacy positional loader: values are matched to keys by POSITION and a trailing size-1 dimension of every
+    # >= 2-d value is squeezed -- so a legacy file (one extra trailing dimension) loads under any key names ...
+    legacy = {f"w{i}": (v.unsqueeze(-1) if v.dim() >= 1 else v) for i, v in enumerate(m.state_dict().values())}
+    wpath = tmp_path / "legacy.pth"
+    torch.save(legacy, wpath)
+    m4 = ExplaiNN(6, 19, 67, 2, weights_file=str(wpath))
+    assert m4._options["weights_file"] == str(wpath)
+    for v1, v2 in zip(m.state_dict().values(), m4.state_dict().values()):
+        assert torch.equal(v1, v2)
+    # ... and, exactly like the reference's loader, the module's OWN state dict does not (its (100U,n,1) weights
+    # lose their last dimension): same exception type as the reference raises
+    torch.save(m.state_dict(), wpath)
+    with pytest.raises(RuntimeError, match="size mismatch"):
+        ExplaiNN(6, 19, 67, 2, weights_file=str(wpath))
+    # transfer learning: `linears[0].weight = nn.Parameter(...)` replaces the registered parameter
+    w = m.linears[0].weight.data
+    w[0] = 1.0
+    w.requires_grad = True
+    m.linears[0].weight = torch.nn.Parameter(w)
+    assert "linears.0.weight" in dict(m.named_parameters())
+    assert float(m.state_dict()["linears.0.weight"][0].min()) == 1.0
+
+
 def test_no_cpu_fallback():
     from explainn_b200.architectures import ExplaiNN, PWM
     m = ExplaiNN(4, 5, 30, 1).eval()

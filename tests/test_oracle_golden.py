@@ -48,6 +48,18 @@ def test_train_step_matches_reference(name, kind):
         U.assert_close(p1.numpy(), d["after." + k], rtol=1e-6, what="adam " + k)
 
 
+def test_train_step_cfg3_matches_reference():
+    """the headline workload at its own shape: ExplaiNN(300,19,600,50), B=32 (reference-generated fixture)"""
+    d, m, x, y = U.cfg3_golden()
+    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    r = O.explainn_train_step(sd, x, y, "linear")
+    U.assert_close(r["loss"].numpy(), d["loss"], rtol=1e-5, what="loss")
+    U.assert_close(r["logits"].numpy(), d["logits"], rtol=1e-5, what="logits")
+    U.check_cfg3_grads(d, {k: r["grads"][k].numpy() for k in O.PARAM_KEYS}, "oracle grad")
+    for k, v in r["running"].items():
+        U.assert_close(v.numpy(), d["after." + k], rtol=1e-5, what=k)
+
+
 def test_interpret_thresholds_and_sites():
     d = U.load_npz("interpret_small.npz")
     e = U.load_npz("eval_small.npz")
@@ -79,6 +91,18 @@ def test_sites_to_pfm_fixtures():
         ref = O.parse_jaspar(pair["jaspar"])
         pfm = O.sites_to_pfm(kmers, ref.shape[1])
         assert np.array_equal(pfm, ref.astype(np.int64)), name
+
+
+def test_sites_to_pfm_all_126_reference_fixtures():
+    """every results/Human-Mouse-Project/CAM/sites/filter*.fa -> motifs/filter*.jaspar pair of the reference
+    (k-mers stored as ASCII bytes): the restated per-column counts equal the Biopython output 126 / 126"""
+    d = U.load_npz("sites_jaspar_all.npz")
+    ids = d["ids"]
+    assert len(ids) == 126
+    for i in ids:
+        kmers = ["".join(map(chr, row)) for row in d[f"kmers{i}"]]
+        ref = O.parse_jaspar(str(d[f"jaspar{i}"]))
+        assert np.array_equal(O.sites_to_pfm(kmers, ref.shape[1]), ref.astype(np.int64)), f"filter{i}"
 
 
 def test_pwm_module_scores():
