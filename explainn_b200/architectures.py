@@ -18,6 +18,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from . import torch_ops  # noqa: F401  (registers torch.ops.explainn_b200.*)
 
 _FULL_KEYS = [str(i) for i in range(14)]
 
@@ -77,87 +78,11 @@ def _bn_momentum(bn):
     return bn.momentum
 
 
-class _UnitBankFn(torch.autograd.Function):
-    """Training-mode forward/backward of the whole unit bank (a3, a4, a6)."""
-
-    @staticmethod
-    def forward(ctx, planes, L, bank, drop_mask, conv_w, conv_b, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3):
-        bn1, bn2, bn3, drop = bank[1], bank[7], bank[11], bank[9]
-        B = planes.shape[0]
-        U, _, k = conv_w.shape
-        Lc = L - k + 1
-        n_pos = B * Lc
-        with torch.no_grad():
-            cnt1, cnt2 = ops.cooc_counts(planes, L, k)
-            scale1, shift1, stats1, cov_w = ops.bn1_train_prepare(
-                cnt1, cnt2, n_pos, conv_w, conv_b, g1, be1, bn1.eps, _bn_momentum(bn1),
-                bn1.running_mean, bn1.running_var)
-            pool, zmax, arg = ops.frontend_fwd(planes, L, conv_w, scale1, shift1, need_argmax=True)
-            p = float(drop.p) if drop.training else 0.0
-            seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and drop_mask is None) else 0
-            tc = ops.mlp_supported(pool.shape[2])
-            if tc:
-                # tensor-core path: the (B,100U) hidden activations are never materialised
-                scale2, shift2, stats2 = ops.mlp_bn2_train_prepare(
-                    pool, w1, b1, g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean, bn2.running_var)
-                opre, bits = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, drop_mask, want_bits=True)
-                hpre = None
-            else:
-                hpre = ops.fc1_fwd(pool, w1, b1)
-                scale2, shift2, stats2 = ops.bn_train_prepare(
-                    hpre.view(B, U * ops.HIDDEN), g2, be2, bn2.eps, _bn_momentum(bn2), bn2.running_mean,
-                    bn2.running_var)
-                opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, drop_mask)
-                bits = None
-            scale3, shift3, stats3 = ops.bn_train_prepare(
-                opre, g3, be3, bn3.eps, _bn_momentum(bn3), bn3.running_mean, bn3.running_var)
-            o, _ = ops.head_fwd(opre, scale3, shift3)
-            for bn in (bn1, bn2, bn3):
-                if bn.num_batches_tracked is not None:
-                    bn.num_batches_tracked += 1
-        ctx.save_for_backward(planes, conv_w, g1, w1, b1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
-                              scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, bits)
-        ctx.meta = (L, k, n_pos, p, seed, drop_mask, tc)
-        return o
-
-    @staticmethod
-    def backward(ctx, do):
-        (planes, conv_w, g1, w1, b1, g2, w2, g3, pool, zmax, arg, hpre, opre, o,
-         scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, bits) = ctx.saved_tensors
-        L, k, n_pos, p, seed, drop_mask, tc = ctx.meta
-        B, U = o.shape
-        n = pool.shape[2]
-        with torch.no_grad():
-            g = do.contiguous().clone()
-            dg3, dbe3, dopre = ops.bn_bwd(g, o, opre, stats3, g3)
-            if tc:
-                dw1, db1, dg2, dbe2, dw2, db2, dy = ops.mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, g2, w2,
-                                                                bits, p)
-            else:
-                dw2, db2, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, p, seed, drop_mask)
-                dg2, dbe2, dhpre = ops.bn_bwd(gh.view(B, U * ops.HIDDEN), None, hpre.view(B, U * ops.HIDDEN), stats2,
-                                              g2)
-                dw1, db1, dy = ops.fc1_bwd(dhpre.view(B, U, ops.HIDDEN), pool, w1)
-            dcw, dcb, dg1, dbe1 = ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos)
-        return (None, None, None, None, dcw, dcb, dg1, dbe1, dw1.view(U * ops.HIDDEN, n, 1), db1,
-                dg2, dbe2, dw2.view(U, ops.HIDDEN, 1), db2, dg3, dbe3)
-
-
-class _FinalLinearFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, w, b):
-        ctx.save_for_backward(x, w)
-        return ops.linear_fwd(x, w, b)
-
-    @staticmethod
-    def backward(ctx, dy):
-        x, w = ctx.saved_tensors
-        dx, dw, db = ops.linear_bwd(dy.contiguous(), w, x)
-        return dx, dw, db
-
-
 class FusedLinear(nn.Linear):
-    """`final` (architectures/__init__.py:104): nn.Linear parameters, our GEMM kernels."""
+    """`final` (architectures/__init__.py:104): nn.Linear parameters, our kernels through the
+    `explainn_b200::linear` custom op (autograd registered on the op: torch_ops.py)."""
+
+    _arena = None      # (flat gradient arena, [offset of dW, offset of db]) for the duration of ExplaiNN.forward
 
     def forward(self, x):
         w = _check_param(self.weight, "final.weight")
@@ -165,10 +90,8 @@ class FusedLinear(nn.Linear):
         if x.dtype != torch.float32 or not x.is_cuda:
             raise RuntimeError("final(x): x must be a float32 CUDA tensor")
         x2 = x.contiguous().view(-1, w.shape[1])
-        if torch.is_grad_enabled() and (x2.requires_grad or w.requires_grad or b.requires_grad):
-            y = _FinalLinearFn.apply(x2, w, b)
-        else:
-            y = ops.linear_fwd(x2.detach(), w.detach(), b.detach())
+        arena, offs = self._arena if (self._arena is not None and torch.is_grad_enabled()) else (None, [])
+        y = torch.ops.explainn_b200.linear(x2, w, b, arena, offs)
         return y.view(*x.shape[:-1], w.shape[0])
 
 
@@ -226,7 +149,7 @@ class UnitBank(nn.Sequential):
             raise ValueError(f"expected 4 or {4 * U} input channels, got {x.shape[1]}")
         if self.input_check == "strict" and not torch.cuda.is_current_stream_capturing():
             return ops.pack_onehot(x, check=True), x.shape[2]
-        return ops.pack_onehot(x, bad=self._bad_flag(x.device)), x.shape[2]
+        return torch.ops.explainn_b200.pack_onehot(x, self._bad_flag(x.device)), x.shape[2]
 
     def _check_kernel_size(self, training_path):
         k = self[0].kernel_size[0]
@@ -250,10 +173,32 @@ class UnitBank(nn.Sequential):
             n_pos = planes.shape[0] * (L - k + 1)
             scale, shift, _, _ = ops.bn1_train_prepare(cnt1, cnt2, n_pos, cw, cb, g1, be1, bn1.eps,
                                                        _bn_momentum(bn1), bn1.running_mean, bn1.running_var)
-            bn1.num_batches_tracked += 1
+            ops.counters_advance_list([bn1.num_batches_tracked])
         else:
             scale, shift = ops.bn_fold_eval(g1, be1, bn1.running_mean, bn1.running_var, cb, bn1.eps)
         return cw, scale, shift
+
+    _arena = None      # (flat gradient arena, offsets of the 12 parameter gradients) during ExplaiNN.forward
+    _draw = None       # device-resident dropout draw counter (int64 (1,)), used while a CUDA graph is captured
+
+    def _dropout_seed(self, p, dropout_mask, device):
+        """(host seed, device draw counter).  Eager: a fresh seed per call from torch's CPU generator (so
+        torch.manual_seed reproduces a run).  Under CUDA-graph capture a host seed would be baked into the graph:
+        the kernels then also mix in a device counter that the graph itself advances on every replay."""
+        if not (p > 0.0 and dropout_mask is None):
+            return 0, None
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        if not torch.cuda.is_current_stream_capturing():
+            return seed, None
+        if self._draw is None or self._draw.device != device:
+            raise RuntimeError("capturing a training step with dropout: call linears.enable_device_draws() first "
+                               "(the draw counter must exist before the capture starts)")
+        ops.counters_advance(self._draw)
+        return seed, self._draw
+
+    def enable_device_draws(self, device):
+        if self._draw is None or self._draw.device != torch.device(device):
+            self.__dict__["_draw"] = torch.zeros(1, dtype=torch.int64, device=device)
 
     def forward(self, x, dropout_mask=None):
         kind = self._kind()
@@ -265,9 +210,8 @@ class UnitBank(nn.Sequential):
         if kind in ("acts", "pool"):
             with torch.no_grad():
                 cw, scale, shift = self._front_affine(planes, L)
-                if kind == "acts":
-                    return ops.frontend_acts(planes, L, cw.detach(), scale, shift)[0]
-                return ops.frontend_fwd(planes, L, cw.detach(), scale, shift, need_argmax=False)[0]
+                op = torch.ops.explainn_b200.frontend_acts if kind == "acts" else torch.ops.explainn_b200.frontend_pool
+                return op(planes, L, cw.detach(), scale, shift)
         bn1, fc1, bn2, drop, fc2, bn3 = self[1], self[6], self[7], self[9], self[10], self[11]
         names = ["linears.0.weight", "linears.0.bias", "linears.1.weight", "linears.1.bias", "linears.6.weight",
                  "linears.6.bias", "linears.7.weight", "linears.7.bias", "linears.10.weight", "linears.10.bias",
@@ -275,40 +219,48 @@ class UnitBank(nn.Sequential):
         params = [conv.weight, conv.bias, bn1.weight, bn1.bias, fc1.weight, fc1.bias, bn2.weight, bn2.bias,
                   fc2.weight, fc2.bias, bn3.weight, bn3.bias]
         params = [_check_param(p, nme) for p, nme in zip(params, names)]
+        # the kernels address W1 as (100U, n) and W2 as (U, 100): same memory as the reference's (.., 1) shapes
         modes = (bn1.training, bn2.training, bn3.training)
         need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        eps = [bn1.eps, bn2.eps, bn3.eps]
+        p = float(drop.p) if drop.training else 0.0
+        if dropout_mask is not None and dropout_mask.dtype != torch.uint8:
+            raise TypeError("dropout_mask: expected a uint8 (B, cnn_units, 100) tensor")
         if all(modes):
-            if need_grad:
-                return _UnitBankFn.apply(planes, L, self, dropout_mask, *params)
+            if planes.shape[0] < 2:
+                raise ValueError("Expected more than 1 value per channel when training")
+            seed, seed_dev = self._dropout_seed(p, dropout_mask, planes.device)
+            arena, offs = self._arena if (need_grad and self._arena is not None) else (None, [])
+            outs = torch.ops.explainn_b200.unit_bank_train(planes, L, params, eps, p, seed, seed_dev, dropout_mask,
+                                                           arena, offs)
+            stats1, stats2, stats3 = outs[8], outs[9], outs[10]
+            B = planes.shape[0]
+            world = _world_for_stats()
+            counts = [float(B * (L - conv.kernel_size[0] + 1) * world), float(B * world), float(B * world)]
             with torch.no_grad():
-                return _UnitBankFn.forward(_NoCtx(), planes, L, self, dropout_mask, *[p.detach() for p in params])
+                bns = [b_ for b_ in (bn1, bn2, bn3)]
+                if all(b_.running_mean is not None and b_.running_var is not None for b_ in bns):
+                    nbt = [b_.num_batches_tracked for b_ in bns]
+                    torch.ops.explainn_b200.bn_running_update(
+                        [stats1, stats2, stats3], [b_.running_mean for b_ in bns], [b_.running_var for b_ in bns],
+                        nbt if all(t is not None for t in nbt) else [], [_bn_momentum(b_) for b_ in bns], counts)
+            return outs[0]
         if need_grad:
             raise NotImplementedError("backward through eval-mode BatchNorm is not implemented: "
                                       "call model.train() for training steps or wrap inference in torch.no_grad()")
         if any(modes):
             raise NotImplementedError("mixed train/eval BatchNorm modes inside the unit bank are not supported")
         with torch.no_grad():
-            cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = [p.detach() for p in params]
-            scale1, shift1 = ops.bn_fold_eval(g1, be1, bn1.running_mean, bn1.running_var, cb, bn1.eps)
-            pool, _, _ = ops.frontend_fwd(planes, L, cw, scale1, shift1, need_argmax=False)
-            scale2, shift2 = ops.bn_fold_eval(g2, be2, bn2.running_mean, bn2.running_var, None, bn2.eps)
-            p = float(drop.p) if drop.training else 0.0
-            seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if (p > 0.0 and dropout_mask is None) else 0
-            if ops.mlp_supported(pool.shape[2]):
-                opre, _ = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, p, seed, dropout_mask)
-            else:
-                hpre = ops.fc1_fwd(pool, w1, b1)
-                opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, p, seed, dropout_mask)
-            scale3, shift3 = ops.bn_fold_eval(g3, be3, bn3.running_mean, bn3.running_var, None, bn3.eps)
-            o, _ = ops.head_fwd(opre, scale3, shift3)
-            return o
+            seed, _ = self._dropout_seed(p, dropout_mask, planes.device)
+            running = [bn1.running_mean, bn1.running_var, bn2.running_mean, bn2.running_var, bn3.running_mean,
+                       bn3.running_var]
+            return torch.ops.explainn_b200.unit_bank_eval(planes, L, [q.detach() for q in params], running, eps, p,
+                                                          seed, dropout_mask)
 
 
-class _NoCtx:
-    """Stand-in ctx so the training forward can run without recording a graph."""
-
-    def save_for_backward(self, *a):
-        pass
+def _world_for_stats():
+    from . import torch_ops
+    return torch_ops._sync["world"] if torch_ops._sync["sum"] else 1
 
 
 class PackedDNA:
@@ -386,7 +338,68 @@ class ExplaiNN(_Model):
     def forward(self, x, dropout_mask=None):
         """x: float32 one-hot (B,4,L) on CUDA (or PackedDNA) -> logits (B,F).  The reference's
         `x.repeat(1, cnn_units, 1)` (:111) is never materialised."""
-        return self.final(self.linears(x, dropout_mask=dropout_mask))
+        arena = None
+        if torch.is_grad_enabled() and self.training:
+            arena = self._grad_arena()
+        if arena is None:
+            return self.final(self.linears(x, dropout_mask=dropout_mask))
+        self.linears._arena = (arena, self._arena_offs[2:])
+        self.final._arena = (arena, self._arena_offs[:2])
+        try:
+            return self.final(self.linears(x, dropout_mask=dropout_mask))
+        finally:
+            self.linears._arena = None
+            self.final._arena = None
+
+    # ---- flat gradient arena -------------------------------------------------------------------------------
+    # Layout (element offsets, each a multiple of 64 = 256 bytes):
+    #   [ final.weight, final.bias | conv_w, conv_b, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 ]
+    # with the conv / BN1 gradients -- the last ones the backward produces -- stored LAST in memory order
+    # (`arena_split`): everything before the split is complete when the MLP backward finishes and is
+    # all-reduced while the conv weight gradient is still being computed (parallel.GradBucket).
+    ARENA_ALIGN = 64
+
+    def _arena_plan(self):
+        names = ["final.weight", "final.bias", "linears.0.weight", "linears.0.bias", "linears.1.weight",
+                 "linears.1.bias", "linears.6.weight", "linears.6.bias", "linears.7.weight", "linears.7.bias",
+                 "linears.10.weight", "linears.10.bias", "linears.11.weight", "linears.11.bias"]
+        pd = dict(self.named_parameters())
+        order = [0, 1, 12, 13, 10, 11, 8, 9, 6, 7, 2, 3, 4, 5]     # memory order: MLP segment first, conv/BN1 last
+        offs, off, split = [0] * len(names), 0, 0
+        for i in order:
+            if i == 2:
+                split = off
+            offs[i] = off
+            off += -(-pd[names[i]].numel() // self.ARENA_ALIGN) * self.ARENA_ALIGN
+        return names, offs, off, split
+
+    def _grad_arena(self):
+        """the arena of THIS forward/backward: the persistent one (use_grad_arena) or a fresh allocation"""
+        names, offs, total, split = self._arena_plan()
+        self.__dict__["_arena_offs"] = offs
+        self.__dict__["arena_split"] = split
+        dev = self.final.weight.device
+        buf = self.__dict__.get("_arena_buf")
+        if buf is not None:
+            if buf.numel() != total or buf.device != dev:
+                raise RuntimeError("the persistent gradient arena no longer matches the parameters: call "
+                                   "use_grad_arena() again after changing / moving the model")
+            return buf
+        return torch.zeros(total, dtype=torch.float32, device=dev) if self.__dict__.get("_arena_zero") else \
+            torch.empty(total, dtype=torch.float32, device=dev)
+
+    def use_grad_arena(self, persistent=True):
+        """Keep ONE flat gradient buffer across steps (data-parallel buckets and CUDA graphs need stable addresses).
+        p.grad of every parameter then aliases it: a gradient kept from an earlier step is overwritten by the next
+        backward -- clone it if it must survive.  Returns the buffer."""
+        if not persistent:
+            self.__dict__.pop("_arena_buf", None)
+            return None
+        names, offs, total, split = self._arena_plan()
+        self.__dict__["_arena_buf"] = torch.zeros(total, dtype=torch.float32, device=self.final.weight.device)
+        self.__dict__["_arena_offs"] = offs
+        self.__dict__["arena_split"] = split
+        return self.__dict__["_arena_buf"]
 
     def check_inputs(self):
         """see UnitBank.input_check"""
@@ -422,13 +435,41 @@ class PWM(nn.Module):
             planes, L = ops.pack_onehot(x), x.shape[2]
         w = _check_param(self.conv1d.weight, "conv1d.weight")
         mode = "max" if self._options["scoring"] == "max" else "sum"
-        out, arg = ops.pwm_scan(planes, L, w, mode, want_argmax=return_argmax and mode == "max")
-        return (out, arg) if return_argmax else out
+        res = torch.ops.explainn_b200.pwm_scan(planes, L, w.detach(), mode, bool(return_argmax and mode == "max"))
+        return (res[0], res[1] if len(res) > 1 else None) if return_argmax else res[0]
+
+
+class _FusedLossMixin:
+    """nn.MSELoss / nn.BCEWithLogitsLoss with the default arguments, computed by the `explainn_b200::loss` custom op
+    (one reduction kernel forward, one elementwise kernel backward; no library kernels on the step path)."""
+    _kind = None
+
+    def forward(self, input, target):
+        if self.reduction != "mean" or getattr(self, "weight", None) is not None or \
+                getattr(self, "pos_weight", None) is not None:
+            raise NotImplementedError("the fused loss implements the reference's configuration only: 'mean' "
+                                      "reduction, no weights (architectures/__init__.py:446-456)")
+        if not (input.is_cuda and target.is_cuda):
+            raise RuntimeError("explainn_b200 losses run on CUDA tensors only; there is no CPU fallback")
+        if input.dtype != torch.float32 or target.dtype != torch.float32:
+            raise TypeError("the fused loss computes in float32")
+        if input.shape != target.shape:
+            raise ValueError(f"input {tuple(input.shape)} and target {tuple(target.shape)} must have the same shape")
+        return torch.ops.explainn_b200.loss(input.contiguous(), target.contiguous(), self._kind)
+
+
+class FusedMSELoss(_FusedLossMixin, nn.MSELoss):
+    _kind = "mse"
+
+
+class FusedBCEWithLogitsLoss(_FusedLossMixin, nn.BCEWithLogitsLoss):
+    _kind = "bce_logits"
 
 
 def get_loss(input_data="binary"):
-    """architectures/__init__.py:446-456"""
-    return nn.BCEWithLogitsLoss() if input_data == "binary" else nn.MSELoss()
+    """architectures/__init__.py:446-456: nn.BCEWithLogitsLoss() for "binary", nn.MSELoss() otherwise (subclasses
+    of those, so isinstance checks and attributes hold)"""
+    return FusedBCEWithLogitsLoss() if input_data == "binary" else FusedMSELoss()
 
 
 def get_metrics(input_data="binary"):

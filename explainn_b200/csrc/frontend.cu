@@ -93,6 +93,9 @@ extern "C" int xnn_cooc_counts(const uint32_t* planes, int B, int L, int k, long
                                xnn_stream_t s) {
     XNN_CHECK_ARG(planes && cnt1 && cnt2, "NULL pointer");
     XNN_CHECK_ARG(k >= 1 && k <= XNN_KMAX && L >= k && B >= 0, "bad sizes (kernel_size <= 32)");
+    // the kernel accumulates with atomics: the counts are cleared here (memset nodes, no library fill kernels)
+    XNN_CUDA(cudaMemsetAsync(cnt1, 0, (size_t)4 * k * sizeof(long long), to_stream(s)));
+    XNN_CUDA(cudaMemsetAsync(cnt2, 0, (size_t)16 * k * k * sizeof(long long), to_stream(s)));
     if (B == 0) return XNN_OK;
     const int Wp = planes_words(L);
     const int threads = ((16 * k + 31) / 32) * 32;

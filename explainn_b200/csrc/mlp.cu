@@ -672,7 +672,13 @@ struct AdamList {
 
 __global__ void __launch_bounds__(256)
 adam_multi_kernel(const __grid_constant__ AdamList L, float lr, float b1, float b2, float eps, float wd, float bc1,
-                  float bc2_sqrt, float grad_scale) {
+                  float bc2_sqrt, float grad_scale, const long long* __restrict__ step_dev) {
+    if (step_dev != nullptr) {
+        // device-resident step count (CUDA-graph replays): the same fp64 bias corrections the host computes
+        const double st = (double)*step_dev;
+        bc1 = (float)(1.0 - pow((double)b1, st));
+        bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, st));
+    }
     int t = 0;
     while (t + 1 < L.n && (int)blockIdx.x >= L.first_block[t + 1]) ++t;
     const long long base = (long long)((int)blockIdx.x - L.first_block[t]) * ADAM_CHUNK;
@@ -696,8 +702,9 @@ adam_multi_kernel(const __grid_constant__ AdamList L, float lr, float b1, float 
 extern "C" int xnn_adam_step_multi(int n_tensors, float* const* params, const float* const* grads,
                                    float* const* exp_avg, float* const* exp_avg_sq, const long long* numels, float lr,
                                    float beta1, float beta2, float eps, float weight_decay, long long step,
-                                   float grad_scale, xnn_stream_t s) {
-    XNN_CHECK_ARG(n_tensors >= 0 && step >= 1, "bad sizes");
+                                   const long long* step_dev, float grad_scale, xnn_stream_t s) {
+    XNN_CHECK_ARG(n_tensors >= 0 && (step >= 1 || step_dev != nullptr), "bad sizes");
+    if (step < 1) step = 1;
     XNN_CHECK_ARG(n_tensors == 0 || (params && grads && exp_avg && exp_avg_sq && numels), "NULL pointer");
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
@@ -718,7 +725,7 @@ extern "C" int xnn_adam_step_multi(int n_tensors, float* const* params, const fl
         if (L.n == 0) continue;
         L.first_block[L.n] = blocks;
         adam_multi_kernel<<<blocks, 256, 0, to_stream(s)>>>(L, lr, beta1, beta2, eps, weight_decay, (float)bc1,
-                                                            (float)sqrt(bc2), grad_scale);
+                                                            (float)sqrt(bc2), grad_scale, step_dev);
         XNN_CHECK_LAUNCH();
     }
     return XNN_OK;

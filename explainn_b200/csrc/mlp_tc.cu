@@ -107,6 +107,7 @@ struct MlpArgs {
     int B, U, n, T, slots;
     float drop_p;
     unsigned long long seed;
+    const unsigned long long* seed_dev;   // optional device-resident draw counter mixed into the seed (graph replays)
 };
 
 enum { MLP_STATS = 0, MLP_APPLY = 1, MLP_BWD_STATS = 2 };
@@ -260,6 +261,7 @@ mlp_fc1_kernel(MlpArgs a) {
     const int ntl = (int)(hi - lo);
     const float inv_keep = 1.0f / (1.0f - a.drop_p);
     const int C = U * MT_H;
+    const unsigned long long seed = a.seed + (a.seed_dev ? *a.seed_dev * 0x9E3779B97F4A7C15ull : 0ull);
 
     if (warp < WS_P_WARPS) {
         // ================= producers =================
@@ -457,8 +459,8 @@ mlp_fc1_kernel(MlpArgs a) {
                 // thread = (batch row, 64 hidden channels = keep-bit words 2cg, 2cg+1)
                 const long long bu = (long long)(b0 + row) * U + u;
                 uint32_t kbw[2], actw[2] = {0u, 0u};
-                kbw[0] = (row < rows) ? dropout_keep_word(a.drop_p, a.seed, bu, a.mask_u8, 2 * cg) : 0u;
-                kbw[1] = (row < rows) ? dropout_keep_word(a.drop_p, a.seed, bu, a.mask_u8, 2 * cg + 1) : 0u;
+                kbw[0] = (row < rows) ? dropout_keep_word(a.drop_p, seed, bu, a.mask_u8, 2 * cg) : 0u;
+                kbw[1] = (row < rows) ? dropout_keep_word(a.drop_p, seed, bu, a.mask_u8, 2 * cg + 1) : 0u;
                 float accv = 0.0f;
 #pragma unroll
                 for (int hh = 0; hh < 4; ++hh) {
@@ -815,8 +817,8 @@ extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, con
 
 extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
                            const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
-                           unsigned long long seed, const uint8_t* mask, uint32_t* maskbits, float* opre,
-                           xnn_stream_t s) {
+                           unsigned long long seed, const unsigned long long* seed_dev, const uint8_t* mask,
+                           uint32_t* maskbits, float* opre, xnn_stream_t s) {
     XNN_CHECK_ARG(pool && w1 && b1 && scale2 && shift2 && w2 && b2 && opre, "NULL pointer");
     XNN_CHECK_ARG(B >= 0 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
     XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
@@ -825,7 +827,7 @@ extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, 
     MlpArgs a{};
     a.pool = pool; a.w1 = w1; a.b1 = b1; a.scale2 = scale2; a.shift2 = shift2; a.w2 = w2; a.b2 = b2;
     a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = 0;
-    a.drop_p = drop_p; a.seed = seed; a.mask_u8 = mask; a.maskbits = maskbits; a.opre = opre;
+    a.drop_p = drop_p; a.seed = seed; a.seed_dev = seed_dev; a.mask_u8 = mask; a.maskbits = maskbits; a.opre = opre;
     if (mt_launch<MLP_APPLY>(a, to_stream(s))) { set_error("xnn_mlp_fwd: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
     return XNN_OK;
 }

@@ -25,7 +25,7 @@ KERNELS_PER_CALL = {
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
     "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_lpm_scan_best_parts": 5, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
-    "xnn_adam_step_multi": 1, "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
+    "xnn_adam_step_multi": 1, "xnn_counters_advance": 1, "xnn_counters_advance_list": 1, "xnn_bn_running_update": 1, "xnn_loss_fwd": 1, "xnn_loss_bwd": 1, "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
 }
 kernel_launches = 0
 
@@ -101,7 +101,7 @@ def sm_count():
 
 
 # ---- a16: encoding -------------------------------------------------------------
-def pack_onehot(x, check=False, bad=None):
+def pack_onehot(x, check=False, bad=None, out=None):
     """float32 one-hot (B,C>=4,L) (channels 0..3 are read) -> planes int32 (B,3,ceil(L/32)).
 
     Mirrors the input contract of explainn/sequence/__init__.py:8-29 (all-zero column = N).  A column that is
@@ -114,7 +114,7 @@ def pack_onehot(x, check=False, bad=None):
     if x.stride(2) != 1:
         x = x.contiguous()
     B, _, L = x.shape
-    planes = torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=x.device)
+    planes = _planes_out(out, B, L, x.device)
     if bad is None and check:
         bad = torch.zeros(1, dtype=torch.int32, device=x.device)
     _call("xnn_pack_onehot_f32", _p(x), x.stride(0), x.stride(1), B, L, _p(planes), _p(bad), _stream())
@@ -125,11 +125,20 @@ def pack_onehot(x, check=False, bad=None):
     return planes
 
 
-def pack_ascii(seqs):
+def _planes_out(out, B, L, dev):
+    if out is None:
+        return torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=dev)
+    _req(out, torch.int32, "out")
+    if tuple(out.shape) != (B, 3, planes_words(L)):
+        raise ValueError(f"out: expected planes of shape {(B, 3, planes_words(L))}, got {tuple(out.shape)}")
+    return out
+
+
+def pack_ascii(seqs, out=None):
     """uint8 ASCII (B,L) -> planes."""
     _req(seqs, torch.uint8, "seqs")
     B, L = seqs.shape
-    planes = torch.empty((B, 3, planes_words(L)), dtype=torch.int32, device=seqs.device)
+    planes = _planes_out(out, B, L, seqs.device)
     _call("xnn_pack_ascii", _p(seqs), seqs.stride(0), B, L, _p(planes), _stream())
     return planes
 
@@ -152,8 +161,8 @@ def revcomp_planes(planes, L):
 # ---- a3: front end -----------------------------------------------------------------
 def cooc_counts(planes, L, k):
     _req(planes, torch.int32, "planes")
-    cnt1 = torch.zeros(4 * k, dtype=torch.int64, device=planes.device)
-    cnt2 = torch.zeros((4 * k, 4 * k), dtype=torch.int64, device=planes.device)
+    cnt1 = torch.empty(4 * k, dtype=torch.int64, device=planes.device)      # cleared by the call itself
+    cnt2 = torch.empty((4 * k, 4 * k), dtype=torch.int64, device=planes.device)
     _call("xnn_cooc_counts", _p(planes), planes.shape[0], L, k, _p(cnt1), _p(cnt2), _stream())
     return cnt1, cnt2
 
@@ -227,7 +236,7 @@ def _work(nbytes, dev):
     return torch.empty((int(nbytes) + 7) // 8, dtype=torch.float64, device=dev)
 
 
-def bn_train_prepare(x2d, gamma, beta, eps, momentum, running_mean, running_var):
+def bn_train_prepare(x2d, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1):
     """x2d: (B, C) view of the BatchNorm input; returns scale, shift, stats."""
     B, C = x2d.shape
     if B < 2:
@@ -257,7 +266,7 @@ def mlp_supported(n):
     return bool(_lib.load().xnn_mlp_supported(int(n)))
 
 
-def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var):
+def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1):
     """BatchNorm (linears.7) batch statistics of hpre = FC1(pool) without materialising hpre (tcgen05)."""
     B, U, n = pool.shape
     if B < 2:
@@ -275,8 +284,9 @@ def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean
     return scale, shift, stats
 
 
-def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None, want_bits=False):
-    """opre (B,U) = FC2(drop(relu(BN2(FC1(pool))))) in one tcgen05 pass; optional keep-bits (B,U,4) int32."""
+def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None, want_bits=False, seed_dev=None):
+    """opre (B,U) = FC2(drop(relu(BN2(FC1(pool))))) in one tcgen05 pass; optional keep-bits (B,U,4) int32.
+    seed_dev: int64 (1,) device draw counter mixed into the seed (CUDA-graph replays)."""
     B, U, n = pool.shape
     dev = pool.device
     opre = torch.empty((B, U), dtype=torch.float32, device=dev)
@@ -285,22 +295,35 @@ def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None,
         _req(mask, torch.uint8, "mask")
     _call("xnn_mlp_fwd", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")), _p(b1),
           _p(scale2), _p(shift2), _p(_req(w2, torch.float32, "w2")), _p(b2), B, U, n, float(drop_p), int(seed),
-          _p(mask), _p(bits), _p(opre), _stream())
+          _p(seed_dev), _p(mask), _p(bits), _p(opre), _stream())
     return opre, bits
 
 
-def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p):
-    """Backward of FC1 -> BN2 -> ReLU -> dropout -> FC2 from dopre (B,U); see xnn_mlp_bwd."""
+def _outs(out, shapes, dev):
+    """`out`: None (allocate) or a list of preallocated contiguous fp32 tensors with these element counts (views
+    of the flat gradient arena: the backward kernels write the gradients where the all-reduce and Adam read them)"""
+    if out is None:
+        return [torch.empty(sh, dtype=torch.float32, device=dev) for sh in shapes]
+    if len(out) != len(shapes):
+        raise ValueError("out: wrong number of tensors")
+    for t, sh in zip(out, shapes):
+        _req(t, torch.float32, "out")
+        numel = 1
+        for d in sh:
+            numel *= int(d)
+        if t.numel() != numel:
+            raise ValueError(f"out: expected {numel} elements, got {t.numel()}")
+    return list(out)
+
+
+def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p, out=None, sync=None, world=1):
+    """Backward of FC1 -> BN2 -> ReLU -> dropout -> FC2 from dopre (B,U); see xnn_mlp_bwd.
+    out: optional [dw1, db1, dg2, dbe2, dw2, db2] destinations."""
     B, U, n = pool.shape
     dev = pool.device
     lib = _lib.load()
     C = U * HIDDEN
-    dw1 = torch.empty((C, n), dtype=torch.float32, device=dev)
-    db1 = torch.empty(C, dtype=torch.float32, device=dev)
-    dg2 = torch.empty(C, dtype=torch.float32, device=dev)
-    dbe2 = torch.empty(C, dtype=torch.float32, device=dev)
-    dw2 = torch.empty((U, HIDDEN), dtype=torch.float32, device=dev)
-    db2 = torch.empty(U, dtype=torch.float32, device=dev)
+    dw1, db1, dg2, dbe2, dw2, db2 = _outs(out, [(C, n), (C,), (C,), (C,), (U, HIDDEN), (U,)], dev)
     dy = torch.empty_like(pool)
     nbytes = int(lib.xnn_mlp_bwd_work_bytes(B, U, n))
     work = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
@@ -335,26 +358,24 @@ def linear_fwd(x, w, b):
 
 
 # ---- a6: backward ----------------------------------------------------------------------
-def linear_bwd(dy, w, x):
+def linear_bwd(dy, w, x, out=None):
     B, F = dy.shape
     U = w.shape[1]
     dev = dy.device
     lib = _lib.load()
     dx = torch.empty((B, U), dtype=torch.float32, device=dev)
-    dw = torch.empty((F, U), dtype=torch.float32, device=dev)
-    db = torch.empty(F, dtype=torch.float32, device=dev)
+    dw, db = _outs(out, [(F, U), (F,)], dev)
     work = _work(lib.xnn_linear_bwd_work_bytes(B, U, F), dev)
     _call("xnn_linear_bwd", _p(_req(dy, torch.float32, "dy")), _p(w), _p(_req(x, torch.float32, "x")), B, U, F,
           _p(dx), _p(dw), _p(db), _p(work), _stream())
     return dx, dw, db
 
 
-def bn_bwd(g2d, relu_out, xpre2d, stats, gamma, inplace=True):
+def bn_bwd(g2d, relu_out, xpre2d, stats, gamma, inplace=True, out=None, sync=None, world=1):
     B, C = g2d.shape
     dev = g2d.device
     lib = _lib.load()
-    dgamma = torch.empty(C, dtype=torch.float32, device=dev)
-    dbeta = torch.empty(C, dtype=torch.float32, device=dev)
+    dgamma, dbeta = _outs(out, [(C,), (C,)], dev)
     dx = g2d if inplace else torch.empty_like(g2d)
     work = _work(lib.xnn_bn_work_bytes(B, C), dev)
     _call("xnn_bn_bwd", _p(_req(g2d, torch.float32, "g")), _p(relu_out), _p(_req(xpre2d, torch.float32, "xpre")),
@@ -388,14 +409,11 @@ def fc1_bwd(dhpre, pool, w1):
     return dw1, db1, dy
 
 
-def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos, simt=False):
+def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos, simt=False, out=None):
     B, U, n = dy.shape
     dev = dy.device
     lib = _lib.load()
-    dconv_w = torch.empty((U, 4, k), dtype=torch.float32, device=dev)
-    dconv_b = torch.empty(U, dtype=torch.float32, device=dev)
-    dgamma = torch.empty(U, dtype=torch.float32, device=dev)
-    dbeta = torch.empty(U, dtype=torch.float32, device=dev)
+    dconv_w, dconv_b, dgamma, dbeta = _outs(out, [(U, 4, k), (U,), (U,), (U,)], dev)
     work = _work(lib.xnn_frontend_bwd_work_bytes(B, U, k), dev)
     _call("xnn_frontend_bwd_simt" if simt else "xnn_frontend_bwd", _p(planes), B, L, U, k,
           _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
@@ -534,9 +552,76 @@ def ipwm_scan_best(codes, offsets, pwm, forward_only=False):
     return best, pos, strand
 
 
-def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
+def counters_advance(counters):
+    """counters (int64 device tensor, <= 32 values) += 1: the device-resident Adam step / dropout draw counters"""
+    _req(counters, torch.int64, "counters")
+    _call("xnn_counters_advance", _p(counters), counters.numel(), _stream())
+
+
+def counters_advance_list(tensors):
+    """every int64 scalar tensor of the list += 1 in one launch (BatchNorm's num_batches_tracked buffers)"""
+    ts = [t for t in tensors if t is not None]
+    if not ts:
+        return
+    for t in ts:
+        _req(t, torch.int64, "counter")
+        _seen_devices.append(t.device)
+    arr = (ctypes.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    _call("xnn_counters_advance_list", len(ts), arr, _stream())
+
+
+def bn_running_update(stats, running_means, running_vars, nbts, momenta, counts):
+    """running statistics (+ num_batches_tracked) of up to 4 train-mode BatchNorm layers in one launch"""
+    n = len(stats)
+    for t in stats:
+        _req(t, torch.float64, "stats")
+        _seen_devices.append(t.device)
+    for t in list(running_means) + list(running_vars):
+        _req(t, torch.float32, "running statistics")
+    P = ctypes.c_void_p * n
+    nb = P(*[(None if t is None else t.data_ptr()) for t in nbts]) if nbts is not None else None
+    _call("xnn_bn_running_update", n, P(*[t.data_ptr() for t in stats]), P(*[t.data_ptr() for t in running_means]),
+          P(*[t.data_ptr() for t in running_vars]), nb, (ctypes.c_int * n)(*[t.shape[0] for t in stats]),
+          (ctypes.c_float * n)(*[float(m) for m in momenta]), (ctypes.c_double * n)(*[float(c) for c in counts]),
+          _stream())
+
+
+_loss_work = {}
+
+
+def _loss_workspace(dev):
+    w = _loss_work.get(dev)
+    if w is None:
+        w = _loss_work[dev] = torch.zeros((int(_lib.load().xnn_loss_work_bytes()) + 7) // 8, dtype=torch.float64,
+                                          device=dev)
+    return w
+
+
+LOSS_KINDS = {"mse": 0, "bce_logits": 1}
+
+
+def loss_fwd(logits, target, kind):
+    """mean MSE / BCE-with-logits over all elements -> float32 scalar tensor (architectures/__init__.py:446-456)"""
+    _req(logits, torch.float32, "logits")
+    _req(target, torch.float32, "target")
+    if logits.shape != target.shape:
+        raise ValueError(f"loss: input {tuple(logits.shape)} and target {tuple(target.shape)} differ in shape")
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    _call("xnn_loss_fwd", _p(logits), _p(target), logits.numel(), LOSS_KINDS[kind], _p(loss),
+          _p(_loss_workspace(logits.device)), _stream())
+    return loss
+
+
+def loss_bwd(logits, target, grad_out, kind):
+    dl = torch.empty_like(logits)
+    _call("xnn_loss_bwd", _p(logits), _p(target), _p(grad_out), logits.numel(), LOSS_KINDS[kind], _p(dl), _stream())
+    return dl
+
+
+def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0,
+                    step_dev=None):
     """One launch for a list of parameter tensors that share `step` (xnn_adam_step_multi); bit-identical to
-    adam_step per tensor."""
+    adam_step per tensor.  step_dev: int64 (1,) device tensor holding the step count (CUDA-graph replays)."""
     n = len(params)
     if not (len(grads) == len(exp_avgs) == len(exp_avg_sqs) == n):
         raise ValueError("adam_step_multi: lists of different lengths")
@@ -548,8 +633,10 @@ def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps,
     arr = ctypes.c_void_p * n
     ptrs = [arr(*[t.data_ptr() for t in lst]) for lst in (params, grads, exp_avgs, exp_avg_sqs)]
     numels = (ctypes.c_longlong * n)(*[t.numel() for t in params])
+    for t in params:
+        _seen_devices.append(t.device)
     _call("xnn_adam_step_multi", n, ptrs[0], ptrs[1], ptrs[2], ptrs[3], numels, float(lr), float(beta1), float(beta2),
-          float(eps), float(weight_decay), int(step), float(grad_scale), _stream())
+          float(eps), float(weight_decay), int(step), _p(step_dev), float(grad_scale), _stream())
 
 
 # ---- validation metrics (explainn_b200/metrics.py is the reference-facing surface) ----

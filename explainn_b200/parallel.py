@@ -35,17 +35,102 @@ def shard_range(n, rank, world):
 
 
 class GradBucket:
-    """Flat fp32 bucket over the gradients of `params`: pack -> one all-reduce -> unpack (mean)."""
+    """The gradient exchange of data-parallel training over the model's FLAT gradient arena
+    (ExplaiNN.use_grad_arena): the backward kernels write every parameter gradient into one fp32 buffer, so the
+    exchange is all-reduce(SUM) on that buffer in place -- no pack / unpack copies -- and the 1/world factor is folded
+    into Adam's `grad_scale` (`scale`).
 
-    def __init__(self, params):
-        self.params = [p for p in params if p.requires_grad]
-        self.numel = sum(p.numel() for p in self.params)
+    overlap: the arena keeps the conv / BN1 gradients (the LAST ones the backward produces, 23 K values at cfg3)
+    behind `model.arena_split`; everything before it (W1 = 9.96 of the 10.6 MB) is complete when xnn_mlp_bwd
+    finishes.  That segment's all-reduce is issued from inside the backward (torch_ops._after_mlp_grads) on NCCL's
+    stream, under xnn_frontend_bwd; `sm_reserve` SMs are left out of the persistent grids so that the NCCL kernel has
+    somewhere to run.  Gradients that an autograd hook replaced (selene/__init__.py:254-257 freezes filters that way)
+    do not live in the arena: they are copied in before their segment is reduced, and a hook on an MLP-segment
+    parameter switches the early all-reduce off.
+
+    Works for any list of parameters too (`GradBucket(params)`): then it is the plain pack -> all-reduce -> unpack."""
+
+    def __init__(self, model_or_params, group=None, overlap=True, sm_reserve=8):
+        self.group = group
+        self.model = model_or_params if hasattr(model_or_params, "use_grad_arena") else None
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.scale = 1.0 / self.world
+        self._early = None
         self.flat = None
+        if self.model is None:
+            self.params = [p for p in model_or_params if p.requires_grad]
+            self.numel = sum(p.numel() for p in self.params)
+            return
+        m = self.model
+        self.arena = m.use_grad_arena()
+        names, offs, total, split = m._arena_plan()
+        pd = dict(m.named_parameters())
+        self.slots = [(pd[nm], off) for nm, off in zip(names, offs)]
+        self.params = [p for p, _ in self.slots]
+        self.split, self.numel = split, total
+        self.overlap = bool(overlap) and self.world > 1 and split > 0
+        if self.overlap:
+            from . import ops, torch_ops
+            torch_ops._after_mlp_grads.append(self._after_mlp_grads)
+            ops.set_sm_reserve(sm_reserve)
+
+    def close(self):
+        if self.model is not None and self.overlap:
+            from . import ops, torch_ops
+            if self._after_mlp_grads in torch_ops._after_mlp_grads:
+                torch_ops._after_mlp_grads.remove(self._after_mlp_grads)
+            ops.set_sm_reserve(0)
+
+    # -- arena path ----------------------------------------------------------------------------------------
+    def _after_mlp_grads(self, arena):
+        if arena is not self.arena:
+            return
+        if any(p._backward_hooks for p, off in self.slots if off < self.split):
+            return                                  # a hook may still replace one of these gradients
+        self._early = dist.all_reduce(self.arena[:self.split], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def _adopt(self, lo, hi):
+        """gradients of [lo, hi) that do not live in the arena (hooks, accumulation) are copied into it"""
+        for p, off in self.slots:
+            if not (lo <= off < hi):
+                continue
+            n = p.numel()
+            view = self.arena[off:off + n]
+            if p.grad is None:
+                view.zero_()
+            elif p.grad.data_ptr() != view.data_ptr():
+                view.copy_(p.grad.reshape(-1))
+            else:
+                continue
+            p.grad = view.view_as(p)
+
+    def allreduce_sum(self):
+        """After backward: all gradients summed over the ranks, in the arena; multiply by `scale` (Adam's
+        grad_scale) for the mean."""
+        if self.world == 1:
+            return
+        if self.model is None:
+            return self._allreduce_list(mean=False)
+        early, self._early = self._early, None
+        if early is None:
+            self._adopt(0, self.numel)
+            dist.all_reduce(self.arena, op=dist.ReduceOp.SUM, group=self.group)
+            return
+        self._adopt(self.split, self.numel)
+        dist.all_reduce(self.arena[self.split:], op=dist.ReduceOp.SUM, group=self.group)
+        early.wait()
 
     def allreduce_mean(self, group=None):
-        world = dist.get_world_size(group) if dist.is_initialized() else 1
-        if world == 1:
+        """gradients averaged over the ranks (the reference-style call: p.grad holds the mean afterwards)"""
+        if self.world == 1:
             return
+        if self.model is None:
+            return self._allreduce_list(mean=True)
+        self.allreduce_sum()
+        self.arena.mul_(self.scale)
+
+    # -- list path -----------------------------------------------------------------------------------------
+    def _allreduce_list(self, mean):
         p0 = self.params[0]
         if self.flat is None or self.flat.device != p0.device:
             self.flat = torch.empty(self.numel, dtype=torch.float32, device=p0.device)
@@ -57,8 +142,9 @@ class GradBucket:
             else:
                 self.flat[off:off + n].copy_(p.grad.reshape(-1))
             off += n
-        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
-        self.flat.mul_(1.0 / world)
+        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+        if mean:
+            self.flat.mul_(1.0 / self.world)
         off = 0
         for p in self.params:
             n = p.numel()

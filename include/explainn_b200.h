@@ -83,7 +83,7 @@ int xnn_revcomp_planes(const uint32_t* planes, int B, int L, uint32_t* out, xnn_
  *   cnt1 int64 [4k]      : s[(c,j)]   = #{(b,p): base(b,p+j)=c}
  *   cnt2 int64 [4k][4k]  : S[(c,j),(c',j')] = #{(b,p): base(p+j)=c & base(p+j')=c'}
  * feature index = c*k + j (same order as the conv weight's (4,k) block).
- * Both buffers are accumulated into (zero them first). */
+ * Both buffers are cleared by the call (cudaMemsetAsync on the stream) before the kernel accumulates. */
 int xnn_cooc_counts(const uint32_t* planes, int B, int L, int k,
                     long long* cnt1, long long* cnt2, xnn_stream_t s);
 /* From counts + weights: batch mean/var of z (biased), the per-unit affine
@@ -166,11 +166,13 @@ int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b
  * Dropout: injected byte mask (B,U,100), else Philox keep-bits from (seed,b,u) when drop_p > 0.
  * maskbits uint32 [B][U][4] (NULL in inference): bit m of a (b,u) row = hidden channel m is ACTIVE (kept by
  * dropout and BN2 output > 0).  xnn_mlp_bwd reuses exactly this decision, so the gradient is the one of
- * the forward that was computed even where a recomputed pre-activation rounds to the other side of 0. */
+ * the forward that was computed even where a recomputed pre-activation rounds to the other side of 0.
+ * seed_dev (optional): a device-resident draw counter; the effective seed is seed + *seed_dev * 0x9E3779B97F4A7C15,
+ * so a captured CUDA graph draws a new mask on every replay (xnn_counters_advance moves the counter). */
 int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
                 const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
-                unsigned long long seed, const uint8_t* mask, uint32_t* maskbits, float* opre,
-                xnn_stream_t s);
+                unsigned long long seed, const unsigned long long* seed_dev, const uint8_t* mask,
+                uint32_t* maskbits, float* opre, xnn_stream_t s);
 
 /* ---- a6: backward ---------------------------------------------------------
  * autograd of the above (selene/__init__.py:289-292). Gradients are shaped
@@ -246,10 +248,35 @@ int xnn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
  * arrays are HOST arrays of device pointers / element counts, read before the call
  * returns; all tensors share step (torch.optim.Adam steps them together).  Results
  * are bit-identical to n_tensors calls of xnn_adam_step. */
+/* step_dev (optional): the step count read from DEVICE memory instead (a captured CUDA graph must not bake the
+ * host's step into its bias corrections); `step` is then ignored. */
 int xnn_adam_step_multi(int n_tensors, float* const* params, const float* const* grads,
                         float* const* exp_avg, float* const* exp_avg_sq, const long long* numels,
                         float lr, float beta1, float beta2, float eps, float weight_decay,
-                        long long step, float grad_scale, xnn_stream_t s);
+                        long long step, const long long* step_dev, float grad_scale, xnn_stream_t s);
+
+/* ---- step-level pieces (no host scalars, no library kernels inside the training step) ----------------------
+ * counters[i] += 1 for i < n: the device-resident Adam step and dropout draw counters. */
+int xnn_counters_advance(long long* counters, int n, xnn_stream_t s);
+/* *ptrs[i] += 1 for up to 8 counters in separate allocations (ptrs is a HOST array of device pointers): the
+ * num_batches_tracked buffers of the three BatchNorm layers (architectures/__init__.py:79,90,99). */
+int xnn_counters_advance_list(int n, long long* const* ptrs, xnn_stream_t s);
+/* nn.BatchNorm1d's running-statistics update of up to 4 train-mode layers (+ num_batches_tracked += 1 where the
+ * pointer is not NULL) in one launch, from the `stats` rows (mean, biased variance, invstd, -) the statistics
+ * calls produced: running = (1-momentum)*running + momentum*(mean | var*count/(count-1))
+ * (architectures/__init__.py:79,90,99).  All array arguments are HOST arrays of n_layers entries; count = values
+ * per channel (B*L' for linears.1, B for linears.7 / .11; the global batch under synchronised statistics). */
+int xnn_bn_running_update(int n_layers, const double* const* stats, float* const* running_mean,
+                          float* const* running_var, long long* const* num_batches_tracked,
+                          const int* channels, const float* momentum, const double* count, xnn_stream_t s);
+/* explainn/architectures/__init__.py:446-456: nn.MSELoss() (kind 0) / nn.BCEWithLogitsLoss() (kind 1), 'mean'
+ * reduction over the n = B*F elements; deterministic (fp64 partials added in block order).
+ * xnn_loss_bwd: dlogits = grad_out[0] * d(loss)/d(logits); grad_out is a DEVICE scalar (NULL = 1). */
+size_t xnn_loss_work_bytes(void);
+int xnn_loss_fwd(const float* logits, const float* target, long long n, int kind, float* loss, void* work,
+                 xnn_stream_t s);
+int xnn_loss_bwd(const float* logits, const float* target, const float* grad_out, long long n, int kind,
+                 float* dlogits, xnn_stream_t s);
 
 /* ---- a7-a10: interpret ------------------------------------------------------
  * test.py:128-166 (fp16 activations), interpret.py:363-454. */

@@ -766,3 +766,204 @@ def test_cfg1_strand_symmetry_property():
     res = I.sites_and_pfms(m, both, t_both, None, True)
     assert (res["pfms"].sum(1) <= res["counts"][:, None]).all()      # every site adds at most 1 per column
     assert (res["pfms"].sum(1).max(1) == res["counts"]).all()        # no N bases in this input: exactly 1
+
+
+# ---------------------------------------------------------------------------------------------------
+# 8(b): the reference's call sites on the model object, the custom-op registration, the step pipeline
+# ---------------------------------------------------------------------------------------------------
+def _plain_steps(m, batches, kind="linear", lr=0.003):
+    """the reference's loop, selene/__init__.py:283-295"""
+    from explainn_b200.architectures import get_loss, get_optimizer
+    crit, opt = get_loss(kind), get_optimizer(m.parameters(), lr)
+    losses = []
+    for x, y in batches:
+        pred = m(x.to(DEV))
+        loss = crit(pred, y.to(DEV))
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    return losses, opt
+
+
+def test_grad_hook_weight_reassignment_and_deepcopy():
+    """selene/__init__.py:254-257,509-515 (freeze_top_n_filters hook on linears[0].weight), train.py:316-324
+    (`linears[0].weight = nn.Parameter(...)`), selene/__init__.py:375 (copy.deepcopy of the live model)"""
+    import copy
+    from functools import partial
+    m = _random_model(12, 19, 88, 3).train().to(DEV)
+    m.linears[9].p = 0.0
+    x = O.random_onehot(24, 88, seed=5, n_frac=0.02).to(DEV)
+    y = torch.randn(24, 3, generator=torch.Generator().manual_seed(1)).to(DEV)
+    # transfer learning: new conv filters assigned as a fresh Parameter
+    w = m.linears[0].weight.data
+    w[:4] = torch.randn(4, 4, 19, generator=torch.Generator().manual_seed(2)).to(DEV) * 0.3
+    w.requires_grad = True
+    m.linears[0].weight = torch.nn.Parameter(w)
+    sd = _sd_cpu(m)
+    ref = O.explainn_train_step(sd, x.cpu(), y.cpu(), "linear")
+    m2 = copy.deepcopy(m)                                 # before any step: same parameters, separate storage
+    torch.nn.functional.mse_loss(m(x), y).backward()
+    g_free = m.linears[0].weight.grad.clone()
+    U.assert_close(g_free.cpu().numpy(), ref["grads"]["linears.0.weight"].numpy(), rtol=2e-4, atol_scale=2e-5,
+                   what="grad of the re-assigned conv weight")
+
+    def freeze_top_n_filters(grad, freeze_top_n_filters=0, use_cuda=False):      # the reference's hook, verbatim math
+        nulls = torch.zeros(grad.shape)
+        if use_cuda:
+            nulls = nulls.cuda()
+        nulls[freeze_top_n_filters:, :, :] = 1
+        return grad * nulls
+
+    m2.linears[0].weight.register_hook(partial(freeze_top_n_filters, use_cuda=True, freeze_top_n_filters=4))
+    torch.nn.functional.mse_loss(m2(x), y).backward()
+    g = m2.linears[0].weight.grad
+    assert float(g[:4].abs().max()) == 0.0 and torch.equal(g[4:], g_free[4:])
+    for (k1, p1), (k2, p2) in zip(m.named_parameters(), m2.named_parameters()):
+        assert k1 == k2 and p1.data_ptr() != p2.data_ptr()
+        if k1 != "linears.0.weight":
+            assert torch.equal(p1.grad, p2.grad), k1
+
+
+def test_non_one_hot_float_input_is_rejected():
+    m = _random_model(8, 19, 60, 1).eval().to(DEV)
+    x = O.random_onehot(4, 60, seed=1).to(DEV)
+    x[1, :, 7] = 0.25                                     # "N as 0.25": not expressible in the packed layout
+    with torch.no_grad(), pytest.raises(ValueError, match="not one-hot"):
+        m(x)
+    m.linears.input_check = "lazy"
+    with torch.no_grad():
+        m(x)                                              # no sync, no error yet
+    with pytest.raises(ValueError, match="not one-hot"):
+        m.check_inputs()
+    m.check_inputs()                                      # the flag was cleared
+
+
+def test_fused_losses_match_torch():
+    from explainn_b200.architectures import get_loss
+    g = torch.Generator().manual_seed(0)
+    for kind, B, F in (("linear", 257, 50), ("binary", 4096, 1), ("linear", 3, 1), ("binary", 100, 7)):
+        x = (torch.randn(B, F, generator=g) * 3).to(DEV).requires_grad_(True)
+        y = (torch.randn(B, F, generator=g) if kind == "linear" else (torch.rand(B, F, generator=g) < 0.5).float()).to(DEV)
+        crit = get_loss(kind)
+        assert isinstance(crit, torch.nn.MSELoss if kind == "linear" else torch.nn.BCEWithLogitsLoss)
+        loss = crit(x, y)
+        (loss * 1.5).backward()
+        xr = x.detach().double().requires_grad_(True)
+        ref = (torch.nn.functional.mse_loss if kind == "linear" else
+               torch.nn.functional.binary_cross_entropy_with_logits)(xr, y.double())
+        (ref * 1.5).backward()
+        U.assert_close(loss.item(), ref.item(), rtol=2e-6, what=kind + " loss")
+        U.assert_close(x.grad.cpu().numpy(), xr.grad.cpu().numpy(), rtol=2e-6, atol_scale=1e-7, what=kind + " grad")
+    with pytest.raises(RuntimeError):
+        get_loss("linear")(torch.zeros(2, 2), torch.zeros(2, 2))       # no CPU fallback
+
+
+def test_custom_ops_are_registered_and_pass_opcheck():
+    """torch.library registration: schema, fake tensor, autograd registration, AOT dispatch"""
+    import torch.library
+    assert {"unit_bank_train", "unit_bank_train_bwd", "unit_bank_eval", "linear", "linear_bwd", "loss", "loss_bwd",
+            "pack_onehot", "frontend_acts", "frontend_pool", "pwm_scan", "bn_running_update"} <= set(dir(torch.ops.explainn_b200))
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(33, 12, generator=g).to(DEV).requires_grad_(True)
+    w = torch.randn(5, 12, generator=g).to(DEV).requires_grad_(True)
+    b = torch.randn(5, generator=g).to(DEV).requires_grad_(True)
+    torch.library.opcheck(torch.ops.explainn_b200.linear.default, (x, w, b, None, []))
+    y = torch.randn(33, 5, generator=g).to(DEV)
+    lg = torch.randn(33, 5, generator=g).to(DEV).requires_grad_(True)
+    torch.library.opcheck(torch.ops.explainn_b200.loss.default, (lg, y, "mse"))
+    torch.library.opcheck(torch.ops.explainn_b200.loss.default, (lg, (y > 0).float(), "bce_logits"))
+    m = _random_model(6, 19, 67, 2).train().to(DEV)
+    from explainn_b200 import ops
+    planes = ops.pack_onehot(O.random_onehot(16, 67, seed=3).to(DEV))
+    bank = m.linears
+    params = [bank[0].weight, bank[0].bias, bank[1].weight, bank[1].bias, bank[6].weight, bank[6].bias, bank[7].weight,
+              bank[7].bias, bank[10].weight, bank[10].bias, bank[11].weight, bank[11].bias]
+    torch.library.opcheck(torch.ops.explainn_b200.unit_bank_train.default,
+                          (planes, 67, params, [1e-5, 1e-5, 1e-5], 0.0, 0, None, None, None, []),
+                          test_utils=("test_schema", "test_autograd_registration", "test_faketensor"))
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops.explainn_b200.linear(x.detach().cpu(), w.detach().cpu(), b.detach().cpu(), None, [])   # cuda only
+
+
+def test_gradients_live_in_the_flat_arena():
+    m = _random_model(12, 19, 88, 3).train().to(DEV)
+    m.linears[9].p = 0.0
+    x = O.random_onehot(16, 88, seed=5).to(DEV)
+    y = torch.randn(16, 3, generator=torch.Generator().manual_seed(1)).to(DEV)
+    torch.nn.functional.mse_loss(m(x), y).backward()
+    fresh = {k: p.grad.clone() for k, p in m.named_parameters()}
+    base = min(p.grad.data_ptr() for p in m.parameters())
+    names, offs, total, split = m._arena_plan()
+    pd = dict(m.named_parameters())
+    for nm, off in zip(names, offs):                       # one allocation, the planned offsets
+        assert pd[nm].grad.data_ptr() == base + 4 * off, nm
+    arena = m.use_grad_arena()
+    m.zero_grad()
+    torch.nn.functional.mse_loss(m(x), y).backward()
+    for nm, off in zip(names, offs):
+        assert pd[nm].grad.data_ptr() == arena.data_ptr() + 4 * off, nm
+        assert torch.equal(pd[nm].grad, fresh[nm]), nm
+    assert 0 < split < total and offs[names.index("linears.0.weight")] == split
+
+
+@pytest.mark.parametrize("mode", ["float", "ascii", "planes"])
+@pytest.mark.parametrize("graph", [False, True])
+def test_step_pipeline_matches_the_plain_loop(mode, graph):
+    """StepPipeline (H2D on a copy stream, lagged loss, optional CUDA graph) against the reference's plain loop on
+    the same batches: losses and parameters; two batch shapes alternate after the warm-up (slot re-allocation,
+    graph re-capture)."""
+    from explainn_b200 import ops
+    from explainn_b200.architectures import get_loss, get_optimizer
+    from explainn_b200.trainer import StepPipeline
+    L, F = 95, 2
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)
+    rng = np.random.default_rng(0)
+    batches = []
+    for i, B in enumerate([48, 48, 48, 31, 48, 31, 31]):
+        codes = rng.integers(0, 4, size=(B, L))
+        x = torch.zeros(B, 4, L)
+        x.scatter_(1, torch.tensor(codes)[:, None, :], 1.0)
+        y = torch.randn(B, F, generator=torch.Generator().manual_seed(i))
+        batches.append((x, y, torch.tensor(letters[codes])))
+    m_ref = _random_model(17, 11, L, F).train().to(DEV)
+    m_ref.linears[9].p = 0.0
+    m = _random_model(17, 11, L, F).train().to(DEV)
+    m.linears[9].p = 0.0
+    ref_losses, _ = _plain_steps(m_ref, [(x, y) for x, y, _ in batches])
+    pipe = StepPipeline(m, get_loss("linear"), get_optimizer(m.parameters(), 0.003), graph=graph)
+    got = []
+    for x, y, asc in batches:
+        if mode == "float":
+            got.append(pipe.step(x.pin_memory(), y.pin_memory()))
+        elif mode == "ascii":
+            got.append(pipe.step(asc.pin_memory(), y.pin_memory()))
+        else:
+            planes = ops.pack_onehot(x.to(DEV)).cpu()
+            got.append(pipe.step(planes.pin_memory(), y.pin_memory(), length=L))
+    got = got[1:] + [pipe.flush()]
+    U.assert_close(np.array(got), np.array(ref_losses), rtol=1e-5, what="losses")
+    for (k1, p1), (k2, p2) in zip(m.named_parameters(), m_ref.named_parameters()):
+        if k1 not in ZERO_CLASS:
+            U.assert_close(p1.detach().cpu().numpy(), p2.detach().cpu().numpy(), rtol=1e-4, atol_scale=1e-4, what=k1)
+    for (k1, b1), (k2, b2) in zip(m.named_buffers(), m_ref.named_buffers()):
+        U.assert_close(b1.cpu().numpy(), b2.cpu().numpy(), rtol=1e-5, what=k1)
+    assert pipe.h2d_bytes > 0 and pipe.d2h_bytes == 8 * len(batches)
+    if graph:
+        assert pipe.graph is not None and pipe.graph_kernels > 10
+        # the optimizer's host-side step count followed the replays
+        steps = {int(st["step"]) for st in pipe.optimizer.state.values()}
+        assert steps == {len(batches)}, steps
+
+
+def test_graphed_step_draws_new_dropout_masks_and_counts_adam_steps():
+    from explainn_b200.architectures import get_loss, get_optimizer
+    from explainn_b200.trainer import StepPipeline
+    m = _random_model(16, 19, 80, 2).train().to(DEV)          # dropout p = 0.3 stays on
+    opt = get_optimizer(m.parameters(), 0.0)                  # lr 0: the parameters never move
+    pipe = StepPipeline(m, get_loss("linear"), opt, graph=True, graph_warmup=1)
+    x = O.random_onehot(64, 80, seed=1).pin_memory()
+    y = torch.randn(64, 2, generator=torch.Generator().manual_seed(0)).pin_memory()
+    losses = [pipe.step(x, y) for _ in range(6)][1:] + [pipe.flush()]
+    assert len(set(losses[1:])) == len(losses[1:]), losses    # same input, same weights: only the masks differ
+    assert int(opt._step_dev.item()) == 6 and int(m.linears[1].num_batches_tracked.item()) == 6
