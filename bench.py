@@ -1,30 +1,38 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the ExplaiNN hot path on B200.
 
-    python bench.py [--gpus N --steps K --warmup W] [--workload cfg3|cfg2|cfg1] [--impl reference]
-    python bench.py --workload cfg1_fwd|cfg3_fwd|cfg4|cfg5     (inference / interpret / PWM scan: bench_paths.py)
+    python bench.py [--gpus N --steps K --warmup W] [--workload cfg3|cfg2|cfg1] [--batch B] [--impl reference]
+                    [--global-batch G (strong scaling)] [--sync-bn] [--no-graph] [--e2e-input ascii|float|planes]
+    python bench.py --workload cfg1_fwd|cfg3_fwd|cfg4|cfg5|metrics   (inference / interpret / PWM scan: bench_paths.py)
 
-Metric (BASELINE.json): sequences/s of the ExplaiNN training step (forward + loss + backward + Adam)
-on synthetic one-hot DNA.  Default workload = cfg3, the configuration the metric is quoted on at
-1/2/4/8 GPUs: ExplaiNN(300 units, k=19, 600 bp, 50 outputs), MSE, Adam lr 0.003, batch 4096 per GPU
-(weak scaling; one rank per GPU, per-rank BatchNorm statistics, one flat gradient all-reduce per step).
+Metric (BASELINE.json): sequences/s of the ExplaiNN training step (forward + loss + backward + Adam) on synthetic
+one-hot DNA.  Default workload = cfg3, the configuration the metric is quoted on at 1/2/4/8 GPUs:
+ExplaiNN(300 units, k=19, 600 bp, 50 outputs), MSE, Adam lr 0.003, batch 4096 per GPU (weak scaling; one rank per GPU,
+one all-reduce of the flat gradient arena per step, its MLP segment overlapped with the conv weight gradient).
 
-`value`   : K steps with the float one-hot batches already resident in HBM.
+`value`   : K steps with the float one-hot batches already resident in HBM; the step (pack, forward, loss, backward,
+            all-reduce, Adam) is ONE CUDA-graph replay plus the encode kernel of the incoming batch.
 `e2e`     : the same step through the host-facing API (explainn_b200/trainer.py StepPipeline, the step of
-            selene/__init__.py:283-295) with HOST buffers: every step copies its pinned float one-hot batch
-            to the device and reads its loss back; the copy of batch i+1 runs on a copy stream under step i.
-`roofline`: every C-ABI call of the timed region is bracketed by CUDA events on the launching stream; the
-            entry point with the largest share is reported against its bound.
-`cpu_baseline` / `--impl reference`: the oracle port (oracle/explainn_oracle.py, torch CPU, the reference's
-            own arithmetic) timed on the host cores on a bounded sample of the same workload.
+            selene/__init__.py:283-295) with HOST buffers: every step copies its pinned batch to the device (raw ASCII
+            bases by default, the column train.py:266-284 reads; `e2e_float_onehot` = the reference's float one-hot
+            tensors) and reads its loss back; the copy of batch i+1 runs on a copy stream under step i.
+`roofline`: an eager pass brackets every C-ABI call with CUDA events on the launching stream; the entry point with
+            the largest share is reported against its bound.  `traffic` is read from the ncu
+            capture summary committed under profiles/ (file named in the line), not typed in here.
+`cpu_baseline` / `--impl reference`: the REFERENCE MODULE ITSELF (explainn/architectures/__init__.py, placed under
+            oracle/_ref/ by build(); `kind: "reference"`) timed on the host cores on a bounded sample of the same
+            workload; the oracle port (`kind: "port"`) only if that file is absent.
 """
 import argparse
+import importlib.util
 import json
 import os
+import statistics
 import subprocess
 import sys
 import threading
 import time
+import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -32,16 +40,7 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels from the committed
-# `ncu --set full` captures (profiles/), cfg3 B=4096; null where no capture exists for the current kernel
-NCU_TRAFFIC = {
-    # profiles/r01_ncu_full_s71.txt (ncu --set full, cfg3 B=4096), bytes per call of the entry point
-    "xnn_mlp_bwd": 1484.2e6,        # mlp_fc1_lockstep_kernel<2> 629.1 + 7.6 MB, mlp_bwd_kernel 464.5 MB read + 383.0 MB written
-    "xnn_frontend_bwd": 923.0e6,    # frontend_bwd_tc_kernel 918.9 MB read + 4.1 MB written
-    "xnn_frontend_fwd": 860.5e6,    # frontend_tc_kernel<1> 2.2 MB read + 858.3 MB written
-    "xnn_mlp_fwd": 661.6e6,         # mlp_fc1_kernel<1,8> 616.9 MB read + 44.7 MB written
-    "xnn_mlp_bn2_train_prepare": 581.4e6,
-}
+import bench_data  # noqa: E402
 
 WORKLOADS = {
     # name: (cnn_units, kernel, length, features, loss kind, per-GPU batch)
@@ -49,6 +48,7 @@ WORKLOADS = {
     "cfg2": (300, 19, 60, 66, "linear", 4096),
     "cfg1": (100, 19, 200, 1, "binary", 8192),
 }
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")
 
 
 def peaks():
@@ -57,6 +57,16 @@ def peaks():
         d = json.load(open(p))
         return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), d.get("bf16_tflops", 1590.0), "measured"
     return 6650.0, 1400.0, 1590.0, "fallback"
+
+
+def ncu_traffic(entry, workload, B):
+    """dram bytes per call of `entry` from the committed ncu --set full summary, or None"""
+    if not os.path.exists(TRAFFIC_FILE):
+        return None, None
+    d = json.load(open(TRAFFIC_FILE))
+    if d.get("workload") != workload or d.get("per_gpu_batch") != B:
+        return None, None
+    return d.get("dram_bytes_per_call", {}).get(entry), os.path.relpath(TRAFFIC_FILE, ROOT)
 
 
 class ClockSampler:
@@ -92,81 +102,150 @@ class ClockSampler:
 
 
 def synthetic_batches(n_batches, B, L, F, kind, seed):
-    from oracle.explainn_oracle import random_onehot  # synthetic generator only (no oracle arithmetic)
-    xs, ys = [], []
+    """(float one-hot, targets, ASCII) per batch"""
+    xs, ys, asc = [], [], []
     g = torch.Generator().manual_seed(seed)
     for i in range(n_batches):
-        xs.append(random_onehot(B, L, seed=seed + i))
+        codes = bench_data.random_codes(B, L, seed + i)
+        xs.append(bench_data.onehot_from_codes(codes))
+        asc.append(bench_data.ascii_from_codes(codes))
         ys.append(torch.randn(B, F, generator=g) if kind == "linear" else (torch.rand(B, F, generator=g) < 0.5).float())
-    return xs, ys
+    return xs, ys, asc
 
 
-def cpu_reference_rate(cfg, steps, warmup, sample_B):
-    """The oracle port on the host cores: full train step (forward, loss, backward, Adam) per step."""
-    from oracle import explainn_oracle as O
+# ---------------------------------------------------------------------------------------------------------
+# CPU arm: the reference module itself
+# ---------------------------------------------------------------------------------------------------------
+def load_reference_module():
+    """oracle/_ref/reference_architectures.py = the reference's explainn/architectures/__init__.py (placed by
+    `make -C oracle`, git-ignored); `Bio` is stubbed (imported at module level, never touched by the model)."""
+    path = os.path.join(ROOT, "oracle", "_ref", "reference_architectures.py")
+    if not os.path.exists(path):
+        return None
+    for name in ("Bio", "Bio.motifs"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["Bio"].motifs = sys.modules["Bio.motifs"]
+    spec = importlib.util.spec_from_file_location("reference_architectures", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def cpu_train_step_times(cfg, B, threads, iters, warmup=1):
+    """per-step seconds of the full training step (model(x), loss, zero_grad, backward, Adam step -- the body of
+    selene/__init__.py:283-292) on the host; returns (times, kind)"""
     U, k, L, F, kind, _ = cfg
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    torch.set_num_threads(threads)
+    ref = load_reference_module()
+    x = bench_data.random_onehot(B, L, 1234)
+    g = torch.Generator().manual_seed(1)
+    y = torch.randn(B, F, generator=g) if kind == "linear" else (torch.rand(B, F, generator=g) < 0.5).float()
+    times = []
+    if ref is not None:
+        torch.manual_seed(0)
+        model = ref.ExplaiNN(U, k, L, F).train()
+        crit, opt = ref.get_loss(kind), ref.get_optimizer(model.parameters(), 0.003)
+        for it in range(warmup + iters):
+            t0 = time.perf_counter()
+            loss = crit(model(x), y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            loss.item()
+            if it >= warmup:
+                times.append(time.perf_counter() - t0)
+        return times, "reference"
+    from oracle import explainn_oracle as O        # the one other place bench.py may execute oracle/ (CPU arm only)
     from explainn_b200.architectures import ExplaiNN
     torch.manual_seed(0)
     sd = {k_: v.detach().clone() for k_, v in ExplaiNN(U, k, L, F).state_dict().items()}
-    xs, ys = synthetic_batches(1, sample_B, L, F, kind, 1234)
-    g = torch.Generator().manual_seed(1)
-    mask = (torch.rand(sample_B, U, 100, generator=g) >= 0.3).to(torch.uint8)
+    mask = (torch.rand(B, U, 100, generator=g) >= 0.3).to(torch.uint8)
     m = {k_: torch.zeros_like(sd[k_]) for k_ in O.PARAM_KEYS}
     v = {k_: torch.zeros_like(sd[k_]) for k_ in O.PARAM_KEYS}
-    times = []
-    for it in range(warmup + steps):
+    for it in range(warmup + iters):
         t0 = time.perf_counter()
-        r = O.explainn_train_step(sd, xs[0], ys[0], kind, dropout_mask=mask)
+        r = O.explainn_train_step(sd, x, y, kind, dropout_mask=mask)
         for k_ in O.PARAM_KEYS:
             sd[k_], m[k_], v[k_] = O.adam_step(sd[k_], r["grads"][k_].reshape(sd[k_].shape), m[k_], v[k_], it + 1, 0.003)
         for k_, val in r["running"].items():
             sd[k_] = val
         if it >= warmup:
             times.append(time.perf_counter() - t0)
-    dt = sum(times)
-    return steps * sample_B / dt, dt / steps * 1e3, cores
+    return times, "port"
 
 
+def cpu_baseline(cfg, sample_B):
+    """all host threads at the reference's default batch (100, train.py:36-41) and at `sample_B`, and ONE thread at
+    the default batch: median of the timed iterations each"""
+    cores = os.cpu_count() or 1
+    out = {}
+    t, kind = cpu_train_step_times(cfg, sample_B, cores, 5)
+    out["value"], out["ms_per_step"] = sample_B / statistics.median(t), statistics.median(t) * 1e3
+    t100, _ = cpu_train_step_times(cfg, 100, cores, 5)
+    t1, _ = cpu_train_step_times(cfg, 100, 1, 3)
+    torch.set_num_threads(cores)
+    out.update({"unit": "sequences/s", "cores": cores, "kind": kind,
+                "sample": f"median of 5 full training steps of {sample_B} sequences, all {cores} host threads, "
+                          + ("the reference module itself (oracle/_ref/reference_architectures.py)" if kind == "reference"
+                             else "oracle port (reference module file absent)"),
+                "batch100_all_threads": {"value": 100 / statistics.median(t100), "unit": "sequences/s",
+                                         "iterations": 5, "note": "reference default batch, train.py:36-41"},
+                "batch100_one_thread": {"value": 100 / statistics.median(t1), "unit": "sequences/s", "cores": 1,
+                                        "iterations": 3}})
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     import bench_paths
     ap.add_argument("--workload", default="cfg3", choices=list(WORKLOADS) + list(bench_paths.AUX))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: workload's)")
+    ap.add_argument("--global-batch", type=int, default=0, help="strong scaling: total batch split over the ranks")
     ap.add_argument("--cpu-sample", type=int, default=128, help="sequences per CPU-baseline step")
+    ap.add_argument("--sync-bn", action="store_true", help="BatchNorm statistics over the GLOBAL batch (reference numerics)")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA-graph replay per step")
+    ap.add_argument("--e2e-input", default="ascii", choices=["ascii", "float", "planes"])
+    ap.add_argument("--no-aux", action="store_true", help="skip the secondary forward fields and the CPU baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
-    if args.workload in bench_paths.AUX:
-        assert args.impl == "ours" and torch.cuda.is_available(), "secondary workloads run on the GPU arm only"
-        lr = int(os.environ.get("LOCAL_RANK", "0"))
-        return bench_paths.run(args.workload, args, int(os.environ.get("RANK", "0")),
-                               int(os.environ.get("WORLD_SIZE", "1")), lr, peaks, ClockSampler(lr))
-    cfg = WORKLOADS[args.workload]
-    U, k, L, F, kind, B = cfg
-    if args.batch:
-        B = args.batch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload in bench_paths.AUX:
+        assert args.impl == "ours" and torch.cuda.is_available(), "secondary workloads run on the GPU arm only"
+        return bench_paths.run(args.workload, args, rank, world, local, peaks, ClockSampler(local))
+    cfg = WORKLOADS[args.workload]
+    U, k, L, F, kind, B = cfg
+    scaling = "weak"
+    if args.global_batch:
+        B, scaling = args.global_batch // world, "strong"
+    elif args.batch:
+        B = args.batch
     workload_name = f"ExplaiNN({U} units,k={k},{L}bp,{F} outputs) train step {kind} loss, Adam lr 0.003"
 
     if args.impl == "reference":
         if rank != 0:
             return
-        rate, ms, cores = cpu_reference_rate(cfg, max(2, min(args.steps, 8)), 1, args.cpu_sample)
+        steps = max(2, min(args.steps, 8))
+        cores = os.cpu_count() or 1
+        t, rkind = cpu_train_step_times(cfg, args.cpu_sample, cores, steps, warmup=1)
+        ms = sum(t) / len(t) * 1e3
+        rate = args.cpu_sample / (sum(t) / len(t))
         print(json.dumps({
             "impl": "reference", "metric": "sequences/sec ExplaiNN fwd+bwd training step", "value": rate,
-            "unit": "sequences/s", "n_gpus": args.gpus, "steps": max(2, min(args.steps, 8)), "warmup": 1,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "unit": "sequences/s", "n_gpus": args.gpus, "steps": steps, "warmup": 1,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": workload_name, "per_step_sample": args.cpu_sample},
-            "cpu_baseline": {"value": rate, "unit": "sequences/s", "cores": cores, "kind": "port",
-                             "sample": f"{args.cpu_sample} sequences per step, oracle port of the reference's "
-                                       f"torch CPU path (the Python reference cannot travel to the GPU box)"},
+            "cpu_baseline": {"value": rate, "unit": "sequences/s", "cores": cores, "kind": rkind,
+                             "sample": f"{steps} full training steps of {args.cpu_sample} sequences each, all {cores} host "
+                                       "threads, " + ("the reference module itself (explainn/architectures/__init__.py "
+                                                      "placed under oracle/_ref/ by build())" if rkind == "reference"
+                                                      else "oracle port (oracle/_ref/reference_architectures.py absent)")},
             "e2e": {"value": rate, "unit": "sequences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }))
         return
@@ -174,6 +253,7 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     from explainn_b200 import ops, parallel
     from explainn_b200.architectures import ExplaiNN, get_loss, get_optimizer
+    from explainn_b200.trainer import StepPipeline
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     parallel.init_from_env("nccl")
@@ -181,38 +261,21 @@ def main():
 
     torch.manual_seed(0)
     model = ExplaiNN(U, k, L, F).to(dev).train()
+    model.linears.input_check = "lazy"
     parallel.broadcast_parameters(model)
     crit = get_loss(kind)
     opt = get_optimizer(model.parameters(), 0.003)
-    bucket = parallel.GradBucket(model.parameters())
+    bucket = parallel.GradBucket(model) if world > 1 else None
+    if args.sync_bn and world > 1:
+        parallel.enable_sync_batchnorm()
+    use_graph = not args.no_graph
 
     # inputs rotate over NB distinct batches so that consecutive steps never re-read an L2-resident input
     NB = max(2, int(140e6 // (B * 4 * L * 4)) + 1)
-    xs_h, ys_h = synthetic_batches(NB, B, L, F, kind, 1234 + 1000 * rank)
-    xs_pin = [x.pin_memory() for x in xs_h]
+    xs_h, ys_h, asc_h = synthetic_batches(NB, B, L, F, kind, 1234 + 1000 * rank)
     ys_pin = [y.pin_memory() for y in ys_h]
     xs_d = [x.to(dev) for x in xs_h]
     ys_d = [y.to(dev) for y in ys_h]
-
-    # event pairs around every C-ABI call (all launched on torch's current stream): the dominant entry point
-    # of the timed region is found from these, not assumed
-    call_events = {}
-    orig_call = ops._call
-
-    def timed_call(name, *a):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        orig_call(name, *a)
-        e1.record()
-        call_events.setdefault(name, []).append((e0, e1))
-
-    def step(x, y):
-        pred = model(x)
-        loss = crit(pred, y)
-        opt.zero_grad()
-        loss.backward()
-        bucket.allreduce_mean()
-        opt.step()
 
     def barrier():
         if world > 1:
@@ -232,40 +295,107 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    def eager_step(x, y):
+        loss = crit(model(x), y)
+        opt.zero_grad()
+        loss.backward()
+        if bucket is not None:
+            bucket.allreduce_sum()
+            opt.step(grad_scale=bucket.scale)
+        else:
+            opt.step()
+
+    # ---- 1. eager pass with CUDA events around every C-ABI call: which entry point dominates ---------------
     for i in range(args.warmup):
-        step(xs_d[i % NB], ys_d[i % NB])
+        eager_step(xs_d[i % NB], ys_d[i % NB])
+    call_events = {}
+    orig_call = ops._call
+
+    def timed_call(name, *a):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        orig_call(name, *a)
+        e1.record()
+        call_events.setdefault(name, []).append((e0, e1))
+
+    n_break = min(20, args.steps)
+    ops._call = timed_call
+    k0 = ops.kernel_launches
+    ms_eager = timed(lambda i: eager_step(xs_d[i % NB], ys_d[i % NB]), n_break)
+    kernels_per_step = (ops.kernel_launches - k0) // n_break
+    ops._call = orig_call
+    call_ms = {nme: sum(a.elapsed_time(b) for a, b in ev) / n_break for nme, ev in call_events.items()}
+
+    # ---- 2. value: device-resident float one-hot batches, one graph replay per step ---------------------------
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ops._call = timed_call
-    k0 = ops.kernel_launches
-    ms_dev = timed(lambda i: step(xs_d[i % NB], ys_d[i % NB]), args.steps)
-    launches = ops.kernel_launches - k0
-    ops._call = orig_call
-    call_ms = {nme: sum(a.elapsed_time(b) for a, b in ev) / args.steps for nme, ev in call_events.items()}
+    graph_note = None
+    pipe_dev = StepPipeline(model, crit, opt, bucket, dev, graph=use_graph)
+    try:
+        for i in range(max(3, args.warmup)):
+            pipe_dev.step_device(xs_d[i % NB], ys_d[i % NB])
+        pipe_dev.flush()
+    except Exception as e:                       # a capture failure must not cost the round its number: say so
+        graph_note = f"graph capture failed ({type(e).__name__}: {str(e)[:200]}); eager launches timed instead"
+        torch.cuda.synchronize()
+        use_graph = False
+        pipe_dev = StepPipeline(model, crit, opt, bucket, dev, graph=False)
+        for i in range(3):
+            pipe_dev.step_device(xs_d[i % NB], ys_d[i % NB])
+        pipe_dev.flush()
+    ms_dev = timed(lambda i: pipe_dev.step_device(xs_d[i % NB], ys_d[i % NB]), args.steps)
+    pipe_dev.flush()
+    graph_kernels = pipe_dev.graph_kernels if use_graph else 0
 
-    # end to end through the host-facing step (explainn_b200/trainer.py): every step copies its batch from
-    # pinned host memory and reads its loss back; copies of batch i+1 overlap step i, losses arrive one call late
-    from explainn_b200.trainer import StepPipeline
-    pipe = StepPipeline(model, crit, opt, bucket, dev)
-    for i in range(3):
-        pipe.step(xs_pin[i % NB], ys_pin[i % NB])
-    pipe.flush()
-    h0, d0 = pipe.h2d_bytes, pipe.d2h_bytes
+    # ---- 3. e2e: host batches through StepPipeline.step ---------------------------------------------------------
+    def host_inputs(mode):
+        if mode == "ascii":
+            return [a.pin_memory() for a in asc_h], None
+        if mode == "float":
+            return [x.pin_memory() for x in xs_h], None
+        return [ops.pack_onehot(x).cpu().pin_memory() for x in xs_d], L
 
-    def e2e_all(_):
-        for i in range(args.steps):
-            pipe.step(xs_pin[i % NB], ys_pin[i % NB])
+    def run_e2e(mode, steps):
+        xs_pin, length = host_inputs(mode)
+        pipe = StepPipeline(model, crit, opt, bucket, dev, graph=use_graph)
+        for i in range(4):
+            pipe.step(xs_pin[i % NB], ys_pin[i % NB], length=length)
         pipe.flush()
+        h0, d0 = pipe.h2d_bytes, pipe.d2h_bytes
 
-    ms_e2e = timed(e2e_all, 1)
-    h2d_step, d2h_step = (pipe.h2d_bytes - h0) // args.steps, (pipe.d2h_bytes - d0) // args.steps
+        def all_steps(_):
+            for i in range(steps):
+                pipe.step(xs_pin[i % NB], ys_pin[i % NB], length=length)
+            pipe.flush()
+
+        ms = timed(all_steps, 1)
+        return ms / steps, (pipe.h2d_bytes - h0) // steps, (pipe.d2h_bytes - d0) // steps
+
+    ms_e2e, h2d_step, d2h_step = run_e2e(args.e2e_input, args.steps)
+    other = "float" if args.e2e_input != "float" else "ascii"
+    ms_e2e2, h2d2, _ = run_e2e(other, max(10, args.steps // 4))
     clocks = sampler.stop() if rank == 0 else None
+    model.check_inputs()
+
+    # ---- 4. secondary: eval forward (the metric is "fwd & fwd+bwd") -------------------------------------------
+    fwd = {}
+    if not args.no_aux:
+        model.eval()
+        with torch.no_grad():
+            for i in range(3):
+                model(xs_d[i % NB])
+            n_f = 20
+            ms_f = timed(lambda i: model(xs_d[i % NB]), n_f)
+        model.train()
+        fwd = {"eval_forward_same_config": {"value": world * B * n_f / (ms_f / 1e3), "unit": "sequences/s",
+                                            "ms_per_batch": ms_f / n_f, "per_gpu_batch": B,
+                                            "input": "float one-hot resident in HBM"}}
 
     if rank != 0:
         return
     value = world * B * args.steps / (ms_dev / 1e3)
-    e2e = world * B * args.steps / (ms_e2e / 1e3)
+    e2e = world * B / (ms_e2e / 1e3)
     hbm, tf_sus, tf_burst, which = peaks()
     Lc = L - k + 1
     n = Lc // 7
@@ -290,33 +420,48 @@ def main():
         achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e12, tf_sus, "TFLOP/s", "bf16_tflops_sustained"
     else:
         achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e9, hbm, "GB/s", "hbm_gbs"
+    traffic, traffic_src = ncu_traffic(top, args.workload, B)
     fe_ms = call_ms.get("xnn_frontend_fwd", 0.0)
-    cpu_rate, cpu_ms, cores = cpu_reference_rate(cfg, 4, 1, args.cpu_sample)
-    print(json.dumps({
+    cpu = cpu_baseline(cfg, args.cpu_sample) if not args.no_aux else None
+    bn_mode = "synchronised BatchNorm statistics (global batch)" if (args.sync_bn and world > 1) else \
+        "per-rank BatchNorm statistics"
+    line = {
         "metric": "sequences/sec ExplaiNN fwd+bwd training step", "value": value, "unit": "sequences/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name, "per_gpu_batch": B, "global_batch": B * world,
-                   "parallelism": f"dp{world}, per-rank BatchNorm statistics, one flat gradient all-reduce",
+                   "parallelism": f"dp{world}, {bn_mode}, one all-reduce of the flat gradient arena per step "
+                                  f"(MLP segment issued under the conv weight gradient)",
+                   "step_launch": ("one CUDA-graph replay per step (+ the encode kernel of the incoming batch)"
+                                   if use_graph else "eager launches") + (f"; {graph_note}" if graph_note else ""),
                    "l2": f"inputs rotate over {NB} distinct batches ({NB * B * 16 * L / 1e6:.0f} MB > 126 MB L2); "
                          f"intermediates exceed L2"},
-        "e2e": {"value": e2e, "unit": "sequences/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step,
-                "api": "explainn_b200.trainer.StepPipeline.step(pinned float one-hot, pinned targets): H2D of batch "
-                       "i+1 on a copy stream under step i, loss read back every step one call late"},
-        "gpu_launches": launches,
+        "e2e": {"value": e2e, "unit": "sequences/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step, "host_input": args.e2e_input,
+                "api": "explainn_b200.trainer.StepPipeline.step(pinned host batch, pinned targets): H2D of batch "
+                       "i+1 on a copy stream under step i, loss (+ input-check flag) read back every step one call late"},
+        "e2e_" + ("float_onehot" if other == "float" else other):
+            {"value": world * B / (ms_e2e2 / 1e3), "unit": "sequences/s", "ms_per_step": ms_e2e2,
+             "h2d_bytes_per_step": h2d2, "steps": max(10, args.steps // 4)},
+        "gpu_launches": (graph_kernels + 1) * args.steps if use_graph else kernels_per_step * args.steps,
+        "launches": {"kernels_per_step": graph_kernels + 1 if use_graph else kernels_per_step,
+                     "host_launch_calls_per_step": 2 if use_graph else kernels_per_step,
+                     "eager_ms_per_step": ms_eager / n_break},
         "roofline": {"kernel": top, "what": what, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
-                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(top), "peak_source": f"{src}, {which}",
-                     "kernel_ms": top_ms, "kernel_share_of_step": top_ms / (ms_dev / args.steps),
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": f"{src}, {which}",
+                     "kernel_ms": top_ms, "kernel_share_of_step": top_ms / (ms_eager / n_break),
                      "algorithmic_per_seq": per_seq,
                      "frontend_fwd": {"bound": "tensor", "kernel_ms": fe_ms,
                                       "achieved": conv_flops * B / (fe_ms / 1e3) / 1e12 if fe_ms else None,
                                       "peak": tf_sus, "unit": "TFLOP/s"},
                      "per_call_ms": {k_: round(v, 4) for k_, v in sorted(call_ms.items(), key=lambda kv: -kv[1])}},
-        "cpu_baseline": {"value": cpu_rate, "unit": "sequences/s", "cores": cores, "kind": "port",
-                         "sample": f"4 train steps of {args.cpu_sample} sequences, oracle port (torch CPU)"},
         "clocks": clocks,
-    }))
+    }
+    line.update(fwd)
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
 
 
 if __name__ == "__main__":

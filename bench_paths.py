@@ -111,7 +111,7 @@ def run_fwd(name, args, rank, world, local, peaks, sampler):
     """Inference: model(x) on float one-hot batches (predict.py:81-82), sequences sharded across ranks."""
     from explainn_b200 import ops
     from explainn_b200.architectures import ExplaiNN
-    from oracle.explainn_oracle import random_onehot   # generator only
+    from bench_data import random_onehot
     _, U, k, L, F, B = AUX[name]
     B = args.batch or B
     dev = torch.device("cuda", local)

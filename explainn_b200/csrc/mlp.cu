@@ -215,43 +215,57 @@ int launch_bn_train_finalize(const double* part, int tiles, int B, int C, const 
 }
 }  // namespace xnn
 
+extern "C" size_t xnn_bn_partial_bytes(int B, int C) {
+    return (size_t)colstats_tiles(B) * 2 * C * sizeof(double);
+}
+
 extern "C" int xnn_bn_train_prepare(const float* x, int B, int C, const float* gamma, const float* beta,
                                     float eps, float momentum, float* running_mean, float* running_var,
-                                    float* scale, float* shift, double* stats, void* work, xnn_stream_t s) {
+                                    float* scale, float* shift, double* stats, void* work, int phase,
+                                    long long count, xnn_stream_t s) {
     XNN_CHECK_ARG(x && gamma && beta && scale && shift && stats && work, "NULL pointer");
-    XNN_CHECK_ARG(B >= 2 && C >= 1, "train-mode BatchNorm needs more than 1 value per channel");
+    XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = partial sums, 2 = finalize");
+    if (phase == 0) count = B;
+    XNN_CHECK_ARG(B >= 1 && C >= 1 && count >= 2 && count < (1LL << 31),
+                  "train-mode BatchNorm needs more than 1 value per channel");
     const int tiles = colstats_tiles(B);
-    dim3 grid(ceil_div(C, 32), tiles);
-    colsums_kernel<<<grid, 256, 0, to_stream(s)>>>(x, nullptr, nullptr, B, C, tiles, (double*)work);
-    XNN_CHECK_LAUNCH();
-    bn_train_finalize_kernel<<<ceil_div(C, 256), 256, 0, to_stream(s)>>>(
-        (const double*)work, tiles, B, C, gamma, beta, eps, momentum, running_mean, running_var, scale, shift, stats);
-    XNN_CHECK_LAUNCH();
+    if (phase != 2) {
+        dim3 grid(ceil_div(C, 32), tiles);
+        colsums_kernel<<<grid, 256, 0, to_stream(s)>>>(x, nullptr, nullptr, B, C, tiles, (double*)work);
+        XNN_CHECK_LAUNCH();
+    }
+    if (phase != 1) {
+        bn_train_finalize_kernel<<<ceil_div(C, 256), 256, 0, to_stream(s)>>>(
+            (const double*)work, tiles, (int)count, C, gamma, beta, eps, momentum, running_mean, running_var, scale,
+            shift, stats);
+        XNN_CHECK_LAUNCH();
+    }
     return XNN_OK;
 }
 
 // dgamma/dbeta from the partial sums, then dx (elementwise)
 __global__ void __launch_bounds__(256)
 bn_bwd_finalize_kernel(const double* __restrict__ part, int tiles, int C, const double* __restrict__ stats,
-                       float* __restrict__ dgamma, float* __restrict__ dbeta, double* __restrict__ coef /* [C][2] */) {
+                       float* __restrict__ dgamma, float* __restrict__ dbeta, double* __restrict__ coef /* [C][2] */,
+                       float out_scale) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     double s1 = 0.0, s2 = 0.0;
     for (int t = 0; t < tiles; ++t) { s1 += part[((long long)t * 2) * C + c]; s2 += part[((long long)t * 2 + 1) * C + c]; }
     const double mean = stats[4 * (long long)c], invstd = stats[4 * (long long)c + 2];
     const double dg = invstd * (s2 - mean * s1);   // sum g * xhat
-    dgamma[c] = (float)dg;
-    dbeta[c] = (float)s1;
+    dgamma[c] = (float)(dg * (double)out_scale);
+    dbeta[c] = (float)(s1 * (double)out_scale);
     coef[2 * (long long)c] = s1; coef[2 * (long long)c + 1] = dg;
 }
 
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const float* g, const float* __restrict__ relu_out, const float* __restrict__ xpre,
                     const double* __restrict__ stats,
-                    const float* __restrict__ gamma, const double* __restrict__ coef, int B, int C,
+                    const float* __restrict__ gamma, const double* __restrict__ coef, int B, int C, long long count,
                     float* dx /* may alias g */) {
     const long long total = (long long)B * C;
-    const float invB = 1.0f / (float)B;
+    const float invB = 1.0f / (float)count;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
@@ -266,21 +280,29 @@ bn_bwd_apply_kernel(const float* g, const float* __restrict__ relu_out, const fl
 
 extern "C" int xnn_bn_bwd(const float* g, const float* relu_out, const float* xpre, const double* stats,
                           const float* gamma, int B, int C, float* dgamma, float* dbeta, float* dx, void* work,
-                          xnn_stream_t s) {
+                          int phase, long long count, float out_scale, xnn_stream_t s) {
     XNN_CHECK_ARG(g && xpre && stats && gamma && dgamma && dbeta && dx && work, "NULL pointer");
-    XNN_CHECK_ARG(B >= 2 && C >= 1, "bad sizes");
+    XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = partial sums, 2 = finalize + apply");
+    if (phase == 0) { count = B; out_scale = 1.0f; }
+    XNN_CHECK_ARG(B >= 1 && C >= 1 && count >= 2, "bad sizes");
     const int tiles = colstats_tiles(B);
-    dim3 grid(ceil_div(C, 32), tiles);
     double* part = (double*)work;
-    colsums_kernel<<<grid, 256, 0, to_stream(s)>>>(g, xpre, relu_out, B, C, tiles, part);
-    XNN_CHECK_LAUNCH();
-    double* coef = part + (size_t)tiles * 2 * C;
-    bn_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, to_stream(s)>>>(part, tiles, C, stats, dgamma, dbeta, coef);
-    XNN_CHECK_LAUNCH();
-    long long blocks = ((long long)B * C + 255) / 256;
-    if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
-    bn_bwd_apply_kernel<<<(int)blocks, 256, 0, to_stream(s)>>>(g, relu_out, xpre, stats, gamma, coef, B, C, dx);
-    XNN_CHECK_LAUNCH();
+    if (phase != 2) {
+        dim3 grid(ceil_div(C, 32), tiles);
+        colsums_kernel<<<grid, 256, 0, to_stream(s)>>>(g, xpre, relu_out, B, C, tiles, part);
+        XNN_CHECK_LAUNCH();
+    }
+    if (phase != 1) {
+        double* coef = part + (size_t)tiles * 2 * C;
+        bn_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, to_stream(s)>>>(part, tiles, C, stats, dgamma, dbeta, coef,
+                                                                          out_scale);
+        XNN_CHECK_LAUNCH();
+        long long blocks = ((long long)B * C + 255) / 256;
+        if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
+        bn_bwd_apply_kernel<<<(int)blocks, 256, 0, to_stream(s)>>>(g, relu_out, xpre, stats, gamma, coef, B, C, count,
+                                                                   dx);
+        XNN_CHECK_LAUNCH();
+    }
     return XNN_OK;
 }
 

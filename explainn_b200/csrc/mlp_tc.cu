@@ -797,18 +797,23 @@ extern "C" size_t xnn_mlp_bn2_work_bytes(int B, int U) {
 extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
                                          const float* gamma, const float* beta, float eps, float momentum,
                                          float* running_mean, float* running_var, float* scale, float* shift,
-                                         double* stats, void* work, xnn_stream_t s) {
+                                         double* stats, void* work, int phase, long long count, xnn_stream_t s) {
     XNN_CHECK_ARG(pool && w1 && b1 && gamma && beta && scale && shift && stats && work, "NULL pointer");
-    XNN_CHECK_ARG(B >= 2 && U >= 1, "train-mode BatchNorm needs more than 1 value per channel");
+    XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = partial sums, 2 = finalize");
+    if (phase == 0) count = B;
+    XNN_CHECK_ARG(B >= 1 && U >= 1 && count >= 2 && count < (1LL << 31),
+                  "train-mode BatchNorm needs more than 1 value per channel");
     XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
     cudaStream_t st = to_stream(s);
     MlpArgs a{};
     a.pool = pool; a.w1 = w1; a.b1 = b1; a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U);
     a.part = (double*)work;
-    XNN_CUDA(cudaMemsetAsync(work, 0, xnn_mlp_bn2_work_bytes(B, U), st));
-    if (mt_launch<MLP_STATS>(a, st)) { set_error("xnn_mlp_bn2_train_prepare: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
-    if (launch_bn_train_finalize(a.part, a.slots, B, U * MT_H, gamma, beta, eps, momentum, running_mean, running_var,
-                                 scale, shift, stats, st)) {
+    if (phase != 2) {
+        XNN_CUDA(cudaMemsetAsync(work, 0, xnn_mlp_bn2_work_bytes(B, U), st));
+        if (mt_launch<MLP_STATS>(a, st)) { set_error("xnn_mlp_bn2_train_prepare: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    }
+    if (phase != 1 && launch_bn_train_finalize(a.part, a.slots, (int)count, U * MT_H, gamma, beta, eps, momentum,
+                                               running_mean, running_var, scale, shift, stats, st)) {
         set_error("xnn_mlp_bn2_train_prepare: finalize launch failed");
         return XNN_ERR_CUDA;
     }
@@ -836,9 +841,9 @@ extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, 
 // backward, pass B1: reductions of the BatchNorm (linears.7) backward and dW2 / db2
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U, const double* __restrict__ stats,
-                        float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2,
-                        float* __restrict__ db2, float2* __restrict__ coef) {
+mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, long long B, int U,
+                        const double* __restrict__ stats, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                        float* __restrict__ dw2, float* __restrict__ db2, float2* __restrict__ coef, float out_scale) {
     const int C = U * MT_H;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
@@ -849,11 +854,12 @@ mlp_bwd_finalize_kernel(const double* __restrict__ part, int slots, int B, int U
     }
     const double mean = stats[4LL * c], invstd = stats[4LL * c + 2];
     const double dg = invstd * (s2 - mean * s1);       // sum g * xhat
-    dgamma[c] = (float)dg;
-    dbeta[c] = (float)s1;
-    dw2[c] = (float)s3;
-    if (c % MT_H == 0) db2[c / MT_H] = (float)s4;
-    coef[c] = make_float2((float)(s1 / B), (float)(dg / B));
+    const double os = (double)out_scale;
+    dgamma[c] = (float)(dg * os);
+    dbeta[c] = (float)(s1 * os);
+    dw2[c] = (float)(s3 * os);
+    if (c % MT_H == 0) db2[c / MT_H] = (float)(s4 * os);
+    coef[c] = make_float2((float)(s1 / (double)B), (float)(dg / (double)B));
 }
 
 // ---------------------------------------------------------------------------
@@ -1266,6 +1272,13 @@ static MbWork mb_work(int B, int U, int n) {
     return w;
 }
 
+// bytes at the start of `work` that hold the partial BN-backward sums after phase 1 (summed over ranks between
+// the phases under synchronised BatchNorm)
+extern "C" size_t xnn_mlp_bwd_partial_bytes(int B, int U) {
+    if (B < 1 || U < 1) return 0;
+    return (size_t)mt_slots(B, U) * 4 * U * MT_H * sizeof(double);
+}
+
 extern "C" size_t xnn_mlp_bwd_work_bytes(int B, int U, int n) {
     if (B < 1 || U < 1 || n < 1) return 0;
     return mb_work(B, U, n).total;
@@ -1275,10 +1288,12 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
                            const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
                            const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
                            float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
-                           float* dy, void* work, xnn_stream_t s) {
+                           float* dy, void* work, int phase, long long count, float out_scale, xnn_stream_t s) {
     XNN_CHECK_ARG(dopre && pool && w1 && b1 && scale2 && shift2 && stats2 && gamma2 && w2 && dw1 && db1 && dgamma2 &&
                   dbeta2 && dw2 && db2 && dy && work, "NULL pointer");
-    XNN_CHECK_ARG(B >= 2 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
+    XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = reductions, 2 = the rest");
+    if (phase == 0) { count = B; out_scale = 1.0f; }
+    XNN_CHECK_ARG(B >= 1 && count >= 2 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
     XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
     XNN_CHECK_ARG(((uintptr_t)work & 255) == 0, "work must be 256-byte aligned");
     XNN_CHECK_ARG(maskbits != nullptr && ((uintptr_t)maskbits & 15) == 0, "maskbits: required, 16-byte aligned");
@@ -1286,17 +1301,18 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     const MbWork w = mb_work(B, U, n);
     const int C = U * MT_H;
     char* base = (char*)work;
-    XNN_CUDA(cudaMemsetAsync(work, 0, w.total, st));
+    if (phase != 2) XNN_CUDA(cudaMemsetAsync(work, 0, w.total, st));
     // B1: reductions
     MlpArgs a{};
     a.pool = pool; a.w1 = w1; a.b1 = b1; a.scale2 = scale2; a.shift2 = shift2; a.w2 = w2; a.dopre = dopre;
     a.maskbits = const_cast<uint32_t*>(maskbits);
     a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U); a.drop_p = drop_p;
     a.part = (double*)(base + w.part1);
-    if (mt_launch<MLP_BWD_STATS>(a, st)) { set_error("xnn_mlp_bwd: B1 launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    if (phase != 2 && mt_launch<MLP_BWD_STATS>(a, st)) { set_error("xnn_mlp_bwd: B1 launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    if (phase == 1) return XNN_OK;
     float2* coef = (float2*)(base + w.coef);
-    mlp_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, st>>>(a.part, a.slots, B, U, stats2, dgamma2, dbeta2, dw2, db2,
-                                                              coef);
+    mlp_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, st>>>(a.part, a.slots, count, U, stats2, dgamma2, dbeta2, dw2,
+                                                              db2, coef, out_scale);
     XNN_CHECK_LAUNCH();
     // B2: dh -> dW1, dy
     MlpBwdArgs g{};

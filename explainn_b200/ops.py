@@ -236,10 +236,18 @@ def _work(nbytes, dev):
     return torch.empty((int(nbytes) + 7) // 8, dtype=torch.float64, device=dev)
 
 
+def _partial_view(work, nbytes):
+    """the leading `nbytes` of a work buffer as float64 (the partial sums a sync-BatchNorm exchange all-reduces)"""
+    return work.view(-1).view(torch.float64)[: int(nbytes) // 8] if work.dtype != torch.float64 else \
+        work.view(-1)[: int(nbytes) // 8]
+
+
 def bn_train_prepare(x2d, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1):
-    """x2d: (B, C) view of the BatchNorm input; returns scale, shift, stats."""
+    """x2d: (B, C) view of the BatchNorm input; returns scale, shift, stats.
+    sync: callable all-reducing (SUM) a tensor in place over the data-parallel ranks -> statistics of the GLOBAL
+    batch (B * world values per channel)."""
     B, C = x2d.shape
-    if B < 2:
+    if B * world < 2:
         raise ValueError("Expected more than 1 value per channel when training")
     lib = _lib.load()
     dev = x2d.device
@@ -247,8 +255,17 @@ def bn_train_prepare(x2d, gamma, beta, eps, momentum, running_mean, running_var,
     shift = torch.empty(C, dtype=torch.float32, device=dev)
     stats = torch.empty((C, 4), dtype=torch.float64, device=dev)
     work = _work(lib.xnn_bn_work_bytes(B, C), dev)
-    _call("xnn_bn_train_prepare", _p(_req(x2d, torch.float32, "x")), B, C, _p(gamma), _p(beta), float(eps),
-          float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift), _p(stats), _p(work), _stream())
+
+    def call(phase):
+        _call("xnn_bn_train_prepare", _p(_req(x2d, torch.float32, "x")), B, C, _p(gamma), _p(beta), float(eps),
+              float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift), _p(stats), _p(work), phase,
+              B * world, _stream())
+    if sync is None:
+        call(0)
+    else:
+        call(1)
+        sync(_partial_view(work, lib.xnn_bn_partial_bytes(B, C)))
+        call(2)
     return scale, shift, stats
 
 
@@ -269,7 +286,7 @@ def mlp_supported(n):
 def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1):
     """BatchNorm (linears.7) batch statistics of hpre = FC1(pool) without materialising hpre (tcgen05)."""
     B, U, n = pool.shape
-    if B < 2:
+    if B * world < 2:
         raise ValueError("Expected more than 1 value per channel when training")
     lib = _lib.load()
     dev = pool.device
@@ -278,9 +295,17 @@ def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean
     shift = torch.empty(C, dtype=torch.float32, device=dev)
     stats = torch.empty((C, 4), dtype=torch.float64, device=dev)
     work = _work(lib.xnn_mlp_bn2_work_bytes(B, U), dev)
-    _call("xnn_mlp_bn2_train_prepare", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")),
-          _p(b1), B, U, n, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var),
-          _p(scale), _p(shift), _p(stats), _p(work), _stream())
+
+    def call(phase):
+        _call("xnn_mlp_bn2_train_prepare", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")),
+              _p(b1), B, U, n, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var),
+              _p(scale), _p(shift), _p(stats), _p(work), phase, B * world, _stream())
+    if sync is None:
+        call(0)
+    else:
+        call(1)
+        sync(work)
+        call(2)
     return scale, shift, stats
 
 
@@ -328,10 +353,20 @@ def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_
     nbytes = int(lib.xnn_mlp_bwd_work_bytes(B, U, n))
     work = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
     off = (-work.data_ptr()) % 256
-    _call("xnn_mlp_bwd", _p(_req(dopre, torch.float32, "dopre")), _p(_req(pool, torch.float32, "pool")),
-          _p(_req(w1, torch.float32, "w1")), _p(b1), _p(scale2), _p(shift2), _p(_req(stats2, torch.float64, "stats2")),
-          _p(gamma2), _p(_req(w2, torch.float32, "w2")), _p(bits), float(drop_p), B, U, n, _p(dw1), _p(db1), _p(dg2),
-          _p(dbe2), _p(dw2), _p(db2), _p(dy), ctypes.c_void_p(work.data_ptr() + off), _stream())
+    wk = work[off:off + nbytes]
+
+    def call(phase):
+        _call("xnn_mlp_bwd", _p(_req(dopre, torch.float32, "dopre")), _p(_req(pool, torch.float32, "pool")),
+              _p(_req(w1, torch.float32, "w1")), _p(b1), _p(scale2), _p(shift2),
+              _p(_req(stats2, torch.float64, "stats2")), _p(gamma2), _p(_req(w2, torch.float32, "w2")), _p(bits),
+              float(drop_p), B, U, n, _p(dw1), _p(db1), _p(dg2), _p(dbe2), _p(dw2), _p(db2), _p(dy), _p(wk), phase,
+              B * world, 1.0 / world, _stream())
+    if sync is None:
+        call(0)
+    else:
+        call(1)
+        sync(_partial_view(wk, lib.xnn_mlp_bwd_partial_bytes(B, U)))
+        call(2)
     return dw1, db1, dg2, dbe2, dw2, db2, dy
 
 
@@ -378,8 +413,17 @@ def bn_bwd(g2d, relu_out, xpre2d, stats, gamma, inplace=True, out=None, sync=Non
     dgamma, dbeta = _outs(out, [(C,), (C,)], dev)
     dx = g2d if inplace else torch.empty_like(g2d)
     work = _work(lib.xnn_bn_work_bytes(B, C), dev)
-    _call("xnn_bn_bwd", _p(_req(g2d, torch.float32, "g")), _p(relu_out), _p(_req(xpre2d, torch.float32, "xpre")),
-          _p(stats), _p(gamma), B, C, _p(dgamma), _p(dbeta), _p(dx), _p(work), _stream())
+
+    def call(phase):
+        _call("xnn_bn_bwd", _p(_req(g2d, torch.float32, "g")), _p(relu_out), _p(_req(xpre2d, torch.float32, "xpre")),
+              _p(stats), _p(gamma), B, C, _p(dgamma), _p(dbeta), _p(dx), _p(work), phase, B * world, 1.0 / world,
+              _stream())
+    if sync is None:
+        call(0)
+    else:
+        call(1)
+        sync(_partial_view(work, lib.xnn_bn_partial_bytes(B, C)))
+        call(2)
     return dgamma, dbeta, dx
 
 

@@ -155,6 +155,27 @@ class GradBucket:
             off += n
 
 
+def enable_sync_batchnorm(group=None):
+    """Synchronised BatchNorm statistics (SURVEY.md 8e option (ii)): the three train-mode BatchNorm layers then
+    normalise with the statistics of the GLOBAL batch -- the reference's single-process numerics at the same global
+    batch (explainn/architectures/__init__.py:79,90,99; single device, selene/__init__.py:176-180).
+      linears.1 : ONE int64 all-reduce of the co-occurrence counts (exact);
+      linears.7 / .11 : fp64 (sum, sum of squares) partials all-reduced between the statistics kernels and their
+                  finalize; the two BatchNorm-backward reductions likewise (torch_ops.unit_bank_train / _bwd).
+    Every rank must run the same number of steps with at least one sample each."""
+    from . import torch_ops
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        torch_ops._sync.update(sum=None, world=1)
+        return
+    torch_ops._sync.update(sum=lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group), world=world)
+
+
+def disable_sync_batchnorm():
+    from . import torch_ops
+    torch_ops._sync.update(sum=None, world=1)
+
+
 def broadcast_parameters(model, src=0):
     if dist.is_initialized() and dist.get_world_size() > 1:
         for t in list(model.parameters()) + list(model.buffers()):

@@ -143,6 +143,14 @@ class StepPipeline:
             self.copied[s].record(self.copy_stream)
         self.h2d_bytes += x_host.numel() * x_host.element_size() + y_host.numel() * y_host.element_size()
         compute.wait_event(self.copied[s])
+        return self._run(s, x_dev, y_dev, length, compute)
+
+    def step_device(self, x_dev, y_dev, length=None):
+        """The same step on a batch that is ALREADY in device memory (float one-hot, ASCII or planes): no H2D copy;
+        the loss still comes back one call late.  bench.py times `value` through this."""
+        return self._run(self.i & 1, x_dev, y_dev, length, torch.cuda.current_stream(self.device))
+
+    def _run(self, s, x_dev, y_dev, length, compute):
         L = length if x_dev.dtype == torch.int32 else x_dev.shape[-1]
         if L is None:
             raise ValueError("packed planes need sequence_length: StepPipeline.step(planes, y, length=L)")

@@ -137,7 +137,15 @@ int xnn_bn_train_prepare(const float* x, int B, int C,
                          const float* gamma, const float* beta, float eps, float momentum,
                          float* running_mean, float* running_var,
                          float* scale, float* shift, double* stats, void* work,
-                         xnn_stream_t s);
+                         int phase, long long count, xnn_stream_t s);
+/* Synchronised BatchNorm over data-parallel ranks (SURVEY.md 8e option (ii); the reference computes its statistics
+ * over the whole single-process batch, architectures/__init__.py:79,90,99): the statistics / backward calls take
+ *   phase 0  the whole call (count and out_scale ignored),
+ *   phase 1  the partial sums only, left at the start of `work` (xnn_*_partial_bytes) for the host to all-reduce,
+ *   phase 2  the rest, with count = values per channel over the GLOBAL batch; parameter gradients that are pure
+ *            functions of the all-reduced sums are multiplied by out_scale (1/world) so that the gradient
+ *            all-reduce(SUM) that follows restores them. */
+size_t xnn_bn_partial_bytes(int B, int C);
 /* opre[b,u] = b2[u] + sum_m W2[u,m]*drop(relu(scale2*hpre+shift2)); dropout is
  * a counter-based Bernoulli(1-p)/ (1-p) mask from (seed,b,u,m); p=0 disables.
  * hpre/b1 note: scale2/shift2 are per (u,m) channel (100U). */
@@ -161,7 +169,7 @@ size_t xnn_mlp_bn2_work_bytes(int B, int U);
 int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
                               const float* gamma, const float* beta, float eps, float momentum,
                               float* running_mean, float* running_var, float* scale, float* shift,
-                              double* stats, void* work, xnn_stream_t s);
+                              double* stats, void* work, int phase, long long count, xnn_stream_t s);
 /* opre[b,u] = b2[u] + sum_m W2[u,m]*drop(relu(scale2*hpre+shift2)) -- xnn_fc1_fwd + xnn_fc2_fwd fused.
  * Dropout: injected byte mask (B,U,100), else Philox keep-bits from (seed,b,u) when drop_p > 0.
  * maskbits uint32 [B][U][4] (NULL in inference): bit m of a (b,u) row = hidden channel m is ACTIVE (kept by
@@ -192,11 +200,12 @@ int xnn_linear_bwd(const float* dy, const float* w, const float* x, int B, int U
  *   dy[b,u,q] = pool * sum_m dhpre*W1 (gradient at the arg-max conv output through exp).
  * work: xnn_mlp_bwd_work_bytes, 256-byte aligned. */
 size_t xnn_mlp_bwd_work_bytes(int B, int U, int n);
+size_t xnn_mlp_bwd_partial_bytes(int B, int U);
 int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w1, const float* b1,
                 const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
                 const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
                 float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
-                float* dy, void* work, xnn_stream_t s);
+                float* dy, void* work, int phase, long long count, float out_scale, xnn_stream_t s);
 /* Train-mode BatchNorm backward over the batch dimension, C channels:
  *   given g = dL/d(out) (B,C), xpre (B,C), stats (mean,var,invstd), gamma; when
  *   relu_out != NULL the BatchNorm is followed by a ReLU whose output it is and
@@ -205,7 +214,7 @@ int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w1, const fl
  * dx may alias g. work: xnn_bn_work_bytes(B,C) */
 int xnn_bn_bwd(const float* g, const float* relu_out, const float* xpre, const double* stats,
                const float* gamma, int B, int C, float* dgamma, float* dbeta, float* dx, void* work,
-               xnn_stream_t s);
+               int phase, long long count, float out_scale, xnn_stream_t s);
 /* FC2 backward + dropout/relu masks: from dopre (B,U) and hpre:
  *   dW2 (U,100), db2 (U), g2[b,u,m] = dopre*W2*mask*(bn2(hpre)>0) (B,U,100). */
 size_t xnn_fc2_bwd_work_bytes(int B, int U);
