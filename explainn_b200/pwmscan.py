@@ -27,42 +27,59 @@ def read_matrix(path, integer=False):
     return np.array(rows, dtype=np.int32 if integer else np.float64).T.copy()
 
 
-def read_fasta(path_or_lines):
-    """pwm_scoring.c:575-673: header = first word after '>', letters upper-cased, A0 C1 G2 T3, any other
-    letter 4, non-letters dropped, empty records skipped.  Returns (headers, codes int8, offsets int64)."""
-    lines = open(path_or_lines) if isinstance(path_or_lines, str) else path_or_lines
+def _fasta_lut():
     lut = np.full(256, -1, dtype=np.int8)
-    for ch in range(256):
-        if chr(ch).isalpha() and ch < 128:
+    for ch in range(128):
+        if chr(ch).isalpha():
             lut[ch] = 4
     for i, ch in enumerate("ACGT"):
         lut[ord(ch)] = i
         lut[ord(ch.lower())] = i
-    headers, chunks, offsets = [], [], [0]
-    cur, hdr = None, None
+    return lut
 
-    def flush():
-        if hdr is not None and cur:
-            rec = np.concatenate(cur) if len(cur) > 1 else cur[0]
-            if rec.size:
-                headers.append(hdr)
-                chunks.append(rec)
-                offsets.append(offsets[-1] + rec.size)
 
-    for line in lines:
-        if line.startswith(">"):
-            flush()
-            parts = line[1:].split()
-            hdr = parts[0] if parts else ""
-            cur = []
-        elif hdr is not None:
-            b = lut[np.frombuffer(line.encode("latin-1", "replace"), dtype=np.uint8)]
-            cur.append(b[b >= 0])
-    flush()
-    if hasattr(lines, "close") and isinstance(path_or_lines, str):
-        lines.close()
-    codes = np.concatenate(chunks) if chunks else np.zeros(0, dtype=np.int8)
-    return headers, codes.astype(np.int8), np.array(offsets, dtype=np.int64)
+def read_fasta(path_or_lines):
+    """pwm_scoring.c:575-673: header = first word after '>', letters upper-cased, A0 C1 G2 T3, any other
+    letter 4, non-letters dropped, empty records skipped.  Returns (headers, codes int8, offsets int64).
+    Vectorised over the whole file (a chromosome-sized FASTA is one LUT gather and two prefix sums, not a Python
+    loop per line)."""
+    if isinstance(path_or_lines, (str, bytes)) and not isinstance(path_or_lines, bytes):
+        with open(path_or_lines, "rb") as fh:
+            data = fh.read()
+    elif hasattr(path_or_lines, "read"):
+        data = path_or_lines.read()
+    else:
+        data = "".join(path_or_lines)
+    if isinstance(data, str):
+        data = data.encode("latin-1", "replace")
+    buf = np.frombuffer(data, dtype=np.uint8)
+    if buf.size == 0:
+        return [], np.zeros(0, dtype=np.int8), np.zeros(1, dtype=np.int64)
+    nl = np.flatnonzero(buf == 10)
+    starts = np.concatenate(([0], nl + 1))
+    starts = starts[starts < buf.size]
+    ends = np.concatenate((nl, [buf.size]))[:starts.size]
+    is_hdr = buf[starts] == ord(">")
+    hs, he = starts[is_hdr], ends[is_hdr]
+    if hs.size == 0:
+        return [], np.zeros(0, dtype=np.int8), np.zeros(1, dtype=np.int64)
+    mapped = _fasta_lut()[buf]
+    delta = np.zeros(buf.size + 1, dtype=np.int8)
+    delta[hs] += 1
+    delta[he] -= 1
+    mapped[np.cumsum(delta[:-1], dtype=np.int8) > 0] = -1        # header lines carry no sequence
+    mapped[:hs[0]] = -1                                          # anything before the first header is ignored
+    keep = mapped >= 0
+    csum = np.concatenate(([0], np.cumsum(keep, dtype=np.int64)))
+    bounds = csum[np.append(hs, buf.size)]
+    lens = np.diff(bounds)
+    headers = []
+    for a, b, ln in zip(hs, he, lens):
+        if ln > 0:
+            parts = data[a + 1:b].decode("latin-1").split()
+            headers.append(parts[0] if parts else "")
+    offsets = np.concatenate(([0], np.cumsum(lens[lens > 0]))).astype(np.int64)
+    return headers, mapped[keep].astype(np.int8), offsets
 
 
 class PwmScoring:
@@ -162,3 +179,128 @@ class PwmScoring:
             else:
                 out.append("%s%g" % (pre, result["sum"][r]))
         return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# command line: the interface of the reference tool (pwm_scoring.c:715-1000), the only native boundary the
+# reference has: argv in, one text line per FASTA record on stdout, exit code 0 / 1,
+# errors on stderr.
+# ---------------------------------------------------------------------------------------------------------
+USAGE = """Usage: %s [options] -m <matrix_file> [<] <fasta_file>
+   where options are:
+     -b[--best]             Compute best single match scores
+     -d[--debug]            Produce debugging output
+     -h[--help]             Show this stuff
+     -f[--forward]          Scan sequences in forward direction [def=bidirectional]
+     -u[--unorm]            Normalize pwm scores by a uniform background base composition (Default=0.25)
+     -p[--prob] <bg freq>   Normalize pwm scores by library-dependent nucleotide frequencies <bg freq>: 0.29,0.21,0.21,0.29
+                            Note that nucleotide frequencies (<bg freq>) MUST BE comma-separated
+     -q[--seqnorm]          Normalize pwm scores by sequence-based nucleotide composition
+     -r[--nohdr]            Output raw scores (with no FASTA header)
+     --lpm                  Input matrix is a letter probability matrix (LPM) [Default]
+     --pwm                  Input matrix is a position weight matrix (PWM)
+     -w[--pweight]          Set a pseudo-weight to re-normalize the frequencies of the letter-probability matrix (LPM)
+                            Recommended value is 0.0001 [Default=0.0]
+
+   Score a set of nucleotide sequences in FASTA format (<fasta_file>), based on matches to a sequence motif
+   represented by an INTEGER position weight matrix [--pwm] or a base probability matrix [--lpm] (<matrix_file>).
+   Note that the background normalization options (-u, -p, -q) are only valid for base probability matrices.
+   For integer PWMs, only the best single match scores are reported, along with the position, strand, and sequence match.
+
+"""
+
+
+def main(argv=None, stdin=None, stdout=None, stderr=None):
+    """`pwm_scoring [options] -m <matrix_file> [<] <fasta_file>` -> exit code.  Options, their precedence
+    (--pwm switches the background normalisations off, :840-843; -u wins over -p, :881-903), messages and exit
+    codes follow pwm_scoring.c:752-821,881-913,986-987; the scoring runs in the CUDA scan kernels."""
+    import getopt
+    import os
+    import sys
+    argv = list(sys.argv if argv is None else argv)
+    stdin = stdin or sys.stdin
+    stdout = stdout or sys.stdout
+    stderr = stderr or sys.stderr
+    prog, args = argv[0], argv[1:]
+    longopts = ["best", "debug", "help", "forward", "matrix=", "prob=", "seqnorm", "unorm", "nohdr", "pweight=",
+                "lpm", "pwm"]
+    opts = []
+    while True:                                        # getopt_long reports an unknown option and carries on
+        try:
+            opts, rest = getopt.gnu_getopt(args, "bdhfm:p:uqrw:", longopts)
+            break
+        except getopt.GetoptError as e:
+            print(f"{prog}: {e.msg}", file=stderr)
+            bad = [a for a in args if a.lstrip("-").split("=")[0] == e.opt and a.startswith("-")]
+            if not bad:
+                opts, rest = [], []
+                break
+            args.remove(bad[0])
+    o = dict(best=False, debug=False, forward=False, matrix=None, prob=None, seqnorm=False, unorm=False, nohdr=False,
+             pweight=0.0, pwm=False)
+    for k, v in opts:
+        if k in ("-b", "--best"): o["best"] = True
+        elif k in ("-d", "--debug"): o["debug"] = True
+        elif k in ("-f", "--forward"): o["forward"] = True
+        elif k in ("-m", "--matrix"): o["matrix"] = v
+        elif k in ("-p", "--prob"): o["prob"] = v
+        elif k in ("-q", "--seqnorm"): o["seqnorm"] = True
+        elif k in ("-u", "--unorm"): o["unorm"] = True
+        elif k in ("-r", "--nohdr"): o["nohdr"] = True
+        elif k in ("-w", "--pweight"):
+            try:
+                o["pweight"] = float(v)                # atof
+            except ValueError:
+                o["pweight"] = 0.0
+        elif k == "--pwm": o["pwm"] = True
+    if o["matrix"] is None:
+        stderr.write(USAGE % prog)
+        return 1
+    try:
+        matrix = read_matrix(o["matrix"], integer=o["pwm"])
+    except OSError as e:
+        print(f"Unable to open '{o['matrix']}': {e.strerror}({e.errno})", file=stderr)
+        return 1
+    except ValueError as e:
+        print(f"Error: {e}", file=stderr)
+        return 1
+    prob = None
+    if not o["pwm"] and not o["unorm"] and o["prob"] is not None:
+        toks = [t for t in o["prob"].split(",") if t != ""]
+        if len(toks) != 4:
+            print(f"Number of TOKENS: {len(toks)}", file=stderr)
+            print("Please, specify correct library-dependent nucleotide frequencies <bg freq>: they MUST BE "
+                  "comma-separated!", file=stderr)
+            return 1
+        prob = toks
+    if rest and rest[0] != "-":
+        try:
+            fh = open(rest[0], "rb")
+        except OSError as e:
+            print(f"Unable to open '{rest[0]}': {e.strerror}({e.errno})", file=stderr)
+            return 1
+        with fh:
+            headers, codes, offsets = read_fasta(fh)
+        if o["debug"]:
+            print(f"Processing file {rest[0]}", file=stderr)
+    else:
+        headers, codes, offsets = read_fasta(getattr(stdin, "buffer", stdin))
+    if o["debug"]:
+        print(f"Motif length: {matrix.shape[1]}", file=stderr)
+    if not headers:
+        return 0
+    if o["pwm"]:
+        ps = PwmScoring(matrix, mode="pwm", forward=o["forward"])
+    else:
+        ps = PwmScoring(matrix, mode="lpm", best=o["best"], forward=o["forward"], unorm=o["unorm"], prob=prob,
+                        seqnorm=o["seqnorm"], pweight=o["pweight"])
+    if headers:
+        res = ps.score(codes, offsets)
+        for line in ps.format(headers, codes, offsets, res, nohdr=o["nohdr"]):
+            stdout.write(line + "\n")
+    return 0
+
+
+if __name__ == "__main__":
+    import sys
+    sys.exit(main())

@@ -192,55 +192,68 @@ def _grad_views(arena, offs, shapes):
     return out, res
 
 
-@custom_op("explainn_b200::unit_bank_train_bwd", mutates_args=("arena",), device_types="cuda")
-def unit_bank_train_bwd(do: torch.Tensor, planes: torch.Tensor, L: int, params: Sequence[torch.Tensor],
-                        saved: Sequence[torch.Tensor], drop_p: float, seed: int,
-                        drop_mask: Optional[torch.Tensor], arena: Optional[torch.Tensor],
-                        offs: Sequence[int]) -> List[torch.Tensor]:
-    """Returns the 12 parameter gradients in BANK_PARAMS order -- or, with an arena, an EMPTY list: the gradients
-    are then at arena[offs[i]:] (the autograd formula hands out views of them)."""
+def _bank_grad_shapes(cw, n):
+    U, _, k = cw.shape
+    C = U * HIDDEN
+    return [(U, 4, k), (U,), (U,), (U,), (C, n), (C,), (C,), (C,), (U, HIDDEN), (U,), (U,), (U,)]
+
+
+def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, arena):
+    """the backward of the unit bank, every parameter gradient written into `flat` (BANK_PARAMS order)"""
     cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = params
     o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre = saved
     B, U = o.shape
     k = cw.shape[2]
-    n = pool.shape[2]
     C = U * HIDDEN
-    n_pos = B * (L - k + 1) * (_sync["world"] if _sync["sum"] else 1)
-    shapes = [(U, 4, k), (U,), (U,), (U,), (C, n), (C,), (C,), (C,), (U, HIDDEN), (U,), (U,), (U,)]
-    if arena is not None:
-        flat, _ = _grad_views(arena, offs, shapes)
-    else:
-        flat = [cw.new_empty(sh) for sh in shapes]
+    sync, world = _sync["sum"], (_sync["world"] if _sync["sum"] else 1)
+    n_pos = B * (L - k + 1) * world
     d_cw, d_cb, d_g1, d_be1, d_w1, d_b1, d_g2, d_be2, d_w2, d_b2, d_g3, d_be3 = flat
-    _, _, dopre = ops.bn_bwd(do.contiguous(), o, opre, stats3, g3, inplace=False, out=[d_g3, d_be3],
-                             sync=_sync["sum"], world=_sync["world"])
+    _, _, dopre = ops.bn_bwd(do.contiguous(), o, opre, stats3, g3, inplace=False, out=[d_g3, d_be3], sync=sync,
+                             world=world)
     if bits.numel():
         dy = ops.mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, g2, w2, bits, drop_p,
-                         out=[d_w1, d_b1, d_g2, d_be2, d_w2, d_b2], sync=_sync["sum"], world=_sync["world"])[6]
+                         out=[d_w1, d_b1, d_g2, d_be2, d_w2, d_b2], sync=sync, world=world)[6]
     else:
         dw2_, db2_, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, drop_p, seed, drop_mask)
         d_w2.view(-1).copy_(dw2_.view(-1)); d_b2.copy_(db2_)
-        _, _, dhpre = ops.bn_bwd(gh.view(B, C), None, hpre.view(B, C), stats2, g2, out=[d_g2, d_be2],
-                                 sync=_sync["sum"], world=_sync["world"])
+        _, _, dhpre = ops.bn_bwd(gh.view(B, C), None, hpre.view(B, C), stats2, g2, out=[d_g2, d_be2], sync=sync,
+                                 world=world)
         dw1_, db1_, dy = ops.fc1_bwd(dhpre.view(B, U, HIDDEN), pool, w1)
         d_w1.view(-1).copy_(dw1_.view(-1)); d_b1.copy_(db1_)
     if arena is not None:
         for hook in _after_mlp_grads:
             hook(arena)
     ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos, out=[d_cw, d_cb, d_g1, d_be1])
-    return [] if arena is not None else [t.view(sh) for t, sh in zip(flat, shapes)]
+
+
+@custom_op("explainn_b200::unit_bank_train_bwd", mutates_args=(), device_types="cuda")
+def unit_bank_train_bwd(do: torch.Tensor, planes: torch.Tensor, L: int, params: Sequence[torch.Tensor],
+                        saved: Sequence[torch.Tensor], drop_p: float, seed: int,
+                        drop_mask: Optional[torch.Tensor]) -> List[torch.Tensor]:
+    """the 12 parameter gradients in BANK_PARAMS order (functional form)"""
+    shapes = _bank_grad_shapes(params[0], saved[1].shape[2])
+    flat = [params[0].new_empty(sh) for sh in shapes]
+    _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, None)
+    return flat
 
 
 @unit_bank_train_bwd.register_fake
+def _(do, planes, L, params, saved, drop_p, seed, drop_mask):
+    return [params[0].new_empty(sh) for sh in _bank_grad_shapes(params[0], saved[1].shape[2])]
+
+
+@custom_op("explainn_b200::unit_bank_train_bwd_arena", mutates_args=("arena",), device_types="cuda")
+def unit_bank_train_bwd_arena(do: torch.Tensor, planes: torch.Tensor, L: int, params: Sequence[torch.Tensor],
+                              saved: Sequence[torch.Tensor], drop_p: float, seed: int,
+                              drop_mask: Optional[torch.Tensor], arena: torch.Tensor, offs: Sequence[int]) -> None:
+    """the same with the gradients written at arena[offs[i]:] (the autograd formula hands out views of them)"""
+    flat, _ = _grad_views(arena, offs, _bank_grad_shapes(params[0], saved[1].shape[2]))
+    _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, arena)
+
+
+@unit_bank_train_bwd_arena.register_fake
 def _(do, planes, L, params, saved, drop_p, seed, drop_mask, arena, offs):
-    if arena is not None:
-        return []
-    cw = params[0]
-    U, _, k = cw.shape
-    n = saved[1].shape[2]
-    C = U * HIDDEN
-    return [cw.new_empty(sh) for sh in
-            [(U, 4, k), (U,), (U,), (U,), (C, n), (C,), (C,), (C,), (U, HIDDEN), (U,), (U,), (U,)]]
+    return None
 
 
 def _bank_setup(ctx, inputs, output):
@@ -255,15 +268,13 @@ def _bank_backward(ctx, *grads):
     saved = ctx.saved_tensors
     params, outs = list(saved[:ctx.n_params]), list(saved[ctx.n_params:])
     do = grads[0][0] if isinstance(grads[0], (list, tuple)) else grads[0]
-    res = torch.ops.explainn_b200.unit_bank_train_bwd(do, ctx.planes, ctx.L, params, outs, ctx.drop_p, ctx.seed,
-                                                      ctx.drop_mask, ctx.arena, ctx.offs)
     if ctx.arena is not None:
-        cw = params[0]
-        U, _, k = cw.shape
-        n = outs[1].shape[2]
-        C = U * HIDDEN
-        shapes = [(U, 4, k), (U,), (U,), (U,), (C, n), (C,), (C,), (C,), (U, HIDDEN), (U,), (U,), (U,)]
-        _, res = _grad_views(ctx.arena, ctx.offs, shapes)
+        torch.ops.explainn_b200.unit_bank_train_bwd_arena(do, ctx.planes, ctx.L, params, outs, ctx.drop_p, ctx.seed,
+                                                          ctx.drop_mask, ctx.arena, ctx.offs)
+        _, res = _grad_views(ctx.arena, ctx.offs, _bank_grad_shapes(params[0], outs[1].shape[2]))
+    else:
+        res = torch.ops.explainn_b200.unit_bank_train_bwd(do, ctx.planes, ctx.L, params, outs, ctx.drop_p, ctx.seed,
+                                                          ctx.drop_mask)
     pg = [g.view_as(p) for g, p in zip(res, params)]
     return None, None, pg, None, None, None, None, None, None, None
 
@@ -285,21 +296,29 @@ def _(x, w, b, arena, offs):
     return x.new_empty((x.shape[0], w.shape[0]))
 
 
-@custom_op("explainn_b200::linear_bwd", mutates_args=("arena",), device_types="cuda")
-def linear_bwd(dy: torch.Tensor, w: torch.Tensor, x: torch.Tensor, arena: Optional[torch.Tensor],
-               offs: Sequence[int]) -> List[torch.Tensor]:
-    """[dx, dw, db], or [dx] with the weight / bias gradients written at arena[offs[0]:], arena[offs[1]:]"""
-    F, U = w.shape
-    if arena is None:
-        return list(ops.linear_bwd(dy, w, x))
-    out = [arena[offs[0]:offs[0] + F * U], arena[offs[1]:offs[1] + F]]
-    return [ops.linear_bwd(dy, w, x, out=out)[0]]
+@custom_op("explainn_b200::linear_bwd", mutates_args=(), device_types="cuda")
+def linear_bwd(dy: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> List[torch.Tensor]:
+    """[dx, dw, db] (functional form)"""
+    return list(ops.linear_bwd(dy, w, x))
 
 
 @linear_bwd.register_fake
+def _(dy, w, x):
+    return [x.new_empty(x.shape), w.new_empty(w.shape), w.new_empty((w.shape[0],))]
+
+
+@custom_op("explainn_b200::linear_bwd_arena", mutates_args=("arena",), device_types="cuda")
+def linear_bwd_arena(dy: torch.Tensor, w: torch.Tensor, x: torch.Tensor, arena: torch.Tensor,
+                     offs: Sequence[int]) -> torch.Tensor:
+    """dx; the weight / bias gradients are written at arena[offs[0]:], arena[offs[1]:]"""
+    F, U = w.shape
+    out = [arena[offs[0]:offs[0] + F * U], arena[offs[1]:offs[1] + F]]
+    return ops.linear_bwd(dy, w, x, out=out)[0]
+
+
+@linear_bwd_arena.register_fake
 def _(dy, w, x, arena, offs):
-    dx = x.new_empty(x.shape)
-    return [dx] if arena is not None else [dx, w.new_empty(w.shape), w.new_empty((w.shape[0],))]
+    return x.new_empty(x.shape)
 
 
 def _linear_setup(ctx, inputs, output):
@@ -311,10 +330,11 @@ def _linear_setup(ctx, inputs, output):
 def _linear_backward(ctx, dy):
     x, w = ctx.saved_tensors
     F, U = w.shape
-    res = torch.ops.explainn_b200.linear_bwd(dy.contiguous(), w, x, ctx.arena, ctx.offs)
     if ctx.arena is not None:
         a, o = ctx.arena, ctx.offs
-        return res[0], a[o[0]:o[0] + F * U].view(F, U), a[o[1]:o[1] + F], None, None
+        dx = torch.ops.explainn_b200.linear_bwd_arena(dy.contiguous(), w, x, a, o)
+        return dx, a[o[0]:o[0] + F * U].view(F, U), a[o[1]:o[1] + F], None, None
+    res = torch.ops.explainn_b200.linear_bwd(dy.contiguous(), w, x)
     return res[0], res[1], res[2], None, None
 
 

@@ -31,6 +31,7 @@ class StepPipeline:
         if self.device.type != "cuda":
             raise RuntimeError("StepPipeline runs on a CUDA device only (explainn_b200 has no CPU fallback)")
         self.copy_stream = torch.cuda.Stream(self.device)
+        self.capture_stream = torch.cuda.Stream(self.device)
         self.slots = [None, None]            # (x_dev, y_dev)
         self.copied = [torch.cuda.Event(), torch.cuda.Event()]
         self.consumed = [None, None]         # event: the step that read slot s has finished with it
@@ -119,8 +120,8 @@ class StepPipeline:
         torch.cuda.current_stream(self.device).synchronize()
         g = torch.cuda.CUDAGraph()
         k0 = ops.kernel_launches
-        with torch.cuda.graph(g):
-            loss = self._step_body(PackedDNA(planes, L), y_static)
+        with torch.cuda.graph(g, stream=self.capture_stream):
+            loss = self._step_body(PackedDNA(planes, L), y_static).detach()
         self.graph_kernels = ops.kernel_launches - k0
         if hasattr(self.optimizer, "note_replays"):
             self.optimizer.note_replays(-1)         # the capture counted one host step without executing it
@@ -165,6 +166,14 @@ class StepPipeline:
             if hasattr(self.optimizer, "note_replays"):
                 self.optimizer.note_replays(1)
             loss = self.static[2]
+        elif self.use_graph:
+            # warm-up steps of a pipeline that will capture: run them on the capture stream, so that the autograd
+            # nodes that outlive an iteration (AccumulateGrad) belong to the stream the graph is captured on
+            cs = self.capture_stream
+            cs.wait_stream(compute)
+            with torch.cuda.stream(cs):
+                loss = self._step_body(self._as_input(x_dev, L), y_dev).detach()
+            compute.wait_stream(cs)
         else:
             loss = self._step_body(self._as_input(x_dev, L), y_dev).detach()
         lh = self.loss_host[s]

@@ -862,8 +862,9 @@ def test_fused_losses_match_torch():
 def test_custom_ops_are_registered_and_pass_opcheck():
     """torch.library registration: schema, fake tensor, autograd registration, AOT dispatch"""
     import torch.library
-    assert {"unit_bank_train", "unit_bank_train_bwd", "unit_bank_eval", "linear", "linear_bwd", "loss", "loss_bwd",
-            "pack_onehot", "frontend_acts", "frontend_pool", "pwm_scan", "bn_running_update"} <= set(dir(torch.ops.explainn_b200))
+    assert {"unit_bank_train", "unit_bank_train_bwd", "unit_bank_train_bwd_arena", "unit_bank_eval", "linear",
+            "linear_bwd", "linear_bwd_arena", "loss", "loss_bwd", "pack_onehot", "frontend_acts", "frontend_pool",
+            "pwm_scan", "bn_running_update"} <= set(dir(torch.ops.explainn_b200))
     g = torch.Generator().manual_seed(0)
     x = torch.randn(33, 12, generator=g).to(DEV).requires_grad_(True)
     w = torch.randn(5, 12, generator=g).to(DEV).requires_grad_(True)
@@ -881,6 +882,9 @@ def test_custom_ops_are_registered_and_pass_opcheck():
               bank[7].bias, bank[10].weight, bank[10].bias, bank[11].weight, bank[11].bias]
     torch.library.opcheck(torch.ops.explainn_b200.unit_bank_train.default,
                           (planes, 67, params, [1e-5, 1e-5, 1e-5], 0.0, 0, None, None, None, []),
+                          test_utils=("test_schema", "test_autograd_registration", "test_faketensor"))
+    arena = torch.zeros(128, device=DEV)
+    torch.library.opcheck(torch.ops.explainn_b200.linear.default, (x, w, b, arena, [0, 64]),
                           test_utils=("test_schema", "test_autograd_registration", "test_faketensor"))
     with pytest.raises((NotImplementedError, RuntimeError)):
         torch.ops.explainn_b200.linear(x.detach().cpu(), w.detach().cpu(), b.detach().cpu(), None, [])   # cuda only
@@ -967,3 +971,25 @@ def test_graphed_step_draws_new_dropout_masks_and_counts_adam_steps():
     losses = [pipe.step(x, y) for _ in range(6)][1:] + [pipe.flush()]
     assert len(set(losses[1:])) == len(losses[1:]), losses    # same input, same weights: only the masks differ
     assert int(opt._step_dev.item()) == 6 and int(m.linears[1].num_batches_tracked.item()) == 6
+
+
+def test_pwm_scoring_command_line_reproduces_the_reference_tool(tmp_path):
+    """a15: `python -m explainn_b200.pwmscan` with the tool's own options (pwm_scoring.c:752-798) against the stdout
+    of the reference ELF for 12 option sets; FASTA from a file and from stdin ('-' and no argument)."""
+    import subprocess
+    import sys
+    g = U.pwmscan_golden()
+    fa, lpm, pwm = tmp_path / "g.fa", tmp_path / "g.lpm", tmp_path / "g.pwm"
+    fa.write_text(g["fasta"]); lpm.write_text(g["lpm"]); pwm.write_text(g["pwm"])
+    env = dict(os.environ, PYTHONPATH=U.ROOT)
+    for i, (name, run) in enumerate(g["runs"].items()):
+        mat = str(pwm) if "--pwm" in run["opts"] else str(lpm)
+        cmd = [sys.executable, "-m", "explainn_b200.pwmscan"] + run["opts"] + ["-m", mat]
+        if i % 3 == 0:
+            r = subprocess.run(cmd + [str(fa)], capture_output=True, text=True, env=env)
+        elif i % 3 == 1:
+            r = subprocess.run(cmd + ["-"], input=g["fasta"], capture_output=True, text=True, env=env)
+        else:
+            r = subprocess.run(cmd, input=g["fasta"], capture_output=True, text=True, env=env)
+        assert r.returncode == 0, (name, r.stderr[-500:])
+        assert r.stdout == run["stdout"], name

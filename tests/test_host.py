@@ -204,3 +204,32 @@ def test_metrics_surface_and_no_cpu_fallback():
     y, s = np.array([0, 0, 1, 1]), np.array([0.1, 0.4, 0.35, 0.8])
     assert abs(MO.get_metrics()["aucROC"](y, s) - 0.75) < 1e-15
     assert abs(MO.get_metrics()["aucPR"](y, s) - 0.8333333333333333) < 1e-15
+
+
+def test_pwm_scoring_command_line_errors(tmp_path):
+    """a15: usage / exit codes / stderr of the command line (pwm_scoring.c:799-821, 893-899, 906-913); no GPU needed
+    for the error paths"""
+    import io
+    from explainn_b200 import pwmscan
+    err = io.StringIO()
+    assert pwmscan.main(["pwm_scoring"], stderr=err) == 1
+    assert err.getvalue().startswith("Usage: pwm_scoring [options] -m <matrix_file> [<] <fasta_file>")
+    assert "--pwm                  Input matrix is a position weight matrix (PWM)" in err.getvalue()
+    err = io.StringIO()
+    assert pwmscan.main(["pwm_scoring", "-m", str(tmp_path / "missing.lpm"), "x.fa"], stderr=err) == 1
+    assert "Unable to open" in err.getvalue()
+    g = U.pwmscan_golden()
+    lpm = tmp_path / "g.lpm"
+    lpm.write_text(g["lpm"])
+    err = io.StringIO()
+    assert pwmscan.main(["pwm_scoring", "-p", "0.3,0.2,0.5", "-m", str(lpm), "x.fa"], stderr=err) == 1
+    assert err.getvalue().splitlines()[0] == "Number of TOKENS: 3"
+    err = io.StringIO()
+    assert pwmscan.main(["pwm_scoring", "-m", str(lpm), str(tmp_path / "missing.fa")], stderr=err) == 1
+    assert err.getvalue().startswith(f"Unable to open '{tmp_path / 'missing.fa'}': No such file or directory(2)")
+    # an empty FASTA is not an error: no output, exit 0 (never reaches a kernel)
+    empty = tmp_path / "e.fa"
+    empty.write_text("")
+    out = io.StringIO()
+    assert pwmscan.main(["pwm_scoring", "-m", str(lpm), str(empty)], stdout=out, stderr=io.StringIO()) == 0
+    assert out.getvalue() == ""
