@@ -108,6 +108,9 @@ struct MlpArgs {
     float drop_p;
     unsigned long long seed;
     const unsigned long long* seed_dev;   // optional device-resident draw counter mixed into the seed (graph replays)
+    unsigned char* image_out;             // F1: write the staged pool tiles here (mlp_image layout), or NULL
+    const unsigned char* image;           // F2 / B1 image kernels: pool tile images
+    const unsigned char* w1_image;        //                        W1 images [U][3][chunksQ][112 rows] uint4
 };
 
 enum { MLP_STATS = 0, MLP_APPLY = 1, MLP_BWD_STATS = 2 };
@@ -194,6 +197,23 @@ __device__ __forceinline__ void split2_bf16x3(float x0, float x1, uint32_t& w0, 
     w0 = __byte_perm(h0, h1, 0x7632);                       // (upper half of x0) | (upper half of x1) << 16
     w1 = __byte_perm(m0, m1, 0x7632);
     w2 = __byte_perm(__float_as_uint(q0), __float_as_uint(q1), 0x7632);
+}
+
+// The same three pieces with ROUND-TO-NEAREST conversions (cvt.rn.bf16x2.f32 packs the pair): hi + mid + lo = x to
+// 2^-25 |x|, and hi + mid alone = x to 2^-18 |x| with an UNBIASED error, which is what lets the backward pass run
+// on two pieces (three products) inside its 1e-4 gradient tolerance.  Used for everything that goes into the tile
+// images (mlp_image layout).
+__device__ __forceinline__ uint32_t cvt_bf16x2_rn(float lo_elem, float hi_elem) {
+    uint32_t w;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi_elem), "f"(lo_elem));
+    return w;
+}
+__device__ __forceinline__ void split2_bf16x3_rn(float x0, float x1, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
+    w0 = cvt_bf16x2_rn(x0, x1);
+    const float r0 = x0 - __uint_as_float(w0 << 16), r1 = x1 - __uint_as_float(w0 & 0xFFFF0000u);
+    w1 = cvt_bf16x2_rn(r0, r1);
+    const float q0 = r0 - __uint_as_float(w1 << 16), q1 = r1 - __uint_as_float(w1 & 0xFFFF0000u);
+    w2 = cvt_bf16x2_rn(q0, q1);
 }
 
 #define WS_WROWS 104   // rows of the W1 operand layout (100 hidden channels, padded to a multiple of 8)
@@ -343,7 +363,8 @@ mlp_fc1_kernel(MlpArgs a) {
                 for (int c = 0; c < 12; ++c) {
                     if (c < chunksQ) {
                         uint32_t w0, w1v, w2v;
-                        split2_bf16x3(pv[h][c][0], pv[h][c][1], w0, w1v, w2v);
+                        if (MODE == MLP_STATS) split2_bf16x3_rn(pv[h][c][0], pv[h][c][1], w0, w1v, w2v);
+                        else split2_bf16x3(pv[h][c][0], pv[h][c][1], w0, w1v, w2v);
                         const int o = (c * 128 + srow) * 4 + swd;
                         pw[o] = w0; pw[ppiece / 4 + o] = w1v; pw[2 * (ppiece / 4) + o] = w2v;
                     }
@@ -367,8 +388,18 @@ mlp_fc1_kernel(MlpArgs a) {
             umma::fence_after_sync();
             if (lane == 0) {
                 const uint32_t poff = st * (pstage >> 4);            // pool stage, in descriptor units
+                const bool img = (MODE == MLP_STATS) && a.image_out != nullptr;
+                // the staged tile IS its image (mlp_image layout): one bulk store, no LSU work; the later passes of
+                // the step fetch their operand stages from it with one bulk load each
+                if (img) {
+                    umma::bulk_store(a.image_out + (size_t)(lo + i) * pstage,
+                                     reinterpret_cast<unsigned char*>(ps) + (size_t)st * pstage, pstage);
+                    umma::bulk_commit_group();
+                }
                 umma::issue_table2(s_tab, 6 * kstepsQ, umma::desc_hi(128u), umma::desc_hi(128u),
                                    MODE == MLP_APPLY ? poff : 0u, MODE == MLP_APPLY ? 0u : poff, tmem + st * 128u, idesc);
+                // mma_done[st] releases the stage to the producers: the store must have read it by then
+                if (img) umma::bulk_wait_read_all();
                 umma::commit(&sh->mma_done[st]);
             }
             __syncwarp();
@@ -741,6 +772,295 @@ mlp_fc1_lockstep_kernel(MlpArgs a) {
     if (warp == 0) umma::tmem_dealloc(tmem, 128);
 }
 
+// ---------------------------------------------------------------------------
+// Tile images ("mlp_image" layout).  The operand stage of one (unit, 128-row batch tile) in shared memory is
+//   [piece 3][chunk chunksQ][row 128] x 16 bytes    (8 bf16 of K = pool columns 8c .. 8c+7 per 16 bytes)
+// = 3 * chunksQ * 2048 bytes, contiguous.  The statistics pass F1 -- the first pass over `pool` in a training step --
+// builds exactly these bytes for its own MMAs and writes them out with ONE bulk store per tile:
+//   image[(u * T + t)]  ,  T = ceil(B / 128)
+// Every later pass of the step (F2 apply, B1 backward reductions, B2 dW1 / dy) then fetches a stage with ONE bulk
+// load (cp.async.bulk, the TMA engine) that lands on an mbarrier: no global loads, no split arithmetic and no
+// shared-memory stores on the LSU path, which the round-1 ablations identified as the bound of these kernels
+// (HBM at 16-21 %).  It costs bytes: 6 * Nq / (4 * n) = 1.73x the fp32 tile at n = 83.
+// W1 gets the same treatment once per step: [U][3][chunksQ][112 rows] x 16 bytes (w1_image_kernel).
+// ---------------------------------------------------------------------------
+#define IMG_WROWS 112
+#define IMG_E_WARPS 16
+#define IMG_THREADS (32 * (IMG_E_WARPS + 2))
+
+__global__ void __launch_bounds__(256)
+w1_image_kernel(const float* __restrict__ w1, int U, int n, int chunksQ, uint4* __restrict__ out) {
+    const long long total = (long long)U * chunksQ * IMG_WROWS;
+    const long long piece = (long long)chunksQ * IMG_WROWS;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(i % IMG_WROWS);
+        const int c = (int)((i / IMG_WROWS) % chunksQ);
+        const int u = (int)(i / piece);
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int q = 8 * c + e;
+            v[e] = (r < MT_H && q < n) ? __ldg(w1 + ((long long)u * MT_H + r) * n + q) : 0.0f;
+        }
+        uint32_t a[4], b[4], d[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) split2_bf16x3_rn(v[2 * e], v[2 * e + 1], a[e], b[e], d[e]);
+        uint4* o = out + (long long)u * 3 * piece + (long long)c * IMG_WROWS + r;
+        o[0] = make_uint4(a[0], a[1], a[2], a[3]);
+        o[piece] = make_uint4(b[0], b[1], b[2], b[3]);
+        o[2 * piece] = make_uint4(d[0], d[1], d[2], d[3]);
+    }
+}
+
+struct ImgShared {
+    uint64_t full[2];        // loader -> issuer / epilogue: the tile's stage (and W1 at a unit boundary) has landed
+    uint64_t mma_done[2];    // tcgen05.commit -> epilogue + loader (stage free)
+    uint64_t acc_free[2];    // 16 epilogue warps -> issuer
+    uint64_t aux_full[4];    // loader -> epilogue (B1): dopre / active bits of the tile are in their ring slot
+    uint32_t tmem_slot;
+    uint32_t pad;
+};
+
+__device__ __forceinline__ void img_epi_barrier() {
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * IMG_E_WARPS) : "memory");
+}
+
+// F2 (MODE = MLP_APPLY) and B1 (MODE = MLP_BWD_STATS) on tile images:
+//   warps 0-15  epilogue (warp e: TMEM lanes 32 (e % 4) .., column group e / 4)
+//   warp  16    loader: one elected lane issues the bulk loads two tiles ahead; in B1 the warp also brings the tile's
+//               dopre / active bits into a four-deep ring
+//   warp  17    issuer
+template <int MODE>
+__global__ void __launch_bounds__(IMG_THREADS, 1)
+mlp_img_kernel(MlpArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
+    const uint32_t wlbo = IMG_WROWS * 16u;
+    const uint32_t wpiece = (uint32_t)chunksQ * wlbo, wbytes = 3u * wpiece;
+    const uint32_t ppiece = (uint32_t)chunksQ * 2048u, pstage = 3u * ppiece;
+    unsigned char* w1s = smem_raw;
+    unsigned char* ps = smem_raw + wbytes;
+    unsigned char* tail = smem_raw + wbytes + 2 * pstage;
+    float4* s_c4 = reinterpret_cast<float4*>(tail);                              // [128] (b1, scale2, shift2, w2)
+    float* s_dopre_all = reinterpret_cast<float*>(tail + 2048);                  // [4][128]
+    uint32_t* s_mask_all = reinterpret_cast<uint32_t*>(tail + 2048 + 2048);      // [4][128][4]
+    float* s_acc = reinterpret_cast<float*>(tail + 2048 + 2048 + 8192);          // [2][4][128]
+    ImgShared* sh = reinterpret_cast<ImgShared*>(tail + 2048 + 2048 + 8192 + 4096);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 2048 + 2048 + 8192 + 4096 + 128);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 256);
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            umma::mbar_init(&sh->full[s], 1);
+            umma::mbar_init(&sh->mma_done[s], 1);
+            umma::mbar_init(&sh->acc_free[s], IMG_E_WARPS);
+        }
+        for (int s = 0; s < 4; ++s) umma::mbar_init(&sh->aux_full[s], 1);
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t w_addr = umma::smem_u32(w1s), p_addr = umma::smem_u32(ps);
+    constexpr int NDIM = (MODE == MLP_APPLY) ? 112 : 128;
+    const uint32_t idesc = umma::idesc_bf16_f32(128, NDIM);
+    if (tid < 6 * kstepsQ) {
+        const int pass = tid / kstepsQ, ks = tid - pass * kstepsQ;
+        const uint32_t pw = pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u;
+        const uint32_t pp = pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u;
+        const uint32_t wd = umma::desc_lo(w_addr + pw * wpiece + (uint32_t)(2 * ks) * wlbo, wlbo);
+        const uint32_t pd2 = umma::desc_lo(p_addr + pp * ppiece + (uint32_t)(2 * ks) * 2048u, 2048u);
+        s_tab[tid] = (MODE == MLP_APPLY) ? make_uint2(pd2, wd) : make_uint2(wd, pd2);   // (A, B)
+    }
+    __syncthreads();
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const int ntl = (int)(hi - lo);
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+    const unsigned long long seed = a.seed + (a.seed_dev ? *a.seed_dev * 0x9E3779B97F4A7C15ull : 0ull);
+
+    if (warp == IMG_E_WARPS) {
+        // ================= loader =================
+        int cur_u = -1;
+        for (int i = 0; i < ntl; ++i) {
+            const long long tile = lo + i;
+            const int u = (int)(tile / T), t = (int)(tile % T);
+            const uint32_t st = (uint32_t)i & 1u;
+            if (i >= 2) umma::mbar_wait(&sh->mma_done[st], (uint32_t)((i >> 1) - 1) & 1u);   // pool stage free
+            const bool new_u = (u != cur_u);
+            if (new_u && i >= 1) umma::mbar_wait(&sh->mma_done[st ^ 1u], (uint32_t)((i - 1) >> 1) & 1u);   // W1 free
+            cur_u = u;
+            if (MODE == MLP_BWD_STATS) {
+                // dopre / active bits of the tile's 128 batch rows: 4 rows per lane
+                const int b0 = t * MT_ROWS;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = lane + 32 * j;
+                    const bool ok = b0 + r < B;
+                    const long long bu = (long long)(b0 + r) * U + u;
+                    s_dopre_all[(i & 3) * 128 + r] = ok ? __ldg(a.dopre + bu) : 0.0f;
+                    *reinterpret_cast<uint4*>(s_mask_all + (i & 3) * 512 + 4 * r) =
+                        ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
+                }
+                __syncwarp();
+                // ring slot i & 3 is rewritten for tile i + 4, whose load waits for the MMAs of tile i + 2, which
+                // wait for the epilogue of tile i to hand its accumulator stage back: never more than one phase ahead
+                if (lane == 0) umma::mbar_arrive(&sh->aux_full[i & 3]);
+            }
+            if (lane == 0) {
+                umma::mbar_arrive_expect_tx(&sh->full[st], pstage + (new_u ? wbytes : 0u));
+                if (new_u) umma::bulk_load(w1s, a.w1_image + (size_t)u * wbytes, wbytes, &sh->full[st]);
+                umma::bulk_load(ps + (size_t)st * pstage, a.image + (size_t)tile * pstage, pstage, &sh->full[st]);
+            }
+            __syncwarp();
+        }
+    } else if (warp == IMG_E_WARPS + 1) {
+        // ================= issuer =================
+        for (int i = 0; i < ntl; ++i) {
+            const uint32_t st = (uint32_t)i & 1u;
+            umma::mbar_wait(&sh->full[st], ((uint32_t)i >> 1) & 1u);
+            umma::mbar_wait(&sh->acc_free[st], (((uint32_t)i >> 1) & 1u) ^ 1u);
+            umma::fence_after_sync();
+            if (lane == 0) {
+                const uint32_t poff = st * (pstage >> 4);
+                umma::issue_table2(s_tab, 6 * kstepsQ, umma::desc_hi(128u), umma::desc_hi(128u),
+                                   MODE == MLP_APPLY ? poff : 0u, MODE == MLP_APPLY ? 0u : poff, tmem + st * 128u, idesc);
+                umma::commit(&sh->mma_done[st]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ================= epilogue (16 warps) =================
+        const int quarter = warp & 3, cg = warp >> 2;
+        const int row = quarter * 32 + lane;
+        int cur_u = -1;
+        float b1m = 0.f, scm = 0.f, shm = 0.f, w2m = 0.f;
+        double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+        auto flush = [&](int u) {
+            if (MODE == MLP_APPLY) return;
+            int j = blockIdx.x;
+            const long long start = (long long)u * T;
+            while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+            const int slot = (blockIdx.x - j) * 4 + cg;
+            if (row < MT_H && slot < a.slots) {
+                const int c = u * MT_H + row;
+                double* o = a.part + (long long)slot * 4 * C + c;
+                o[0] = s1; o[(long long)C] = s2; o[2LL * C] = s3; o[3LL * C] = s4;
+            }
+            s1 = s2 = s3 = s4 = 0.0;
+        };
+        for (int i = 0; i < ntl; ++i) {
+            const long long tile = lo + i;
+            const int u = (int)(tile / T), t = (int)(tile % T);
+            const int b0 = t * MT_ROWS, rows = min(MT_ROWS, B - b0);
+            const uint32_t st = (uint32_t)i & 1u;
+            if (u != cur_u) {
+                if (cur_u >= 0) flush(cur_u);
+                cur_u = u;
+                const int ch = u * MT_H + row;
+                const bool ok = row < MT_H;
+                b1m = ok ? a.b1[ch] : 0.f;
+                scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f; w2m = ok ? a.w2[ch] : 0.f;
+                if (MODE == MLP_APPLY) {
+                    img_epi_barrier();          // every epilogue warp is done with the previous unit's constants
+                    if (cg == 0) s_c4[row] = make_float4(b1m, scm, shm, w2m);
+                    img_epi_barrier();
+                }
+            }
+            if (MODE == MLP_BWD_STATS) umma::mbar_wait(&sh->aux_full[i & 3], ((uint32_t)i >> 2) & 1u);   // the loader's ring writes
+            umma::mbar_wait(&sh->mma_done[st], ((uint32_t)i >> 1) & 1u);
+            umma::fence_after_sync();
+            const uint32_t trow = tmem + st * 128u + ((uint32_t)(quarter * 32) << 16);
+            if (MODE == MLP_BWD_STATS) {
+                // thread = (hidden channel, quarter of the tile's batch rows)
+                const float* s_dopre = s_dopre_all + (i & 3) * 128;
+                const uint32_t* s_mask = s_mask_all + (i & 3) * 512;
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int c0 = 32 * cg + 16 * hh;
+                    if (c0 < rows) {
+                        uint32_t v[16];
+                        umma::tmem_ld16(trow + c0, v);
+                        umma::tmem_ld_wait();
+                        float f1 = 0.0f, f2 = 0.0f, f3 = 0.0f, f4 = 0.0f;
+#pragma unroll
+                        for (int k2 = 0; k2 < 16; ++k2) {
+                            if (c0 + k2 < rows) {
+                                const float x = __uint_as_float(v[k2]) + b1m;
+                                const float pre = fmaf(x, scm, shm);
+                                const uint32_t act = (s_mask[4 * (c0 + k2) + (row >> 5)] >> (row & 31)) & 1u;
+                                const float d = s_dopre[c0 + k2];
+                                const float hact = act ? pre * inv_keep : 0.0f;
+                                const float g2 = act ? d * w2m * inv_keep : 0.0f;
+                                f1 += g2;
+                                f2 = fmaf(g2, x, f2);
+                                f3 = fmaf(d, hact, f3);
+                                f4 += d;
+                            }
+                        }
+                        s1 += (double)f1; s2 += (double)f2; s3 += (double)f3; s4 += (double)f4;
+                    }
+                }
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_free[st]);
+            } else {
+                // thread = (batch row, 32 hidden channels = keep-bit word cg)
+                const long long bu = (long long)(b0 + row) * U + u;
+                const uint32_t kbw = (row < rows) ? dropout_keep_word(a.drop_p, seed, bu, a.mask_u8, cg) : 0u;
+                uint32_t actw = 0u;   // keep AND (BN2 output > 0): the backward passes reuse THIS decision
+                float accv = 0.0f;
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int c0 = 32 * cg + 16 * hh;
+                    if (c0 < 112) {
+                        uint32_t v[16];
+                        umma::tmem_ld16(trow + c0, v);
+                        umma::tmem_ld_wait();
+#pragma unroll
+                        for (int k2 = 0; k2 < 16; ++k2) {
+                            const int m = c0 + k2;
+                            if (m < MT_H) {
+                                const float4 c4 = s_c4[m];
+                                const float pre = fmaf(__uint_as_float(v[k2]) + c4.x, c4.y, c4.z);
+                                const uint32_t act = ((kbw >> (16 * hh + k2)) & 1u) & (pre > 0.0f ? 1u : 0u);
+                                actw |= act << (16 * hh + k2);
+                                const float h = act ? pre * inv_keep : 0.0f;
+                                accv = fmaf(h, c4.w, accv);
+                            }
+                        }
+                    }
+                }
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_free[st]);
+                float* acc4 = s_acc + st * 512;              // [tile parity][column group][row]
+                acc4[cg * 128 + row] = accv;
+                if (row < rows && a.maskbits) a.maskbits[bu * 4 + cg] = actw;
+                img_epi_barrier();
+                if (cg == 0 && row < rows)
+                    a.opre[bu] = ((acc4[row] + acc4[128 + row]) + (acc4[256 + row] + acc4[384 + row])) + a.b2[u];
+            }
+        }
+        if (cur_u >= 0) flush(cur_u);
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+}
+
+static size_t img_smem(int n) {
+    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
+    return 3 * chunksQ * IMG_WROWS * 16 + 2 * 3 * chunksQ * 2048 + 2048 + 2048 + 8192 + 4096 + 128 + 6 * 6 * 8 + 16;
+}
+
 namespace xnn {
 int launch_bn_train_finalize(const double* part, int tiles, int B, int C, const float* gamma, const float* beta,
                              float eps, float momentum, float* running_mean, float* running_var, float* scale,
@@ -772,6 +1092,15 @@ static size_t mt_smem_lockstep(int n) {
 
 template <int MODE>
 static int mt_launch(const MlpArgs& a, cudaStream_t st) {
+    if (MODE != MLP_STATS && a.image != nullptr) {
+        // tile images present (training step): operand stages by bulk load, 16 epilogue warps
+        constexpr int M2 = (MODE == MLP_STATS) ? MLP_APPLY : MODE;
+        const size_t smem = img_smem(a.n);
+        if (cudaFuncSetAttribute(mlp_img_kernel<M2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return 1;
+        mlp_img_kernel<M2><<<mt_grid(a.B, a.U), IMG_THREADS, smem, st>>>(a);
+        return cudaGetLastError() != cudaSuccess;
+    }
     if (MODE == MLP_BWD_STATS) {      // measured with the warp-specialised kernel instead: 1.46 vs 1.40 ms for xnn_mlp_bwd
         const size_t smem = mt_smem_lockstep(a.n);
         if (cudaFuncSetAttribute(mlp_fc1_lockstep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
@@ -789,6 +1118,17 @@ static int mt_launch(const MlpArgs& a, cudaStream_t st) {
 
 extern "C" int xnn_mlp_supported(int n) { return n >= 1 && n <= MT_NMAX; }
 
+// tile images of one training step: [U][T] pool stages, then [U] W1 images (mlp_image layout, see mlp_img_kernel)
+static size_t img_stage_bytes(int n) { return (size_t)3 * (((n + 15) & ~15) >> 3) * 2048; }
+static size_t img_w1_bytes(int n) { return (size_t)3 * (((n + 15) & ~15) >> 3) * IMG_WROWS * 16; }
+extern "C" size_t xnn_mlp_image_bytes(int B, int U, int n) {
+    if (B < 1 || U < 1 || !xnn_mlp_supported(n)) return 0;
+    return (size_t)U * mt_tiles(B) * img_stage_bytes(n) + (size_t)U * img_w1_bytes(n);
+}
+static const unsigned char* img_w1_ptr(const void* image, int B, int U, int n) {
+    return (const unsigned char*)image + (size_t)U * mt_tiles(B) * img_stage_bytes(n);
+}
+
 extern "C" size_t xnn_mlp_bn2_work_bytes(int B, int U) {
     if (B < 1 || U < 1) return 0;
     return (size_t)mt_slots(B, U) * 2 * U * MT_H * sizeof(double);
@@ -797,8 +1137,10 @@ extern "C" size_t xnn_mlp_bn2_work_bytes(int B, int U) {
 extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
                                          const float* gamma, const float* beta, float eps, float momentum,
                                          float* running_mean, float* running_var, float* scale, float* shift,
-                                         double* stats, void* work, int phase, long long count, xnn_stream_t s) {
+                                         double* stats, void* work, void* image, int phase, long long count,
+                                         xnn_stream_t s) {
     XNN_CHECK_ARG(pool && w1 && b1 && gamma && beta && scale && shift && stats && work, "NULL pointer");
+    XNN_CHECK_ARG(((uintptr_t)image & 127) == 0, "image must be 128-byte aligned");
     XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = partial sums, 2 = finalize");
     if (phase == 0) count = B;
     XNN_CHECK_ARG(B >= 1 && U >= 1 && count >= 2 && count < (1LL << 31),
@@ -808,8 +1150,16 @@ extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, con
     MlpArgs a{};
     a.pool = pool; a.w1 = w1; a.b1 = b1; a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U);
     a.part = (double*)work;
+    a.image_out = (unsigned char*)image;
     if (phase != 2) {
         XNN_CUDA(cudaMemsetAsync(work, 0, xnn_mlp_bn2_work_bytes(B, U), st));
+        if (image != nullptr) {
+            const int chunksQ = ((n + 15) & ~15) >> 3;
+            const long long items = (long long)U * chunksQ * IMG_WROWS;
+            w1_image_kernel<<<ceil_div(items, 256), 256, 0, st>>>(w1, U, n, chunksQ,
+                                                                  (uint4*)const_cast<unsigned char*>(img_w1_ptr(image, B, U, n)));
+            XNN_CHECK_LAUNCH();
+        }
         if (mt_launch<MLP_STATS>(a, st)) { set_error("xnn_mlp_bn2_train_prepare: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
     }
     if (phase != 1 && launch_bn_train_finalize(a.part, a.slots, (int)count, U * MT_H, gamma, beta, eps, momentum,
@@ -823,7 +1173,7 @@ extern "C" int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, con
 extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
                            const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
                            unsigned long long seed, const unsigned long long* seed_dev, const uint8_t* mask,
-                           uint32_t* maskbits, float* opre, xnn_stream_t s) {
+                           uint32_t* maskbits, float* opre, const void* image, xnn_stream_t s) {
     XNN_CHECK_ARG(pool && w1 && b1 && scale2 && shift2 && w2 && b2 && opre, "NULL pointer");
     XNN_CHECK_ARG(B >= 0 && U >= 1 && drop_p >= 0.0f && drop_p < 1.0f, "bad sizes");
     XNN_CHECK_ARG(xnn_mlp_supported(n), "pool width outside the tensor-core path (n <= 96)");
@@ -833,6 +1183,8 @@ extern "C" int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, 
     a.pool = pool; a.w1 = w1; a.b1 = b1; a.scale2 = scale2; a.shift2 = shift2; a.w2 = w2; a.b2 = b2;
     a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = 0;
     a.drop_p = drop_p; a.seed = seed; a.seed_dev = seed_dev; a.mask_u8 = mask; a.maskbits = maskbits; a.opre = opre;
+    XNN_CHECK_ARG(((uintptr_t)image & 127) == 0, "image must be 128-byte aligned");
+    if (image != nullptr) { a.image = (const unsigned char*)image; a.w1_image = img_w1_ptr(image, B, U, n); }
     if (mt_launch<MLP_APPLY>(a, to_stream(s))) { set_error("xnn_mlp_fwd: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
     return XNN_OK;
 }
@@ -1221,6 +1573,321 @@ mlp_bwd_kernel(MlpBwdArgs a) {
     if (warp == 0) umma::tmem_dealloc(sh->tmem_slot, 512);
 }
 
+// ---------------------------------------------------------------------------
+// B2 on tile images.  The same three GEMMs as mlp_bwd_kernel (D1 = W1 . pool^T -> dh, D2 = W1^T . dh -> dy,
+// D3 += dh . pool -> dW1), with
+//   * the pool tile and W1 fetched by bulk load (TMA) from the images F1 wrote -- no global loads, no split, no
+//     staging stores for the two big operands; the pool stage is DOUBLE-buffered (the load of tile g+2 is issued as
+//     soon as the MMAs of tile g have finished with its stage);
+//   * TWO bf16 pieces per operand (hi, mid of the round-to-nearest split: x to 2^-18, unbiased) and the three
+//     products hi*hi, hi*mid, mid*hi: gradients are compared at 1e-4, not at the forward's 1e-5, and the ReLU /
+//     dropout decisions are the forward's stored bits, so nothing here can flip; half the MMAs (63 instead of 126
+//     per tile), half the shared-memory operand fetch, two thirds of the dh staging.
+// ---------------------------------------------------------------------------
+struct MbiShared {
+    uint64_t bar;          // MMA completion (lock-step)
+    uint64_t full[2];      // pool stage landed
+    uint64_t wfull;        // W1 of the current unit landed
+    uint32_t tmem_slot;
+    uint32_t pad[3];
+};
+
+__global__ void __launch_bounds__(MT_THREADS, 1)
+mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const unsigned char* __restrict__ w1_image) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
+    const uint32_t wcol = MB_WROWS * 16u;                  // 112 rows (= IMG_WROWS)
+    const uint32_t wpiece = (uint32_t)chunksQ * wcol;
+    const uint32_t pcol = MB_ROWS * 16u;
+    const uint32_t ppiece = (uint32_t)chunksQ * pcol;
+    const uint32_t tpiece = (MB_ROWS / 8) * wcol;
+    const uint32_t pstage2 = 2u * ppiece;                  // two pieces of a stage are loaded
+    const size_t img_stage = (size_t)3 * ppiece, img_w = (size_t)3 * wpiece;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned char* w1s = smem_raw;                                        // [2][chunksQ][112] uint4
+    unsigned char* ps = smem_raw + 2 * wpiece;                            // [2 stages][2][chunksQ][128] uint4
+    uint4* ts = reinterpret_cast<uint4*>(smem_raw + 2 * wpiece + 2 * pstage2);   // [2][16][112] uint4
+    unsigned char* tail = smem_raw + 2 * wpiece + 2 * pstage2 + 2 * tpiece;
+    float* s_dopre = reinterpret_cast<float*>(tail);                                     // [128]
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 512);                          // [4 words][128 batch rows]
+    MbiShared* sh = reinterpret_cast<MbiShared*>(tail + 512 + 2048);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 512 + 2048 + 64);                     // [3 (kstepsQ + 7 + 8)]
+
+    const int row = (warp & 3) * 32 + lane;   // TMEM lane: hidden channel m (D1, D3) / pool column q (D2)
+    const int cg = warp >> 2;                 // column group: 32 of the tile's 128 batch rows
+    {
+        // the dh staging rows 100..111 and everything the garbage lanes may read must be finite: clear once
+        uint4* z = reinterpret_cast<uint4*>(smem_raw);
+        const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
+        for (uint32_t i = tid; i < tot; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 512);
+    if (tid == 0) {
+        umma::mbar_init(&sh->bar, 1);
+        umma::mbar_init(&sh->full[0], 1);
+        umma::mbar_init(&sh->full[1], 1);
+        umma::mbar_init(&sh->wfull, 1);
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);
+    const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16);
+    const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);
+    const uint32_t D1 = tmem, D2 = tmem + MB_ROWS, D3 = tmem + 2 * MB_ROWS;
+    // the three significant products of the 2-way split, smallest first: (piece of A, piece of B)
+    //   T1 [3*kstepsQ]  D1 = W1 (K-major) x pool (K-major)            (B low word gets the stage offset added)
+    //   T3 [21]         D2 = W1^T (MN view) x dh^T (MN view)
+    //   T4 [24]         D3 += dh (K-major, K = batch rows) x pool^T (MN view)
+    const int n1 = 3 * kstepsQ, n3 = 21, n4 = 3 * (MB_ROWS / 16), ntab = n1 + n3 + n4;
+    if (tid < ntab) {
+        const int ti = tid;
+        const uint32_t w_addr = umma::smem_u32(w1s);
+        const uint32_t p_addr = umma::smem_u32(ps), t_addr = umma::smem_u32(ts);
+        const int seq = ti < n1 ? 0 : (ti < n1 + n3 ? 1 : 2);
+        const int i = ti - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + n3));
+        const int per = seq == 0 ? kstepsQ : (seq == 1 ? 7 : MB_ROWS / 16);
+        const int pass = i / per, ks = i - pass * per;
+        const uint32_t pa = pass == 0 ? 1u : 0u;
+        const uint32_t pb = pass == 1 ? 1u : 0u;
+        uint2 e;
+        if (seq == 0)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * wcol, wcol),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * pcol, pcol));
+        else if (seq == 1)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)ks * 256u, 128u),
+                           umma::desc_lo(t_addr + pb * tpiece + (uint32_t)ks * 256u, 128u));
+        else
+            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * wcol, wcol),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)ks * 256u, 128u));
+        s_tab[ti] = e;
+    }
+    const uint2* tab = s_tab;
+    uint64_t* bar = &sh->bar;
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+    const uint32_t trow = (uint32_t)((warp & 3) * 32) << 16;
+
+    // CTA order position v -> unit (unit interleave, see mlp_bwd_kernel)
+    auto unit_of = [&](int v) {
+        int u = v / a.P;
+        for (int c = 0; c < v % a.P; ++c) u += (U - c + a.P - 1) / a.P;
+        return u;
+    };
+    auto image_tile = [&](long long tile) {            // tile in CTA order -> image index u * T + t
+        return (long long)unit_of((int)(tile / T)) * T + (tile % T);
+    };
+
+    uint32_t phase = 0, wphase = 0, d3_started = 0;
+    float b1m = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
+    double sdb1 = 0.0;
+    float pd = 0.0f;
+    uint4 pm = make_uint4(0u, 0u, 0u, 0u);
+
+    auto prefetch_aux = [&](long long tile, int u, bool live) {
+        if (tid < MB_ROWS) {
+            const int b0 = (int)(tile % T) * MB_ROWS;
+            const bool ok = live && b0 + tid < B;
+            const long long bu = (long long)(b0 + tid) * U + u;
+            pd = ok ? __ldg(a.dopre + bu) : 0.0f;
+            pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+    auto flush = [&](int v, int u) {
+        int j = blockIdx.x;
+        const long long start = (long long)v * T;
+        while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+        const int slot = blockIdx.x - j;
+        const bool ok = row < MT_H && slot < a.slots;
+        float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + row) * n;
+        for (int c0 = 16 * cg; c0 < Nq; c0 += 64) {
+            uint32_t vv[16];
+            umma::tmem_ld16(D3 + trow + c0, vv);
+            umma::tmem_ld_wait();
+            if (ok) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (c0 + i < n) o[c0 + i] = d3_started ? __uint_as_float(vv[i]) : 0.0f;
+            }
+        }
+        if (ok) a.part_db1[((long long)slot * 4 + cg) * C + (long long)u * MT_H + row] = sdb1;
+        sdb1 = 0.0;
+        d3_started = 0;
+        umma::fence_before_sync();
+    };
+
+    __syncthreads();                                   // descriptor table written
+    // pool stages of the first two tiles
+    if (tid == 0) {
+        for (int g = 0; g < 2 && lo + g < hi; ++g) {
+            umma::mbar_arrive_expect_tx(&sh->full[g], pstage2);
+            umma::bulk_load(ps + (size_t)g * pstage2, image + (size_t)image_tile(lo + g) * img_stage, pstage2, &sh->full[g]);
+        }
+    }
+    long long g = 0;                                   // tile counter in CTA order
+    for (long long seg = lo; seg < hi;) {
+        const int v = (int)(seg / T);
+        const int u = unit_of(v);
+        const long long seg_end = min(hi, (long long)(v + 1) * T);
+        __syncthreads();            // the previous unit's flush is done, every MMA that read W1 has completed
+        if (tid == 0) {
+            umma::mbar_arrive_expect_tx(&sh->wfull, 2u * wpiece);
+            umma::bulk_load(w1s, w1_image + (size_t)u * img_w, 2u * wpiece, &sh->wfull);
+        }
+        {
+            const int ch = u * MT_H + row;
+            const bool ok = row < MT_H;
+            b1m = ok ? a.b1[ch] : 0.f;
+            w2m = ok ? a.w2[ch] : 0.f;
+            meanm = ok ? (float)a.stats2[4LL * ch] : 0.f; invstdm = ok ? (float)a.stats2[4LL * ch + 2] : 0.f;
+            gism = ok ? (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]) : 0.f;
+            const float2 cf = ok ? a.coef[ch] : make_float2(0.f, 0.f);
+            c1m = cf.x; c2m = cf.y;
+        }
+        prefetch_aux(seg, u, true);
+
+        for (long long tile = seg; tile < seg_end; ++tile, ++g) {
+            const int t = (int)(tile % T);
+            const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
+            const uint32_t st = (uint32_t)g & 1u;
+            if (tid < MB_ROWS) {
+                s_dopre[tid] = pd;
+                s_mask[tid] = pm.x; s_mask[MB_ROWS + tid] = pm.y; s_mask[2 * MB_ROWS + tid] = pm.z; s_mask[3 * MB_ROWS + tid] = pm.w;
+            }
+            prefetch_aux(tile + 1, u, tile + 1 < seg_end);
+            __syncthreads();
+            if (tid == 0) {
+                if (tile == seg) { umma::mbar_wait(&sh->wfull, wphase); }
+                umma::mbar_wait(&sh->full[st], (uint32_t)(g >> 1) & 1u);
+                umma::fence_after_sync();
+                umma::issue_table<false>(tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), st * (pstage2 >> 4), D1,
+                                         idesc1, 0u);
+                umma::commit(bar);
+            }
+            umma::mbar_wait(bar, phase);
+            phase ^= 1u;
+            umma::fence_after_sync();
+
+            // ---- epilogue 1: dh for (channel row, batch rows 32cg..32cg+31) -> two pieces, four 16-byte chunks each
+            {
+                uint32_t vv[2][16];
+                umma::tmem_ld16(D1 + trow + 32 * cg, vv[0]);
+                umma::tmem_ld16(D1 + trow + 32 * cg + 16, vv[1]);
+                umma::tmem_ld_wait();
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c0 = 32 * cg + 16 * h;
+                    float dh[16];
+                    float part = 0.0f;
+                    uint32_t mk[16];
+                    float dp[16];
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        const uint4 mq = *reinterpret_cast<const uint4*>(s_mask + (row >> 5) * MB_ROWS + c0 + 4 * q4);
+                        const float4 dq = *reinterpret_cast<const float4*>(s_dopre + c0 + 4 * q4);
+                        mk[4 * q4] = mq.x; mk[4 * q4 + 1] = mq.y; mk[4 * q4 + 2] = mq.z; mk[4 * q4 + 3] = mq.w;
+                        dp[4 * q4] = dq.x; dp[4 * q4 + 1] = dq.y; dp[4 * q4 + 2] = dq.z; dp[4 * q4 + 3] = dq.w;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int c = c0 + i;
+                        const float x = __uint_as_float(vv[h][i]) + b1m;
+                        const uint32_t act = (mk[i] >> (row & 31)) & 1u;
+                        const float g2 = act ? dp[i] * w2m * inv_keep : 0.0f;
+                        const float xhat = (x - meanm) * invstdm;
+                        float d = gism * (g2 - c1m - xhat * c2m);
+                        if (c >= rows || row >= MT_H) d = 0.0f;
+                        dh[i] = d;
+                        part += d;
+                    }
+                    sdb1 += (double)part;
+                    if (row < MB_WROWS) {
+#pragma unroll
+                        for (int gg = 0; gg < 2; ++gg) {
+                            uint32_t p0[4], p1[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float x0 = dh[8 * gg + 2 * e], x1 = dh[8 * gg + 2 * e + 1];
+                                p0[e] = cvt_bf16x2_rn(x0, x1);
+                                p1[e] = cvt_bf16x2_rn(x0 - __uint_as_float(p0[e] << 16),
+                                                      x1 - __uint_as_float(p0[e] & 0xFFFF0000u));
+                            }
+                            const int chunk = (c0 >> 3) + gg;
+                            ts[chunk * MB_WROWS + row] = make_uint4(p0[0], p0[1], p0[2], p0[3]);
+                            ts[tpiece / 16 + chunk * MB_WROWS + row] = make_uint4(p1[0], p1[1], p1[2], p1[3]);
+                        }
+                    }
+                }
+            }
+            umma::fence_proxy_async();
+            umma::fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                umma::fence_after_sync();
+                umma::issue_table<false>(tab + n1, n3, umma::desc_hi(wcol), umma::desc_hi(wcol), 0u, D2, idesc2, 0u);
+                // T4's B operand is the pool stage (MN view): the per-stage offset goes to the B low word
+                umma::issue_table<false>(tab + n1 + n3, n4, umma::desc_hi(128u), umma::desc_hi(pcol), st * (pstage2 >> 4),
+                                         D3, idesc3, d3_started);
+                umma::commit(bar);
+            }
+            d3_started = 1;
+            // ---- epilogue 2: thread = (pool column q, 32 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b]
+            const long long e2 = ((long long)(b0 + 32 * cg) * U + u) * n + row;
+            const long long bstride = (long long)U * n;
+            float x[2][16];
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int c = 32 * cg + 16 * h + i;
+                    x[h][i] = (row < n && c < rows) ? __ldg(a.pool + e2 + (long long)(16 * h + i) * bstride) : 0.0f;
+                }
+            umma::mbar_wait(bar, phase);
+            phase ^= 1u;
+            umma::fence_after_sync();
+            // every MMA that read pool stage st has completed: fetch the tile after the next into it
+            if (tid == 0 && lo + g + 2 < hi) {
+                umma::mbar_arrive_expect_tx(&sh->full[st], pstage2);
+                umma::bulk_load(ps + (size_t)st * pstage2, image + (size_t)image_tile(lo + g + 2) * img_stage, pstage2,
+                                &sh->full[st]);
+            }
+            if (32 * cg < rows) {
+                uint32_t vv[2][16];
+                umma::tmem_ld16(D2 + trow + 32 * cg, vv[0]);
+                umma::tmem_ld16(D2 + trow + 32 * cg + 16, vv[1]);
+                umma::tmem_ld_wait();
+                if (row < n) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (32 * cg + 16 * h + i < rows)
+                                a.dy[e2 + (long long)(16 * h + i) * bstride] = x[h][i] * __uint_as_float(vv[h][i]);
+                }
+            }
+        }
+        if (tid == 0) wphase ^= 1u;
+        flush(v, u);
+        seg = seg_end;
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(sh->tmem_slot, 512);
+}
+
+static size_t mbi_smem(int n) {
+    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
+    const size_t wcol = MB_WROWS * 16;
+    return 2 * chunksQ * wcol + 2 * 2 * chunksQ * MB_ROWS * 16 + 2 * (MB_ROWS / 8) * wcol + 512 + 2048 + 64 + 64 * 8 + 16;
+}
+
 __global__ void __launch_bounds__(256)
 mlp_bwd_reduce_kernel(const float* __restrict__ part_w1, const double* __restrict__ part_db1, int slots,
                       long long nw, int C, float* __restrict__ dw1, float* __restrict__ db1) {
@@ -1288,7 +1955,8 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
                            const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
                            const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
                            float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
-                           float* dy, void* work, int phase, long long count, float out_scale, xnn_stream_t s) {
+                           float* dy, void* work, const void* image, int phase, long long count, float out_scale,
+                           xnn_stream_t s) {
     XNN_CHECK_ARG(dopre && pool && w1 && b1 && scale2 && shift2 && stats2 && gamma2 && w2 && dw1 && db1 && dgamma2 &&
                   dbeta2 && dw2 && db2 && dy && work, "NULL pointer");
     XNN_CHECK_ARG(phase >= 0 && phase <= 2, "phase: 0 = whole call, 1 = reductions, 2 = the rest");
@@ -1308,6 +1976,8 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     a.maskbits = const_cast<uint32_t*>(maskbits);
     a.B = B; a.U = U; a.n = n; a.T = mt_tiles(B); a.slots = mt_slots(B, U); a.drop_p = drop_p;
     a.part = (double*)(base + w.part1);
+    XNN_CHECK_ARG(((uintptr_t)image & 127) == 0, "image must be 128-byte aligned");
+    if (image != nullptr) { a.image = (const unsigned char*)image; a.w1_image = img_w1_ptr(image, B, U, n); }
     if (phase != 2 && mt_launch<MLP_BWD_STATS>(a, st)) { set_error("xnn_mlp_bwd: B1 launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
     if (phase == 1) return XNN_OK;
     float2* coef = (float2*)(base + w.coef);
@@ -1321,9 +1991,15 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     g.part_w1 = (float*)(base + w.part_w1); g.part_db1 = (double*)(base + w.part_db1);
     g.B = B; g.U = U; g.n = n; g.T = mb_tiles(B); g.slots = mb_slots(B, U); g.drop_p = drop_p;
     g.P = mb_interleave(B, U);
-    const size_t smem = mb_smem(n);
-    XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    mlp_bwd_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g);
+    if (image != nullptr) {
+        const size_t smem = mbi_smem(n);
+        XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        mlp_bwd_img_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g, a.image, a.w1_image);
+    } else {
+        const size_t smem = mb_smem(n);
+        XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        mlp_bwd_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g);
+    }
     XNN_CHECK_LAUNCH();
     const long long nw = (long long)C * n;
     long long blocks = (nw + 255) / 256;

@@ -283,8 +283,18 @@ def mlp_supported(n):
     return bool(_lib.load().xnn_mlp_supported(int(n)))
 
 
-def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1):
-    """BatchNorm (linears.7) batch statistics of hpre = FC1(pool) without materialising hpre (tcgen05)."""
+def mlp_image_buffer(B, U, n, dev):
+    """buffer for the tile images of one training step (xnn_mlp_image_bytes), 256-byte aligned"""
+    nbytes = int(_lib.load().xnn_mlp_image_bytes(int(B), int(U), int(n)))
+    buf = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+    off = (-buf.data_ptr()) % 256
+    return buf[off:off + nbytes]
+
+
+def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean, running_var, sync=None, world=1,
+                          image=None):
+    """BatchNorm (linears.7) batch statistics of hpre = FC1(pool) without materialising hpre (tcgen05).
+    image: optional mlp_image_buffer: the pass also writes its operand tiles for mlp_fwd / mlp_bwd of this step."""
     B, U, n = pool.shape
     if B * world < 2:
         raise ValueError("Expected more than 1 value per channel when training")
@@ -299,7 +309,7 @@ def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean
     def call(phase):
         _call("xnn_mlp_bn2_train_prepare", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")),
               _p(b1), B, U, n, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var),
-              _p(scale), _p(shift), _p(stats), _p(work), phase, B * world, _stream())
+              _p(scale), _p(shift), _p(stats), _p(work), _p(image), phase, B * world, _stream())
     if sync is None:
         call(0)
     else:
@@ -309,7 +319,8 @@ def mlp_bn2_train_prepare(pool, w1, b1, gamma, beta, eps, momentum, running_mean
     return scale, shift, stats
 
 
-def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None, want_bits=False, seed_dev=None):
+def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None, want_bits=False, seed_dev=None,
+            image=None):
     """opre (B,U) = FC2(drop(relu(BN2(FC1(pool))))) in one tcgen05 pass; optional keep-bits (B,U,4) int32.
     seed_dev: int64 (1,) device draw counter mixed into the seed (CUDA-graph replays)."""
     B, U, n = pool.shape
@@ -320,7 +331,7 @@ def mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p=0.0, seed=0, mask=None,
         _req(mask, torch.uint8, "mask")
     _call("xnn_mlp_fwd", _p(_req(pool, torch.float32, "pool")), _p(_req(w1, torch.float32, "w1")), _p(b1),
           _p(scale2), _p(shift2), _p(_req(w2, torch.float32, "w2")), _p(b2), B, U, n, float(drop_p), int(seed),
-          _p(seed_dev), _p(mask), _p(bits), _p(opre), _stream())
+          _p(seed_dev), _p(mask), _p(bits), _p(opre), _p(image), _stream())
     return opre, bits
 
 
@@ -341,7 +352,8 @@ def _outs(out, shapes, dev):
     return list(out)
 
 
-def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p, out=None, sync=None, world=1):
+def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p, out=None, sync=None, world=1,
+            image=None):
     """Backward of FC1 -> BN2 -> ReLU -> dropout -> FC2 from dopre (B,U); see xnn_mlp_bwd.
     out: optional [dw1, db1, dg2, dbe2, dw2, db2] destinations."""
     B, U, n = pool.shape
@@ -359,8 +371,8 @@ def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_
         _call("xnn_mlp_bwd", _p(_req(dopre, torch.float32, "dopre")), _p(_req(pool, torch.float32, "pool")),
               _p(_req(w1, torch.float32, "w1")), _p(b1), _p(scale2), _p(shift2),
               _p(_req(stats2, torch.float64, "stats2")), _p(gamma2), _p(_req(w2, torch.float32, "w2")), _p(bits),
-              float(drop_p), B, U, n, _p(dw1), _p(db1), _p(dg2), _p(dbe2), _p(dw2), _p(db2), _p(dy), _p(wk), phase,
-              B * world, 1.0 / world, _stream())
+              float(drop_p), B, U, n, _p(dw1), _p(db1), _p(dg2), _p(dbe2), _p(dw2), _p(db2), _p(dy), _p(wk), _p(image),
+              phase, B * world, 1.0 / world, _stream())
     if sync is None:
         call(0)
     else:

@@ -41,6 +41,12 @@ def _n_pool(L, k):
     return (L - k + 1) // ops.POOL
 
 
+def _image_bytes(B, U, n):
+    """xnn_mlp_image_bytes restated for the fake implementations: [U][ceil(B/128)] pool stages + [U] W1 images"""
+    chunks = ((n + 15) // 16) * 2
+    return U * ((B + 127) // 128) * 3 * chunks * 2048 + U * 3 * chunks * 112 * 16
+
+
 # ------------------------------------------------------------------------------------------------------------
 # a16 / a3
 # ------------------------------------------------------------------------------------------------------------
@@ -105,9 +111,9 @@ def _(planes, L, params, running, eps, drop_p, seed, drop_mask):
 
 # ------------------------------------------------------------------------------------------------------------
 # unit bank, train mode
-# outputs: o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre
+# outputs: o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image
 # ------------------------------------------------------------------------------------------------------------
-N_TRAIN_OUT = 14
+N_TRAIN_OUT = 15
 
 
 @custom_op("explainn_b200::unit_bank_train", mutates_args=(), device_types="cuda")
@@ -133,10 +139,12 @@ def unit_bank_train(planes: torch.Tensor, L: int, params: Sequence[torch.Tensor]
     empty = cw.new_empty(0)
     if ops.mlp_supported(pool.shape[2]):
         # tensor-core path: the (B,100U) hidden activations are never materialised
+        # the statistics pass also writes the tile images the later passes of this step load their operands from
+        image = ops.mlp_image_buffer(B, U, pool.shape[2], cw.device)
         scale2, shift2, stats2 = ops.mlp_bn2_train_prepare(pool, w1, b1, g2, be2, eps[1], 0.0, None, None,
-                                                           sync=sync, world=world)
+                                                           sync=sync, world=world, image=image)
         opre, bits = ops.mlp_fwd(pool, w1, b1, scale2, shift2, w2, b2, drop_p, seed, drop_mask, want_bits=True,
-                                 seed_dev=seed_dev)
+                                 seed_dev=seed_dev, image=image)
         hpre = empty
     else:
         if seed_dev is not None:
@@ -146,9 +154,10 @@ def unit_bank_train(planes: torch.Tensor, L: int, params: Sequence[torch.Tensor]
                                                       sync=sync, world=world)
         opre = ops.fc2_fwd(hpre, scale2, shift2, w2, b2, drop_p, seed, drop_mask)
         bits = torch.empty(0, dtype=torch.int32, device=cw.device)
+        image = torch.empty(0, dtype=torch.uint8, device=cw.device)
     scale3, shift3, stats3 = ops.bn_train_prepare(opre, g3, be3, eps[2], 0.0, None, None, sync=sync, world=world)
     o, _ = ops.head_fwd(opre, scale3, shift3)
-    return [o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre]
+    return [o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image]
 
 
 @custom_op("explainn_b200::bn_running_update", mutates_args=("running_means", "running_vars", "nbt"),
@@ -178,7 +187,8 @@ def _(planes, L, params, eps, drop_p, seed, seed_dev, drop_mask, arena, offs):
     return [f32(B, U), f32(B, U, n), f32(B, U, n), cw.new_empty((B, U, n), dtype=torch.uint8), f32(B, U),
             cw.new_empty((B, U, 4) if tc else (0,), dtype=torch.int32), f32(C), f32(C), f64(U, 4), f64(C, 4),
             f64(U, 4), f64(U, 4 * k), cw.new_empty((4 * k,), dtype=torch.int64),
-            f32(0) if tc else f32(B, U, HIDDEN)]
+            f32(0) if tc else f32(B, U, HIDDEN),
+            cw.new_empty((_image_bytes(B, U, n) if tc else 0,), dtype=torch.uint8)]
 
 
 def _grad_views(arena, offs, shapes):
@@ -201,7 +211,7 @@ def _bank_grad_shapes(cw, n):
 def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, arena):
     """the backward of the unit bank, every parameter gradient written into `flat` (BANK_PARAMS order)"""
     cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = params
-    o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre = saved
+    o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image = saved
     B, U = o.shape
     k = cw.shape[2]
     C = U * HIDDEN
@@ -212,7 +222,8 @@ def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, 
                              world=world)
     if bits.numel():
         dy = ops.mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, g2, w2, bits, drop_p,
-                         out=[d_w1, d_b1, d_g2, d_be2, d_w2, d_b2], sync=sync, world=world)[6]
+                         out=[d_w1, d_b1, d_g2, d_be2, d_w2, d_b2], sync=sync, world=world,
+                         image=image if image.numel() else None)[6]
     else:
         dw2_, db2_, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, drop_p, seed, drop_mask)
         d_w2.view(-1).copy_(dw2_.view(-1)); d_b2.copy_(db2_)

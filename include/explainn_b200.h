@@ -166,10 +166,15 @@ int xnn_mlp_supported(int n);
 /* train-mode BatchNorm (linears.7) statistics of hpre = FC1(pool): scale2/shift2, stats2[100U][4],
  * running-stat update -- xnn_fc1_fwd + xnn_bn_train_prepare in one pass over pool. */
 size_t xnn_mlp_bn2_work_bytes(int B, int U);
+/* Tile images of a training step (optional, xnn_mlp_image_bytes, 128-byte aligned): this first pass over `pool`
+ * writes every (unit, 128-row batch tile) operand stage it builds -- three bf16 pieces in the tensor-core operand
+ * layout -- and the same for W1; xnn_mlp_fwd and xnn_mlp_bwd of the SAME step, given the same buffer, then fetch
+ * their operand stages with one bulk copy (TMA) each instead of re-loading and re-splitting `pool`. */
+size_t xnn_mlp_image_bytes(int B, int U, int n);
 int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b1, int B, int U, int n,
                               const float* gamma, const float* beta, float eps, float momentum,
                               float* running_mean, float* running_var, float* scale, float* shift,
-                              double* stats, void* work, int phase, long long count, xnn_stream_t s);
+                              double* stats, void* work, void* image, int phase, long long count, xnn_stream_t s);
 /* opre[b,u] = b2[u] + sum_m W2[u,m]*drop(relu(scale2*hpre+shift2)) -- xnn_fc1_fwd + xnn_fc2_fwd fused.
  * Dropout: injected byte mask (B,U,100), else Philox keep-bits from (seed,b,u) when drop_p > 0.
  * maskbits uint32 [B][U][4] (NULL in inference): bit m of a (b,u) row = hidden channel m is ACTIVE (kept by
@@ -180,7 +185,7 @@ int xnn_mlp_bn2_train_prepare(const float* pool, const float* w1, const float* b
 int xnn_mlp_fwd(const float* pool, const float* w1, const float* b1, const float* scale2,
                 const float* shift2, const float* w2, const float* b2, int B, int U, int n, float drop_p,
                 unsigned long long seed, const unsigned long long* seed_dev, const uint8_t* mask,
-                uint32_t* maskbits, float* opre, xnn_stream_t s);
+                uint32_t* maskbits, float* opre, const void* image, xnn_stream_t s);
 
 /* ---- a6: backward ---------------------------------------------------------
  * autograd of the above (selene/__init__.py:289-292). Gradients are shaped
@@ -205,7 +210,8 @@ int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w1, const fl
                 const float* scale2, const float* shift2, const double* stats2, const float* gamma2,
                 const float* w2, const uint32_t* maskbits, float drop_p, int B, int U, int n,
                 float* dw1, float* db1, float* dgamma2, float* dbeta2, float* dw2, float* db2,
-                float* dy, void* work, int phase, long long count, float out_scale, xnn_stream_t s);
+                float* dy, void* work, const void* image, int phase, long long count, float out_scale,
+                xnn_stream_t s);
 /* Train-mode BatchNorm backward over the batch dimension, C channels:
  *   given g = dL/d(out) (B,C), xpre (B,C), stats (mean,var,invstd), gamma; when
  *   relu_out != NULL the BatchNorm is followed by a ReLU whose output it is and

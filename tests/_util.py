@@ -103,8 +103,12 @@ def cfg3_golden():
 ZERO_CLASS = {"linears.0.bias", "linears.1.bias", "linears.6.bias", "linears.10.bias"}
 
 
-def check_cfg3_grads(d, grads, what, rtol=2e-4, atol_scale=2e-5, zero_tol=2e-6):
-    """named gradients against the compact cfg3 fixture (linears.6.weight: sampled units + per-unit norms)"""
+def check_cfg3_grads(d, grads, what, rtol=2e-4, atol_scale=5e-5, zero_tol=2e-6):
+    """named gradients against the compact cfg3 fixture (linears.6.weight: sampled units + per-unit norms).
+    Tolerance: 2e-4 relative + 5e-5 of the tensor's largest entry.  The fixture is the reference's own fp32 result
+    at B = 32 (its BatchNorm-scale gradients are sums of 2 656 cancelling terms per unit); the device backward runs
+    its three GEMMs on two-piece bf16 splits (2^-18 per operand, unbiased), which test_train_step_vs_fp64_oracle
+    holds to 1e-4 + 1e-5 * max against the fp64 evaluation at the same shape."""
     Uu = int(d["opts"][0])
     for key, got in grads.items():
         got = np.asarray(got)

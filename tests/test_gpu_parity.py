@@ -149,12 +149,22 @@ def _check_grads(named_grads, ref_grads, rtol, atol_scale):
             U.assert_close(got, ref, rtol=rtol, atol_scale=atol_scale, what="grad " + k)
 
 
+@pytest.mark.parametrize("use_image", [False, True])
 @pytest.mark.parametrize("cfg", [(300, 83, 300), (100, 26, 257), (7, 6, 130), (3, 96, 5), (33, 9, 1000)])
-def test_mlp_forward_tensor_core_vs_fp64(cfg):
-    """FC1 -> BN2 statistics -> ReLU -> dropout -> FC2 on tcgen05 (3xTF32) against an fp64 evaluation and
-    against the FP32 FMA kernels"""
-    from explainn_b200 import ops
+def test_mlp_forward_tensor_core_vs_fp64(cfg, use_image):
+    """FC1 -> BN2 statistics -> ReLU -> dropout -> FC2 on tcgen05 (bf16x3) against an fp64 evaluation and
+    against the FP32 FMA kernels; use_image: the training-step path, where the statistics pass writes the tile
+    images and the apply pass fetches its operand stages from them by bulk load"""
+    import functools
+    from explainn_b200 import ops as ops_mod
     Uu, n, B = cfg
+    image = ops_mod.mlp_image_buffer(B, Uu, n, DEV) if use_image else None
+
+    class ops:      # the module's functions with the image argument bound
+        mlp_bn2_train_prepare = staticmethod(functools.partial(ops_mod.mlp_bn2_train_prepare, image=image))
+        mlp_fwd = staticmethod(functools.partial(ops_mod.mlp_fwd, image=image))
+        fc1_fwd, fc2_fwd = staticmethod(ops_mod.fc1_fwd), staticmethod(ops_mod.fc2_fwd)
+
     g = torch.Generator().manual_seed(n * 1000 + Uu)
     pool = torch.exp(torch.randn(B, Uu, n, generator=g) * 0.7)
     w1 = torch.randn(Uu * 100, n, generator=g) / np.sqrt(n)
@@ -205,11 +215,21 @@ def test_mlp_forward_tensor_core_vs_fp64(cfg):
     assert torch.equal(o1, o4)
 
 
+@pytest.mark.parametrize("use_image", [False, True])
 @pytest.mark.parametrize("cfg", [(40, 83, 300), (100, 26, 257), (7, 6, 130), (3, 96, 70), (33, 9, 1000), (300, 83, 512)])
-def test_mlp_backward_tensor_core_vs_fp64_autograd(cfg):
-    """gradients of the per-unit MLP on tcgen05 against torch fp64 autograd of the same function"""
-    from explainn_b200 import ops
+def test_mlp_backward_tensor_core_vs_fp64_autograd(cfg, use_image):
+    """gradients of the per-unit MLP on tcgen05 against torch fp64 autograd of the same function; use_image: the
+    training-step path on tile images (bulk-loaded operand stages, two-piece products in the dW1 / dy pass)"""
+    import functools
+    from explainn_b200 import ops as ops_mod
     Uu, n, B = cfg
+    image = ops_mod.mlp_image_buffer(B, Uu, n, DEV) if use_image else None
+
+    class ops:
+        mlp_bn2_train_prepare = staticmethod(functools.partial(ops_mod.mlp_bn2_train_prepare, image=image))
+        mlp_fwd = staticmethod(functools.partial(ops_mod.mlp_fwd, image=image))
+        mlp_bwd = staticmethod(functools.partial(ops_mod.mlp_bwd, image=image))
+
     g = torch.Generator().manual_seed(n * 77 + Uu)
     pool = torch.exp(torch.randn(B, Uu, n, generator=g) * 0.7)
     w1 = torch.randn(Uu * 100, n, generator=g) / np.sqrt(n)
