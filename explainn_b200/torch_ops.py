@@ -272,6 +272,10 @@ def _bank_setup(ctx, inputs, output):
     ctx.L, ctx.drop_p, ctx.seed, ctx.drop_mask, ctx.arena, ctx.offs = L, drop_p, seed, drop_mask, arena, list(offs)
     ctx.planes = planes
     ctx.n_params = len(params)
+    # only `o` carries a gradient: without this autograd would ZERO-FILL a gradient for every other output of the
+    # list (pool, zmax, the tile images ...: 1.5 GB of library fill kernels per step)
+    ctx.set_materialize_grads(False)
+    ctx.mark_non_differentiable(*output[1:])
     ctx.save_for_backward(*params, *output)
 
 

@@ -296,8 +296,11 @@ def test_frontend_bwd_tensor_core_vs_brute_force(cfg):
     args = (planes, L, k, dy.to(DEV), zmax.to(DEV), arg.to(DEV), gamma.to(DEV), stats, cov_w, cnt1, n_pos)
     tc = [t.cpu().numpy() for t in ops.frontend_bwd(*args)]
     simt = [t.cpu().numpy() for t in ops.frontend_bwd(*args, simt=True)]
+    # the tensor-core kernel splits dy into TWO bf16 pieces (2^-18 per term, unbiased): the weight gradient is held
+    # to 5e-5 + 1e-5 * max against the FP64 paths; the BatchNorm sums are fp32/fp64 sums in both kernels
     for a, b_, nme in zip(tc, simt, ("dconv_w", "dconv_b", "dgamma", "dbeta")):
-        U.assert_close(a, b_, rtol=1e-5, atol_scale=2e-6, what=nme + " tc vs simt")
+        tol = dict(rtol=5e-5, atol_scale=1e-5) if nme == "dconv_w" else dict(rtol=1e-5, atol_scale=2e-6)
+        U.assert_close(a, b_, what=nme + " tc vs simt", **tol)
     # brute force of the sparse scatter term G_u[c,j] = sum dy * x[b,c,7q+arg+j] (fp64)
     xs = x.numpy().astype(np.float64)
     G = np.zeros((Uu, 4, k))
@@ -315,7 +318,7 @@ def test_frontend_bwd_tensor_core_vs_brute_force(cfg):
     cw = cov_w.cpu().numpy().reshape(Uu, 4, k)
     ref = (gamma.numpy().astype(np.float64) * invstd)[:, None, None] * (
         G - (db / N)[:, None, None] * c1[None] - (dg * invstd)[:, None, None] * cw)
-    U.assert_close(tc[0], ref, rtol=1e-5, atol_scale=2e-6, what="dconv_w vs brute force")
+    U.assert_close(tc[0], ref, rtol=5e-5, atol_scale=1e-5, what="dconv_w vs brute force")
     U.assert_close(tc[2], dg, rtol=1e-5, atol_scale=2e-6, what="dgamma")
     U.assert_close(tc[3], db, rtol=1e-5, atol_scale=2e-6, what="dbeta")
 
