@@ -247,7 +247,7 @@ def main():
                                                       "placed under oracle/_ref/ by build())" if rkind == "reference"
                                                       else "oracle port (oracle/_ref/reference_architectures.py absent)")},
             "e2e": {"value": rate, "unit": "sequences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        }))
+        }), flush=True)
         return
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
@@ -347,6 +347,7 @@ def main():
     ms_dev = timed(lambda i: pipe_dev.step_device(xs_d[i % NB], ys_d[i % NB]), args.steps)
     pipe_dev.flush()
     graph_kernels = pipe_dev.graph_kernels if use_graph else 0
+    pipe_dev.close()
 
     # ---- 3. e2e: host batches through StepPipeline.step ---------------------------------------------------------
     def host_inputs(mode):
@@ -370,6 +371,7 @@ def main():
             pipe.flush()
 
         ms = timed(all_steps, 1)
+        pipe.close()
         return ms / steps, (pipe.h2d_bytes - h0) // steps, (pipe.d2h_bytes - d0) // steps
 
     ms_e2e, h2d_step, d2h_step = run_e2e(args.e2e_input, args.steps)
@@ -461,11 +463,23 @@ def main():
     line.update(fwd)
     if cpu is not None:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
+    if os.environ.get("XNN_BENCH_WATCHDOG"):        # debugging aid: dump every thread's stack and exit after N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["XNN_BENCH_WATCHDOG"]), exit=True)
     main()
+    sys.stdout.flush()
     import torch.distributed as _dist
     if _dist.is_available() and _dist.is_initialized():
-        _dist.destroy_process_group()
+        # the line is out; tearing NCCL down must never hold the run: give it 20 s, then leave
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        _t = threading.Thread(target=_dist.destroy_process_group, daemon=True)
+        _t.start()
+        _t.join(20.0)
+        if _t.is_alive():
+            os._exit(0)

@@ -43,8 +43,8 @@ class GradBucket:
     overlap: the arena keeps the conv / BN1 gradients (the LAST ones the backward produces, 23 K values at cfg3)
     behind `model.arena_split`; everything before it (W1 = 9.96 of the 10.6 MB) is complete when xnn_mlp_bwd
     finishes.  That segment's all-reduce is issued from inside the backward (torch_ops._after_mlp_grads) on NCCL's
-    stream, under xnn_frontend_bwd; `sm_reserve` SMs are left out of the persistent grids so that the NCCL kernel has
-    somewhere to run.  Gradients that an autograd hook replaced (selene/__init__.py:254-257 freezes filters that way)
+    stream, under xnn_frontend_bwd; `sm_reserve` SMs are left out of THAT kernel's persistent grid (and of no other
+    kernel's) so that the NCCL kernel has somewhere to run.  Gradients that an autograd hook replaced (selene/__init__.py:254-257 freezes filters that way)
     do not live in the arena: they are copied in before their segment is reduced, and a hook on an MLP-segment
     parameter switches the early all-reduce off.
 
@@ -69,25 +69,27 @@ class GradBucket:
         self.params = [p for p, _ in self.slots]
         self.split, self.numel = split, total
         self.overlap = bool(overlap) and self.world > 1 and split > 0
+        self.sm_reserve = int(sm_reserve)
         if self.overlap:
-            from . import ops, torch_ops
+            from . import torch_ops
             torch_ops._after_mlp_grads.append(self._after_mlp_grads)
-            ops.set_sm_reserve(sm_reserve)
 
     def close(self):
         if self.model is not None and self.overlap:
-            from . import ops, torch_ops
+            from . import torch_ops
             if self._after_mlp_grads in torch_ops._after_mlp_grads:
                 torch_ops._after_mlp_grads.remove(self._after_mlp_grads)
-            ops.set_sm_reserve(0)
 
     # -- arena path ----------------------------------------------------------------------------------------
     def _after_mlp_grads(self, arena):
+        """returns the number of SMs the conv weight gradient (the kernel this all-reduce runs under) should leave
+        to the NCCL kernel"""
         if arena is not self.arena:
-            return
+            return 0
         if any(p._backward_hooks for p, off in self.slots if off < self.split):
-            return                                  # a hook may still replace one of these gradients
+            return 0                                # a hook may still replace one of these gradients
         self._early = dist.all_reduce(self.arena[:self.split], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        return self.sm_reserve
 
     def _adopt(self, lo, hi):
         """gradients of [lo, hi) that do not live in the arena (hooks, accumulation) are copied into it"""

@@ -231,10 +231,19 @@ def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, 
                                  world=world)
         dw1_, db1_, dy = ops.fc1_bwd(dhpre.view(B, U, HIDDEN), pool, w1)
         d_w1.view(-1).copy_(dw1_.view(-1)); d_b1.copy_(db1_)
+    reserve = 0
     if arena is not None:
         for hook in _after_mlp_grads:
-            hook(arena)
-    ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos, out=[d_cw, d_cb, d_g1, d_be1])
+            reserve = max(reserve, int(hook(arena) or 0))
+    # a hook that started a collective asks for a few SMs to be left out of the NEXT kernel's persistent grid (only
+    # that one: every other kernel of the step keeps the whole chip)
+    if reserve:
+        ops.set_sm_reserve(reserve)
+    try:
+        ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos, out=[d_cw, d_cb, d_g1, d_be1])
+    finally:
+        if reserve:
+            ops.set_sm_reserve(0)
 
 
 @custom_op("explainn_b200::unit_bank_train_bwd", mutates_args=(), device_types="cuda")

@@ -202,3 +202,11 @@ class StepPipeline:
     def flush(self):
         """Loss of the most recent step (waits for it)."""
         return self._previous((self.i - 1) & 1) if self.i else None
+
+    def close(self):
+        """Release the captured graph and its static buffers.  A CUDA graph that holds captured NCCL kernels must be
+        destroyed BEFORE its process group is: `destroy_process_group()` waits for it otherwise."""
+        if self.i:
+            torch.cuda.current_stream(self.device).synchronize()
+        self.graph, self.static = None, None
+        self.slots = [None, None]

@@ -31,6 +31,8 @@ def _worker(rank, world, port, out):
     from explainn_b200.architectures import get_loss, get_optimizer
     from explainn_b200.trainer import StepPipeline
     from oracle import explainn_oracle as O
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get("XNN_TEST_WATCHDOG", "240")), exit=True)      # a lost collective must fail with a stack, not hang the box
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
                       LOCAL_RANK=str(rank))
     torch.cuda.set_device(rank)
@@ -114,9 +116,16 @@ def _worker(rank, world, port, out):
                 U.assert_close(pg.detach().cpu().numpy(), pe.detach().cpu().numpy(), rtol=1e-4, atol_scale=1e-4,
                                what="graphed DP " + n_)
         bg.close()
+        pipe.close()                       # the graph holds captured NCCL kernels: it goes before the process group
         res["ok"] = True
+    except Exception as e:                 # report through the manager dict: the parent prints it
+        import traceback
+        res["error"] = f"{type(e).__name__}: {e}\n{traceback.format_exc()[-1500:]}"
     finally:
         out[rank] = res
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 
