@@ -466,6 +466,25 @@ class FusedBCEWithLogitsLoss(_FusedLossMixin, nn.BCEWithLogitsLoss):
     _kind = "bce_logits"
 
 
+def pwm_best_sites(pwm_module, x):
+    """Best site per (sequence, PWM) with the strand rule of the reference's cudamo.py: both strands are scored by the
+    same forward correlation (`Conv1d` + `MaxPool1d(return_indices=True)`, cudamo.py:217-228 -- the FIRST maximum of a
+    strand wins), and the forward strand is chosen only if its score is STRICTLY greater (`fwd[0] > rev[0]`,
+    cudamo.py:254-265); on a tie the reverse strand wins.  Returns (score (B,G) float32, strand (B,G) int32 with
+    0 = forward / 1 = reverse complement, start (B,G) int32 = position on the chosen strand's own string).
+
+    One scan of the REVERSE-COMPLEMENTED batch gives exactly this: its concatenated axis is [rc strand | forward
+    strand], the scan keeps the first maximum of that axis, so an index below L-w+1 means "rc strand >= forward
+    strand, first rc maximum" and anything else "forward strictly greater, first forward maximum"."""
+    if pwm_module._options["scoring"] != "max":
+        raise ValueError("best sites need a PWM module with scoring='max'")
+    packed = x if isinstance(x, PackedDNA) else PackedDNA.from_onehot(x)
+    score, arg = pwm_module(packed.revcomp(), return_argmax=True)
+    Lc = packed.length - pwm_module._options["kernel_size"] + 1
+    strand = (arg < Lc).to(torch.int32)
+    return score, strand, torch.where(arg < Lc, arg, arg - Lc)
+
+
 def get_loss(input_data="binary"):
     """architectures/__init__.py:446-456: nn.BCEWithLogitsLoss() for "binary", nn.MSELoss() otherwise (subclasses
     of those, so isinstance checks and attributes hold)"""

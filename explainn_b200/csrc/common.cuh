@@ -44,6 +44,57 @@ static inline cudaStream_t to_stream(xnn_stream_t s) { return reinterpret_cast<c
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline int planes_words(int L) { return (L + 31) / 32; }
 
+// ---- unequal batch slices per M tile ---------------------------------------
+// The front-end kernels tile the units in blocks of 128 (UMMA M) and split the batch into slices, one CTA per
+// (tile, slice).  With U = 300 the third tile holds 44 units: its CTAs have a third of the epilogue / producer work
+// of a full tile, and with equal slice counts they idle while the full tiles finish.  A TileMap gives every tile a
+// slice count proportional to its cost; CTA c of a 1-D grid finds (tile, slice, slices of that tile) from it.
+#define XNN_TILEMAP_MAX 16
+struct TileMap {
+    int first[XNN_TILEMAP_MAX + 1];   // first CTA of tile t; first[n] = grid size
+    int n;                            // 0: plain 2-D grid (tile = blockIdx.x, slice = blockIdx.y)
+};
+// weight of a tile with `live` of `rows` unit rows in use: a floor for the work that does not shrink with the
+// rows (MMAs, TMEM read-out), whole warps of 32 rows otherwise
+static inline TileMap make_tile_map(int U, int rows, int ctas, long long B, float floor_w) {
+    TileMap m{};
+    const int mt = (U + rows - 1) / rows;
+    if (mt < 2 || mt > XNN_TILEMAP_MAX || ctas < 2 * mt || (U % rows) == 0) return m;   // n = 0
+    float w[XNN_TILEMAP_MAX], tot = 0.0f;
+    for (int t = 0; t < mt; ++t) {
+        const int live = (t == mt - 1) ? U - t * rows : rows;
+        const float f = (float)(((live + 31) / 32) * 32) / (float)rows;
+        w[t] = f > floor_w ? f : floor_w;
+        tot += w[t];
+    }
+    int ns[XNN_TILEMAP_MAX], used = 0;
+    for (int t = 0; t < mt; ++t) {
+        ns[t] = (int)((float)ctas * w[t] / tot);
+        if (ns[t] < 1) ns[t] = 1;
+        if ((long long)ns[t] > B) ns[t] = (int)B;
+        used += ns[t];
+    }
+    // leftovers go round-robin to the full tiles
+    for (int rem = ctas - used, t = 0, guard = 0; rem > 0 && guard < 4 * ctas; ++guard, t = (t + 1) % (mt - 1))
+        if ((long long)ns[t] < B) { ++ns[t]; --rem; }
+    m.n = mt;
+    m.first[0] = 0;
+    for (int t = 0; t < mt; ++t) m.first[t + 1] = m.first[t] + ns[t];
+    return m;
+}
+static inline int tile_map_max_slices(const TileMap& m) {
+    int mx = 0;
+    for (int t = 0; t < m.n; ++t) mx = (m.first[t + 1] - m.first[t] > mx) ? m.first[t + 1] - m.first[t] : mx;
+    return mx;
+}
+__device__ __forceinline__ void tile_of_cta(const TileMap& m, int& tile, int& slice, int& ns) {
+    if (m.n == 0) { tile = blockIdx.x; slice = blockIdx.y; ns = gridDim.y; return; }
+    const int c = blockIdx.x;
+    int t = 0;
+    while (t + 1 < m.n && c >= m.first[t + 1]) ++t;
+    tile = t; slice = c - m.first[t]; ns = m.first[t + 1] - m.first[t];
+}
+
 // ---- device helpers -------------------------------------------------------
 // base code at position i of one sequence's planes (lo,hi,nmask each Wp words):
 // 0..3 = A,C,G,T, 4 = N (all-zero one-hot column)

@@ -397,6 +397,10 @@ extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int
     const size_t smem = bt_smem_bytes(n, &Lbuf, &nstages);
     XNN_CHECK_ARG(smem <= 227 * 1024, "sequence too long for the front-end backward staging buffers");
     cudaStream_t st = to_stream(s);
+    // equal batch slices per M tile.  Measured alternatives (cfg3, B = 4096): half the slices for the partly filled
+    // last tile (44 of 128 units) 0.65 -> 1.07 ms -- a tile costs the same whatever its fill, the issue / MMA chain
+    // bounds it, not the producers' rows; skipping the dead row groups in the producers 0.65 -> 0.74 ms (the
+    // extra predicates cost the instruction-bound loop more than the skipped stores save)
     const int slices = bt_slices(U, B);
     // MN-major Toeplitz view of the one-hot pair buffer: K-group (pool window) stride 112 B, N-chunk
     // stride 32 B (pinned by test_frontend_bwd_tensor_core_vs_brute_force).

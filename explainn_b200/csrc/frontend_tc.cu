@@ -151,7 +151,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, int U, int n, int kpad, int Lbuf,
                    int noh, int linear, const __nv_bfloat16* __restrict__ wsplit, const float* __restrict__ scale,
                    const float* __restrict__ shift, float* __restrict__ pool, float* __restrict__ zmax,
-                   uint8_t* __restrict__ argmax) {
+                   uint8_t* __restrict__ argmax, const __grid_constant__ TileMap tmap) {
+    int bx, by, ns;
+    tile_of_cta(tmap, bx, by, ns);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int chunks = kpad >> 3, ksteps = kpad >> 4;
     const uint32_t a_bytes = 3u * chunks * 2048u;
@@ -169,14 +171,13 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
     TcShared* sh = reinterpret_cast<TcShared*>(reinterpret_cast<unsigned char*>(s_pl) + ((3 * Wp * 4 + 15) & ~15));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int u0 = blockIdx.x * TC_ROWS;
+    const int u0 = bx * TC_ROWS;
     const int nu = min(TC_ROWS, U - u0);
-    const int ns = gridDim.y;
 
     // ---- one-time setup: weights -> smem, TMEM, barriers
     {
         const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(wsplit) +
-                                                          (size_t)blockIdx.x * a_bytes);
+                                                          (size_t)bx * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
         for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
     }
@@ -195,7 +196,7 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
     umma::fence_after_sync();
     const uint32_t tmem = sh->tmem_slot;
     const int ntiles = (n + TC_WIN - 1) / TC_WIN;
-    const int nseq = (B - 1 - (int)blockIdx.y) / ns + 1;
+    const int nseq = (B - 1 - by) / ns + 1;
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps =================
@@ -247,7 +248,7 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
         // latency never sits between two sequences (up to 128 words; longer sequences load the rest directly)
         uint32_t nx[4];
         auto load_planes = [&](int sq) {
-            const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)sq * ns) * 3 * Wp;
+            const uint32_t* sp = planes + (long long)(by + (long long)sq * ns) * 3 * Wp;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int i = lane + 32 * j;
@@ -257,7 +258,7 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
         load_planes(0);
         for (int sq = 0; sq < nseq; ++sq) {
             const int so = sq % noh;
-            const uint32_t* sp = planes + (long long)(blockIdx.y + (long long)sq * ns) * 3 * Wp;
+            const uint32_t* sp = planes + (long long)(by + (long long)sq * ns) * 3 * Wp;
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -292,7 +293,7 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
         const uint32_t tlane = tmem + ((uint32_t)(quarter * 32) << 16);
         int g = 0;
         for (int sq = 0; sq < nseq; ++sq) {
-            const long long b = blockIdx.y + (long long)sq * ns;
+            const long long b = by + (long long)sq * ns;
             const long long gbase = (b * U + u0) * n;              // first element of this CTA's block
             const int ph4 = linear ? (int)(gbase & 3) : 0, ph16 = linear ? (int)(gbase & 15) : 0;
             for (int t = 0; t < ntiles; ++t, ++g) {
@@ -424,16 +425,21 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
     if (slices < 1) slices = 1;
     if (slices > B) slices = B;
     dim3 grid(mt, slices);
+    // slices per M tile from a TileMap.  Weight floor 1.0 = equal weights (the 148th SM gets a CTA too): giving the
+    // partly filled last tile (44 of 128 units at U = 300) HALF the slices was measured SLOWER -- 0.55 -> 0.66 ms --
+    // i.e. a tile costs the same whatever its fill: the MMAs and the TMEM read-out bound it, not the live rows
+    const TileMap tmap = make_tile_map(U, TC_ROWS, num_sms(), B, 1.0f);
+    if (tmap.n) grid = dim3(tmap.first[tmap.n], 1);
     if (train) {
         XNN_CUDA(cudaFuncSetAttribute(frontend_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         frontend_tc_kernel<true><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh, (int)linear,
                                                                  reinterpret_cast<const __nv_bfloat16*>(work), scale,
-                                                                 shift, pool, zmax, argmax);
+                                                                 shift, pool, zmax, argmax, tmap);
     } else {
         XNN_CUDA(cudaFuncSetAttribute(frontend_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         frontend_tc_kernel<false><<<grid, TC_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, n, kpad, Lbuf, noh, (int)linear,
                                                                   reinterpret_cast<const __nv_bfloat16*>(work), scale,
-                                                                  shift, pool, zmax, argmax);
+                                                                  shift, pool, zmax, argmax, tmap);
     }
     XNN_CHECK_LAUNCH();
     return XNN_OK;

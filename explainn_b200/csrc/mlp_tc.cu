@@ -967,10 +967,13 @@ mlp_img_kernel(MlpArgs a) {
                 const int ch = u * MT_H + row;
                 const bool ok = row < MT_H;
                 b1m = ok ? a.b1[ch] : 0.f;
-                scm = ok ? a.scale2[ch] : 0.f; shm = ok ? a.shift2[ch] : 0.f; w2m = ok ? a.w2[ch] : 0.f;
+                const float sc = ok ? a.scale2[ch] : 0.f, shf = ok ? a.shift2[ch] : 0.f;
+                // folded per-channel constants: BN2(acc + b1) / keep = acc * scm + shm;  w2m = w2 / keep
+                scm = sc * inv_keep; shm = fmaf(b1m, sc, shf) * inv_keep; w2m = ok ? a.w2[ch] * inv_keep : 0.f;
                 if (MODE == MLP_APPLY) {
                     img_epi_barrier();          // every epilogue warp is done with the previous unit's constants
-                    if (cg == 0) s_c4[row] = make_float4(b1m, scm, shm, w2m);
+                    // (scale, shift') of the UNSCALED pre-activation (its sign is the ReLU decision), w2 / keep
+                    if (cg == 0) s_c4[row] = make_float4(sc, fmaf(b1m, sc, shf), w2m, 0.f);
                     img_epi_barrier();
                 }
             }
@@ -989,23 +992,24 @@ mlp_img_kernel(MlpArgs a) {
                         uint32_t v[16];
                         umma::tmem_ld16(trow + c0, v);
                         umma::tmem_ld_wait();
+                        // t = dopre where the channel was active: sum g2 = w2m * sum t, sum g2 * x = w2m * (sum t * acc +
+                        // b1 * sum t), sum dopre * h = sum t * (acc * scm + shm)
                         float f1 = 0.0f, f2 = 0.0f, f3 = 0.0f, f4 = 0.0f;
+                        const uint32_t bit = 1u << (row & 31);
+                        const int wsel = row >> 5;
 #pragma unroll
                         for (int k2 = 0; k2 < 16; ++k2) {
-                            if (c0 + k2 < rows) {
-                                const float x = __uint_as_float(v[k2]) + b1m;
-                                const float pre = fmaf(x, scm, shm);
-                                const uint32_t act = (s_mask[4 * (c0 + k2) + (row >> 5)] >> (row & 31)) & 1u;
+                            if (rows == MT_ROWS || c0 + k2 < rows) {
+                                const float acc = __uint_as_float(v[k2]);
                                 const float d = s_dopre[c0 + k2];
-                                const float hact = act ? pre * inv_keep : 0.0f;
-                                const float g2 = act ? d * w2m * inv_keep : 0.0f;
-                                f1 += g2;
-                                f2 = fmaf(g2, x, f2);
-                                f3 = fmaf(d, hact, f3);
+                                const float t = (s_mask[4 * (c0 + k2) + wsel] & bit) ? d : 0.0f;
+                                f1 += t;
+                                f2 = fmaf(t, acc, f2);
+                                f3 = fmaf(t, fmaf(acc, scm, shm), f3);
                                 f4 += d;
                             }
                         }
-                        s1 += (double)f1; s2 += (double)f2; s3 += (double)f3; s4 += (double)f4;
+                        s1 += (double)(w2m * f1); s2 += (double)(w2m * fmaf(b1m, f1, f2)); s3 += (double)f3; s4 += (double)f4;
                     }
                 }
                 umma::fence_before_sync();
@@ -1029,11 +1033,10 @@ mlp_img_kernel(MlpArgs a) {
                             const int m = c0 + k2;
                             if (m < MT_H) {
                                 const float4 c4 = s_c4[m];
-                                const float pre = fmaf(__uint_as_float(v[k2]) + c4.x, c4.y, c4.z);
+                                const float pre = fmaf(__uint_as_float(v[k2]), c4.x, c4.y);
                                 const uint32_t act = ((kbw >> (16 * hh + k2)) & 1u) & (pre > 0.0f ? 1u : 0u);
                                 actw |= act << (16 * hh + k2);
-                                const float h = act ? pre * inv_keep : 0.0f;
-                                accv = fmaf(h, c4.w, accv);
+                                accv = fmaf(act ? pre : 0.0f, c4.z, accv);
                             }
                         }
                     }
@@ -1686,7 +1689,7 @@ mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const 
     };
 
     uint32_t phase = 0, wphase = 0, d3_started = 0;
-    float b1m = 0.f, w2m = 0.f, meanm = 0.f, invstdm = 0.f, gism = 0.f, c1m = 0.f, c2m = 0.f;
+    float k0m = 0.f, k1m = 0.f, k2m = 0.f;
     double sdb1 = 0.0;
     float pd = 0.0f;
     uint4 pm = make_uint4(0u, 0u, 0u, 0u);
@@ -1742,14 +1745,21 @@ mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const 
             umma::bulk_load(w1s, w1_image + (size_t)u * img_w, 2u * wpiece, &sh->wfull);
         }
         {
+            // dh = gamma*invstd * (g2 - c1 - xhat*c2), xhat = (acc + b1 - mean)*invstd, g2 = act ? dopre*w2/keep : 0
+            //    = (act ? k1 * dopre : 0) + k0 + k2 * acc          (three per-channel constants, one FFMA chain)
             const int ch = u * MT_H + row;
             const bool ok = row < MT_H;
-            b1m = ok ? a.b1[ch] : 0.f;
-            w2m = ok ? a.w2[ch] : 0.f;
-            meanm = ok ? (float)a.stats2[4LL * ch] : 0.f; invstdm = ok ? (float)a.stats2[4LL * ch + 2] : 0.f;
-            gism = ok ? (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]) : 0.f;
-            const float2 cf = ok ? a.coef[ch] : make_float2(0.f, 0.f);
-            c1m = cf.x; c2m = cf.y;
+            if (ok) {
+                const float b1v = a.b1[ch], w2v = a.w2[ch];
+                const float mean = (float)a.stats2[4LL * ch], invstd = (float)a.stats2[4LL * ch + 2];
+                const float gis = (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]);
+                const float2 cf = a.coef[ch];
+                k1m = gis * w2v * inv_keep;
+                k2m = -gis * cf.y * invstd;
+                k0m = -gis * cf.x + k2m * (b1v - mean);
+            } else {
+                k0m = k1m = k2m = 0.f;
+            }
         }
         prefetch_aux(seg, u, true);
 
@@ -1795,17 +1805,24 @@ mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const 
                         mk[4 * q4] = mq.x; mk[4 * q4 + 1] = mq.y; mk[4 * q4 + 2] = mq.z; mk[4 * q4 + 3] = mq.w;
                         dp[4 * q4] = dq.x; dp[4 * q4 + 1] = dq.y; dp[4 * q4 + 2] = dq.z; dp[4 * q4 + 3] = dq.w;
                     }
+                    const uint32_t bit = 1u << (row & 31);
+                    if (rows == MB_ROWS) {                     // every batch row of the tile is real (all but the last tile)
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int c = c0 + i;
-                        const float x = __uint_as_float(vv[h][i]) + b1m;
-                        const uint32_t act = (mk[i] >> (row & 31)) & 1u;
-                        const float g2 = act ? dp[i] * w2m * inv_keep : 0.0f;
-                        const float xhat = (x - meanm) * invstdm;
-                        float d = gism * (g2 - c1m - xhat * c2m);
-                        if (c >= rows || row >= MT_H) d = 0.0f;
-                        dh[i] = d;
-                        part += d;
+                        for (int i = 0; i < 16; ++i) {
+                            const float base = fmaf(k2m, __uint_as_float(vv[h][i]), k0m);
+                            const float d = (mk[i] & bit) ? fmaf(k1m, dp[i], base) : base;
+                            dh[i] = d;
+                            part += d;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float base = fmaf(k2m, __uint_as_float(vv[h][i]), k0m);
+                            float d = (mk[i] & bit) ? fmaf(k1m, dp[i], base) : base;
+                            if (c0 + i >= rows) d = 0.0f;
+                            dh[i] = d;
+                            part += d;
+                        }
                     }
                     sdb1 += (double)part;
                     if (row < MB_WROWS) {
@@ -1841,14 +1858,25 @@ mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const 
             // ---- epilogue 2: thread = (pool column q, 32 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b]
             const long long e2 = ((long long)(b0 + 32 * cg) * U + u) * n + row;
             const long long bstride = (long long)U * n;
+            const bool full_cols = (32 * cg + 32 <= rows);   // warp-uniform: all 32 batch rows of this column group are real
             float x[2][16];
+            if (row < n) {
+                const float* pp = a.pool + e2;
+                if (full_cols) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h)
+                    for (int h = 0; h < 2; ++h)
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int c = 32 * cg + 16 * h + i;
-                    x[h][i] = (row < n && c < rows) ? __ldg(a.pool + e2 + (long long)(16 * h + i) * bstride) : 0.0f;
+                        for (int i = 0; i < 16; ++i) { x[h][i] = __ldg(pp); pp += bstride; }
+                } else {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            x[h][i] = (32 * cg + 16 * h + i < rows) ? __ldg(pp) : 0.0f;
+                            pp += bstride;
+                        }
                 }
+            }
             umma::mbar_wait(bar, phase);
             phase ^= 1u;
             umma::fence_after_sync();
@@ -1864,12 +1892,21 @@ mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const 
                 umma::tmem_ld16(D2 + trow + 32 * cg + 16, vv[1]);
                 umma::tmem_ld_wait();
                 if (row < n) {
+                    float* dp2 = a.dy + e2;
+                    if (full_cols) {
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                        for (int h = 0; h < 2; ++h)
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (32 * cg + 16 * h + i < rows)
-                                a.dy[e2 + (long long)(16 * h + i) * bstride] = x[h][i] * __uint_as_float(vv[h][i]);
+                            for (int i = 0; i < 16; ++i) { *dp2 = x[h][i] * __uint_as_float(vv[h][i]); dp2 += bstride; }
+                    } else {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                if (32 * cg + 16 * h + i < rows) *dp2 = x[h][i] * __uint_as_float(vv[h][i]);
+                                dp2 += bstride;
+                            }
+                    }
                 }
             }
         }

@@ -201,3 +201,91 @@ def pfm_to_jaspar(pfm, matrix_id, name):
     for letter, row in zip("ACGT", np.asarray(pfm)):
         out.append("%s [%s]\n" % (letter, " ".join("%6.2f" % v for v in row)))
     return "".join(out)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# row f3: what interpret.py does around the activations -- well-predicted selection (interpret.py:315-361), filter
+# importances restricted to the sequences a filter fires on (:175-192, :485-490), the per-filter median table, and
+# the MEME file of the filters (:259-274 -> utils/jaspar2others.py:46-83).
+# ---------------------------------------------------------------------------------------------------------
+def _fwd_rev(a, strand):
+    """first / second half along axis 0 (test.py `__get_fwd_rev`: the data set is [forward ; reverse complement])"""
+    half = len(a) // 2
+    return a[:half] if strand == "fwd" else a[half:]
+
+
+def well_predicted_sequences(preds, labels, input_data="binary", rev_complement=False):
+    """interpret.py:315-361.  Binary: sequences whose every (sigmoid) prediction is on the label's side of 0.5.
+    Otherwise: intersection of the top 5 % of the labels and of the predictions (flattened indices, as the reference
+    computes them).  preds are the float16 arrays of acts_outs_preds; the arithmetic keeps the reference's dtypes
+    (float16 sigmoid for single-strand input, float64 mean of the two strands otherwise)."""
+    n = .05
+    preds, labels = np.asarray(preds), np.asarray(labels)
+    if rev_complement:
+        fwd, rev = _fwd_rev(preds, "fwd"), _fwd_rev(preds, "rev")
+        ys = _fwd_rev(labels, "fwd")
+        p = np.empty(fwd.shape)
+        for i in range(p.shape[1]):
+            p[:, i] = np.mean([fwd[:, i], rev[:, i]], axis=0)
+            if input_data == "binary":
+                p[:, i] = torch.sigmoid(torch.from_numpy(p[:, i])).numpy()
+    else:
+        p = torch.sigmoid(torch.from_numpy(preds)).numpy() if input_data == "binary" else preds
+        ys = labels
+    if input_data == "binary":
+        ok = (ys == (p > .5).astype(int))
+        # the reference counts matches per row in first-seen order of np.where(...)[0] (ascending rows)
+        return np.flatnonzero(ok.sum(axis=1) == ys.shape[1])
+    k_y, k_p = int(max(ys.shape) * n), int(max(p.shape) * n)
+    idxs_ys = np.argsort(-ys.flatten())[:k_y]
+    idxs_p = np.argsort(-p.flatten())[:k_p]
+    return np.intersect1d(idxs_ys, idxs_p)
+
+
+def filtered_filter_importances(imps_u, idxs, acts_u, threshold):
+    """interpret.py:485-490: importances (F, N) of ONE filter over the well-predicted sequences on which its
+    activation exceeds the threshold anywhere ((N, L') fp16 activations; np.where(acts > thr)[0] may repeat a row,
+    intersect1d makes the rows unique and sorted)"""
+    rows = np.intersect1d(idxs, np.where(acts_u > threshold)[0])
+    return imps_u[:, rows]
+
+
+def filter_importance_table(outs, final_weight, idxs, fired):
+    """The two tables of interpret.py:175-192 without the (N, U, L') activation array: `fired` (U, N) bool says on
+    which sequences a filter exceeds its threshold (site counts > 0 of interpret.site_totals / sites_and_pfms).
+    Returns (rows, medians): rows = [(filter index, importances (F,)) ...] in the reference's order (filter, then
+    ascending sequence), medians (U, F) with NaN for filters that fire nowhere (pandas drops them)."""
+    outs, W = np.asarray(outs), np.asarray(final_weight)
+    U = W.shape[1]
+    rows, med = [], np.full((U, W.shape[0]), np.nan)
+    for u in range(U):
+        sel = np.intersect1d(idxs, np.flatnonzero(fired[u]))
+        if sel.size:
+            imp = outs[sel, u][:, None] * W[:, u][None, :]          # (n_sel, F) = np.multiply(outs, weights[f])[:, u]
+            rows.extend((u, r) for r in imp)
+            med[u] = np.median(imp, axis=0)
+    return rows, med
+
+
+def pfms_to_meme(pfms, names=None, matrix_ids=None):
+    """utils/jaspar2others.py:46-83 (`reformat_motif(..., "meme")`) for count matrices (U, 4, k): header, then per
+    motif `MOTIF id name consensus`, `letter-probability matrix: alength= 4 w= k nsites= N E= 0` and the
+    column-normalised counts printed as str(round(p, 8)).rjust(11).  Motifs without sites are skipped (the
+    reference reads only the JASPAR files that exist).  The consensus and the probabilities come from Biopython's
+    `pssm.consensus` / `pwm` there (counts / column sum, no pseudocounts; arg-max letter, first of A,C,G,T on
+    ties): Biopython is absent here, so this writer is PARITY-UNPINNED beyond that published behaviour."""
+    s = ["MEME version 4\n\n", "ALPHABET= ACGT\n\n", "strands: + -\n\n",
+         "Background letter frequencies (from uniform background):\n", "A 0.25000 C 0.25000 G 0.25000 T 0.25000\n"]
+    for u, pfm in enumerate(np.asarray(pfms, dtype=np.float64)):
+        tot = pfm.sum(axis=0)
+        if not (tot > 0).all():
+            continue
+        pwm = pfm / tot
+        cons = "".join("ACGT"[int(np.argmax(col))] for col in pwm.T)
+        mid = matrix_ids[u] if matrix_ids is not None else f"filter{u}"
+        name = names[u] if names is not None else mid
+        s.append("\nMOTIF %s %s %s\n" % (mid, name, cons))
+        s.append("letter-probability matrix: alength= 4 w= %s nsites= %s E= 0\n" % (pwm.shape[1], int(pfm[:, 0].sum())))
+        for row in pwm.T:
+            s.append(" ".join(str(round(float(r), 8)).rjust(11) for r in row) + "\n")
+    return "".join(s)

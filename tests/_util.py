@@ -103,12 +103,11 @@ def cfg3_golden():
 ZERO_CLASS = {"linears.0.bias", "linears.1.bias", "linears.6.bias", "linears.10.bias"}
 
 
-def check_cfg3_grads(d, grads, what, rtol=2e-4, atol_scale=5e-5, zero_tol=2e-6):
+def check_cfg3_grads(d, grads, what, rtol=2e-4, atol_scale=2e-5, zero_tol=2e-6):
     """named gradients against the compact cfg3 fixture (linears.6.weight: sampled units + per-unit norms).
-    Tolerance: 2e-4 relative + 5e-5 of the tensor's largest entry.  The fixture is the reference's own fp32 result
-    at B = 32 (its BatchNorm-scale gradients are sums of 2 656 cancelling terms per unit); the device backward runs
-    its three GEMMs on two-piece bf16 splits (2^-18 per operand, unbiased), which test_train_step_vs_fp64_oracle
-    holds to 1e-4 + 1e-5 * max against the fp64 evaluation at the same shape."""
+    Tolerance: 2e-4 relative + 2e-5 of the tensor's largest entry; 1e-4 for the two gradients downstream of dy (conv
+    weight, first BatchNorm scale: sums of thousands of cancelling terms), the stated tolerance of the two-piece bf16
+    backward (tests/test_gpu_parity.py FRONT_GRADS)."""
     Uu = int(d["opts"][0])
     for key, got in grads.items():
         got = np.asarray(got)
@@ -122,13 +121,16 @@ def check_cfg3_grads(d, grads, what, rtol=2e-4, atol_scale=5e-5, zero_tol=2e-6):
         elif key in ZERO_CLASS:
             assert np.abs(got - d["grad." + key].reshape(got.shape)).max() < zero_tol, key
         else:
-            assert_close(got, d["grad." + key].reshape(got.shape), rtol=rtol, atol_scale=atol_scale, what=f"{what} {key}")
+            front = key in ("linears.0.weight", "linears.1.weight")
+            assert_close(got, d["grad." + key].reshape(got.shape), rtol=rtol, atol_scale=1e-4 if front else atol_scale,
+                         what=f"{what} {key}")
 
 
 def check_cfg3_after(d, params, rtol=1e-4, atol_scale=1e-4):
     """parameters after one Adam step against the fixture.  Adam's first step is -lr * g / (|g| + eps): an element
-    whose gradient is round-off noise moves by +-lr with the sign of the noise, so only elements whose reference
-    gradient is above 1e-5 of the tensor's largest are compared (and none of the zero-class tensors)."""
+    whose gradient is round-off noise moves by +-lr with the sign of the noise, and one whose gradient is not far
+    above eps = 1e-8 moves by an amount that depends on its magnitude: only elements whose reference gradient is
+    above 1e-3 of the tensor's largest AND above 1e-6 are compared (and none of the zero-class tensors)."""
     Uu = int(d["opts"][0])
     for key, got in params.items():
         if key in ZERO_CLASS:
@@ -139,8 +141,8 @@ def check_cfg3_after(d, params, rtol=1e-4, atol_scale=1e-4):
             ref, g = d["after." + key + ".units"], d["grad." + key + ".units"]
         else:
             ref, g = d["after." + key].reshape(got.shape), d["grad." + key].reshape(got.shape)
-        keep = np.abs(g) > 1e-5 * np.abs(g).max()
-        assert keep.mean() > 0.5, key
+        keep = (np.abs(g) > 1e-3 * np.abs(g).max()) & (np.abs(g) > 1e-6)
+        assert keep.mean() > 0.2, key
         assert_close(got[keep], ref[keep], rtol=rtol, atol_scale=atol_scale, what=f"after {key}")
 
 

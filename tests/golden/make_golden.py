@@ -284,6 +284,25 @@ def main():
     json.dump({"fasta": fasta, "lpm": lpm_text, "pwm": pwm_text, "runs": runs},
               open(os.path.join(HERE, "pwmscan_golden.json"), "w"), indent=1)
 
+    # ---- 5b. interpret post-processing (f3): the reference's own selection / importance functions ----------
+    rngp = np.random.default_rng(11)
+    post = {}
+    for tag_, (N_, F_) in {"bin": (40, 3), "lin": (60, 2)}.items():
+        preds16 = (rngp.standard_normal((N_, F_)) * 2).astype(np.float16)
+        labels = (rngp.random((N_, F_)) < 0.5).astype(np.float64) if tag_ == "bin" else rngp.standard_normal((N_, F_))
+        if tag_ == "bin":                                  # make a good share of the rows well predicted
+            labels[: N_ // 2] = (preds16[: N_ // 2] > 0).astype(np.float64)
+        post[f"{tag_}.preds"], post[f"{tag_}.labels"] = preds16, labels
+        for rc_ in (False, True):
+            post[f"{tag_}.idxs.rc{int(rc_)}"] = np.asarray(ref_interpret._get_well_predicted_sequences(
+                preds16, labels, "binary" if tag_ == "bin" else "linear", rc_), dtype=np.int64)
+    acts_u = (rngp.random((40, 30)) * 3).astype(np.float16)
+    imps_u = rngp.standard_normal((3, 40))
+    post["imp.acts"], post["imp.imps"], post["imp.idxs"] = acts_u, imps_u, np.arange(0, 40, 3)
+    post["imp.thr"] = np.float16(2.7)
+    post["imp.out"] = ref_interpret._filter_filter_importances(imps_u, post["imp.idxs"], acts_u, post["imp.thr"])
+    np.savez_compressed(os.path.join(HERE, "postproc.npz"), **post)
+
     # ---- 6. sites -> JASPAR fixtures of the reference (a10) -------------------------------------------
     cam = os.path.join(REF, "results", "Human-Mouse-Project", "CAM")
     fx = {}

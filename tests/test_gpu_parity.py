@@ -136,6 +136,11 @@ def test_packed_input_equals_float_input():
 # a6: training step
 # ---------------------------------------------------------------------------------------------------
 ZERO_CLASS = {"linears.0.bias", "linears.1.bias", "linears.6.bias", "linears.10.bias"}
+# Stated tolerance of the bf16-split backward (BASELINE.json: "stated looser tolerance for any bf16 mode"): the dW1 / dy
+# pass and the conv weight gradient run on TWO round-to-nearest bf16 pieces per operand (2^-18, unbiased).  Gradients
+# downstream of dy -- the conv weight and the first BatchNorm's scale, sums of thousands of cancelling terms -- are held
+# to 1e-4 of the tensor's largest entry, every other gradient to 1e-5 (2e-5 against the fp32 reference fixtures).
+FRONT_GRADS = {"linears.0.weight", "linears.1.weight"}
 
 
 def _check_grads(named_grads, ref_grads, rtol, atol_scale):
@@ -146,7 +151,7 @@ def _check_grads(named_grads, ref_grads, rtol, atol_scale):
             # the reference returns round-off noise; absolute comparison only
             assert np.abs(got - ref).max() < 2e-6, k
         else:
-            U.assert_close(got, ref, rtol=rtol, atol_scale=atol_scale, what="grad " + k)
+            U.assert_close(got, ref, rtol=rtol, atol_scale=1e-4 if k in FRONT_GRADS else atol_scale, what="grad " + k)
 
 
 @pytest.mark.parametrize("use_image", [False, True])
@@ -412,7 +417,7 @@ def test_train_step_vs_fp64_oracle(cfg):
             got, rn = got[:, keep], rn[:, keep]
         elif k_ != "final.bias":
             got, rn = got.reshape(Uu, -1)[keep], rn.reshape(Uu, -1)[keep]
-        U.assert_close(got, rn, rtol=1e-4, atol_scale=1e-5, what="grad " + k_)
+        U.assert_close(got, rn, rtol=1e-4, atol_scale=1e-4 if k_ in FRONT_GRADS else 1e-5, what="grad " + k_)
     after = _sd_cpu(m)
     for k_, v in ref["running"].items():
         U.assert_close(after[k_].numpy(), v.numpy(), what=k_)
@@ -1016,3 +1021,31 @@ def test_pwm_scoring_command_line_reproduces_the_reference_tool(tmp_path):
             r = subprocess.run(cmd, input=g["fasta"], capture_output=True, text=True, env=env)
         assert r.returncode == 0, (name, r.stderr[-500:])
         assert r.stdout == run["stdout"], name
+
+
+def test_pwm_best_sites_cudamo_semantics():
+    """argmax semantics (ii) of SURVEY.md 8(a): cudamo.py:217-228 (`MaxPool1d(return_indices=True)`, first maximum of a
+    strand) with the strand rule of cudamo.py:254-265 (forward only if STRICTLY greater), restated with torch CPU ops"""
+    from explainn_b200.architectures import PWM, pwm_best_sites
+    rng = np.random.default_rng(4)
+    G, w, L, B = 9, 8, 60, 40
+    # weights that are small multiples of 1/4: every window sum is exact in fp32 whatever the summation order, so ties
+    # between positions and between strands are exact ties on the CPU and on the tensor cores alike, and common
+    pw = -0.25 * rng.integers(1, 5, size=(G, 4, w)).astype(np.float64)
+    x = O.random_onehot(B, L, seed=6, n_frac=0.02)
+    x[5] = x[4].flip(0).flip(1)                       # a sequence next to its own reverse complement
+    pal = O.random_onehot(1, L // 2, seed=9)[0]
+    x[7] = torch.cat((pal, pal.flip(0).flip(1)), dim=1)   # a reverse-complement palindrome: both strands tie everywhere
+    score, strand, start = [t.cpu().numpy() for t in pwm_best_sites(PWM(pw, L, "max").to(DEV), x.to(DEV))]
+    conv = torch.nn.Conv1d(4, G, w, bias=False)
+    conv.weight.data = torch.tensor(pw, dtype=torch.float32)
+    pool = torch.nn.MaxPool1d(L - w + 1, 1, return_indices=True)
+    with torch.no_grad():
+        f_s, f_i = pool(conv(x))
+        r_s, r_i = pool(conv(x.flip(1).flip(2)))
+    f_s, f_i, r_s, r_i = [t[:, :, 0].numpy() for t in (f_s, f_i, r_s, r_i)]
+    fwd_wins = f_s > r_s
+    assert (~fwd_wins & (f_s == r_s)).sum() >= G           # the tie rule is exercised
+    assert np.array_equal(strand, (~fwd_wins).astype(np.int32))
+    assert np.array_equal(start, np.where(fwd_wins, f_i, r_i))
+    U.assert_close(score, np.where(fwd_wins, f_s, r_s), what="best-site scores")

@@ -233,3 +233,43 @@ def test_pwm_scoring_command_line_errors(tmp_path):
     out = io.StringIO()
     assert pwmscan.main(["pwm_scoring", "-m", str(lpm), str(empty)], stdout=out, stderr=io.StringIO()) == 0
     assert out.getvalue() == ""
+
+
+def test_interpret_postprocessing_matches_reference_functions():
+    """f3: well-predicted selection (interpret.py:315-361) and per-filter importance filtering (:485-490) against the
+    outputs of the reference's own functions (tests/golden/postproc.npz), the importance table against its
+    definition, and the MEME writer's format (utils/jaspar2others.py:46-83)."""
+    from explainn_b200 import interpret as I
+    d = U.load_npz("postproc.npz")
+    for tag, kind in (("bin", "binary"), ("lin", "linear")):
+        for rc in (False, True):
+            got = I.well_predicted_sequences(d[f"{tag}.preds"], d[f"{tag}.labels"], kind, rc)
+            assert np.array_equal(np.sort(got), np.sort(d[f"{tag}.idxs.rc{int(rc)}"])), (tag, rc)
+    out = I.filtered_filter_importances(d["imp.imps"], d["imp.idxs"], d["imp.acts"], d["imp.thr"])
+    assert np.array_equal(out, d["imp.out"])
+    # importance table: the same rows through the `fired` matrix instead of the (N, L') activations
+    rng = np.random.default_rng(0)
+    outs, W = rng.random((40, 5)), rng.standard_normal((3, 5))
+    acts = (rng.random((40, 5, 30)) * 3).astype(np.float16)
+    thr = np.full(5, 2.9, dtype=np.float16)
+    thr[4] = np.float16(9.0)                                        # a filter that fires nowhere
+    idxs = np.arange(0, 40, 2)
+    fired = (acts > thr[None, :, None]).any(axis=2).T
+    rows, med = I.filter_importance_table(outs, W, idxs, fired)
+    imps = np.array([outs * W[f] for f in range(3)])                # interpret.py:180-181
+    k = 0
+    for u in range(5):
+        ref = I.filtered_filter_importances(imps[:, :, u], idxs, acts[:, u, :], thr[u]).T
+        for r in ref:
+            assert rows[k][0] == u and np.allclose(rows[k][1], r, rtol=0, atol=1e-15)
+            k += 1
+        if len(ref):
+            assert np.allclose(med[u], np.median(ref, axis=0))
+        else:
+            assert np.isnan(med[u]).all()
+    assert k == len(rows)
+    pfm = np.array([[[3, 0, 1], [0, 4, 1], [1, 0, 1], [0, 0, 1]], [[0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 0]]])
+    text = I.pfms_to_meme(pfm)
+    assert text.startswith("MEME version 4\n\nALPHABET= ACGT\n\nstrands: + -\n\n")
+    assert "\nMOTIF filter0 filter0 ACA\nletter-probability matrix: alength= 4 w= 3 nsites= 4 E= 0\n" in text
+    assert "       0.75         0.0        0.25         0.0\n" in text and "filter1" not in text
