@@ -80,6 +80,7 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
                        const float* __restrict__ dy, const float* __restrict__ zmax,
                        const uint8_t* __restrict__ argmax, const double* __restrict__ stats,
                        uint32_t b_lbo, uint32_t b_sbo,
+                       const float* __restrict__ act_scale, const float* __restrict__ act_shift,
                        double* __restrict__ part /* [gridDim.y][U][4k+2] */) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* g_smem = smem_raw;                                                  // [nstages][3][16][8][144]
@@ -187,14 +188,17 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
         const int rsub = lane >> 3, qsub = lane & 7;
         int row[BT_RGS];
         long long rowoff[BT_RGS];
-        float wsr[BT_RGS];
+        float wsr[BT_RGS], scr[BT_RGS], shr[BT_RGS];
         uint32_t soff[BT_RGS];
+        const bool dpool_in = (act_scale != nullptr);   // dy holds dL/dpool: multiply by pool = exp(scale * zmax + shift)
 #pragma unroll
         for (int rg = 0; rg < BT_RGS; ++rg) {
             row[rg] = 16 * wg + 4 * rg + rsub;
             const int lrow = min(row[rg], nu - 1);       // rows past the tile load a valid row, then zero it
             rowoff[rg] = ((long long)blockIdx.y * U + u0 + lrow) * n;
             wsr[rg] = (float)stats[4 * (u0 + lrow) + 3];
+            scr[rg] = dpool_in ? act_scale[u0 + lrow] : 0.0f;
+            shr[rg] = dpool_in ? act_shift[u0 + lrow] : 0.0f;
             soff[rg] = (uint32_t)((row[rg] >> 3) * BT_SBO_A + (row[rg] & 7) * 16 + qsub * BT_LBO_A);
         }
         double sbd[BT_RGS], sgd[BT_RGS];
@@ -281,7 +285,10 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
             const bool q_ok = (c_t * BT_WIN + qsub) < n;
 #pragma unroll
             for (int rg = 0; rg < BT_RGS; ++rg) {
-                const float dv = (q_ok && row[rg] < nu) ? cur.d[rg] : 0.0f;
+                // pool is recomputed with the forward's own expression (|s| * (sgn(s) z) == s * z exactly), so the
+                // factor is bit-identical to the pooled activation the forward wrote
+                float dv = (q_ok && row[rg] < nu) ? cur.d[rg] : 0.0f;
+                if (dpool_in) dv *= expf(fmaf(scr[rg], cur.z[rg], shr[rg]));
                 // two-way round-to-nearest split: dv = hi + mid to 2^-18 |dv| with an unbiased error; the one-hot
                 // operand is exact, so the weight gradient (a sum over B * n such terms, compared at 1e-4) keeps
                 // fp32-class accuracy with two thirds of the MMAs and staging stores of a three-way split
@@ -386,11 +393,13 @@ extern "C" size_t xnn_frontend_bwd_work_bytes(int B, int U, int k) {
 extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int k, const float* dy,
                                 const float* zmax, const uint8_t* argmax, const float* gamma,
                                 const double* stats, const double* cov_w, const long long* cnt1, long long n_pos,
+                                const float* act_scale, const float* act_shift,
                                 float* dconv_w, float* dconv_b, float* dgamma, float* dbeta, void* work,
                                 xnn_stream_t s) {
     XNN_CHECK_ARG(planes && dy && zmax && argmax && gamma && stats && cov_w && cnt1 && dconv_w && dgamma && dbeta && work,
                   "NULL pointer");
     XNN_CHECK_ARG(k >= 1 && k <= BT_KMAX && L >= k && U >= 1 && B >= 1 && n_pos >= 1, "bad sizes (kernel_size <= 32)");
+    XNN_CHECK_ARG((act_scale == nullptr) == (act_shift == nullptr), "act_scale and act_shift go together");
     const int n = (L - k + 1) / XNN_POOL;
     XNN_CHECK_ARG(n >= 1, "sequence shorter than one pool window");
     int Lbuf = 0, nstages = 0;
@@ -408,8 +417,8 @@ extern "C" int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int
     XNN_CUDA(cudaFuncSetAttribute(frontend_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(bt_mtiles(U), slices);
     frontend_bwd_tc_kernel<<<grid, BT_THREADS, smem, st>>>(planes, B, L, planes_words(L), U, k, n, bt_npad(k), Lbuf,
-                                                          nstages, dy, zmax, argmax, stats, lbo, sbo,
-                                                          (double*)work);
+                                                          nstages, dy, zmax, argmax, stats, lbo, sbo, act_scale,
+                                                          act_shift, (double*)work);
     XNN_CHECK_LAUNCH();
     if (launch_frontend_bwd_finalize((const double*)work, slices, U, k, gamma, stats, cov_w, cnt1, n_pos, dconv_w,
                                      dconv_b, dgamma, dbeta, st)) {

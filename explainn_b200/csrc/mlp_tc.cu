@@ -1925,6 +1925,365 @@ static size_t mbi_smem(int n) {
     return 2 * chunksQ * wcol + 2 * 2 * chunksQ * MB_ROWS * 16 + 2 * (MB_ROWS / 8) * wcol + 512 + 2048 + 64 + 64 * 8 + 16;
 }
 
+// ---------------------------------------------------------------------------
+// B2 on tile images, PIPELINED.  mlp_bwd_img_kernel runs its phases in lock-step (T1 -> dh epilogue -> T3/T4 -> dy
+// epilogue, every warp in every phase): 24 % tensor-pipe active, 42 % issue-active, the rest is waiting at the two
+// barriers of a tile.  Here the phases of neighbouring tiles overlap:
+//   warps 0-11   E1: dh of tile g out of D1 (three warps per TMEM lane quarter, 16-column chunks k, k+3, k+6),
+//                staged as two bf16 pieces; the unit's dW1 read-out (D3) at a unit boundary
+//   warps 12-15  E2: dpool of tile g-1 out of D2[(g-1) & 1] (thread = pool column, all 128 batch rows in four
+//                passes); no loads: the factor pool of dy = dpool * pool is applied by xnn_frontend_bwd
+//   warp  16     issuer: T1(g) as soon as D1 is free, T3/T4(g) when dh is staged -- T1(g+1) therefore queues right
+//                behind T3/T4(g) and E1(g+1) starts while E2(g) is still writing dy
+//   warp  17     loader: bulk loads of the pool stage two tiles ahead and of W1 at a unit boundary, dopre / active
+//                bits of the tile into a four-deep ring
+// TMEM: D1 128 | D2[2] 2 x 128 | D3 96 columns.  Critical chain per tile: T3/T4(g) -> T1(g+1) -> E1(g+1) -> T3/T4(g+1).
+// ---------------------------------------------------------------------------
+#define MBP_E1_WARPS 12
+#define MBP_E2_WARPS 4
+#define MBP_THREADS (32 * (MBP_E1_WARPS + MBP_E2_WARPS + 2))
+
+struct MbpShared {
+    uint64_t full[2];        // pool stage landed (tx)
+    uint64_t wfull;          // W1 landed (tx)
+    uint64_t aux_full[4];    // dopre / active bits ring slot written
+    uint64_t d1_full;        // T1 done (commit)
+    uint64_t d1_free;        // 12 E1 warps have D1 in registers
+    uint64_t dh_full;        // 12 E1 warps staged dh
+    uint64_t d2_full[2];     // T3 / T4 done (commit): dy accumulator ready, pool stage and dh staging free
+    uint64_t d2_free[2];     // 4 E2 warps have read D2[s]
+    uint64_t d3_free;        // 12 E1 warps have read D3 (unit boundary)
+    uint32_t tmem_slot;
+    uint32_t pad;
+};
+
+__global__ void __launch_bounds__(MBP_THREADS, 1)
+mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const unsigned char* __restrict__ w1_image) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int n = a.n, U = a.U, B = a.B, T = a.T;
+    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
+    const uint32_t wcol = MB_WROWS * 16u;
+    const uint32_t wpiece = (uint32_t)chunksQ * wcol;
+    const uint32_t pcol = MB_ROWS * 16u;
+    const uint32_t ppiece = (uint32_t)chunksQ * pcol;
+    const uint32_t tpiece = (MB_ROWS / 8) * wcol;
+    const uint32_t pstage2 = 2u * ppiece;
+    const size_t img_stage = (size_t)3 * ppiece, img_w = (size_t)3 * wpiece;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned char* w1s = smem_raw;
+    unsigned char* ps = smem_raw + 2 * wpiece;
+    uint4* ts = reinterpret_cast<uint4*>(smem_raw + 2 * wpiece + 2 * pstage2);
+    unsigned char* tail = smem_raw + 2 * wpiece + 2 * pstage2 + 2 * tpiece;
+    float* s_dopre_all = reinterpret_cast<float*>(tail);                                 // [4][128]
+    uint32_t* s_mask_all = reinterpret_cast<uint32_t*>(tail + 2048);                     // [4][4 words][128 rows]
+    MbpShared* sh = reinterpret_cast<MbpShared*>(tail + 2048 + 8192);
+    uint2* s_tab = reinterpret_cast<uint2*>(tail + 2048 + 8192 + 128);
+
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw);
+        const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
+        for (uint32_t i = tid; i < tot; i += MBP_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 512);
+    if (tid == 0) {
+        umma::mbar_init(&sh->full[0], 1); umma::mbar_init(&sh->full[1], 1);
+        umma::mbar_init(&sh->wfull, 1);
+        for (int s = 0; s < 4; ++s) umma::mbar_init(&sh->aux_full[s], 1);
+        umma::mbar_init(&sh->d1_full, 1);
+        umma::mbar_init(&sh->d1_free, MBP_E1_WARPS);
+        umma::mbar_init(&sh->dh_full, MBP_E1_WARPS);
+        umma::mbar_init(&sh->d2_full[0], 1); umma::mbar_init(&sh->d2_full[1], 1);
+        umma::mbar_init(&sh->d2_free[0], MBP_E2_WARPS); umma::mbar_init(&sh->d2_free[1], MBP_E2_WARPS);
+        umma::mbar_init(&sh->d3_free, MBP_E1_WARPS);
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const uint32_t D1 = tmem, D2 = tmem + MB_ROWS, D3 = tmem + 3 * MB_ROWS;
+    const int n1 = 3 * kstepsQ, n3 = 21, n4 = 3 * (MB_ROWS / 16), ntab = n1 + n3 + n4;
+    if (tid < ntab) {
+        const int ti = tid;
+        const uint32_t w_addr = umma::smem_u32(w1s);
+        const uint32_t p_addr = umma::smem_u32(ps), t_addr = umma::smem_u32(ts);
+        const int seq = ti < n1 ? 0 : (ti < n1 + n3 ? 1 : 2);
+        const int i = ti - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + n3));
+        const int per = seq == 0 ? kstepsQ : (seq == 1 ? 7 : MB_ROWS / 16);
+        const int pass = i / per, ks = i - pass * per;
+        const uint32_t pa = pass == 0 ? 1u : 0u, pb = pass == 1 ? 1u : 0u;      // mid*hi, hi*mid, hi*hi
+        uint2 e;
+        if (seq == 0)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * wcol, wcol),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * pcol, pcol));
+        else if (seq == 1)
+            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)ks * 256u, 128u),
+                           umma::desc_lo(t_addr + pb * tpiece + (uint32_t)ks * 256u, 128u));
+        else
+            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * wcol, wcol),
+                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)ks * 256u, 128u));
+        s_tab[ti] = e;
+    }
+    __syncthreads();
+
+    const long long tiles_total = (long long)U * T;
+    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
+    const int ntl = (int)(hi - lo);
+    const float inv_keep = 1.0f / (1.0f - a.drop_p);
+    const int C = U * MT_H;
+    auto unit_of = [&](int v) {
+        int u = v / a.P;
+        for (int c = 0; c < v % a.P; ++c) u += (U - c + a.P - 1) / a.P;
+        return u;
+    };
+    // tile g of this CTA: position v in the CTA order, unit, batch tile, first / last tile of its unit IN THIS CTA
+    auto tile_info = [&](int g, int& v, int& t, bool& first, bool& last) {
+        const long long tile = lo + g;
+        v = (int)(tile / T); t = (int)(tile % T);
+        first = (g == 0) || t == 0;
+        last = (g == ntl - 1) || t == T - 1;
+    };
+
+    if (warp == MBP_E1_WARPS + MBP_E2_WARPS + 1) {
+        // ================= loader =================
+        for (int g = 0; g < ntl; ++g) {
+            int v, t; bool first, last;
+            tile_info(g, v, t, first, last);
+            const int u = unit_of(v);
+            const uint32_t st = (uint32_t)g & 1u;
+            if (g >= 2) umma::mbar_wait(&sh->d2_full[st], (uint32_t)((g >> 1) - 1) & 1u);        // stage free
+            if (first) {
+                if (g >= 1) umma::mbar_wait(&sh->d2_full[st ^ 1u], (uint32_t)((g - 1) >> 1) & 1u);   // every MMA of the previous unit
+                if (lane == 0) {
+                    umma::mbar_arrive_expect_tx(&sh->wfull, 2u * wpiece);
+                    umma::bulk_load(w1s, w1_image + (size_t)u * img_w, 2u * wpiece, &sh->wfull);
+                }
+            }
+            {
+                const int b0 = t * MB_ROWS;
+                float* sd = s_dopre_all + (g & 3) * 128;
+                uint32_t* sm = s_mask_all + (g & 3) * 512;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = lane + 32 * j;
+                    const bool ok = b0 + r < B;
+                    const long long bu = (long long)(b0 + r) * U + u;
+                    sd[r] = ok ? __ldg(a.dopre + bu) : 0.0f;
+                    const uint4 pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
+                    sm[r] = pm.x; sm[128 + r] = pm.y; sm[256 + r] = pm.z; sm[384 + r] = pm.w;
+                }
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->aux_full[g & 3]);
+            }
+            if (lane == 0) {
+                umma::mbar_arrive_expect_tx(&sh->full[st], pstage2);
+                umma::bulk_load(ps + (size_t)st * pstage2, image + (size_t)((long long)u * T + t) * img_stage, pstage2,
+                                &sh->full[st]);
+            }
+            __syncwarp();
+        }
+    } else if (warp == MBP_E1_WARPS + MBP_E2_WARPS) {
+        // ================= issuer =================
+        const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);
+        const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16);
+        const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);
+        int ui = 0;                                                   // units started by this CTA
+        for (int g = 0; g < ntl; ++g) {
+            int v, t; bool first, last;
+            tile_info(g, v, t, first, last);
+            const uint32_t st = (uint32_t)g & 1u;
+            if (first) { umma::mbar_wait(&sh->wfull, (uint32_t)ui & 1u); }
+            umma::mbar_wait(&sh->full[st], (uint32_t)(g >> 1) & 1u);
+            umma::mbar_wait(&sh->d1_free, ((uint32_t)g & 1u) ^ 1u);
+            umma::fence_after_sync();
+            if (lane == 0) {
+                umma::issue_table<false>(s_tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), st * (pstage2 >> 4), D1,
+                                         idesc1, 0u);
+                umma::commit(&sh->d1_full);
+            }
+            __syncwarp();
+            umma::mbar_wait(&sh->dh_full, (uint32_t)g & 1u);
+            umma::mbar_wait(&sh->d2_free[st], (((uint32_t)g >> 1) & 1u) ^ 1u);
+            if (first && ui > 0) umma::mbar_wait(&sh->d3_free, (uint32_t)(ui - 1) & 1u);
+            umma::fence_after_sync();
+            if (lane == 0) {
+                umma::issue_table<false>(s_tab + n1, n3, umma::desc_hi(wcol), umma::desc_hi(wcol), 0u, D2 + st * MB_ROWS,
+                                         idesc2, 0u);
+                umma::issue_table<false>(s_tab + n1 + n3, n4, umma::desc_hi(128u), umma::desc_hi(pcol),
+                                         st * (pstage2 >> 4), D3, idesc3, first ? 0u : 1u);
+                umma::commit(&sh->d2_full[st]);
+            }
+            __syncwarp();
+            if (first) ++ui;
+        }
+    } else if (warp < MBP_E1_WARPS) {
+        // ================= E1: dh, and dW1 at unit boundaries =================
+        const int quarter = warp & 3, k3 = warp >> 2;                 // k3 = 0..2: 16-column chunks k3, k3 + 3, k3 + 6
+        const int row = quarter * 32 + lane;
+        const uint32_t trow = (uint32_t)(quarter * 32) << 16;
+        const uint32_t bit = 1u << (row & 31);
+        const int wsel = row >> 5;
+        float k0m = 0.f, k1m = 0.f, k2m = 0.f;
+        double sdb1 = 0.0;
+        for (int g = 0; g < ntl; ++g) {
+            int v, t; bool first, last;
+            tile_info(g, v, t, first, last);
+            const int u = unit_of(v);
+            const int rows = min(MB_ROWS, B - t * MB_ROWS);
+            if (first) {
+                const int ch = u * MT_H + row;
+                if (row < MT_H) {
+                    const float b1v = a.b1[ch], w2v = a.w2[ch];
+                    const float mean = (float)a.stats2[4LL * ch], invstd = (float)a.stats2[4LL * ch + 2];
+                    const float gis = (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]);
+                    const float2 cf = a.coef[ch];
+                    k1m = gis * w2v * inv_keep;
+                    k2m = -gis * cf.y * invstd;
+                    k0m = -gis * cf.x + k2m * (b1v - mean);
+                } else {
+                    k0m = k1m = k2m = 0.f;
+                }
+            }
+            umma::mbar_wait(&sh->aux_full[g & 3], ((uint32_t)g >> 2) & 1u);
+            umma::mbar_wait(&sh->d1_full, (uint32_t)g & 1u);
+            umma::fence_after_sync();
+            uint32_t vv[3][16];
+#pragma unroll
+            for (int m = 0; m < 3; ++m)
+                if (k3 + 3 * m < 8) umma::tmem_ld16(D1 + trow + 16 * (k3 + 3 * m), vv[m]);
+            umma::tmem_ld_wait();
+            umma::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->d1_free);
+            const float* s_dopre = s_dopre_all + (g & 3) * 128;
+            const uint32_t* s_mask = s_mask_all + (g & 3) * 512 + wsel * 128;
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                if (k3 + 3 * m < 8) {
+                    const int c0 = 16 * (k3 + 3 * m);
+                    float dh[16];
+                    float part = 0.0f;
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        const uint4 mq = *reinterpret_cast<const uint4*>(s_mask + c0 + 4 * q4);
+                        const float4 dq = *reinterpret_cast<const float4*>(s_dopre + c0 + 4 * q4);
+                        const uint32_t mk[4] = {mq.x, mq.y, mq.z, mq.w};
+                        const float dp[4] = {dq.x, dq.y, dq.z, dq.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int i = 4 * q4 + e;
+                            const float base = fmaf(k2m, __uint_as_float(vv[m][i]), k0m);
+                            float d = (mk[e] & bit) ? fmaf(k1m, dp[e], base) : base;
+                            if (c0 + i >= rows) d = 0.0f;
+                            dh[i] = d;
+                            part += d;
+                        }
+                    }
+                    sdb1 += (double)part;
+                    if (row < MB_WROWS) {
+#pragma unroll
+                        for (int gg = 0; gg < 2; ++gg) {
+                            uint32_t p0[4], p1[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float x0 = dh[8 * gg + 2 * e], x1 = dh[8 * gg + 2 * e + 1];
+                                p0[e] = cvt_bf16x2_rn(x0, x1);
+                                p1[e] = cvt_bf16x2_rn(x0 - __uint_as_float(p0[e] << 16),
+                                                      x1 - __uint_as_float(p0[e] & 0xFFFF0000u));
+                            }
+                            const int chunk = (c0 >> 3) + gg;
+                            ts[chunk * MB_WROWS + row] = make_uint4(p0[0], p0[1], p0[2], p0[3]);
+                            ts[tpiece / 16 + chunk * MB_WROWS + row] = make_uint4(p1[0], p1[1], p1[2], p1[3]);
+                        }
+                    }
+                }
+            }
+            umma::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->dh_full);
+            if (last) {
+                // dW1 of the unit: every T4 has completed when the last tile's commit arrives
+                umma::mbar_wait(&sh->d2_full[g & 1], ((uint32_t)g >> 1) & 1u);
+                umma::fence_after_sync();
+                int j = blockIdx.x;
+                const long long start = (long long)v * T;
+                while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
+                const int slot = blockIdx.x - j;
+                const bool ok = row < MT_H && slot < a.slots;
+                float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + row) * n;
+                for (int c0 = 16 * k3; c0 < Nq; c0 += 48) {
+                    uint32_t w[16];
+                    umma::tmem_ld16(D3 + trow + c0, w);
+                    umma::tmem_ld_wait();
+                    if (ok) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (c0 + i < n) o[c0 + i] = __uint_as_float(w[i]);
+                    }
+                }
+                if (ok) a.part_db1[((long long)slot * 4 + k3) * C + (long long)u * MT_H + row] = sdb1;
+                sdb1 = 0.0;
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->d3_free);
+            }
+        }
+    } else {
+        // ================= E2: dpool[b,u,q] = D2[q][b] =================
+        // (the factor pool[b,u,q] of dy = dpool * pool -- the derivative of exp at the pooled maximum -- is applied
+        //  by the conv weight gradient kernel, which recomputes pool from the zmax it reads anyway: this pass
+        //  then has no global loads at all)
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;                          // pool column q
+        const uint32_t trow = (uint32_t)(quarter * 32) << 16;
+        const long long bstride = (long long)U * n;
+        for (int g = 0; g < ntl; ++g) {
+            int v, t; bool first, last;
+            tile_info(g, v, t, first, last);
+            const int u = unit_of(v);
+            const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
+            const uint32_t st = (uint32_t)g & 1u;
+            umma::mbar_wait(&sh->d2_full[st], ((uint32_t)g >> 1) & 1u);
+            umma::fence_after_sync();
+#pragma unroll 1
+            for (int pass = 0; pass < 4; ++pass) {
+                uint32_t w[2][16];
+                umma::tmem_ld16(D2 + st * MB_ROWS + trow + 32 * pass, w[0]);
+                umma::tmem_ld16(D2 + st * MB_ROWS + trow + 32 * pass + 16, w[1]);
+                umma::tmem_ld_wait();
+                if (pass == 3) {
+                    umma::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) umma::mbar_arrive(&sh->d2_free[st]);
+                }
+                if (row < n && 32 * pass < rows) {
+                    float* dp2 = a.dy + ((long long)(b0 + 32 * pass) * U + u) * n + row;
+                    if (32 * pass + 32 <= rows) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) { *dp2 = __uint_as_float(w[i >> 4][i & 15]); dp2 += bstride; }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            if (32 * pass + i < rows) *dp2 = __uint_as_float(w[i >> 4][i & 15]);
+                            dp2 += bstride;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(sh->tmem_slot, 512);
+}
+
+static size_t mbp_smem(int n) {
+    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
+    const size_t wcol = MB_WROWS * 16;
+    return 2 * chunksQ * wcol + 2 * 2 * chunksQ * MB_ROWS * 16 + 2 * (MB_ROWS / 8) * wcol + 2048 + 8192 + 128 + 64 * 8 + 16;
+}
+
 __global__ void __launch_bounds__(256)
 mlp_bwd_reduce_kernel(const float* __restrict__ part_w1, const double* __restrict__ part_db1, int slots,
                       long long nw, int C, float* __restrict__ dw1, float* __restrict__ db1) {
@@ -2029,9 +2388,9 @@ extern "C" int xnn_mlp_bwd(const float* dopre, const float* pool, const float* w
     g.B = B; g.U = U; g.n = n; g.T = mb_tiles(B); g.slots = mb_slots(B, U); g.drop_p = drop_p;
     g.P = mb_interleave(B, U);
     if (image != nullptr) {
-        const size_t smem = mbi_smem(n);
-        XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        mlp_bwd_img_kernel<<<mb_grid(B, U), MT_THREADS, smem, st>>>(g, a.image, a.w1_image);
+        const size_t smem = mbp_smem(n);
+        XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        mlp_bwd_pipe_kernel<<<mb_grid(B, U), MBP_THREADS, smem, st>>>(g, a.image, a.w1_image);
     } else {
         const size_t smem = mb_smem(n);
         XNN_CUDA(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -355,7 +355,8 @@ def _outs(out, shapes, dev):
 def mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, gamma2, w2, bits, drop_p, out=None, sync=None, world=1,
             image=None):
     """Backward of FC1 -> BN2 -> ReLU -> dropout -> FC2 from dopre (B,U); see xnn_mlp_bwd.
-    out: optional [dw1, db1, dg2, dbe2, dw2, db2] destinations."""
+    out: optional [dw1, db1, dg2, dbe2, dw2, db2] destinations.
+    The last result is dy = dpool * pool -- or, with `image`, dpool alone (frontend_bwd applies the factor)."""
     B, U, n = pool.shape
     dev = pool.device
     lib = _lib.load()
@@ -465,16 +466,25 @@ def fc1_bwd(dhpre, pool, w1):
     return dw1, db1, dy
 
 
-def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos, simt=False, out=None):
+def frontend_bwd(planes, L, k, dy, zmax, argmax, gamma, stats, cov_w, cnt1, n_pos, simt=False, out=None,
+                 act_scale=None, act_shift=None):
+    """act_scale / act_shift: `dy` is dL/dpool (what mlp_bwd returns on tile images); the kernel multiplies by
+    pool = exp(act_scale * zmax + act_shift)."""
     B, U, n = dy.shape
     dev = dy.device
     lib = _lib.load()
     dconv_w, dconv_b, dgamma, dbeta = _outs(out, [(U, 4, k), (U,), (U,), (U,)], dev)
     work = _work(lib.xnn_frontend_bwd_work_bytes(B, U, k), dev)
-    _call("xnn_frontend_bwd_simt" if simt else "xnn_frontend_bwd", _p(planes), B, L, U, k,
-          _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
-          _p(gamma), _p(stats), _p(cov_w), _p(cnt1), int(n_pos), _p(dconv_w), _p(dconv_b), _p(dgamma), _p(dbeta),
-          _p(work), _stream())
+    if simt:
+        if act_scale is not None:
+            raise ValueError("the FP64 cross-check kernel takes the true dy")
+        _call("xnn_frontend_bwd_simt", _p(planes), B, L, U, k, _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
+              _p(gamma), _p(stats), _p(cov_w), _p(cnt1), int(n_pos), _p(dconv_w), _p(dconv_b), _p(dgamma), _p(dbeta),
+              _p(work), _stream())
+    else:
+        _call("xnn_frontend_bwd", _p(planes), B, L, U, k, _p(_req(dy, torch.float32, "dy")), _p(zmax), _p(argmax),
+              _p(gamma), _p(stats), _p(cov_w), _p(cnt1), int(n_pos), _p(act_scale), _p(act_shift), _p(dconv_w),
+              _p(dconv_b), _p(dgamma), _p(dbeta), _p(work), _stream())
     return dconv_w, dconv_b, dgamma, dbeta
 
 

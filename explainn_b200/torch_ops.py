@@ -111,9 +111,10 @@ def _(planes, L, params, running, eps, drop_p, seed, drop_mask):
 
 # ------------------------------------------------------------------------------------------------------------
 # unit bank, train mode
-# outputs: o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image
+# outputs: o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image,
+#          scale1, shift1
 # ------------------------------------------------------------------------------------------------------------
-N_TRAIN_OUT = 15
+N_TRAIN_OUT = 17
 
 
 @custom_op("explainn_b200::unit_bank_train", mutates_args=(), device_types="cuda")
@@ -157,7 +158,8 @@ def unit_bank_train(planes: torch.Tensor, L: int, params: Sequence[torch.Tensor]
         image = torch.empty(0, dtype=torch.uint8, device=cw.device)
     scale3, shift3, stats3 = ops.bn_train_prepare(opre, g3, be3, eps[2], 0.0, None, None, sync=sync, world=world)
     o, _ = ops.head_fwd(opre, scale3, shift3)
-    return [o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image]
+    return [o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image,
+            scale1, shift1]
 
 
 @custom_op("explainn_b200::bn_running_update", mutates_args=("running_means", "running_vars", "nbt"),
@@ -188,7 +190,7 @@ def _(planes, L, params, eps, drop_p, seed, seed_dev, drop_mask, arena, offs):
             cw.new_empty((B, U, 4) if tc else (0,), dtype=torch.int32), f32(C), f32(C), f64(U, 4), f64(C, 4),
             f64(U, 4), f64(U, 4 * k), cw.new_empty((4 * k,), dtype=torch.int64),
             f32(0) if tc else f32(B, U, HIDDEN),
-            cw.new_empty((_image_bytes(B, U, n) if tc else 0,), dtype=torch.uint8)]
+            cw.new_empty((_image_bytes(B, U, n) if tc else 0,), dtype=torch.uint8), f32(U), f32(U)]
 
 
 def _grad_views(arena, offs, shapes):
@@ -211,7 +213,8 @@ def _bank_grad_shapes(cw, n):
 def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, arena):
     """the backward of the unit bank, every parameter gradient written into `flat` (BANK_PARAMS order)"""
     cw, cb, g1, be1, w1, b1, g2, be2, w2, b2, g3, be3 = params
-    o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image = saved
+    (o, pool, zmax, arg, opre, bits, scale2, shift2, stats1, stats2, stats3, cov_w, cnt1, hpre, image, scale1,
+     shift1) = saved
     B, U = o.shape
     k = cw.shape[2]
     C = U * HIDDEN
@@ -220,10 +223,13 @@ def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, 
     d_cw, d_cb, d_g1, d_be1, d_w1, d_b1, d_g2, d_be2, d_w2, d_b2, d_g3, d_be3 = flat
     _, _, dopre = ops.bn_bwd(do.contiguous(), o, opre, stats3, g3, inplace=False, out=[d_g3, d_be3], sync=sync,
                              world=world)
+    act = {}
     if bits.numel():
         dy = ops.mlp_bwd(dopre, pool, w1, b1, scale2, shift2, stats2, g2, w2, bits, drop_p,
                          out=[d_w1, d_b1, d_g2, d_be2, d_w2, d_b2], sync=sync, world=world,
                          image=image if image.numel() else None)[6]
+        if image.numel():        # on tile images the pass returns dL/dpool: the conv weight gradient applies exp'
+            act = dict(act_scale=scale1, act_shift=shift1)
     else:
         dw2_, db2_, gh = ops.fc2_bwd(dopre, hpre, scale2, shift2, w2, drop_p, seed, drop_mask)
         d_w2.view(-1).copy_(dw2_.view(-1)); d_b2.copy_(db2_)
@@ -240,7 +246,8 @@ def _bank_bwd_into(flat, do, planes, L, params, saved, drop_p, seed, drop_mask, 
     if reserve:
         ops.set_sm_reserve(reserve)
     try:
-        ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos, out=[d_cw, d_cb, d_g1, d_be1])
+        ops.frontend_bwd(planes, L, k, dy, zmax, arg, g1, stats1, cov_w, cnt1, n_pos, out=[d_cw, d_cb, d_g1, d_be1],
+                         **act)
     finally:
         if reserve:
             ops.set_sm_reserve(0)

@@ -202,7 +202,8 @@ int xnn_linear_bwd(const float* dy, const float* w, const float* x, int B, int U
  * xnn_fc2_bwd + xnn_bn_bwd (linears.7) + xnn_fc1_bwd fused; hpre is recomputed from pool, neither it
  * nor its gradient is written.  maskbits: the active bits xnn_mlp_fwd wrote (required).
  *   dw1 (100U,n), db1 (100U), dgamma2/dbeta2 (100U), dw2 (U,100), db2 (U),
- *   dy[b,u,q] = pool * sum_m dhpre*W1 (gradient at the arg-max conv output through exp).
+ *   dy[b,u,q] = pool * sum_m dhpre*W1 (gradient at the arg-max conv output through exp); with `image` given the
+ *   factor pool is left out (dy = dL/dpool) and xnn_frontend_bwd applies it (act_scale / act_shift).
  * work: xnn_mlp_bwd_work_bytes, 256-byte aligned. */
 size_t xnn_mlp_bwd_work_bytes(int B, int U, int n);
 size_t xnn_mlp_bwd_partial_bytes(int B, int U);
@@ -239,10 +240,14 @@ int xnn_fc1_bwd(const float* dhpre, const float* pool, const float* w1,
  * closed-form dense BatchNorm terms (Cov.w from xnn_bn1_train_prepare).
  *   dconv_w (U,4,k), dconv_b (U) (exactly 0 in train mode), dgamma1, dbeta1 (U) */
 size_t xnn_frontend_bwd_work_bytes(int B, int U, int k);
+/* act_scale / act_shift (optional, both or neither, (U) each): `dy` then holds dL/dpool and the kernel multiplies
+ * every value by pool = exp(act_scale[u] * zmax + act_shift[u]) -- the forward's own expression, bit-identical to
+ * the pooled activation it wrote -- before using it (xnn_mlp_bwd on tile images leaves that factor to this call). */
 int xnn_frontend_bwd(const uint32_t* planes, int B, int L, int U, int k,
                      const float* dy, const float* zmax, const uint8_t* argmax,
                      const float* gamma, const double* stats, const double* cov_w,
                      const long long* cnt1, long long n_pos,
+                     const float* act_scale, const float* act_shift,
                      float* dconv_w, float* dconv_b, float* dgamma, float* dbeta,
                      void* work, xnn_stream_t s);
 /* debugging cross-check only: the same contract as a sparse FP64 scatter (no tensor cores) */
