@@ -187,25 +187,27 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
         const int grp = warp / BT_GROUP_WARPS, wg = warp % BT_GROUP_WARPS;
         const int rsub = lane >> 3, qsub = lane & 7;
         int row[BT_RGS];
-        long long rowoff[BT_RGS];
+        int rowd[BT_RGS];                                // element offset of the row from the warp's first row
         float wsr[BT_RGS], scr[BT_RGS], shr[BT_RGS];
-        uint32_t soff[BT_RGS];
         const bool dpool_in = (act_scale != nullptr);   // dy holds dL/dpool: multiply by pool = exp(scale * zmax + shift)
+        // rows 16wg + 4rg + rsub: (row >> 3) = 2wg + (rg >> 1), (row & 7) = 4 (rg & 1) + rsub, so the stage offset of
+        // row group rg is ONE base plus the compile-time delta (rg >> 1) * BT_SBO_A + (rg & 1) * 64
+        const uint32_t soff0 = (uint32_t)(2 * wg * BT_SBO_A + rsub * 16 + qsub * BT_LBO_A);
+        const int row0 = min(16 * wg, nu - 1);
+        const long long rowbase = ((long long)blockIdx.y * U + u0 + row0) * n;
 #pragma unroll
         for (int rg = 0; rg < BT_RGS; ++rg) {
             row[rg] = 16 * wg + 4 * rg + rsub;
             const int lrow = min(row[rg], nu - 1);       // rows past the tile load a valid row, then zero it
-            rowoff[rg] = ((long long)blockIdx.y * U + u0 + lrow) * n;
+            rowd[rg] = (lrow - row0) * n;
             wsr[rg] = (float)stats[4 * (u0 + lrow) + 3];
             scr[rg] = dpool_in ? act_scale[u0 + lrow] : 0.0f;
             shr[rg] = dpool_in ? act_shift[u0 + lrow] : 0.0f;
-            soff[rg] = (uint32_t)((row[rg] >> 3) * BT_SBO_A + (row[rg] & 7) * 16 + qsub * BT_LBO_A);
         }
         double sbd[BT_RGS], sgd[BT_RGS];
         float a_d[BT_RGS], a_dz[BT_RGS];
 #pragma unroll
         for (int rg = 0; rg < BT_RGS; ++rg) { sbd[rg] = 0.0; sgd[rg] = 0.0; a_d[rg] = 0.0f; a_dz[rg] = 0.0f; }
-        const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
         const long long seq_step = (long long)ns * U * n;
 
         // 8 lanes share a row: fold the per-lane float partial sums of one sequence into the fp64 row sums
@@ -231,12 +233,15 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
         auto fetch = [&](BtVals& v) {
             if (f_sq < nseq) {
                 const int q = min(f_t * BT_WIN + qsub, n - 1);     // windows past n load a valid one, then zero it
+                const long long g0 = rowbase + f_seq + q;          // one 64-bit base, 32-bit row deltas
+                const float* pd = dy + g0;
+                const float* pz = zmax + g0;
+                const uint8_t* pa = argmax + g0;
 #pragma unroll
                 for (int rg = 0; rg < BT_RGS; ++rg) {
-                    const long long g = rowoff[rg] + f_seq + q;
-                    v.d[rg] = __ldg(dy + g);
-                    v.z[rg] = __ldg(zmax + g);
-                    v.a[rg] = (int)__ldg(argmax + g);
+                    v.d[rg] = __ldg(pd + rowd[rg]);
+                    v.z[rg] = __ldg(pz + rowd[rg]);
+                    v.a[rg] = (int)__ldg(pa + rowd[rg]);
                 }
             }
             f_t += BT_GROUPS;
@@ -294,9 +299,12 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
                 // fp32-class accuracy with two thirds of the MMAs and staging stores of a three-way split
                 const __nv_bfloat16 hi = __float2bfloat16_rn(dv);
                 const __nv_bfloat16 mid = __float2bfloat16_rn(dv - __bfloat162float(hi));
-                unsigned char* e = st + soff[rg];
+                unsigned char* e = st + soff0 + (rg >> 1) * BT_SBO_A + (rg & 1) * 64;
                 // zero the window's 16-byte chunk of each piece, then drop the value at slot arg (same thread,
-                // program order); piece order mid, hi: the small piece enters the fp32 accumulator first
+                // program order); piece order mid, hi: the small piece enters the fp32 accumulator first.
+                // (Building the chunk in registers for ONE store per piece was measured slower: 0.685 -> 0.711 ms,
+                // eight selects cost this instruction-bound loop more than the second store.)
+                const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
                 *reinterpret_cast<uint4*>(e + 0 * BT_PIECE_BYTES) = zero4;
                 *reinterpret_cast<uint4*>(e + 1 * BT_PIECE_BYTES) = zero4;
                 unsigned char* e2 = e + 2 * cur.a[rg];

@@ -2037,10 +2037,13 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
         for (int c = 0; c < v % a.P; ++c) u += (U - c + a.P - 1) / a.P;
         return u;
     };
-    // tile g of this CTA: position v in the CTA order, unit, batch tile, first / last tile of its unit IN THIS CTA
+    // tile g of this CTA: position v in the CTA order, unit, batch tile, first / last tile of its unit IN THIS CTA.
+    // Every role walks its tiles in order, so (v, t, u) advance incrementally (no 64-bit divisions per tile).
+    const int v_lo = (int)(lo / T), t_lo = (int)(lo % T);
+    int cur_v = v_lo, cur_t = t_lo - 1, cur_u = unit_of(v_lo);
     auto tile_info = [&](int g, int& v, int& t, bool& first, bool& last) {
-        const long long tile = lo + g;
-        v = (int)(tile / T); t = (int)(tile % T);
+        if (++cur_t == T) { cur_t = 0; ++cur_v; cur_u = unit_of(cur_v); }
+        v = cur_v; t = cur_t;
         first = (g == 0) || t == 0;
         last = (g == ntl - 1) || t == T - 1;
     };
@@ -2050,7 +2053,7 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
         for (int g = 0; g < ntl; ++g) {
             int v, t; bool first, last;
             tile_info(g, v, t, first, last);
-            const int u = unit_of(v);
+            const int u = cur_u;
             const uint32_t st = (uint32_t)g & 1u;
             if (g >= 2) umma::mbar_wait(&sh->d2_full[st], (uint32_t)((g >> 1) - 1) & 1u);        // stage free
             if (first) {
@@ -2060,26 +2063,34 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
                     umma::bulk_load(w1s, w1_image + (size_t)u * img_w, 2u * wpiece, &sh->wfull);
                 }
             }
+            // the big transfer first: the ring values below come through the LSU with a global-load latency of their own
+            if (lane == 0) {
+                umma::mbar_arrive_expect_tx(&sh->full[st], pstage2);
+                umma::bulk_load(ps + (size_t)st * pstage2, image + (size_t)((long long)u * T + t) * img_stage, pstage2,
+                                &sh->full[st]);
+            }
             {
                 const int b0 = t * MB_ROWS;
                 float* sd = s_dopre_all + (g & 3) * 128;
                 uint32_t* sm = s_mask_all + (g & 3) * 512;
+                float dv[4];
+                uint4 pm[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int r = lane + 32 * j;
                     const bool ok = b0 + r < B;
                     const long long bu = (long long)(b0 + r) * U + u;
-                    sd[r] = ok ? __ldg(a.dopre + bu) : 0.0f;
-                    const uint4 pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
-                    sm[r] = pm.x; sm[128 + r] = pm.y; sm[256 + r] = pm.z; sm[384 + r] = pm.w;
+                    dv[j] = ok ? __ldg(a.dopre + bu) : 0.0f;
+                    pm[j] = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = lane + 32 * j;
+                    sd[r] = dv[j];
+                    sm[r] = pm[j].x; sm[128 + r] = pm[j].y; sm[256 + r] = pm[j].z; sm[384 + r] = pm[j].w;
                 }
                 __syncwarp();
                 if (lane == 0) umma::mbar_arrive(&sh->aux_full[g & 3]);
-            }
-            if (lane == 0) {
-                umma::mbar_arrive_expect_tx(&sh->full[st], pstage2);
-                umma::bulk_load(ps + (size_t)st * pstage2, image + (size_t)((long long)u * T + t) * img_stage, pstage2,
-                                &sh->full[st]);
             }
             __syncwarp();
         }
@@ -2129,7 +2140,7 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
         for (int g = 0; g < ntl; ++g) {
             int v, t; bool first, last;
             tile_info(g, v, t, first, last);
-            const int u = unit_of(v);
+            const int u = cur_u;
             const int rows = min(MB_ROWS, B - t * MB_ROWS);
             if (first) {
                 const int ch = u * MT_H + row;
@@ -2241,7 +2252,7 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
         for (int g = 0; g < ntl; ++g) {
             int v, t; bool first, last;
             tile_info(g, v, t, first, last);
-            const int u = unit_of(v);
+            const int u = cur_u;
             const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
             const uint32_t st = (uint32_t)g & 1u;
             umma::mbar_wait(&sh->d2_full[st], ((uint32_t)g >> 1) & 1u);
