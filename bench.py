@@ -417,12 +417,23 @@ def main():
     }
     top = max(call_ms, key=call_ms.get)
     top_ms = call_ms[top]
-    bound, per_seq, what = ALG.get(top, ("hbm", 0.0, "unlisted"))
-    if bound == "tensor":
-        achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e12, tf_sus, "TFLOP/s", "bf16_tflops_sustained"
-    else:
-        achieved, peak, unit, src = per_seq * B / (top_ms / 1e3) / 1e9, hbm, "GB/s", "hbm_gbs"
+
+    def roof(entry, ms):
+        bound_, per_seq_, what_ = ALG.get(entry, ("hbm", 0.0, "unlisted"))
+        if bound_ == "tensor":
+            return bound_, per_seq_, what_, per_seq_ * B / (ms / 1e3) / 1e12, tf_sus, "TFLOP/s", "bf16_tflops_sustained"
+        return bound_, per_seq_, what_, per_seq_ * B / (ms / 1e3) / 1e9, hbm, "GB/s", "hbm_gbs"
+
+    bound, per_seq, what, achieved, peak, unit, src = roof(top, top_ms)
     traffic, traffic_src = ncu_traffic(top, args.workload, B)
+    per_entry = []
+    for nme, ms_ in sorted(call_ms.items(), key=lambda kv: -kv[1])[:6]:
+        if nme in ALG:
+            b_, ps_, _, ach_, pk_, un_, _ = roof(nme, ms_)
+            tr_, _ = ncu_traffic(nme, args.workload, B)
+            per_entry.append({"entry": nme, "ms": round(ms_, 4), "bound": b_, "algorithmic_per_seq": ps_,
+                              "achieved": ach_, "peak": pk_, "unit": un_, "frac": ach_ / pk_, "traffic": tr_,
+                              "traffic_gbs": (tr_ / (ms_ / 1e3) / 1e9) if tr_ else None})
     fe_ms = call_ms.get("xnn_frontend_fwd", 0.0)
     cpu = cpu_baseline(cfg, args.cpu_sample) if not args.no_aux else None
     bn_mode = "synchronised BatchNorm statistics (global batch)" if (args.sync_bn and world > 1) else \
@@ -453,7 +464,7 @@ def main():
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": f"{src}, {which}",
                      "kernel_ms": top_ms, "kernel_share_of_step": top_ms / (ms_eager / n_break),
-                     "algorithmic_per_seq": per_seq,
+                     "algorithmic_per_seq": per_seq, "entries": per_entry,
                      "frontend_fwd": {"bound": "tensor", "kernel_ms": fe_ms,
                                       "achieved": conv_flops * B / (fe_ms / 1e3) / 1e12 if fe_ms else None,
                                       "peak": tf_sus, "unit": "TFLOP/s"},

@@ -6,7 +6,7 @@ Reference: `explainn/architectures/__init__.py:458-461` returns
 `metric(y_true.flatten(), y_score.flatten())` and takes `score[0]` when the result is not a float;
 `pwm-scoring.py:115-120` calls them once per PWM column (750 sklearn calls over the same `y_true`).
 
-Here the arrays stay on the device: one `torch.sort` per column batch (library plumbing) and the kernels of
+Here the arrays stay on the device: one segmented radix sort per column batch (`xnn_sort_columns`, csrc/sort.cu) and the kernels of
 `csrc/metrics.cu`.  `get_metrics()` keeps the reference's names and call signature (numpy or torch inputs, float /
 `(r, pvalue)` results); `column_metrics` is the batched form for the per-PWM loop.  No CPU fallback: inputs are moved
 to the CUDA device and the kernels raise without one.

@@ -25,7 +25,7 @@ KERNELS_PER_CALL = {
     "xnn_linear_fwd": 1, "xnn_linear_bwd": 5, "xnn_bn_bwd": 3, "xnn_fc2_bwd": 2, "xnn_fc1_bwd": 5,
     "xnn_frontend_bwd": 2, "xnn_frontend_bwd_simt": 2, "xnn_adam_step": 1, "xnn_act_max": 1, "xnn_site_counts": 1, "xnn_site_emit": 1,
     "xnn_pwm_scan": 1, "xnn_pwm_scan_tc": 2, "xnn_act_max_tc": 2, "xnn_site_counts_tc": 2, "xnn_site_emit_tc": 2, "xnn_mlp_bn2_train_prepare": 2, "xnn_mlp_fwd": 1, "xnn_mlp_bwd": 4, "xnn_lpm_scan_sum": 1, "xnn_lpm_scan_sum_parts": 2, "xnn_lpm_scan_best_parts": 5, "xnn_ipwm_scan_best_parts": 2, "xnn_lpm_scan_best": 1, "xnn_ipwm_scan_best": 1,
-    "xnn_adam_step_multi": 1, "xnn_counters_advance": 1, "xnn_counters_advance_list": 1, "xnn_bn_running_update": 1, "xnn_loss_fwd": 1, "xnn_loss_bwd": 1, "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
+    "xnn_adam_step_multi": 1, "xnn_counters_advance": 1, "xnn_counters_advance_list": 1, "xnn_bn_running_update": 1, "xnn_loss_fwd": 1, "xnn_loss_bwd": 1, "xnn_sort_columns": 1, "xnn_metric_auc": 2, "xnn_metric_ranks": 1, "xnn_metric_pearson_f32": 1, "xnn_metric_pearson_f64": 1,
 }
 kernel_launches = 0
 
@@ -706,10 +706,24 @@ def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps,
 
 
 # ---- validation metrics (explainn_b200/metrics.py is the reference-facing surface) ----
+def sort_columns(vals, descending=False):
+    """every row of vals float32 (G,N) sorted on its own -> (sorted values, int64 permutation); xnn_sort_columns
+    (stable radix sort, one block per row) instead of torch.sort"""
+    _req(vals, torch.float32, "vals")
+    G, N = vals.shape
+    sv = torch.empty_like(vals)
+    perm = torch.empty((G, N), dtype=torch.int64, device=vals.device)
+    if G == 0 or N == 0:
+        return sv, perm
+    work = torch.empty(int(_lib.load().xnn_sort_columns_work_bytes(N, G)) // 4, dtype=torch.int32, device=vals.device)
+    _call("xnn_sort_columns", _p(vals), N, G, int(bool(descending)), _p(sv), _p(perm), _p(work), _stream())
+    return sv, perm
+
+
 def metric_auc(scores, labels):
     """scores float32 (G,N) columns contiguous; labels uint8 (N,) shared or (G,N).  Returns (auroc, aupr) float64 (G,).
-    The descending sort is torch.sort (library plumbing); ranks over ties, the cumulative positives and both
-    reductions are xnn_metric_auc."""
+    The descending sort is xnn_sort_columns; ranks over ties, the cumulative positives and both reductions are
+    xnn_metric_auc."""
     _req(scores, torch.float32, "scores")
     _req(labels, torch.uint8, "labels")
     G, N = scores.shape
@@ -721,7 +735,7 @@ def metric_auc(scores, labels):
         if tuple(labels.shape) != (G, N):
             raise ValueError("labels: expected shape (N,) or (G,N)")
         stride = N
-    sv, perm = torch.sort(scores, dim=1, descending=True)
+    sv, perm = sort_columns(scores, descending=True)
     auroc = torch.empty(G, dtype=torch.float64, device=scores.device)
     aupr = torch.empty(G, dtype=torch.float64, device=scores.device)
     lib = _lib.load()
@@ -734,7 +748,7 @@ def metric_ranks(vals):
     """Average 1-based ranks (ties share their mean position) of every row of vals float32 (G,N) -> float64 (G,N)."""
     _req(vals, torch.float32, "vals")
     G, N = vals.shape
-    sv, perm = torch.sort(vals, dim=1)
+    sv, perm = sort_columns(vals)
     ranks = torch.empty((G, N), dtype=torch.float64, device=vals.device)
     _call("xnn_metric_ranks", _p(sv), _p(perm), N, G, _p(ranks), _stream())
     return ranks

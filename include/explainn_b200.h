@@ -441,6 +441,12 @@ int xnn_ipwm_scan_best_parts(const int8_t* codes, const long long* offsets, int 
  * "average") as double [G][N] in the original order.
  * xnn_metric_pearson_*: r double [G] of column g of x against column g of y
  * (y_stride 0 = shared y); fp64 two-pass; NaN for a constant column. */
+/* Every column of vals (G, N) sorted on its own (ascending, or descending), stable, with the int64 permutation:
+ * the sort the metric entry points below need (sklearn / scipy sort each column on the host).  One block per
+ * column, 8-bit LSD radix sort; work = xnn_sort_columns_work_bytes(N, G) bytes (16 B per element). */
+size_t xnn_sort_columns_work_bytes(long long N, int G);
+int xnn_sort_columns(const float* vals, long long N, int G, int descending, float* sorted, long long* perm,
+                     void* work, xnn_stream_t s);
 size_t xnn_metric_auc_work_bytes(long long N, int G);
 int xnn_metric_auc(const float* sorted_scores, const long long* perm, const uint8_t* labels,
                    long long label_stride, long long N, int G, double* auroc, double* aupr,

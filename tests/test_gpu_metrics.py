@@ -129,3 +129,27 @@ def test_ranks_vs_scipy_rankdata():
     r = ops.metric_ranks(torch.tensor(v).cuda()).cpu().numpy()
     for g in range(4):
         assert np.array_equal(r[g], rankdata(v[g], method="average"))
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (3, 1023), (5, 1024), (7, 1025), (37, 10007), (750, 4000)])
+def test_sort_columns_matches_torch_sort(shape):
+    """xnn_sort_columns (one block per column, stable 8-bit LSD radix sort) against torch.sort: values identical,
+    the permutation is a permutation that reproduces them, equal keys keep their original order (stability)"""
+    from explainn_b200 import ops
+    G, N = shape
+    g = torch.Generator().manual_seed(G * 1000 + N)
+    v = torch.randn(G, N, generator=g)
+    v[:, ::7] = torch.round(v[:, ::7] * 2) / 2            # many ties, including +-0
+    v[0, :min(N, 5)] = torch.tensor([0.0, -0.0, 3e38, -3e38, 1e-42])[:min(N, 5)]
+    vd = v.cuda()
+    for desc in (False, True):
+        sv, perm = ops.sort_columns(vd, descending=desc)
+        ref = torch.sort(v, dim=1, descending=desc, stable=True)
+        assert torch.equal(sv.cpu(), ref.values)
+        p = perm.cpu()
+        assert torch.equal(torch.gather(v, 1, p), ref.values)
+        assert torch.equal(torch.sort(p, dim=1).values, torch.arange(N).expand(G, N))
+        # stability: inside a run of equal values the original indices ascend (-0.0 and +0.0 are distinct keys here:
+        # compare with the bit pattern torch's stable sort would group only by value, so test value-equal AND sign-equal)
+        same = (sv.cpu()[:, 1:] == sv.cpu()[:, :-1]) & (torch.signbit(sv.cpu()[:, 1:]) == torch.signbit(sv.cpu()[:, :-1]))
+        assert bool(((p[:, 1:] > p[:, :-1]) | ~same).all())
