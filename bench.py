@@ -211,6 +211,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA-graph replay per step")
     ap.add_argument("--e2e-input", default="ascii", choices=["ascii", "float", "planes"])
     ap.add_argument("--no-aux", action="store_true", help="skip the secondary forward fields and the CPU baseline")
+    ap.add_argument("--sm-reserve", type=int, default=8,
+                    help="SMs the conv weight gradient leaves to the overlapped NCCL all-reduce (N > 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -265,7 +267,7 @@ def main():
     parallel.broadcast_parameters(model)
     crit = get_loss(kind)
     opt = get_optimizer(model.parameters(), 0.003)
-    bucket = parallel.GradBucket(model) if world > 1 else None
+    bucket = parallel.GradBucket(model, sm_reserve=args.sm_reserve) if world > 1 else None
     if args.sync_bn and world > 1:
         parallel.enable_sync_batchnorm()
     use_graph = not args.no_graph

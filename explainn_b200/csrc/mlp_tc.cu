@@ -1577,358 +1577,17 @@ mlp_bwd_kernel(MlpBwdArgs a) {
 }
 
 // ---------------------------------------------------------------------------
-// B2 on tile images.  The same three GEMMs as mlp_bwd_kernel (D1 = W1 . pool^T -> dh, D2 = W1^T . dh -> dy,
-// D3 += dh . pool -> dW1), with
+// B2 on tile images, pipelined.  The same three GEMMs as mlp_bwd_kernel (D1 = W1 . pool^T -> dh, D2 = W1^T . dh ->
+// dpool, D3 += dh . pool -> dW1), with
 //   * the pool tile and W1 fetched by bulk load (TMA) from the images F1 wrote -- no global loads, no split, no
-//     staging stores for the two big operands; the pool stage is DOUBLE-buffered (the load of tile g+2 is issued as
-//     soon as the MMAs of tile g have finished with its stage);
+//     staging stores for the two big operands; the pool stage is double-buffered;
 //   * TWO bf16 pieces per operand (hi, mid of the round-to-nearest split: x to 2^-18, unbiased) and the three
 //     products hi*hi, hi*mid, mid*hi: gradients are compared at 1e-4, not at the forward's 1e-5, and the ReLU /
 //     dropout decisions are the forward's stored bits, so nothing here can flip; half the MMAs (63 instead of 126
-//     per tile), half the shared-memory operand fetch, two thirds of the dh staging.
-// ---------------------------------------------------------------------------
-struct MbiShared {
-    uint64_t bar;          // MMA completion (lock-step)
-    uint64_t full[2];      // pool stage landed
-    uint64_t wfull;        // W1 of the current unit landed
-    uint32_t tmem_slot;
-    uint32_t pad[3];
-};
-
-__global__ void __launch_bounds__(MT_THREADS, 1)
-mlp_bwd_img_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const unsigned char* __restrict__ w1_image) {
-    extern __shared__ __align__(1024) unsigned char smem_raw[];
-    const int n = a.n, U = a.U, B = a.B, T = a.T;
-    const int Nq = (n + 15) & ~15, chunksQ = Nq >> 3, kstepsQ = Nq >> 4;
-    const uint32_t wcol = MB_WROWS * 16u;                  // 112 rows (= IMG_WROWS)
-    const uint32_t wpiece = (uint32_t)chunksQ * wcol;
-    const uint32_t pcol = MB_ROWS * 16u;
-    const uint32_t ppiece = (uint32_t)chunksQ * pcol;
-    const uint32_t tpiece = (MB_ROWS / 8) * wcol;
-    const uint32_t pstage2 = 2u * ppiece;                  // two pieces of a stage are loaded
-    const size_t img_stage = (size_t)3 * ppiece, img_w = (size_t)3 * wpiece;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    unsigned char* w1s = smem_raw;                                        // [2][chunksQ][112] uint4
-    unsigned char* ps = smem_raw + 2 * wpiece;                            // [2 stages][2][chunksQ][128] uint4
-    uint4* ts = reinterpret_cast<uint4*>(smem_raw + 2 * wpiece + 2 * pstage2);   // [2][16][112] uint4
-    unsigned char* tail = smem_raw + 2 * wpiece + 2 * pstage2 + 2 * tpiece;
-    float* s_dopre = reinterpret_cast<float*>(tail);                                     // [128]
-    uint32_t* s_mask = reinterpret_cast<uint32_t*>(tail + 512);                          // [4 words][128 batch rows]
-    MbiShared* sh = reinterpret_cast<MbiShared*>(tail + 512 + 2048);
-    uint2* s_tab = reinterpret_cast<uint2*>(tail + 512 + 2048 + 64);                     // [3 (kstepsQ + 7 + 8)]
-
-    const int row = (warp & 3) * 32 + lane;   // TMEM lane: hidden channel m (D1, D3) / pool column q (D2)
-    const int cg = warp >> 2;                 // column group: 32 of the tile's 128 batch rows
-    {
-        // the dh staging rows 100..111 and everything the garbage lanes may read must be finite: clear once
-        uint4* z = reinterpret_cast<uint4*>(smem_raw);
-        const uint32_t tot = (uint32_t)(tail - smem_raw) / 16;
-        for (uint32_t i = tid; i < tot; i += MT_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
-    }
-    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, 512);
-    if (tid == 0) {
-        umma::mbar_init(&sh->bar, 1);
-        umma::mbar_init(&sh->full[0], 1);
-        umma::mbar_init(&sh->full[1], 1);
-        umma::mbar_init(&sh->wfull, 1);
-    }
-    umma::fence_proxy_async();
-    umma::fence_before_sync();
-    __syncthreads();
-    umma::fence_after_sync();
-    const uint32_t tmem = sh->tmem_slot;
-    const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);
-    const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16);
-    const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);
-    const uint32_t D1 = tmem, D2 = tmem + MB_ROWS, D3 = tmem + 2 * MB_ROWS;
-    // the three significant products of the 2-way split, smallest first: (piece of A, piece of B)
-    //   T1 [3*kstepsQ]  D1 = W1 (K-major) x pool (K-major)            (B low word gets the stage offset added)
-    //   T3 [21]         D2 = W1^T (MN view) x dh^T (MN view)
-    //   T4 [24]         D3 += dh (K-major, K = batch rows) x pool^T (MN view)
-    const int n1 = 3 * kstepsQ, n3 = 21, n4 = 3 * (MB_ROWS / 16), ntab = n1 + n3 + n4;
-    if (tid < ntab) {
-        const int ti = tid;
-        const uint32_t w_addr = umma::smem_u32(w1s);
-        const uint32_t p_addr = umma::smem_u32(ps), t_addr = umma::smem_u32(ts);
-        const int seq = ti < n1 ? 0 : (ti < n1 + n3 ? 1 : 2);
-        const int i = ti - (seq == 0 ? 0 : (seq == 1 ? n1 : n1 + n3));
-        const int per = seq == 0 ? kstepsQ : (seq == 1 ? 7 : MB_ROWS / 16);
-        const int pass = i / per, ks = i - pass * per;
-        const uint32_t pa = pass == 0 ? 1u : 0u;
-        const uint32_t pb = pass == 1 ? 1u : 0u;
-        uint2 e;
-        if (seq == 0)
-            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)(2 * ks) * wcol, wcol),
-                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)(2 * ks) * pcol, pcol));
-        else if (seq == 1)
-            e = make_uint2(umma::desc_lo(w_addr + pa * wpiece + (uint32_t)ks * 256u, 128u),
-                           umma::desc_lo(t_addr + pb * tpiece + (uint32_t)ks * 256u, 128u));
-        else
-            e = make_uint2(umma::desc_lo(t_addr + pa * tpiece + (uint32_t)(2 * ks) * wcol, wcol),
-                           umma::desc_lo(p_addr + pb * ppiece + (uint32_t)ks * 256u, 128u));
-        s_tab[ti] = e;
-    }
-    const uint2* tab = s_tab;
-    uint64_t* bar = &sh->bar;
-
-    const long long tiles_total = (long long)U * T;
-    const long long lo = (long long)blockIdx.x * tiles_total / gridDim.x;
-    const long long hi = (long long)(blockIdx.x + 1) * tiles_total / gridDim.x;
-    const float inv_keep = 1.0f / (1.0f - a.drop_p);
-    const int C = U * MT_H;
-    const uint32_t trow = (uint32_t)((warp & 3) * 32) << 16;
-
-    // CTA order position v -> unit (unit interleave, see mlp_bwd_kernel)
-    auto unit_of = [&](int v) {
-        int u = v / a.P;
-        for (int c = 0; c < v % a.P; ++c) u += (U - c + a.P - 1) / a.P;
-        return u;
-    };
-    auto image_tile = [&](long long tile) {            // tile in CTA order -> image index u * T + t
-        return (long long)unit_of((int)(tile / T)) * T + (tile % T);
-    };
-
-    uint32_t phase = 0, wphase = 0, d3_started = 0;
-    float k0m = 0.f, k1m = 0.f, k2m = 0.f;
-    double sdb1 = 0.0;
-    float pd = 0.0f;
-    uint4 pm = make_uint4(0u, 0u, 0u, 0u);
-
-    auto prefetch_aux = [&](long long tile, int u, bool live) {
-        if (tid < MB_ROWS) {
-            const int b0 = (int)(tile % T) * MB_ROWS;
-            const bool ok = live && b0 + tid < B;
-            const long long bu = (long long)(b0 + tid) * U + u;
-            pd = ok ? __ldg(a.dopre + bu) : 0.0f;
-            pm = ok ? __ldg(reinterpret_cast<const uint4*>(a.maskbits + bu * 4)) : make_uint4(0u, 0u, 0u, 0u);
-        }
-    };
-    auto flush = [&](int v, int u) {
-        int j = blockIdx.x;
-        const long long start = (long long)v * T;
-        while (j > 0 && ((long long)j * tiles_total) / gridDim.x > start) --j;
-        const int slot = blockIdx.x - j;
-        const bool ok = row < MT_H && slot < a.slots;
-        float* o = a.part_w1 + ((long long)slot * C + (long long)u * MT_H + row) * n;
-        for (int c0 = 16 * cg; c0 < Nq; c0 += 64) {
-            uint32_t vv[16];
-            umma::tmem_ld16(D3 + trow + c0, vv);
-            umma::tmem_ld_wait();
-            if (ok) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (c0 + i < n) o[c0 + i] = d3_started ? __uint_as_float(vv[i]) : 0.0f;
-            }
-        }
-        if (ok) a.part_db1[((long long)slot * 4 + cg) * C + (long long)u * MT_H + row] = sdb1;
-        sdb1 = 0.0;
-        d3_started = 0;
-        umma::fence_before_sync();
-    };
-
-    __syncthreads();                                   // descriptor table written
-    // pool stages of the first two tiles
-    if (tid == 0) {
-        for (int g = 0; g < 2 && lo + g < hi; ++g) {
-            umma::mbar_arrive_expect_tx(&sh->full[g], pstage2);
-            umma::bulk_load(ps + (size_t)g * pstage2, image + (size_t)image_tile(lo + g) * img_stage, pstage2, &sh->full[g]);
-        }
-    }
-    long long g = 0;                                   // tile counter in CTA order
-    for (long long seg = lo; seg < hi;) {
-        const int v = (int)(seg / T);
-        const int u = unit_of(v);
-        const long long seg_end = min(hi, (long long)(v + 1) * T);
-        __syncthreads();            // the previous unit's flush is done, every MMA that read W1 has completed
-        if (tid == 0) {
-            umma::mbar_arrive_expect_tx(&sh->wfull, 2u * wpiece);
-            umma::bulk_load(w1s, w1_image + (size_t)u * img_w, 2u * wpiece, &sh->wfull);
-        }
-        {
-            // dh = gamma*invstd * (g2 - c1 - xhat*c2), xhat = (acc + b1 - mean)*invstd, g2 = act ? dopre*w2/keep : 0
-            //    = (act ? k1 * dopre : 0) + k0 + k2 * acc          (three per-channel constants, one FFMA chain)
-            const int ch = u * MT_H + row;
-            const bool ok = row < MT_H;
-            if (ok) {
-                const float b1v = a.b1[ch], w2v = a.w2[ch];
-                const float mean = (float)a.stats2[4LL * ch], invstd = (float)a.stats2[4LL * ch + 2];
-                const float gis = (float)((double)a.gamma2[ch] * a.stats2[4LL * ch + 2]);
-                const float2 cf = a.coef[ch];
-                k1m = gis * w2v * inv_keep;
-                k2m = -gis * cf.y * invstd;
-                k0m = -gis * cf.x + k2m * (b1v - mean);
-            } else {
-                k0m = k1m = k2m = 0.f;
-            }
-        }
-        prefetch_aux(seg, u, true);
-
-        for (long long tile = seg; tile < seg_end; ++tile, ++g) {
-            const int t = (int)(tile % T);
-            const int b0 = t * MB_ROWS, rows = min(MB_ROWS, B - b0);
-            const uint32_t st = (uint32_t)g & 1u;
-            if (tid < MB_ROWS) {
-                s_dopre[tid] = pd;
-                s_mask[tid] = pm.x; s_mask[MB_ROWS + tid] = pm.y; s_mask[2 * MB_ROWS + tid] = pm.z; s_mask[3 * MB_ROWS + tid] = pm.w;
-            }
-            prefetch_aux(tile + 1, u, tile + 1 < seg_end);
-            __syncthreads();
-            if (tid == 0) {
-                if (tile == seg) { umma::mbar_wait(&sh->wfull, wphase); }
-                umma::mbar_wait(&sh->full[st], (uint32_t)(g >> 1) & 1u);
-                umma::fence_after_sync();
-                umma::issue_table<false>(tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), st * (pstage2 >> 4), D1,
-                                         idesc1, 0u);
-                umma::commit(bar);
-            }
-            umma::mbar_wait(bar, phase);
-            phase ^= 1u;
-            umma::fence_after_sync();
-
-            // ---- epilogue 1: dh for (channel row, batch rows 32cg..32cg+31) -> two pieces, four 16-byte chunks each
-            {
-                uint32_t vv[2][16];
-                umma::tmem_ld16(D1 + trow + 32 * cg, vv[0]);
-                umma::tmem_ld16(D1 + trow + 32 * cg + 16, vv[1]);
-                umma::tmem_ld_wait();
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int c0 = 32 * cg + 16 * h;
-                    float dh[16];
-                    float part = 0.0f;
-                    uint32_t mk[16];
-                    float dp[16];
-#pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4) {
-                        const uint4 mq = *reinterpret_cast<const uint4*>(s_mask + (row >> 5) * MB_ROWS + c0 + 4 * q4);
-                        const float4 dq = *reinterpret_cast<const float4*>(s_dopre + c0 + 4 * q4);
-                        mk[4 * q4] = mq.x; mk[4 * q4 + 1] = mq.y; mk[4 * q4 + 2] = mq.z; mk[4 * q4 + 3] = mq.w;
-                        dp[4 * q4] = dq.x; dp[4 * q4 + 1] = dq.y; dp[4 * q4 + 2] = dq.z; dp[4 * q4 + 3] = dq.w;
-                    }
-                    const uint32_t bit = 1u << (row & 31);
-                    if (rows == MB_ROWS) {                     // every batch row of the tile is real (all but the last tile)
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float base = fmaf(k2m, __uint_as_float(vv[h][i]), k0m);
-                            const float d = (mk[i] & bit) ? fmaf(k1m, dp[i], base) : base;
-                            dh[i] = d;
-                            part += d;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float base = fmaf(k2m, __uint_as_float(vv[h][i]), k0m);
-                            float d = (mk[i] & bit) ? fmaf(k1m, dp[i], base) : base;
-                            if (c0 + i >= rows) d = 0.0f;
-                            dh[i] = d;
-                            part += d;
-                        }
-                    }
-                    sdb1 += (double)part;
-                    if (row < MB_WROWS) {
-#pragma unroll
-                        for (int gg = 0; gg < 2; ++gg) {
-                            uint32_t p0[4], p1[4];
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float x0 = dh[8 * gg + 2 * e], x1 = dh[8 * gg + 2 * e + 1];
-                                p0[e] = cvt_bf16x2_rn(x0, x1);
-                                p1[e] = cvt_bf16x2_rn(x0 - __uint_as_float(p0[e] << 16),
-                                                      x1 - __uint_as_float(p0[e] & 0xFFFF0000u));
-                            }
-                            const int chunk = (c0 >> 3) + gg;
-                            ts[chunk * MB_WROWS + row] = make_uint4(p0[0], p0[1], p0[2], p0[3]);
-                            ts[tpiece / 16 + chunk * MB_WROWS + row] = make_uint4(p1[0], p1[1], p1[2], p1[3]);
-                        }
-                    }
-                }
-            }
-            umma::fence_proxy_async();
-            umma::fence_before_sync();
-            __syncthreads();
-            if (tid == 0) {
-                umma::fence_after_sync();
-                umma::issue_table<false>(tab + n1, n3, umma::desc_hi(wcol), umma::desc_hi(wcol), 0u, D2, idesc2, 0u);
-                // T4's B operand is the pool stage (MN view): the per-stage offset goes to the B low word
-                umma::issue_table<false>(tab + n1 + n3, n4, umma::desc_hi(128u), umma::desc_hi(pcol), st * (pstage2 >> 4),
-                                         D3, idesc3, d3_started);
-                umma::commit(bar);
-            }
-            d3_started = 1;
-            // ---- epilogue 2: thread = (pool column q, 32 batch rows); dy[b,u,q] = pool[b,u,q] * D2[q][b]
-            const long long e2 = ((long long)(b0 + 32 * cg) * U + u) * n + row;
-            const long long bstride = (long long)U * n;
-            const bool full_cols = (32 * cg + 32 <= rows);   // warp-uniform: all 32 batch rows of this column group are real
-            float x[2][16];
-            if (row < n) {
-                const float* pp = a.pool + e2;
-                if (full_cols) {
-#pragma unroll
-                    for (int h = 0; h < 2; ++h)
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) { x[h][i] = __ldg(pp); pp += bstride; }
-                } else {
-#pragma unroll
-                    for (int h = 0; h < 2; ++h)
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            x[h][i] = (32 * cg + 16 * h + i < rows) ? __ldg(pp) : 0.0f;
-                            pp += bstride;
-                        }
-                }
-            }
-            umma::mbar_wait(bar, phase);
-            phase ^= 1u;
-            umma::fence_after_sync();
-            // every MMA that read pool stage st has completed: fetch the tile after the next into it
-            if (tid == 0 && lo + g + 2 < hi) {
-                umma::mbar_arrive_expect_tx(&sh->full[st], pstage2);
-                umma::bulk_load(ps + (size_t)st * pstage2, image + (size_t)image_tile(lo + g + 2) * img_stage, pstage2,
-                                &sh->full[st]);
-            }
-            if (32 * cg < rows) {
-                uint32_t vv[2][16];
-                umma::tmem_ld16(D2 + trow + 32 * cg, vv[0]);
-                umma::tmem_ld16(D2 + trow + 32 * cg + 16, vv[1]);
-                umma::tmem_ld_wait();
-                if (row < n) {
-                    float* dp2 = a.dy + e2;
-                    if (full_cols) {
-#pragma unroll
-                        for (int h = 0; h < 2; ++h)
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) { *dp2 = x[h][i] * __uint_as_float(vv[h][i]); dp2 += bstride; }
-                    } else {
-#pragma unroll
-                        for (int h = 0; h < 2; ++h)
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) {
-                                if (32 * cg + 16 * h + i < rows) *dp2 = x[h][i] * __uint_as_float(vv[h][i]);
-                                dp2 += bstride;
-                            }
-                    }
-                }
-            }
-        }
-        if (tid == 0) wphase ^= 1u;
-        flush(v, u);
-        seg = seg_end;
-    }
-    umma::fence_before_sync();
-    __syncthreads();
-    if (warp == 0) umma::tmem_dealloc(sh->tmem_slot, 512);
-}
-
-static size_t mbi_smem(int n) {
-    const size_t chunksQ = (size_t)(((n + 15) & ~15) >> 3);
-    const size_t wcol = MB_WROWS * 16;
-    return 2 * chunksQ * wcol + 2 * 2 * chunksQ * MB_ROWS * 16 + 2 * (MB_ROWS / 8) * wcol + 512 + 2048 + 64 + 64 * 8 + 16;
-}
-
-// ---------------------------------------------------------------------------
-// B2 on tile images, PIPELINED.  mlp_bwd_img_kernel runs its phases in lock-step (T1 -> dh epilogue -> T3/T4 -> dy
-// epilogue, every warp in every phase): 24 % tensor-pipe active, 42 % issue-active, the rest is waiting at the two
-// barriers of a tile.  Here the phases of neighbouring tiles overlap:
+//     per tile), half the shared-memory operand fetch, two thirds of the dh staging;
+//   * the phases of neighbouring tiles overlapped (a lock-step version of this kernel -- every warp in every phase:
+//     T1 -> dh epilogue -> T3/T4 -> dy epilogue -- measured 0.53 ms with 24 % tensor-pipe active, this one 0.38 ms
+//     with 37 %):
 //   warps 0-11   E1: dh of tile g out of D1 (three warps per TMEM lane quarter, 16-column chunks k, k+3, k+6),
 //                staged as two bf16 pieces; the unit's dW1 read-out (D3) at a unit boundary
 //   warps 12-15  E2: dpool of tile g-1 out of D2[(g-1) & 1] (thread = pool column, all 128 batch rows in four
