@@ -211,7 +211,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA-graph replay per step")
     ap.add_argument("--e2e-input", default="ascii", choices=["ascii", "float", "planes"])
     ap.add_argument("--no-aux", action="store_true", help="skip the secondary forward fields and the CPU baseline")
-    ap.add_argument("--sm-reserve", type=int, default=8,
+    ap.add_argument("--sm-reserve", type=int, default=4,
                     help="SMs the conv weight gradient leaves to the overlapped NCCL all-reduce (N > 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -50,7 +50,7 @@ class GradBucket:
 
     Works for any list of parameters too (`GradBucket(params)`): then it is the plain pack -> all-reduce -> unpack."""
 
-    def __init__(self, model_or_params, group=None, overlap=True, sm_reserve=8):
+    def __init__(self, model_or_params, group=None, overlap=True, sm_reserve=4):
         self.group = group
         self.model = model_or_params if hasattr(model_or_params, "use_grad_arena") else None
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
