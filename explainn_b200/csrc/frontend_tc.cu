@@ -458,6 +458,7 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
 // ===========================================================================
 struct PwShared {
     uint64_t acc_full[2], acc_empty[2], oh_full[2], oh_empty[2];
+    uint64_t codes_full[8];        // pass 2b: the one-hot warp wrote the base codes of a sequence (ring of 8)
     uint32_t tmem_slot, pad;
     float val[2][4][TC_ROWS];      // [sequence parity][column share][row]
     int idx[2][4][TC_ROWS];
@@ -513,6 +514,41 @@ __device__ __forceinline__ float key_float(uint32_t k) {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
 }
 
+// Site predicate of one thread's 56 window starts (E = even, O = odd local starts of its share) as a bit mask,
+// bit pl <-> local start pl.  The common case is two compares and two predicated ORs per start, without a branch:
+// D >= Dhi is a site, D <= Dlo is not; the starts in between (within 64 ulps of the point where the fp16
+// activation crosses the threshold) are evaluated exactly afterwards -- a warp almost never has one.
+// Dhi = Dlo = NaN switches a row off (every compare false).
+__device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28], const uint32_t (&O)[28], int limit,
+                                                          float Dlo, float Dhi, float asc, float shf, float thr) {
+    uint32_t h0 = 0u, h1 = 0u, n0 = 0u, n1 = 0u;               // starts 0..31 / 32..55
+#pragma unroll
+    for (int pl = 0; pl < 56; ++pl) {
+        const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+        if (pl < 32) {
+            if (z >= Dhi) h0 |= 1u << pl;
+            if (z > Dlo) n0 |= 1u << pl;
+        } else {
+            if (z >= Dhi) h1 |= 1u << (pl - 32);
+            if (z > Dlo) n1 |= 1u << (pl - 32);
+        }
+    }
+    n0 &= ~h0; n1 &= ~h1;
+    if ((n0 | n1) != 0u) {
+#pragma unroll
+        for (int pl = 0; pl < 56; ++pl) {
+            const uint32_t bit = (pl < 32) ? (n0 >> pl) & 1u : (n1 >> (pl - 32)) & 1u;
+            if (bit) {
+                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+                if (act16_of(asc, z, shf) > thr) { if (pl < 32) h0 |= 1u << pl; else h1 |= 1u << (pl - 32); }
+            }
+        }
+    }
+    unsigned long long hit = ((unsigned long long)h1 << 32) | h0;
+    if (limit < 56) hit &= limit > 0 ? ((1ull << limit) - 1ull) : 0ull;
+    return hit;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(ScanArgs a) {
@@ -527,8 +563,8 @@ scan_tc_kernel(ScanArgs a) {
     const int pl_bytes = (3 * Wp * 4 + 15) & ~15;
     PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + pl_bytes);
     const int code_bytes = (L + 15) & ~15;
-    uint8_t* s_codes = reinterpret_cast<uint8_t*>(sh + 1);                   // [2][L] (emit): base codes 0..3 / 4 of the
-    int* s_pfm = reinterpret_cast<int*>(s_codes + 2 * code_bytes);           // sequence in the epilogue; [128][4][k]
+    uint8_t* s_codes = reinterpret_cast<uint8_t*>(sh + 1);                   // [8][L] (emit): base codes 0..3 / 4 of the
+    int* s_pfm = reinterpret_cast<int*>(s_codes + 8 * code_bytes);           // sequence in the epilogue; [128][4][k]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g0 = blockIdx.x * TC_ROWS;
@@ -550,6 +586,7 @@ scan_tc_kernel(ScanArgs a) {
             umma::mbar_init(&sh->oh_full[s], 1);
             umma::mbar_init(&sh->oh_empty[s], 2);
         }
+        for (int s = 0; s < 8; ++s) umma::mbar_init(&sh->codes_full[s], 1);
     }
     umma::fence_proxy_async();
     umma::fence_before_sync();
@@ -609,6 +646,24 @@ scan_tc_kernel(ScanArgs a) {
                 const uint32_t* sp = planes + b * 3 * Wp;
                 __syncwarp();
                 for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
+                if (MODE == SCAN_SITE_EMIT) {
+                    // base codes of the sequence for the epilogue's k-mer counts, from the planes already in shared
+                    // memory (the epilogue used to expand them itself from GLOBAL memory at the start of every
+                    // sequence, every epilogue warp waiting behind that latency).
+                    // Ring of 8: this warp is at most 4 sequences ahead of the epilogue (2 one-hot buffers + 2
+                    // accumulator stages), so slot sn & 7 is free and its barrier never more than one phase ahead.
+                    __syncwarp();
+                    const int sn = (nstr == 2) ? (v >> 1) : v;
+                    uint8_t* codes = s_codes + (sn & 7) * code_bytes;
+                    for (int i = lane; i < L; i += 32) {
+                        const int w = i >> 5;
+                        const uint32_t lo = (s_pl[w] >> lane) & 1u, hi = (s_pl[Wp + w] >> lane) & 1u,
+                                       nm = (s_pl[2 * Wp + w] >> lane) & 1u;
+                        codes[i] = (uint8_t)(nm ? 4u : (lo | (hi << 1)));
+                    }
+                    __syncwarp();
+                    if (lane == 0) umma::mbar_arrive(&sh->codes_full[sn & 7]);
+                }
             }
             if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
             __syncwarp();
@@ -656,6 +711,11 @@ scan_tc_kernel(ScanArgs a) {
         int bidx = 0x7fffffff, cnt = 0;
         int g = 0;
         for (int sq = 0; sq < nseq; ++sq) {
+            // pass 2b: the exclusive site offset of (unit, sequence) is fetched at the START of the sequence, under the
+            // MMAs -- loaded at its first use it was a dependent global load inside the emission loop of every tile
+            long long site_off = 0;
+            if (MODE == SCAN_SITE_EMIT && row < ng)
+                site_off = __ldg(a.offsets + (long long)(g0 + row) * a.n_items + (blockIdx.y + sq * ns));
             for (int strand = 0; strand < nstr; ++strand) {
                 for (int t = 0; t < ntiles; ++t, ++g) {
                     const uint32_t stage = (uint32_t)g & 1u;
@@ -675,30 +735,12 @@ scan_tc_kernel(ScanArgs a) {
                     if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
                     if (MODE == SCAN_SITE_EMIT) {
                         // hit mask of this thread's 56 starts, ascending
-                        unsigned long long mask = 0ull;
-                        if (live) {
-#pragma unroll
-                            for (int pl = 0; pl < 56; ++pl) {
-                                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
-                                bool hit = z >= Dhi;
-                                if (!hit && z > Dlo) hit = act16_of(asc, z, shf) > thr;
-                                if (hit && pl < limit) mask |= 1ull << pl;
-                            }
-                        }
+                        unsigned long long mask = live ? site_mask56(E, O, limit, Dlo, Dhi, asc, shf, thr) : 0ull;
                         const int tp = g & 1;
                         const int item = blockIdx.y + sq * ns;
-                        uint8_t* codes = s_codes + (sq & 1) * code_bytes;
+                        uint8_t* codes = s_codes + (sq & 7) * code_bytes;
                         sh->idx[tp][wq][row] = __popcll(mask);
-                        if (t == 0 && warp == 0) {                 // base codes of this sequence for the k-mer counts
-                            const long long b = a.idx ? (long long)a.idx[item] : (long long)item;
-                            const uint32_t* sp = planes + b * 3 * Wp;
-                            for (int i = lane; i < L; i += 32) {
-                                const int w = i >> 5;
-                                const uint32_t lo = (__ldg(sp + w) >> lane) & 1u, hi = (__ldg(sp + Wp + w) >> lane) & 1u,
-                                               nm = (__ldg(sp + 2 * Wp + w) >> lane) & 1u;
-                                codes[i] = (uint8_t)(nm ? 4u : (lo | (hi << 1)));
-                            }
-                        }
+                        if (t == 0 && strand == 0) umma::mbar_wait(&sh->codes_full[sq & 7], ((uint32_t)sq >> 3) & 1u);
                         epi_barrier();
                         int before = 0, total = 0;
 #pragma unroll
@@ -709,7 +751,7 @@ scan_tc_kernel(ScanArgs a) {
                         }
                         if (mask != 0ull && row < ng) {
                             const int u = g0 + row, k = a.k;
-                            long long rank = a.offsets[(long long)u * a.n_items + item] + cnt + before;
+                            long long rank = site_off + cnt + before;
                             while (mask != 0ull && rank < a.cap) {
                                 const int pl = __ffsll((long long)mask) - 1;
                                 mask &= mask - 1ull;
@@ -729,6 +771,8 @@ scan_tc_kernel(ScanArgs a) {
                             }
                         }
                         cnt += total;                              // sites at earlier starts of this sequence
+                    } else if (MODE == SCAN_SITE_COUNT) {
+                        if (live) cnt += __popcll(site_mask56(E, O, limit, Dlo, Dhi, asc, shf, thr));
                     } else if (live) {
                         const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
                         const bool full = limit >= 56;
@@ -739,10 +783,6 @@ scan_tc_kernel(ScanArgs a) {
                                 if (MODE == SCAN_SUM) acc += z;
                                 else if (MODE == SCAN_MAX_ARG) { if (z > best) { best = z; bidx = base + pl; } }
                                 else if (MODE == SCAN_MAX || MODE == SCAN_ACT_MAX) best = fmaxf(best, z);
-                                else {
-                                    if (z >= Dhi) ++cnt;
-                                    else if (z > Dlo) cnt += (act16_of(asc, z, shf) > thr) ? 1 : 0;
-                                }
                             }
                         }
                     }
@@ -798,6 +838,401 @@ scan_tc_kernel(ScanArgs a) {
         }
 }
 
+// ===========================================================================
+// Pass 2b without site records (interpret.py:423-454 keeps only the PFMs): the k-mer counts are a SECOND GEMM
+// on the one-hot buffers the scan already holds in shared memory,
+//
+//   PFM[u, 4j+c] = sum over the sites p of unit u of onehot[p+j][c] = sum_p H[u,p] . X[p, 4j+c],
+//
+// H[u,p] = 1 where start p is a site of unit u whose rank is below the cap.  X is never built: position q sits
+// 8 bytes after position q-1 in the one-hot buffer, so the even starts of a tile read through an MN-major view
+// (K row r <-> start 2r, 16 bytes apart; N chunk c <-> taps 2c, 2c+1, 16 bytes apart) ARE the Toeplitz
+// matrix, and the odd starts are the same view of the buffer shifted by one position (the pair the scan uses
+// for its odd window starts).  The epilogue turns the scan's accumulators into H -- bf16 0 / 1, two compares
+// and half a byte-permute per start, written K-major in 8-byte pieces -- and issuer warp 0 runs the PFM MMAs
+// of tile g-1 between the scan MMAs of tiles g and g+1.  The counts stay in TMEM (fp32, exact below 2^24, and
+// a unit emits at most `cap` sites) for the CTA's whole share of the list and are added to the PFM once.
+// No shared-memory atomics, no per-site loop, no CTA-wide barrier in the loop.
+//
+// TMEM: scan accumulator (one stage: the epilogue frees it right after the tcgen05.ld, and the PFM MMAs of the
+// previous tile fill the gap) in columns 0..255, PFM accumulator 128 x pad16(4k) from column 256.
+//
+// The cap: a row whose offset has reached the cap contributes nothing (its thresholds become NaN); a row with
+// room for every start of the sequence needs no ranks at all.  Only the ONE sequence per unit that crosses the
+// cap needs the rank of each site: the warps holding such a row read the other column shares of the tile
+// from TMEM as well, count the sites before their own share and trim their mask to what is left.
+// Sequences after the point where every unit of the CTA is capped are not visited at all (offsets are
+// exclusive prefix sums, so non-decreasing along the list; found by bisection at kernel start).
+// ===========================================================================
+#define PF_HCHUNKS 28                                    // 16-byte K chunks of H per tile: 14 even + 14 odd
+#define PF_HBYTES (PF_HCHUNKS * TC_ROWS * 16)            // 57344
+#define PF_COL TC_STAGE_COLS                             // first TMEM column of the PFM accumulator
+
+struct PfShared {
+    uint64_t acc_full, acc_empty;          // scan accumulator: MMAs completed / read out (16 warp arrivals)
+    uint64_t oh_full[3], oh_empty[3];      // one-hot ring: written / both issuers done with the sequence
+    uint64_t h_full[2], h_empty[2];        // H buffers: written (16 warp arrivals) / PFM MMAs of the tile completed
+    uint64_t pfm_done;                     // the last PFM MMA completed
+    uint32_t tmem_slot, pad;
+};
+
+__device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// bf16 pair (lo = a is a site, hi = b is a site) and the "needs the exact predicate" accumulator
+__device__ __forceinline__ uint32_t site_pair(uint32_t a, uint32_t b, float Dlo, float Dhi, uint32_t& near) {
+    const float za = __uint_as_float(a), zb = __uint_as_float(b);
+    const uint32_t ha = __float_as_uint(za >= Dhi ? 1.0f : 0.0f), hb = __float_as_uint(zb >= Dhi ? 1.0f : 0.0f);
+    const uint32_t na = __float_as_uint(za > Dlo ? 1.0f : 0.0f), nb = __float_as_uint(zb > Dlo ? 1.0f : 0.0f);
+    near |= (ha ^ na) | (hb ^ nb);
+    return __byte_perm(ha, hb, 0x7632);                  // 1.0f >> 16 == bf16 1.0
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+site_pfm_tc_kernel(ScanArgs a, int nh) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t* __restrict__ planes = a.planes;
+    const int L = a.L, Wp = a.Wp, Lw = a.Lw, kpad = a.kpad, Lbuf = a.Lbuf, noh = a.noh;
+    const int chunks = kpad >> 3, ksteps = kpad >> 4;
+    const uint32_t a_bytes = 3u * chunks * 2048u;
+    unsigned char* a_smem = smem_raw;
+    unsigned char* h_smem = smem_raw + a_bytes;                              // [nh][28][128] x 16 B
+    uint2* oh = reinterpret_cast<uint2*>(h_smem + (size_t)nh * PF_HBYTES);   // [noh][2][Lbuf]
+    const int pl_words = (3 * Wp + 3) & ~3;
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);   // [2][pl_words]
+    PfShared* sh = reinterpret_cast<PfShared*>(s_pl + 2 * pl_words);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g0 = blockIdx.x * TC_ROWS;
+    const int ng = min(TC_ROWS, a.R - g0);
+    const int ns = gridDim.y;
+    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
+    int nseq = (a.n_items - 1 - (int)blockIdx.y) / ns + 1;
+    {
+        // sequences from the first one at which every unit of this CTA is capped contribute nothing
+        auto all_capped = [&](int sq) -> bool {
+            bool c = true;
+            if (tid < ng)
+                c = __ldg(a.offsets + (long long)(g0 + tid) * a.n_items + (blockIdx.y + (long long)sq * ns)) >= a.cap;
+            return __syncthreads_and(c) != 0;
+        };
+        if (all_capped(nseq - 1)) {
+            if (all_capped(0)) return;
+            int lo = 0, hi = nseq - 1;                                       // all_capped: false at lo, true at hi
+            while (hi - lo > 1) {
+                const int mid = lo + ((hi - lo) >> 1);
+                if (all_capped(mid)) hi = mid; else lo = mid;
+            }
+            nseq = hi;
+        }
+    }
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(a.wsplit) +
+                                                          (size_t)blockIdx.x * a_bytes);
+        uint4* dst = reinterpret_cast<uint4*>(a_smem);
+        for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
+    }
+    if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
+    if (tid == 0) {
+        umma::mbar_init(&sh->acc_full, 2);
+        umma::mbar_init(&sh->acc_empty, TC_EPI_WARPS);
+        for (int s = 0; s < 3; ++s) {
+            umma::mbar_init(&sh->oh_full[s], 1);
+            umma::mbar_init(&sh->oh_empty[s], 2);
+        }
+        for (int s = 0; s < 2; ++s) {
+            umma::mbar_init(&sh->h_full[s], TC_EPI_WARPS);
+            umma::mbar_init(&sh->h_empty[s], 1);
+        }
+        umma::mbar_init(&sh->pfm_done, 1);
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = sh->tmem_slot;
+    const int npfm = (4 * a.k + 15) & ~15;                                   // UMMA N of the PFM GEMM
+
+    if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
+        // ================= issuer warps: scan MMAs of the even / odd window starts; warp 0 also the PFM GEMM ==========
+        const int par = warp - TC_EPI_WARPS;
+        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
+        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
+        const uint32_t hi128 = umma::desc_hi(128u);
+        const uint32_t h_lo = umma::desc_lo(umma::smem_u32(h_smem), 2048u);  // H: K-major, chunk pitch 2048, SBO 128
+        const uint32_t x_lo = umma::desc_lo(umma::smem_u32(oh), 128u);       // X: MN-major, K group pitch 128,
+        const uint32_t hi16 = umma::desc_hi(16u);                            //    N chunk pitch 16
+        const uint32_t idesc_p = umma::idesc_bf16_f32(TC_ROWS, npfm) | (1u << 16);
+        uint32_t pacc = 0;
+        // the PFM MMAs of tile tp of the sequence in one-hot slot sp, H in buffer gp % nh
+        auto issue_pfm = [&](int gp, int sp, int tp) {
+            const int hb = gp % nh;
+            umma::mbar_wait(&sh->h_full[hb], (uint32_t)(gp / nh) & 1u);
+            umma::fence_after_sync();
+            const int cnt = min(TC_TILE_POS, Lw - tp * TC_TILE_POS);
+            const uint32_t x_t = x_lo + (uint32_t)sp * (uint32_t)Lbuf + 112u * (uint32_t)tp;
+            const uint32_t h_b = h_lo + (uint32_t)hb * (uint32_t)(PF_HBYTES >> 4);
+#pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {
+                const int nk = (((cnt + 1 - p2) >> 1) + 15) >> 4;            // K steps of 16 even / odd starts
+#pragma unroll
+                for (int ks = 0; ks < 7; ++ks) {
+                    if (ks < nk) {
+                        const uint64_t ad = ((uint64_t)hi128 << 32) | (uint64_t)(h_b + (uint32_t)(p2 * 14 + 2 * ks) * 128u);
+                        const uint64_t bd = ((uint64_t)hi16 << 32) |
+                                            (uint64_t)(x_t + (uint32_t)p2 * (uint32_t)(Lbuf >> 1) + 16u * ks);
+                        umma::mma_bf16_elect(tmem + PF_COL, ad, bd, idesc_p, pacc);
+                        pacc = 1;
+                    }
+                }
+            }
+            umma::commit_elect(&sh->h_empty[hb]);
+            if (tp == ntiles - 1) umma::commit_elect(&sh->oh_empty[sp]);
+            __syncwarp();
+        };
+        int g = 0, pso = 0, pt = 0;
+        for (int v = 0; v < nseq; ++v) {
+            const int so = v % noh;
+            umma::mbar_wait(&sh->oh_full[so], (uint32_t)(v / noh) & 1u);
+            const uint32_t b_sq = b_lo + (uint32_t)so * (uint32_t)Lbuf;
+            for (int t = 0; t < ntiles; ++t, ++g) {
+                umma::mbar_wait(&sh->acc_empty, ((uint32_t)g & 1u) ^ 1u);
+                umma::fence_after_sync();
+                const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
+                const int N = (((cnt + 1) >> 1) + 15) & ~15;
+                const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
+                const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
+                const uint32_t d = tmem + (par ? TC_ODD_COL : 0);
+                uint32_t acc = 0;
+#pragma unroll
+                for (int s3 = 0; s3 < 3; ++s3) {
+#pragma unroll
+                    for (int ks = 0; ks < TC_KMAX / 4; ++ks) {
+                        if (ks < ksteps) {
+                            const uint64_t ad = ((uint64_t)hi128 << 32) |
+                                                (uint64_t)(a_lo + (uint32_t)(s3 * chunks + 2 * ks) * 128u);
+                            const uint64_t bd = ((uint64_t)hi128 << 32) | (uint64_t)(b_t + 2u * ks);
+                            umma::mma_bf16_elect(d, ad, bd, idesc, acc);
+                            acc = 1;
+                        }
+                    }
+                }
+                umma::commit_elect(&sh->acc_full);
+                if (par == 1 && t == ntiles - 1) umma::commit_elect(&sh->oh_empty[so]);
+                __syncwarp();
+                if (par == 0 && g > 0) issue_pfm(g - 1, pso, pt);
+                pso = so; pt = t;
+            }
+        }
+        if (par == 0) {
+            if (g > 0) issue_pfm(g - 1, pso, pt);
+            umma::commit_elect(&sh->pfm_done);
+        }
+    } else if (warp == TC_EPI_WARPS + 2) {
+        // ================= one-hot warp: planes of sequence v+1 in flight (cp.async) while v is expanded =================
+        auto fetch = [&](int v) {
+            const int item = blockIdx.y + v * ns;
+            const long long b = a.idx ? (long long)__ldg(a.idx + item) : (long long)item;
+            const uint32_t* sp = planes + b * 3 * Wp;
+            const uint32_t dst = umma::smem_u32(s_pl + (v & 1) * pl_words);
+            for (int i = lane; i < 3 * Wp; i += 32) cp_async4(dst + 4u * i, sp + i);
+            cp_async_commit();
+        };
+        if (nseq > 0) fetch(0);
+        for (int v = 0; v < nseq; ++v) {
+            const int so = v % noh;
+            cp_async_wait_all();
+            __syncwarp();
+            if (v + 1 < nseq) fetch(v + 1);
+            const uint32_t* pl = s_pl + (v & 1) * pl_words;
+            if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
+            __syncwarp();
+            uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
+            uint2* buf1 = buf0 + Lbuf;
+            for (int i = lane; i < Lbuf; i += 32) {
+                const uint2 x = onehot_bf16x4(pl, Wp, L, i);
+                buf0[i] = x;
+                if (i > 0) buf1[i - 1] = x;
+                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
+            }
+            umma::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
+        }
+    } else {
+        // ================= epilogue warps: accumulators -> H =================
+        const int quarter = warp & 3, wq = warp >> 2;
+        const int row = quarter * 32 + lane;
+        const bool rows_live = quarter * 32 < ng;
+        const uint32_t tq = tmem + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t tlane = tq + 28u * wq;
+        float asc = 0.0f, shf = 0.0f, thr = 0.0f;
+        float Dlo = INFINITY, Dhi = INFINITY;
+        if (row < ng) {
+            asc = fabsf(a.scale[g0 + row]);
+            shf = a.shift[g0 + row];
+            thr = a.thr[g0 + row];
+            if (act16_of(asc, -INFINITY, shf) > thr) {
+                Dlo = -INFINITY; Dhi = -INFINITY;
+            } else if (act16_of(asc, INFINITY, shf) > thr) {
+                uint32_t lo = float_key(-INFINITY), hi = float_key(INFINITY);
+                while (hi - lo > 1u) {
+                    const uint32_t mid = lo + ((hi - lo) >> 1);
+                    if (act16_of(asc, key_float(mid), shf) > thr) hi = mid; else lo = mid;
+                }
+                const uint32_t kmin = float_key(-INFINITY), kmax = float_key(INFINITY);
+                Dlo = key_float(hi - kmin > 64u ? hi - 64u : kmin);
+                Dhi = key_float(kmax - hi > 64u ? hi + 64u : kmax);
+            }
+        }
+        const float qnan = __uint_as_float(0x7FC00000u);
+        // this thread's 8-byte pieces of H: even-start index 28 wq + 4m -> chunk (28 wq + 4m) / 8, half ((7 wq + m) & 1)
+        unsigned char* hrow = h_smem + (size_t)row * 16;
+        int g = 0;
+        for (int sq = 0; sq < nseq; ++sq) {
+            long long rem = 0;                                   // sites this row may still emit
+            if (row < ng)
+                rem = a.cap - __ldg(a.offsets + (long long)(g0 + row) * a.n_items + (blockIdx.y + (long long)sq * ns));
+            const bool crossing = rem > 0 && rem < (long long)Lw; // the cap may fall inside this sequence
+            const bool any_crossing = __any_sync(0xffffffffu, crossing);
+            const float dlo = rem > 0 ? Dlo : qnan, dhi = rem > 0 ? Dhi : qnan;
+            long long seen = 0;                                  // crossing rows: sites at earlier tiles of the sequence
+            for (int t = 0; t < ntiles; ++t, ++g) {
+                umma::mbar_wait(&sh->acc_full, (uint32_t)g & 1u);
+                umma::fence_after_sync();
+                const int p0 = t * TC_TILE_POS + 56 * wq;
+                const int limit = Lw - p0;
+                const bool live = rows_live && limit > 0;
+                int before = 0, total = 0;
+                if (any_crossing && rows_live) {
+                    // ranks are needed: the sites of the other column shares of this tile, from TMEM
+#pragma unroll 1
+                    for (int s2 = 0; s2 < 4; ++s2) {
+                        const int lim2 = Lw - (t * TC_TILE_POS + 56 * s2);
+                        if (s2 == wq || lim2 <= 0) continue;
+                        uint32_t E2[28], O2[28];
+                        umma::tmem_ld28(tq + 28u * s2, E2);
+                        umma::tmem_ld28(tq + 28u * s2 + TC_ODD_COL, O2);
+                        umma::tmem_ld_wait();
+                        const int c2 = __popcll(site_mask56(E2, O2, lim2, dlo, dhi, asc, shf, thr));
+                        total += c2;
+                        if (s2 < wq) before += c2;
+                    }
+                }
+                uint32_t E[28], O[28];
+                if (live) {
+                    umma::tmem_ld28(tlane, E);
+                    umma::tmem_ld28(tlane + TC_ODD_COL, O);
+                    umma::tmem_ld_wait();
+                }
+                umma::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->acc_empty);
+
+                const int hb = g % nh;
+                if (g >= nh) umma::mbar_wait(&sh->h_empty[hb], (uint32_t)(g / nh - 1) & 1u);
+                // piece m of this thread = piece 7 wq + m of the tile's even (and, 14 chunks further, odd) starts
+                unsigned char* hbuf = hrow + (size_t)hb * PF_HBYTES;
+                auto put = [&](int m, uint32_t e0, uint32_t e1, uint32_t o0, uint32_t o1) {
+                    const int e = 7 * wq + m;
+                    unsigned char* pe = hbuf + (e >> 1) * 2048 + (e & 1) * 8;
+                    *reinterpret_cast<uint2*>(pe) = make_uint2(e0, e1);
+                    *reinterpret_cast<uint2*>(pe + 14 * 2048) = make_uint2(o0, o1);
+                };
+                uint32_t near = 0u;
+                if (live) {
+#pragma unroll
+                    for (int m = 0; m < 7; ++m) {
+                        if (limit >= 8 * m + 8) {
+                            const uint32_t e0 = site_pair(E[4 * m], E[4 * m + 1], dlo, dhi, near);
+                            const uint32_t e1 = site_pair(E[4 * m + 2], E[4 * m + 3], dlo, dhi, near);
+                            const uint32_t o0 = site_pair(O[4 * m], O[4 * m + 1], dlo, dhi, near);
+                            const uint32_t o1 = site_pair(O[4 * m + 2], O[4 * m + 3], dlo, dhi, near);
+                            put(m, e0, e1, o0, o1);
+                        } else if (limit > 8 * m) {              // the piece straddles Lw: starts >= limit compare as NaN
+                            uint32_t x[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const uint32_t z = (i & 1) ? O[4 * m + (i >> 1)] : E[4 * m + (i >> 1)];
+                                x[i] = (8 * m + i < limit) ? z : 0x7FC00000u;
+                            }
+                            const uint32_t e0 = site_pair(x[0], x[2], dlo, dhi, near);
+                            const uint32_t e1 = site_pair(x[4], x[6], dlo, dhi, near);
+                            const uint32_t o0 = site_pair(x[1], x[3], dlo, dhi, near);
+                            const uint32_t o1 = site_pair(x[5], x[7], dlo, dhi, near);
+                            put(m, e0, e1, o0, o1);
+                        } else {
+                            put(m, 0u, 0u, 0u, 0u);
+                        }
+                    }
+                } else if (rows_live) {
+#pragma unroll
+                    for (int m = 0; m < 7; ++m) put(m, 0u, 0u, 0u, 0u);
+                }
+                if (__any_sync(0xffffffffu, near != 0u || (crossing && live))) {
+                    // rare: exact predicate and / or the cap, from the bit mask; the pieces are written again
+                    unsigned long long mask = live ? site_mask56(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
+                    if (crossing) {
+                        const int own = __popcll(mask);
+                        long long room = rem - seen - before;
+                        if (room < 0) room = 0;
+                        if ((long long)own > room) {
+                            unsigned long long keep = 0ull;
+                            for (long long i = 0; i < room; ++i) {
+                                const unsigned long long b = mask & (0ull - mask);
+                                keep |= b;
+                                mask ^= b;
+                            }
+                            mask = keep;
+                        }
+                        seen += total + own;
+                    }
+                    if (live) {
+#pragma unroll
+                        for (int m = 0; m < 7; ++m) {
+                            uint32_t w4[4];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {        // q: parity * 2 + half
+                                const int pl0 = 8 * m + 4 * (q & 1) + (q >> 1);
+                                const uint32_t b0 = (uint32_t)(mask >> pl0) & 1u, b1 = (uint32_t)(mask >> (pl0 + 2)) & 1u;
+                                w4[q] = b0 * 0x3F80u + b1 * 0x3F800000u;
+                            }
+                            put(m, w4[0], w4[1], w4[2], w4[3]);
+                        }
+                    }
+                }
+                umma::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->h_full[hb]);
+            }
+        }
+        // ---- the CTA's counts: TMEM -> global PFM (U, 4, k) ----
+        umma::mbar_wait(&sh->pfm_done, 0u);
+        umma::fence_after_sync();
+        if (rows_live && nseq > 0) {
+            for (int c0 = 16 * wq; c0 < npfm; c0 += 64) {
+                uint32_t r[16];
+                umma::tmem_ld16(tq + PF_COL + (uint32_t)c0, r);
+                umma::tmem_ld_wait();
+                if (row < ng) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int n = c0 + i, j = n >> 2, c = n & 3;
+                        const int v = (int)__uint_as_float(r[i]);
+                        if (j < a.k && v != 0) atomicAdd(&a.pfm[((long long)(g0 + row) * 4 + c) * a.k + j], v);
+                    }
+                }
+            }
+        }
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
+}
+
 static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_out, bool emit = false) {
     if (w < 1 || w > TC_KMAX || L < w) return false;
     const int Lw = L - w + 1, kpad = tc_kpad(w);
@@ -807,7 +1242,7 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
     for (int noh = 2; noh >= 1; --noh) {
         const size_t plb = (size_t)((3 * Wp * 4 + 15) & ~15);
         const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + plb + sizeof(PwShared) + 16 +
-                            (emit ? 2 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * (4 * w + 1) * 4 : 0);
+                            (emit ? 8 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * (4 * w + 1) * 4 : 0);
         if (smem <= 227 * 1024) {
             if (noh_out) *noh_out = noh;
             if (Lbuf_out) *Lbuf_out = Lbuf;
@@ -815,6 +1250,27 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
             return true;
         }
     }
+    return false;
+}
+
+// shared memory of site_pfm_tc_kernel: prefers two H buffers and a one-hot ring of three (the one-hot buffer of a
+// sequence lives until the PFM MMAs of its last tile, which are issued after the scan MMAs of the NEXT tile; a
+// ring of one would deadlock)
+static bool site_pfm_fits(int L, int w, int* noh_out, int* nh_out, int* Lbuf_out, size_t* smem_out) {
+    if (w < 1 || w > TC_KMAX || L < w) return false;
+    const int Lw = L - w + 1, kpad = tc_kpad(w);
+    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
+    const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;
+    const int Wp = (L + 31) / 32, pl_words = (3 * Wp + 3) & ~3;
+    for (int nh = 2; nh >= 1; --nh)
+        for (int noh = 3; noh >= 2; --noh) {
+            const size_t smem = tc_split_bytes(w) + (size_t)nh * PF_HBYTES + (size_t)noh * 2 * Lbuf * 8 +
+                                (size_t)2 * pl_words * 4 + sizeof(PfShared) + 16;
+            if (smem <= 227 * 1024) {
+                *noh_out = noh; *nh_out = nh; *Lbuf_out = Lbuf; *smem_out = smem;
+                return true;
+            }
+        }
     return false;
 }
 
@@ -838,9 +1294,11 @@ static int launch_scan_tc(int mode, const uint32_t* planes, int n_items, const i
                           int32_t* argmax, uint32_t* amax_bits, int32_t* counts, void* work, cudaStream_t st,
                           const long long* offsets = nullptr, long long cap = 0, int32_t* pfm = nullptr,
                           int32_t* sites = nullptr, long long site_cap = 0) {
-    int noh = 0, Lbuf = 0;
+    int noh = 0, Lbuf = 0, nh = 0;
     size_t smem = 0;
-    if (!pwm_tc_fits(L, w, &noh, &Lbuf, &smem, mode == SCAN_SITE_EMIT)) return 1;
+    // pass 2b without site records: the PFM as a second GEMM (site_pfm_tc_kernel)
+    const bool pfm_gemm = mode == SCAN_SITE_EMIT && sites == nullptr && site_pfm_fits(L, w, &noh, &nh, &Lbuf, &smem);
+    if (!pfm_gemm && !pwm_tc_fits(L, w, &noh, &Lbuf, &smem, mode == SCAN_SITE_EMIT)) return 1;
     const int kpad = tc_kpad(w), mt = tc_mtiles(R);
     tc_split_weights_kernel<<<dim3(ceil_div((long long)TC_ROWS * kpad, 256), mt), 256, 0, st>>>(
         weights, scale, R, w, kpad, reinterpret_cast<__nv_bfloat16*>(work));
@@ -855,6 +1313,12 @@ static int launch_scan_tc(int mode, const uint32_t* planes, int n_items, const i
     a.wsplit = reinterpret_cast<const __nv_bfloat16*>(work); a.scale = scale; a.shift = shift; a.thr = thr;
     a.out = out; a.argmax = argmax; a.amax_bits = amax_bits; a.counts = counts;
     a.offsets = offsets; a.cap = cap; a.pfm = pfm; a.sites = sites; a.site_cap = site_cap; a.k = w;
+    if (pfm_gemm) {
+        if (cudaFuncSetAttribute(site_pfm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return -1;
+        site_pfm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(a, nh);
+        return cudaGetLastError() == cudaSuccess ? 0 : -1;
+    }
     switch (mode) {
         case SCAN_SUM: return launch_scan<SCAN_SUM>(a, grid, smem, st);
         case SCAN_MAX: return launch_scan<SCAN_MAX>(a, grid, smem, st);

@@ -210,3 +210,52 @@ class StepPipeline:
             torch.cuda.current_stream(self.device).synchronize()
         self.graph, self.static = None, None
         self.slots = [None, None]
+
+
+class PackedDataset:
+    """The training set kept PACKED in device memory ("keep data 2-bit-packed on device"): the
+    reference re-encodes and re-copies its float one-hot batch every step (train.py:266-295: 16*L bytes per sequence
+    over PCIe per step); here the whole set is packed once -- 12*ceil(L/32) bytes per sequence, 228 B at 600 bp, so
+    10^6 sequences are 228 MB of the 180 GB -- and a step takes a slice or a gathered batch of it.
+
+        ds = PackedDataset.from_ascii(seqs_uint8, targets, device)      # or .from_onehot(x_float, targets, device)
+        for planes, y in ds.batches(4096, shuffle=True, generator=g):
+            pipe.step_device(planes, y, length=ds.length)
+    """
+
+    def __init__(self, planes, targets, length):
+        self.planes, self.targets, self.length = planes, targets, int(length)
+
+    @classmethod
+    def from_ascii(cls, seqs, targets, device, chunk=1 << 16):
+        """seqs: uint8 (N, L) ASCII bases (host or device); packed on the device chunk by chunk"""
+        N, L = seqs.shape
+        planes = torch.empty((N, 3, ops.planes_words(L)), dtype=torch.int32, device=device)
+        for i in range(0, N, chunk):
+            ops.pack_ascii(seqs[i:i + chunk].to(device, non_blocking=True).contiguous(), out=planes[i:i + chunk])
+        return cls(planes, torch.as_tensor(targets, dtype=torch.float32).to(device), L)
+
+    @classmethod
+    def from_onehot(cls, x, targets, device, chunk=1 << 14):
+        """x: float32 one-hot (N, 4, L) (host or device); every column is checked to be one-hot or all-zero"""
+        N, _, L = x.shape
+        planes = torch.empty((N, 3, ops.planes_words(L)), dtype=torch.int32, device=device)
+        for i in range(0, N, chunk):
+            ops.pack_onehot(x[i:i + chunk].to(device, non_blocking=True), check=True, out=planes[i:i + chunk])
+        return cls(planes, torch.as_tensor(targets, dtype=torch.float32).to(device), L)
+
+    def __len__(self):
+        return self.planes.shape[0]
+
+    def batches(self, batch_size, shuffle=False, generator=None, drop_last=False):
+        """(planes (B,3,W) int32, targets (B,F)) device tensors; contiguous slices, or gathered rows when shuffled"""
+        N = len(self)
+        order = torch.randperm(N, device=self.planes.device, generator=generator) if shuffle else None
+        for i in range(0, N, batch_size):
+            if drop_last and i + batch_size > N:
+                break
+            if order is None:
+                yield self.planes[i:i + batch_size], self.targets[i:i + batch_size]
+            else:
+                idx = order[i:i + batch_size]
+                yield self.planes.index_select(0, idx), self.targets.index_select(0, idx)

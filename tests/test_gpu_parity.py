@@ -599,6 +599,48 @@ def test_interpret_tensor_core_passes_vs_fp32_passes(cfg):
     assert int(none.sum()) == 0 and bool((every == L - k + 1).all())
 
 
+@pytest.mark.parametrize("cfg", [(100, 19, 200, 257), (300, 19, 600, 40), (37, 11, 95, 64), (130, 24, 24, 9),
+                                 (5, 32, 300, 33), (64, 3, 500, 21)])
+def test_interpret_pfm_gemm_vs_site_records(cfg):
+    """Pass 2b without site records (the PFM as a second tcgen05 GEMM, site_pfm_tc_kernel) against the
+    site-record kernel of the same pass: the same predicate and the same cap, so the PFMs are bit-identical --
+    with the cap inside a sequence, on a sequence boundary, never reached, zero, and with carries that put whole
+    units (or every unit: the early exit) beyond it."""
+    from explainn_b200 import ops
+    Uu, k, L, B = cfg
+    g = torch.Generator().manual_seed(Uu + k)
+    cw = (torch.randn(Uu, 4, k, generator=g) * 0.3).to(DEV)
+    scale = ((torch.rand(Uu, generator=g) + 0.5) * torch.where(torch.rand(Uu, generator=g) < 0.15, -1.0, 1.0)).to(DEV)
+    shift = (torch.randn(Uu, generator=g) * 0.3).to(DEV)
+    planes = ops.pack_onehot(O.random_onehot(B, L, seed=11, n_frac=0.02).to(DEV))
+    idx = torch.arange(B - 1, -1, -3, dtype=torch.int32, device=DEV)           # a descending selection
+    for sel in (None, idx):
+        mx = ops.act_max(planes, L, cw, scale, shift, sel).cpu().numpy()
+        for frac in (0.5, 0.05):
+            thr = torch.tensor((frac * mx.astype(np.float16)).astype(np.float32), device=DEV)
+            thr[0] = -1.0                                                       # every start of unit 0 is a site
+            thr[Uu - 1] = 6.0e4                                                 # unit U-1 has none
+            cnt = ops.site_counts(planes, L, cw, scale, shift, thr, sel)
+            csum = torch.cumsum(cnt.to(torch.int64), dim=1)
+            tot = csum[:, -1]
+            assert int(tot[0]) == cnt.shape[1] * (L - k + 1) and int(tot[Uu - 1]) == 0
+            carries = [torch.zeros(Uu, dtype=torch.int64, device=DEV),
+                       torch.arange(Uu, dtype=torch.int64, device=DEV) * 7]
+            for carry in carries:
+                offs = (csum - cnt + carry[:, None]).contiguous()
+                boundary = int(csum[Uu // 2, cnt.shape[1] // 2])                 # a cap on a sequence boundary
+                for cap in (0, 1, 7, 300, boundary, int(tot.max()) // 2 + 3, 10 ** 9):
+                    sites = torch.full((Uu, 4, 2), -1, dtype=torch.int32, device=DEV)
+                    ref = ops.site_emit(planes, L, cw, scale, shift, thr, offs, cap, sel, None, sites).cpu().numpy()
+                    got = ops.site_emit(planes, L, cw, scale, shift, thr, offs, cap, sel, None, None).cpu().numpy()
+                    assert np.array_equal(got, ref), (cfg, frac, cap)
+                    exp = np.clip(np.minimum(tot.cpu().numpy() + carry.cpu().numpy(), cap) - carry.cpu().numpy(), 0, None)
+                    assert np.array_equal(got.sum(1).max(1) <= exp, np.ones(Uu, bool))
+                    if k == 1 or frac == 0.5:
+                        # column 0 of a PFM counts every emitted site whose first base is not N
+                        assert (got[:, :, 0].sum(1) <= exp).all()
+
+
 def test_interpret_sequence_shards_reproduce_the_unsharded_result():
     """contiguous shards + exclusive carries place the site cap on the same global prefix
     (both strands); the two-shard exchange is emulated in-process, the collective itself is covered by
@@ -1053,3 +1095,32 @@ def test_pwm_best_sites_cudamo_semantics():
     assert np.array_equal(strand, (~fwd_wins).astype(np.int32))
     assert np.array_equal(start, np.where(fwd_wins, f_i, r_i))
     U.assert_close(score, np.where(fwd_wins, f_s, r_s), what="best-site scores")
+
+
+def test_packed_dataset_feeds_the_pipeline():
+    """f1: the training set packed once in device memory; batches taken from it reproduce the plain loop"""
+    from explainn_b200.architectures import get_loss, get_optimizer
+    from explainn_b200.trainer import PackedDataset, StepPipeline
+    L, F, N, B = 80, 2, 96, 32
+    rng = np.random.default_rng(3)
+    codes = rng.integers(0, 4, size=(N, L))
+    asc = torch.tensor(np.frombuffer(b"ACGT", dtype=np.uint8)[codes])
+    x = torch.zeros(N, 4, L)
+    x.scatter_(1, torch.tensor(codes)[:, None, :], 1.0)
+    y = torch.randn(N, F, generator=torch.Generator().manual_seed(0))
+    ds = PackedDataset.from_ascii(asc, y, DEV)
+    ds2 = PackedDataset.from_onehot(x, y, DEV)
+    assert torch.equal(ds.planes, ds2.planes) and len(ds) == N and ds.length == L
+    m_ref = _random_model(12, 11, L, F).train().to(DEV)
+    m_ref.linears[9].p = 0.0
+    ref_losses, _ = _plain_steps(m_ref, [(x[i:i + B], y[i:i + B]) for i in range(0, N, B)])
+    m = _random_model(12, 11, L, F).train().to(DEV)
+    m.linears[9].p = 0.0
+    pipe = StepPipeline(m, get_loss("linear"), get_optimizer(m.parameters(), 0.003), graph=True)
+    got = [pipe.step_device(p, t, length=ds.length) for p, t in ds.batches(B)][1:] + [pipe.flush()]
+    U.assert_close(np.array(got), np.array(ref_losses), rtol=1e-5, what="losses from the packed data set")
+    # shuffled batches are a permutation of the rows
+    g = torch.Generator(device=DEV).manual_seed(1)
+    rows = torch.cat([p for p, _ in ds.batches(B, shuffle=True, generator=g)])
+    assert rows.shape == ds.planes.shape and not torch.equal(rows, ds.planes)
+    assert torch.equal(torch.sort(rows.view(N, -1)[:, 0]).values, torch.sort(ds.planes.view(N, -1)[:, 0]).values)
