@@ -456,8 +456,21 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
 // its index on the concatenated axis, first maximum wins) or the running sum of its 56-column share of
 // every tile, and the four column shares of a row are merged through shared memory once per sequence.
 // ===========================================================================
+// The scan kernels run SCAN_OH_WARPS one-hot warps (sequence sn is expanded by warp sn % SCAN_OH_WARPS): one warp
+// expanding every sequence bounded the whole pipeline (ncu: tensor pipe 40 % active in pass 1, whose epilogue is
+// 56 fmaxf per thread).
+#define SCAN_OH_WARPS 2
+#define SCAN_NOH_MAX 4       // one-hot ring: deep enough to hide the expansion latency of a sequence (~1 us) behind the MMAs
+#define SCAN_THREADS (32 * (TC_EPI_WARPS + 2 + SCAN_OH_WARPS))
+
+// both one-hot buffers of a sequence (x at buf0[i], x shifted by one position at buf1[i]) by one warp, four
+// positions per lane in flight
+__device__ __forceinline__ void build_onehot_pair(uint2* __restrict__ buf0, uint2* __restrict__ buf1,
+                                                  const uint32_t* __restrict__ pl, int Wp, int L, int Lbuf, int lane,
+                                                  bool rc);
+
 struct PwShared {
-    uint64_t acc_full[2], acc_empty[2], oh_full[2], oh_empty[2];
+    uint64_t acc_full[2], acc_empty[2], oh_full[SCAN_NOH_MAX], oh_empty[SCAN_NOH_MAX];
     uint64_t codes_full[8];        // pass 2b: the one-hot warp wrote the base codes of a sequence (ring of 8)
     uint32_t tmem_slot, pad;
     float val[2][4][TC_ROWS];      // [sequence parity][column share][row]
@@ -476,6 +489,28 @@ __device__ __forceinline__ uint2 onehot_rc_bf16x4(const uint32_t* __restrict__ s
         }
     }
     return v;
+}
+
+__device__ __forceinline__ void build_onehot_pair(uint2* __restrict__ buf0, uint2* __restrict__ buf1,
+                                                  const uint32_t* __restrict__ pl, int Wp, int L, int Lbuf, int lane,
+                                                  bool rc) {
+    for (int i0 = lane; i0 < Lbuf; i0 += 128) {
+        uint2 x[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = i0 + 32 * j;
+            x[j] = rc ? onehot_rc_bf16x4(pl, Wp, L, i) : onehot_bf16x4(pl, Wp, L, i);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = i0 + 32 * j;
+            if (i < Lbuf) {
+                buf0[i] = x[j];
+                if (i > 0) buf1[i - 1] = x[j];
+                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
+            }
+        }
+    }
 }
 
 // The same pipeline serves the interpret passes 1 and 2a (test.py:128-166, interpret.py:363-421): rows are
@@ -502,6 +537,12 @@ struct ScanArgs {
     uint32_t* amax_bits; int32_t* counts;                       // interpret
     const long long* offsets; long long cap; int32_t* pfm; int32_t* sites; long long site_cap; int k;   // emit
 };
+
+__device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ float act16_of(float asc, float D, float shf) {
     return __half2float(__float2half_rn(expf(fmaf(asc, D, shf))));
@@ -550,7 +591,7 @@ __device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(SCAN_THREADS, 1)
 scan_tc_kernel(ScanArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t* __restrict__ planes = a.planes;
@@ -559,9 +600,9 @@ scan_tc_kernel(ScanArgs a) {
     const uint32_t a_bytes = 3u * chunks * 2048u;
     unsigned char* a_smem = smem_raw;
     uint2* oh = reinterpret_cast<uint2*>(smem_raw + a_bytes);                // [noh][2][Lbuf]
-    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);
-    const int pl_bytes = (3 * Wp * 4 + 15) & ~15;
-    PwShared* sh = reinterpret_cast<PwShared*>(reinterpret_cast<unsigned char*>(s_pl) + pl_bytes);
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);       // [one-hot warp][2][pl_words]
+    const int pl_words = (3 * Wp + 3) & ~3;
+    PwShared* sh = reinterpret_cast<PwShared*>(s_pl + SCAN_OH_WARPS * 2 * pl_words);
     const int code_bytes = (L + 15) & ~15;
     uint8_t* s_codes = reinterpret_cast<uint8_t*>(sh + 1);                   // [8][L] (emit): base codes 0..3 / 4 of the
     int* s_pfm = reinterpret_cast<int*>(s_codes + 8 * code_bytes);           // sequence in the epilogue; [128][4][k]
@@ -570,19 +611,21 @@ scan_tc_kernel(ScanArgs a) {
     const int g0 = blockIdx.x * TC_ROWS;
     const int ng = min(TC_ROWS, a.R - g0);
     if (MODE == SCAN_SITE_EMIT)
-        for (int i = tid; i < TC_ROWS * (4 * a.k + 1); i += TC_THREADS) s_pfm[i] = 0;
+        for (int i = tid; i < TC_ROWS * (4 * a.k + 1); i += SCAN_THREADS) s_pfm[i] = 0;
     const int ns = gridDim.y;
     {
         const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(a.wsplit) +
                                                           (size_t)blockIdx.x * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
-        for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
+        for (uint32_t i = tid; i < a_bytes / 16; i += SCAN_THREADS) dst[i] = src[i];
     }
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
         for (int s = 0; s < 2; ++s) {
             umma::mbar_init(&sh->acc_full[s], 2);
             umma::mbar_init(&sh->acc_empty[s], TC_EPI_WARPS);
+        }
+        for (int s = 0; s < SCAN_NOH_MAX; ++s) {
             umma::mbar_init(&sh->oh_full[s], 1);
             umma::mbar_init(&sh->oh_empty[s], 2);
         }
@@ -599,9 +642,15 @@ scan_tc_kernel(ScanArgs a) {
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps (even / odd window starts) =================
-        const int par = warp - TC_EPI_WARPS;
-        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
-        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
+        // Every operand of the MMAs is made warp-uniform up front (shfl from lane 0) and the whole tile is issued by
+        // one elected lane: per-MMA elect.sync with descriptors built from threadIdx-derived values cost ~30
+        // instructions and ~170 cycles per MMA (R2UR / VOTEU chains), three times the tensor time of the MMA --
+        // measured with clock64: the issue loop, not the MMAs, the one-hot expansion or the epilogue, bounded all
+        // three interpret passes.
+        const uint32_t par = umma::warp_uniform((uint32_t)(warp - TC_EPI_WARPS));
+        const uint32_t a_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(a_smem), 2048u));
+        const uint32_t b_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(oh), 16u)) + par * (uint32_t)(Lbuf >> 1);
+        const uint32_t d_par = umma::warp_uniform(tmem) + (par ? TC_ODD_COL : 0);
         const uint32_t hi128 = umma::desc_hi(128u);
         int g = 0;
         for (int v = 0; v < nvs; ++v) {
@@ -612,69 +661,73 @@ scan_tc_kernel(ScanArgs a) {
                 const uint32_t stage = (uint32_t)g & 1u;
                 umma::mbar_wait(&sh->acc_empty[stage], (((uint32_t)g >> 1) & 1u) ^ 1u);
                 umma::fence_after_sync();
-                const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
-                const int N = (((cnt + 1) >> 1) + 15) & ~15;
-                const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
-                const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
-                const uint32_t d = tmem + stage * TC_STAGE_COLS + (par ? TC_ODD_COL : 0);
-                uint32_t acc = 0;
-#pragma unroll
-                for (int s3 = 0; s3 < 3; ++s3) {
-#pragma unroll
-                    for (int ks = 0; ks < TC_KMAX / 4; ++ks) {
-                        if (ks < ksteps) {
-                            const uint64_t ad = ((uint64_t)hi128 << 32) |
-                                                (uint64_t)(a_lo + (uint32_t)(s3 * chunks + 2 * ks) * 128u);
-                            const uint64_t bd = ((uint64_t)hi128 << 32) | (uint64_t)(b_t + 2u * ks);
-                            umma::mma_bf16_elect(d, ad, bd, idesc, acc);
+                if (umma::elect_one()) {
+                    const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
+                    const int N = (((cnt + 1) >> 1) + 15) & ~15;
+                    const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
+                    const uint32_t b_t = b_sq + 112u * (uint32_t)t;
+                    const uint32_t d = d_par + stage * TC_STAGE_COLS;
+                    uint32_t acc = 0;
+                    for (int s3 = 0; s3 < 3; ++s3) {
+                        uint32_t a_k = a_lo + (uint32_t)(s3 * chunks) * 128u, b_k = b_t;
+#pragma unroll 4
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma::mma_bf16(d, ((uint64_t)hi128 << 32) | (uint64_t)a_k, ((uint64_t)hi128 << 32) | (uint64_t)b_k,
+                                           idesc, acc);
                             acc = 1;
+                            a_k += 256u;
+                            b_k += 2u;
                         }
                     }
+                    umma::commit(&sh->acc_full[stage]);
+                    if (t == ntiles - 1) umma::commit(&sh->oh_empty[so]);
                 }
-                umma::commit_elect(&sh->acc_full[stage]);
-                if (t == ntiles - 1) umma::commit_elect(&sh->oh_empty[so]);
                 __syncwarp();
             }
         }
-    } else if (warp == TC_EPI_WARPS + 2) {
-        // ================= one-hot warp: x, then RC(x), of every sequence =================
-        for (int v = 0; v < nvs; ++v) {
+    } else if (warp >= TC_EPI_WARPS + 2) {
+        // ================= one-hot warps: x or RC(x) of the (sequence, strand) pairs v = ow, ow + nw, ... =================
+        // The planes of the warp's NEXT pair are in flight (cp.async) while this one is expanded.  Pairs are dealt by v,
+        // and nw <= noh: a warp then never reaches the wait for ring slot v % noh before the slot's phase of pair
+        // v - 2 noh has completed (its previous wait covered pair v - nw - noh, and pairs complete in order), so the
+        // parity wait cannot alias.
+        const int ow = warp - (TC_EPI_WARPS + 2);
+        const int nw = min(SCAN_OH_WARPS, noh);
+        uint32_t* my_pl = s_pl + ow * 2 * pl_words;
+        auto fetch = [&](int v, int q) {
+            const int item = blockIdx.y + (nstr == 2 ? (v >> 1) : v) * ns;
+            const long long b = a.idx ? (long long)__ldg(a.idx + item) : (long long)item;
+            const uint32_t* sp = planes + b * 3 * Wp;
+            const uint32_t dst = umma::smem_u32(my_pl + (q & 1) * pl_words);
+            for (int i = lane; i < 3 * Wp; i += 32) cp_async4(dst + 4u * i, sp + i);
+            cp_async_commit();
+        };
+        if (ow < nw && ow < nvs) fetch(ow, 0);
+        int q = 0;
+        for (int v = ow; ow < nw && v < nvs; v += nw, ++q) {
             const int so = v % noh, strand = (nstr == 2) ? (v & 1) : 0;
-            if (!strand) {
-                const int item = blockIdx.y + (nstr == 2 ? (v >> 1) : v) * ns;
-                const long long b = a.idx ? (long long)a.idx[item] : (long long)item;
-                const uint32_t* sp = planes + b * 3 * Wp;
-                __syncwarp();
-                for (int i = lane; i < 3 * Wp; i += 32) s_pl[i] = __ldg(sp + i);
-                if (MODE == SCAN_SITE_EMIT) {
-                    // base codes of the sequence for the epilogue's k-mer counts, from the planes already in shared
-                    // memory (the epilogue used to expand them itself from GLOBAL memory at the start of every
-                    // sequence, every epilogue warp waiting behind that latency).
-                    // Ring of 8: this warp is at most 4 sequences ahead of the epilogue (2 one-hot buffers + 2
-                    // accumulator stages), so slot sn & 7 is free and its barrier never more than one phase ahead.
-                    __syncwarp();
-                    const int sn = (nstr == 2) ? (v >> 1) : v;
-                    uint8_t* codes = s_codes + (sn & 7) * code_bytes;
-                    for (int i = lane; i < L; i += 32) {
-                        const int w = i >> 5;
-                        const uint32_t lo = (s_pl[w] >> lane) & 1u, hi = (s_pl[Wp + w] >> lane) & 1u,
-                                       nm = (s_pl[2 * Wp + w] >> lane) & 1u;
-                        codes[i] = (uint8_t)(nm ? 4u : (lo | (hi << 1)));
-                    }
-                    __syncwarp();
-                    if (lane == 0) umma::mbar_arrive(&sh->codes_full[sn & 7]);
-                }
-            }
+            const uint32_t* pl = my_pl + (q & 1) * pl_words;
+            cp_async_wait_all();
+            __syncwarp();
+            if (v + nw < nvs) fetch(v + nw, q + 1);
             if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
             __syncwarp();
-            uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
-            uint2* buf1 = buf0 + Lbuf;
-            for (int i = lane; i < Lbuf; i += 32) {
-                const uint2 x = strand ? onehot_rc_bf16x4(s_pl, Wp, L, i) : onehot_bf16x4(s_pl, Wp, L, i);
-                buf0[i] = x;
-                if (i > 0) buf1[i - 1] = x;
-                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
+            if (MODE == SCAN_SITE_EMIT) {
+                // base codes of the sequence for the epilogue's k-mer counts (one strand in this mode: v is the
+                // sequence).  Ring of 8: past the wait above the epilogue is at most 6 sequences behind (<= 4 one-hot
+                // buffers + 2 accumulator stages), so slot v & 7 is free and its barrier at most one phase ahead.
+                uint8_t* codes = s_codes + (v & 7) * code_bytes;
+                for (int i = lane; i < L; i += 32) {
+                    const int w = i >> 5;
+                    const uint32_t lo = (pl[w] >> lane) & 1u, hi = (pl[Wp + w] >> lane) & 1u,
+                                   nm = (pl[2 * Wp + w] >> lane) & 1u;
+                    codes[i] = (uint8_t)(nm ? 4u : (lo | (hi << 1)));
+                }
+                __syncwarp();
+                if (lane == 0) umma::mbar_arrive(&sh->codes_full[v & 7]);
             }
+            uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
+            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, Lbuf, lane, strand != 0);
             umma::fence_proxy_async();
             __syncwarp();
             if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
@@ -831,7 +884,7 @@ scan_tc_kernel(ScanArgs a) {
     __syncthreads();
     if (warp == 0) umma::tmem_dealloc(tmem, TC_TMEM_COLS);
     if (MODE == SCAN_SITE_EMIT)
-        for (int i = tid; i < ng * 4 * a.k; i += TC_THREADS) {
+        for (int i = tid; i < ng * 4 * a.k; i += SCAN_THREADS) {
             const int r = i / (4 * a.k), e = i - r * 4 * a.k;
             const int v = s_pfm[r * (4 * a.k + 1) + e];
             if (v) atomicAdd(&a.pfm[(long long)g0 * 4 * a.k + i], v);
@@ -870,17 +923,11 @@ scan_tc_kernel(ScanArgs a) {
 
 struct PfShared {
     uint64_t acc_full, acc_empty;          // scan accumulator: MMAs completed / read out (16 warp arrivals)
-    uint64_t oh_full[3], oh_empty[3];      // one-hot ring: written / both issuers done with the sequence
+    uint64_t oh_full[SCAN_NOH_MAX], oh_empty[SCAN_NOH_MAX];   // one-hot ring: written / both issuers done with it
     uint64_t h_full[2], h_empty[2];        // H buffers: written (16 warp arrivals) / PFM MMAs of the tile completed
     uint64_t pfm_done;                     // the last PFM MMA completed
     uint32_t tmem_slot, pad;
 };
-
-__device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // bf16 pair (lo = a is a site, hi = b is a site) and the "needs the exact predicate" accumulator
 __device__ __forceinline__ uint32_t site_pair(uint32_t a, uint32_t b, float Dlo, float Dhi, uint32_t& near) {
@@ -891,7 +938,7 @@ __device__ __forceinline__ uint32_t site_pair(uint32_t a, uint32_t b, float Dlo,
     return __byte_perm(ha, hb, 0x7632);                  // 1.0f >> 16 == bf16 1.0
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(SCAN_THREADS, 1)
 site_pfm_tc_kernel(ScanArgs a, int nh) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t* __restrict__ planes = a.planes;
@@ -902,8 +949,8 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
     unsigned char* h_smem = smem_raw + a_bytes;                              // [nh][28][128] x 16 B
     uint2* oh = reinterpret_cast<uint2*>(h_smem + (size_t)nh * PF_HBYTES);   // [noh][2][Lbuf]
     const int pl_words = (3 * Wp + 3) & ~3;
-    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);   // [2][pl_words]
-    PfShared* sh = reinterpret_cast<PfShared*>(s_pl + 2 * pl_words);
+    uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);   // [one-hot warp][2][pl_words]
+    PfShared* sh = reinterpret_cast<PfShared*>(s_pl + SCAN_OH_WARPS * 2 * pl_words);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g0 = blockIdx.x * TC_ROWS;
@@ -933,13 +980,13 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(a.wsplit) +
                                                           (size_t)blockIdx.x * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
-        for (uint32_t i = tid; i < a_bytes / 16; i += TC_THREADS) dst[i] = src[i];
+        for (uint32_t i = tid; i < a_bytes / 16; i += SCAN_THREADS) dst[i] = src[i];
     }
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
         umma::mbar_init(&sh->acc_full, 2);
         umma::mbar_init(&sh->acc_empty, TC_EPI_WARPS);
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < SCAN_NOH_MAX; ++s) {
             umma::mbar_init(&sh->oh_full[s], 1);
             umma::mbar_init(&sh->oh_empty[s], 2);
         }
@@ -958,13 +1005,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps: scan MMAs of the even / odd window starts; warp 0 also the PFM GEMM ==========
-        const int par = warp - TC_EPI_WARPS;
-        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
-        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
+        // (operands warp-uniform, one elected lane issues a whole tile: see scan_tc_kernel)
+        const uint32_t par = umma::warp_uniform((uint32_t)(warp - TC_EPI_WARPS));
+        const uint32_t tmem_u = umma::warp_uniform(tmem);
+        const uint32_t a_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(a_smem), 2048u));
+        const uint32_t b_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(oh), 16u)) + par * (uint32_t)(Lbuf >> 1);
         const uint32_t hi128 = umma::desc_hi(128u);
-        const uint32_t h_lo = umma::desc_lo(umma::smem_u32(h_smem), 2048u);  // H: K-major, chunk pitch 2048, SBO 128
-        const uint32_t x_lo = umma::desc_lo(umma::smem_u32(oh), 128u);       // X: MN-major, K group pitch 128,
-        const uint32_t hi16 = umma::desc_hi(16u);                            //    N chunk pitch 16
+        const uint32_t h_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(h_smem), 2048u));   // H: K-major, chunk pitch 2048, SBO 128
+        const uint32_t x_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(oh), 128u));        // X: MN-major, K group pitch 128,
+        const uint32_t hi16 = umma::desc_hi(16u);                                                 //    N chunk pitch 16
         const uint32_t idesc_p = umma::idesc_bf16_f32(TC_ROWS, npfm) | (1u << 16);
         uint32_t pacc = 0;
         // the PFM MMAs of tile tp of the sequence in one-hot slot sp, H in buffer gp % nh
@@ -972,25 +1021,26 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             const int hb = gp % nh;
             umma::mbar_wait(&sh->h_full[hb], (uint32_t)(gp / nh) & 1u);
             umma::fence_after_sync();
-            const int cnt = min(TC_TILE_POS, Lw - tp * TC_TILE_POS);
-            const uint32_t x_t = x_lo + (uint32_t)sp * (uint32_t)Lbuf + 112u * (uint32_t)tp;
-            const uint32_t h_b = h_lo + (uint32_t)hb * (uint32_t)(PF_HBYTES >> 4);
-#pragma unroll
-            for (int p2 = 0; p2 < 2; ++p2) {
-                const int nk = (((cnt + 1 - p2) >> 1) + 15) >> 4;            // K steps of 16 even / odd starts
-#pragma unroll
-                for (int ks = 0; ks < 7; ++ks) {
-                    if (ks < nk) {
-                        const uint64_t ad = ((uint64_t)hi128 << 32) | (uint64_t)(h_b + (uint32_t)(p2 * 14 + 2 * ks) * 128u);
-                        const uint64_t bd = ((uint64_t)hi16 << 32) |
-                                            (uint64_t)(x_t + (uint32_t)p2 * (uint32_t)(Lbuf >> 1) + 16u * ks);
-                        umma::mma_bf16_elect(tmem + PF_COL, ad, bd, idesc_p, pacc);
+            if (umma::elect_one()) {
+                const int cnt = min(TC_TILE_POS, Lw - tp * TC_TILE_POS);
+                const uint32_t x_t = x_lo + (uint32_t)sp * (uint32_t)Lbuf + 112u * (uint32_t)tp;
+                const uint32_t h_b = h_lo + (uint32_t)hb * (uint32_t)(PF_HBYTES >> 4);
+                for (int p2 = 0; p2 < 2; ++p2) {
+                    const int nk = (((cnt + 1 - p2) >> 1) + 15) >> 4;            // K steps of 16 even / odd starts
+                    uint32_t h_k = h_b + (uint32_t)(p2 * 14) * 128u, x_k = x_t + (uint32_t)p2 * (uint32_t)(Lbuf >> 1);
+#pragma unroll 4
+                    for (int ks = 0; ks < nk; ++ks) {
+                        umma::mma_bf16(tmem_u + PF_COL, ((uint64_t)hi128 << 32) | (uint64_t)h_k,
+                                       ((uint64_t)hi16 << 32) | (uint64_t)x_k, idesc_p, pacc);
                         pacc = 1;
+                        h_k += 256u;
+                        x_k += 16u;
                     }
                 }
+                umma::commit(&sh->h_empty[hb]);
+                if (tp == ntiles - 1) umma::commit(&sh->oh_empty[sp]);
             }
-            umma::commit_elect(&sh->h_empty[hb]);
-            if (tp == ntiles - 1) umma::commit_elect(&sh->oh_empty[sp]);
+            pacc = 1;
             __syncwarp();
         };
         int g = 0, pso = 0, pt = 0;
@@ -1001,27 +1051,27 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             for (int t = 0; t < ntiles; ++t, ++g) {
                 umma::mbar_wait(&sh->acc_empty, ((uint32_t)g & 1u) ^ 1u);
                 umma::fence_after_sync();
-                const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
-                const int N = (((cnt + 1) >> 1) + 15) & ~15;
-                const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
-                const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
-                const uint32_t d = tmem + (par ? TC_ODD_COL : 0);
-                uint32_t acc = 0;
-#pragma unroll
-                for (int s3 = 0; s3 < 3; ++s3) {
-#pragma unroll
-                    for (int ks = 0; ks < TC_KMAX / 4; ++ks) {
-                        if (ks < ksteps) {
-                            const uint64_t ad = ((uint64_t)hi128 << 32) |
-                                                (uint64_t)(a_lo + (uint32_t)(s3 * chunks + 2 * ks) * 128u);
-                            const uint64_t bd = ((uint64_t)hi128 << 32) | (uint64_t)(b_t + 2u * ks);
-                            umma::mma_bf16_elect(d, ad, bd, idesc, acc);
+                if (umma::elect_one()) {
+                    const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
+                    const int N = (((cnt + 1) >> 1) + 15) & ~15;
+                    const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
+                    const uint32_t b_t = b_sq + 112u * (uint32_t)t;
+                    const uint32_t d = tmem_u + (par ? TC_ODD_COL : 0);
+                    uint32_t acc = 0;
+                    for (int s3 = 0; s3 < 3; ++s3) {
+                        uint32_t a_k = a_lo + (uint32_t)(s3 * chunks) * 128u, b_k = b_t;
+#pragma unroll 4
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma::mma_bf16(d, ((uint64_t)hi128 << 32) | (uint64_t)a_k, ((uint64_t)hi128 << 32) | (uint64_t)b_k,
+                                           idesc, acc);
                             acc = 1;
+                            a_k += 256u;
+                            b_k += 2u;
                         }
                     }
+                    umma::commit(&sh->acc_full);
+                    if (par == 1 && t == ntiles - 1) umma::commit(&sh->oh_empty[so]);
                 }
-                umma::commit_elect(&sh->acc_full);
-                if (par == 1 && t == ntiles - 1) umma::commit_elect(&sh->oh_empty[so]);
                 __syncwarp();
                 if (par == 0 && g > 0) issue_pfm(g - 1, pso, pt);
                 pso = so; pt = t;
@@ -1029,35 +1079,33 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         }
         if (par == 0) {
             if (g > 0) issue_pfm(g - 1, pso, pt);
-            umma::commit_elect(&sh->pfm_done);
+            if (umma::elect_one()) umma::commit(&sh->pfm_done);
+            __syncwarp();
         }
-    } else if (warp == TC_EPI_WARPS + 2) {
-        // ================= one-hot warp: planes of sequence v+1 in flight (cp.async) while v is expanded =================
+    } else if (warp >= TC_EPI_WARPS + 2) {
+        // ================= one-hot warps: sequences v = ow, ow + 2, ...; the planes of the warp's next sequence are in
+        // flight (cp.async) while this one is expanded (2 warps <= noh: the parity waits cannot alias, see scan_tc_kernel)
+        const int ow = warp - (TC_EPI_WARPS + 2);
+        uint32_t* my_pl = s_pl + ow * 2 * pl_words;
         auto fetch = [&](int v) {
             const int item = blockIdx.y + v * ns;
             const long long b = a.idx ? (long long)__ldg(a.idx + item) : (long long)item;
             const uint32_t* sp = planes + b * 3 * Wp;
-            const uint32_t dst = umma::smem_u32(s_pl + (v & 1) * pl_words);
+            const uint32_t dst = umma::smem_u32(my_pl + ((v / SCAN_OH_WARPS) & 1) * pl_words);
             for (int i = lane; i < 3 * Wp; i += 32) cp_async4(dst + 4u * i, sp + i);
             cp_async_commit();
         };
-        if (nseq > 0) fetch(0);
-        for (int v = 0; v < nseq; ++v) {
+        if (ow < nseq) fetch(ow);
+        for (int v = ow; v < nseq; v += SCAN_OH_WARPS) {
             const int so = v % noh;
+            const uint32_t* pl = my_pl + ((v / SCAN_OH_WARPS) & 1) * pl_words;
             cp_async_wait_all();
             __syncwarp();
-            if (v + 1 < nseq) fetch(v + 1);
-            const uint32_t* pl = s_pl + (v & 1) * pl_words;
+            if (v + SCAN_OH_WARPS < nseq) fetch(v + SCAN_OH_WARPS);
             if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
             __syncwarp();
             uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
-            uint2* buf1 = buf0 + Lbuf;
-            for (int i = lane; i < Lbuf; i += 32) {
-                const uint2 x = onehot_bf16x4(pl, Wp, L, i);
-                buf0[i] = x;
-                if (i > 0) buf1[i - 1] = x;
-                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
-            }
+            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, Lbuf, lane, false);
             umma::fence_proxy_async();
             __syncwarp();
             if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
@@ -1069,12 +1117,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         const bool rows_live = quarter * 32 < ng;
         const uint32_t tq = tmem + ((uint32_t)(quarter * 32) << 16);
         const uint32_t tlane = tq + 28u * wq;
-        float asc = 0.0f, shf = 0.0f, thr = 0.0f;
+        // the exact predicate's constants are reloaded where it is evaluated (rare): three registers less in the loop
+        auto exact_consts = [&](float& asc, float& shf, float& thr) {
+            asc = shf = thr = 0.0f;
+            if (row < ng) { asc = fabsf(__ldg(a.scale + g0 + row)); shf = __ldg(a.shift + g0 + row); thr = __ldg(a.thr + g0 + row); }
+        };
         float Dlo = INFINITY, Dhi = INFINITY;
         if (row < ng) {
-            asc = fabsf(a.scale[g0 + row]);
-            shf = a.shift[g0 + row];
-            thr = a.thr[g0 + row];
+            float asc, shf, thr;
+            exact_consts(asc, shf, thr);
             if (act16_of(asc, -INFINITY, shf) > thr) {
                 Dlo = -INFINITY; Dhi = -INFINITY;
             } else if (act16_of(asc, INFINITY, shf) > thr) {
@@ -1093,13 +1144,16 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         unsigned char* hrow = h_smem + (size_t)row * 16;
         int g = 0;
         for (int sq = 0; sq < nseq; ++sq) {
-            long long rem = 0;                                   // sites this row may still emit
-            if (row < ng)
-                rem = a.cap - __ldg(a.offsets + (long long)(g0 + row) * a.n_items + (blockIdx.y + (long long)sq * ns));
-            const bool crossing = rem > 0 && rem < (long long)Lw; // the cap may fall inside this sequence
+            int rem = 0;                                         // sites this row may still emit, clamped to 0 .. Lw
+            if (row < ng) {
+                const long long r64 =
+                    a.cap - __ldg(a.offsets + (long long)(g0 + row) * a.n_items + (blockIdx.y + (long long)sq * ns));
+                rem = (int)max(0ll, min(r64, (long long)Lw));
+            }
+            const bool crossing = rem > 0 && rem < Lw;           // the cap may fall inside this sequence
             const bool any_crossing = __any_sync(0xffffffffu, crossing);
             const float dlo = rem > 0 ? Dlo : qnan, dhi = rem > 0 ? Dhi : qnan;
-            long long seen = 0;                                  // crossing rows: sites at earlier tiles of the sequence
+            int seen = 0;                                        // crossing rows: sites at earlier tiles of the sequence
             for (int t = 0; t < ntiles; ++t, ++g) {
                 umma::mbar_wait(&sh->acc_full, (uint32_t)g & 1u);
                 umma::fence_after_sync();
@@ -1109,6 +1163,8 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                 int before = 0, total = 0;
                 if (any_crossing && rows_live) {
                     // ranks are needed: the sites of the other column shares of this tile, from TMEM
+                    float asc, shf, thr;
+                    exact_consts(asc, shf, thr);
 #pragma unroll 1
                     for (int s2 = 0; s2 < 4; ++s2) {
                         const int lim2 = Lw - (t * TC_TILE_POS + 56 * s2);
@@ -1174,14 +1230,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                 }
                 if (__any_sync(0xffffffffu, near != 0u || (crossing && live))) {
                     // rare: exact predicate and / or the cap, from the bit mask; the pieces are written again
+                    float asc, shf, thr;
+                    exact_consts(asc, shf, thr);
                     unsigned long long mask = live ? site_mask56(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
                     if (crossing) {
                         const int own = __popcll(mask);
-                        long long room = rem - seen - before;
-                        if (room < 0) room = 0;
-                        if ((long long)own > room) {
+                        const int room = max(0, rem - seen - before);
+                        if (own > room) {
                             unsigned long long keep = 0ull;
-                            for (long long i = 0; i < room; ++i) {
+                            for (int i = 0; i < room; ++i) {
                                 const unsigned long long b = mask & (0ull - mask);
                                 keep |= b;
                                 mask ^= b;
@@ -1239,8 +1296,8 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
     const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
     const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;   // last tile reads up to start + 224 + kpad/4 + 2
     const int Wp = (L + 31) / 32;
-    for (int noh = 2; noh >= 1; --noh) {
-        const size_t plb = (size_t)((3 * Wp * 4 + 15) & ~15);
+    for (int noh = SCAN_NOH_MAX; noh >= 1; --noh) {
+        const size_t plb = (size_t)SCAN_OH_WARPS * 2 * ((3 * Wp + 3) & ~3) * 4;
         const size_t smem = tc_split_bytes(w) + (size_t)noh * 2 * Lbuf * 8 + plb + sizeof(PwShared) + 16 +
                             (emit ? 8 * (size_t)((L + 15) & ~15) + (size_t)TC_ROWS * (4 * w + 1) * 4 : 0);
         if (smem <= 227 * 1024) {
@@ -1253,7 +1310,7 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
     return false;
 }
 
-// shared memory of site_pfm_tc_kernel: prefers two H buffers and a one-hot ring of three (the one-hot buffer of a
+// shared memory of site_pfm_tc_kernel: prefers two H buffers and a one-hot ring of four (the one-hot buffer of a
 // sequence lives until the PFM MMAs of its last tile, which are issued after the scan MMAs of the NEXT tile; a
 // ring of one would deadlock)
 static bool site_pfm_fits(int L, int w, int* noh_out, int* nh_out, int* Lbuf_out, size_t* smem_out) {
@@ -1263,9 +1320,9 @@ static bool site_pfm_fits(int L, int w, int* noh_out, int* nh_out, int* Lbuf_out
     const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;
     const int Wp = (L + 31) / 32, pl_words = (3 * Wp + 3) & ~3;
     for (int nh = 2; nh >= 1; --nh)
-        for (int noh = 3; noh >= 2; --noh) {
+        for (int noh = SCAN_NOH_MAX; noh >= 2; --noh) {
             const size_t smem = tc_split_bytes(w) + (size_t)nh * PF_HBYTES + (size_t)noh * 2 * Lbuf * 8 +
-                                (size_t)2 * pl_words * 4 + sizeof(PfShared) + 16;
+                                (size_t)SCAN_OH_WARPS * 2 * pl_words * 4 + sizeof(PfShared) + 16;
             if (smem <= 227 * 1024) {
                 *noh_out = noh; *nh_out = nh; *Lbuf_out = Lbuf; *smem_out = smem;
                 return true;
@@ -1284,7 +1341,7 @@ template <int MODE>
 static int launch_scan(const ScanArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
     if (cudaFuncSetAttribute(scan_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return -1;
-    scan_tc_kernel<MODE><<<grid, TC_THREADS, smem, st>>>(a);
+    scan_tc_kernel<MODE><<<grid, SCAN_THREADS, smem, st>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
@@ -1316,7 +1373,7 @@ static int launch_scan_tc(int mode, const uint32_t* planes, int n_items, const i
     if (pfm_gemm) {
         if (cudaFuncSetAttribute(site_pfm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
             return -1;
-        site_pfm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(a, nh);
+        site_pfm_tc_kernel<<<grid, SCAN_THREADS, smem, st>>>(a, nh);
         return cudaGetLastError() == cudaSuccess ? 0 : -1;
     }
     switch (mode) {

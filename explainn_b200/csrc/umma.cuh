@@ -58,6 +58,22 @@ __device__ __forceinline__ void mma_bf16_elect(uint32_t d_tmem, uint64_t adesc, 
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// one lane of the (converged) warp: the body of `if (elect_one())` is a single-thread region in which
+// tcgen05.mma / tcgen05.commit issue once
+__device__ __forceinline__ bool elect_one() {
+    uint32_t p;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, q;\n\t"
+        "}\n"
+        : "=r"(p));
+    return p != 0u;
+}
+// a value every lane holds identically, in a form the compiler can keep in a uniform register
+__device__ __forceinline__ uint32_t warp_uniform(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 __device__ __forceinline__ void commit_elect(uint64_t* bar) {
     asm volatile(
         "{\n\t"
