@@ -463,11 +463,10 @@ extern "C" int xnn_frontend_fwd(const uint32_t* planes, int B, int L, int U, int
 #define SCAN_NOH_MAX 4       // one-hot ring: deep enough to hide the expansion latency of a sequence (~1 us) behind the MMAs
 #define SCAN_THREADS (32 * (TC_EPI_WARPS + 2 + SCAN_OH_WARPS))
 
-// both one-hot buffers of a sequence (x at buf0[i], x shifted by one position at buf1[i]) by one warp, four
-// positions per lane in flight
+// both one-hot buffers of a sequence (x at buf0[i], x shifted by one position at buf1[i]) by one warp; only the
+// L positions of the sequence are written, the zero tails of the ring are laid down once at kernel start
 __device__ __forceinline__ void build_onehot_pair(uint2* __restrict__ buf0, uint2* __restrict__ buf1,
-                                                  const uint32_t* __restrict__ pl, int Wp, int L, int Lbuf, int lane,
-                                                  bool rc);
+                                                  const uint32_t* __restrict__ pl, int Wp, int L, int lane, bool rc);
 
 struct PwShared {
     uint64_t acc_full[2], acc_empty[2], oh_full[SCAN_NOH_MAX], oh_empty[SCAN_NOH_MAX];
@@ -492,23 +491,26 @@ __device__ __forceinline__ uint2 onehot_rc_bf16x4(const uint32_t* __restrict__ s
 }
 
 __device__ __forceinline__ void build_onehot_pair(uint2* __restrict__ buf0, uint2* __restrict__ buf1,
-                                                  const uint32_t* __restrict__ pl, int Wp, int L, int Lbuf, int lane,
-                                                  bool rc) {
-    for (int i0 = lane; i0 < Lbuf; i0 += 128) {
-        uint2 x[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int i = i0 + 32 * j;
-            x[j] = rc ? onehot_rc_bf16x4(pl, Wp, L, i) : onehot_bf16x4(pl, Wp, L, i);
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int i = i0 + 32 * j;
-            if (i < Lbuf) {
-                buf0[i] = x[j];
-                if (i > 0) buf1[i - 1] = x[j];
-                if (i == Lbuf - 1) buf1[i] = make_uint2(0u, 0u);
+                                                  const uint32_t* __restrict__ pl, int Wp, int L, int lane, bool rc) {
+    if (!rc) {
+        // position 32 w + lane is bit `lane` of word w of each plane (lo, hi, N mask): three broadcast loads, a
+        // handful of bit operations and two stores per position
+#pragma unroll 4
+        for (int w = 0; w < Wp; ++w) {
+            const int i = 32 * w + lane;
+            const uint32_t lo = (pl[w] >> lane) & 1u, hi = (pl[Wp + w] >> lane) & 1u, nm = (pl[2 * Wp + w] >> lane) & 1u;
+            const uint32_t half = nm ? 0u : (0x3F80u << (16u * lo));          // bf16 1.0 in the lower / upper half
+            const uint2 x = make_uint2(hi ? 0u : half, hi ? half : 0u);
+            if (i < L) {
+                buf0[i] = x;
+                if (i > 0) buf1[i - 1] = x;
             }
+        }
+    } else {
+        for (int i = lane; i < L; i += 32) {
+            const uint2 x = onehot_rc_bf16x4(pl, Wp, L, i);
+            buf0[i] = x;
+            if (i > 0) buf1[i - 1] = x;
         }
     }
 }
@@ -555,11 +557,37 @@ __device__ __forceinline__ float key_float(uint32_t k) {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
 }
 
+// The site predicate fp16(exp(asc D + shf)) > thr as compares on D.  It is monotone in D up to the last-ulp
+// behaviour of expf, so: bisect (on the float order) the first D for which it holds, then evaluate it at all
+// 128 floats within 64 ulps of that point.  If it is a clean step there (false below, true from the crossing
+// on), the predicate IS "D >= Dhi" and the function returns true with Dlo the float just below Dhi.  Otherwise
+// (never seen; a threshold on +-0 is the one constructible case) it returns false with the band
+//   D >= Dhi: a site,  D <= Dlo: not a site,  in between: evaluate exactly,
+// which is also what the callers use when any row of the CTA is not exact.
+// No D satisfies the predicate: Dlo = Dhi = NaN (every compare false), also the "row switched off" value.
+__device__ __forceinline__ bool site_thresholds(float asc, float shf, float thr, float& Dlo, float& Dhi) {
+    const float qnan = __uint_as_float(0x7FC00000u);
+    if (act16_of(asc, -INFINITY, shf) > thr) { Dlo = Dhi = -INFINITY; return true; }    // every start is a site
+    if (!(act16_of(asc, INFINITY, shf) > thr)) { Dlo = Dhi = qnan; return true; }       // no start is
+    uint32_t lo = float_key(-INFINITY), hi = float_key(INFINITY);                       // predicate false at lo, true at hi
+    while (hi - lo > 1u) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (act16_of(asc, key_float(mid), shf) > thr) hi = mid; else lo = mid;
+    }
+    const uint32_t kmin = float_key(-INFINITY), kmax = float_key(INFINITY);
+    const uint32_t k0 = hi - kmin > 64u ? hi - 64u : kmin, k1 = kmax - hi > 64u ? hi + 64u : kmax;
+    bool step = true;
+    for (uint32_t kk = k0; kk <= k1; ++kk) step = step && ((act16_of(asc, key_float(kk), shf) > thr) == (kk >= hi));
+    Dhi = key_float(step ? hi : k1);
+    Dlo = key_float(step ? hi - 1u : k0);
+    return step;
+}
+
 // Site predicate of one thread's 56 window starts (E = even, O = odd local starts of its share) as a bit mask,
-// bit pl <-> local start pl.  The common case is two compares and two predicated ORs per start, without a branch:
-// D >= Dhi is a site, D <= Dlo is not; the starts in between (within 64 ulps of the point where the fp16
-// activation crosses the threshold) are evaluated exactly afterwards -- a warp almost never has one.
-// Dhi = Dlo = NaN switches a row off (every compare false).
+// bit pl <-> local start pl.  EXACT (every row of the CTA has a clean step): one compare and one predicated OR
+// per start.  Otherwise two of each, without a branch, and the starts inside the band are evaluated exactly
+// afterwards -- a warp almost never has one.
+template <bool EXACT>
 __device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28], const uint32_t (&O)[28], int limit,
                                                           float Dlo, float Dhi, float asc, float shf, float thr) {
     uint32_t h0 = 0u, h1 = 0u, n0 = 0u, n1 = 0u;               // starts 0..31 / 32..55
@@ -568,20 +596,22 @@ __device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28
         const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
         if (pl < 32) {
             if (z >= Dhi) h0 |= 1u << pl;
-            if (z > Dlo) n0 |= 1u << pl;
+            if (!EXACT && z > Dlo) n0 |= 1u << pl;
         } else {
             if (z >= Dhi) h1 |= 1u << (pl - 32);
-            if (z > Dlo) n1 |= 1u << (pl - 32);
+            if (!EXACT && z > Dlo) n1 |= 1u << (pl - 32);
         }
     }
-    n0 &= ~h0; n1 &= ~h1;
-    if ((n0 | n1) != 0u) {
+    if (!EXACT) {
+        n0 &= ~h0; n1 &= ~h1;
+        if ((n0 | n1) != 0u) {
 #pragma unroll
-        for (int pl = 0; pl < 56; ++pl) {
-            const uint32_t bit = (pl < 32) ? (n0 >> pl) & 1u : (n1 >> (pl - 32)) & 1u;
-            if (bit) {
-                const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
-                if (act16_of(asc, z, shf) > thr) { if (pl < 32) h0 |= 1u << pl; else h1 |= 1u << (pl - 32); }
+            for (int pl = 0; pl < 56; ++pl) {
+                const uint32_t bit = (pl < 32) ? (n0 >> pl) & 1u : (n1 >> (pl - 32)) & 1u;
+                if (bit) {
+                    const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
+                    if (act16_of(asc, z, shf) > thr) { if (pl < 32) h0 |= 1u << pl; else h1 |= 1u << (pl - 32); }
+                }
             }
         }
     }
@@ -618,6 +648,7 @@ scan_tc_kernel(ScanArgs a) {
                                                           (size_t)blockIdx.x * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
         for (uint32_t i = tid; i < a_bytes / 16; i += SCAN_THREADS) dst[i] = src[i];
+        for (int i = tid; i < noh * 2 * Lbuf; i += SCAN_THREADS) oh[i] = make_uint2(0u, 0u);   // the zero tails stay
     }
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
@@ -630,6 +661,7 @@ scan_tc_kernel(ScanArgs a) {
             umma::mbar_init(&sh->oh_empty[s], 2);
         }
         for (int s = 0; s < 8; ++s) umma::mbar_init(&sh->codes_full[s], 1);
+        sh->pad = 0u;                                          // set by a row whose site predicate is not a clean step
     }
     umma::fence_proxy_async();
     umma::fence_before_sync();
@@ -727,7 +759,7 @@ scan_tc_kernel(ScanArgs a) {
                 if (lane == 0) umma::mbar_arrive(&sh->codes_full[v & 7]);
             }
             uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
-            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, Lbuf, lane, strand != 0);
+            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, lane, strand != 0);
             umma::fence_proxy_async();
             __syncwarp();
             if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
@@ -740,25 +772,19 @@ scan_tc_kernel(ScanArgs a) {
         const uint32_t tlane = tmem + ((uint32_t)(quarter * 32) << 16) + 28u * wq;
         constexpr bool INTERP = (MODE >= SCAN_ACT_MAX);
         float asc = 0.0f, shf = 0.0f, thr = 0.0f;
-        float Dlo = INFINITY, Dhi = INFINITY;      // SITE_COUNT: D >= Dhi is a site, D <= Dlo is not, between: evaluate
+        float Dlo = __uint_as_float(0x7FC00000u), Dhi = Dlo;   // site passes: see site_thresholds (NaN: no site)
+        bool all_exact = true;
         if (INTERP && row < ng) {
             asc = fabsf(a.scale[g0 + row]);
             shf = a.shift[g0 + row];
             if (MODE == SCAN_SITE_COUNT || MODE == SCAN_SITE_EMIT) {
                 thr = a.thr[g0 + row];
-                if (act16_of(asc, -INFINITY, shf) > thr) {
-                    Dlo = -INFINITY; Dhi = -INFINITY;                      // every start is a site
-                } else if (act16_of(asc, INFINITY, shf) > thr) {
-                    uint32_t lo = float_key(-INFINITY), hi = float_key(INFINITY);   // predicate false at lo, true at hi
-                    while (hi - lo > 1u) {
-                        const uint32_t mid = lo + ((hi - lo) >> 1);
-                        if (act16_of(asc, key_float(mid), shf) > thr) hi = mid; else lo = mid;
-                    }
-                    const uint32_t kmin = float_key(-INFINITY), kmax = float_key(INFINITY);
-                    Dlo = key_float(hi - kmin > 64u ? hi - 64u : kmin);
-                    Dhi = key_float(kmax - hi > 64u ? hi + 64u : kmax);
-                }
+                if (!site_thresholds(asc, shf, thr, Dlo, Dhi)) sh->pad = 1u;
             }
+        }
+        if (MODE == SCAN_SITE_COUNT || MODE == SCAN_SITE_EMIT) {
+            epi_barrier();
+            all_exact = sh->pad == 0u;                         // CTA-uniform: one compare per start
         }
         float best = -INFINITY, acc = 0.0f;
         int bidx = 0x7fffffff, cnt = 0;
@@ -788,7 +814,9 @@ scan_tc_kernel(ScanArgs a) {
                     if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
                     if (MODE == SCAN_SITE_EMIT) {
                         // hit mask of this thread's 56 starts, ascending
-                        unsigned long long mask = live ? site_mask56(E, O, limit, Dlo, Dhi, asc, shf, thr) : 0ull;
+                        unsigned long long mask = !live ? 0ull
+                                                  : all_exact ? site_mask56<true>(E, O, limit, Dlo, Dhi, asc, shf, thr)
+                                                              : site_mask56<false>(E, O, limit, Dlo, Dhi, asc, shf, thr);
                         const int tp = g & 1;
                         const int item = blockIdx.y + sq * ns;
                         uint8_t* codes = s_codes + (sq & 7) * code_bytes;
@@ -825,7 +853,9 @@ scan_tc_kernel(ScanArgs a) {
                         }
                         cnt += total;                              // sites at earlier starts of this sequence
                     } else if (MODE == SCAN_SITE_COUNT) {
-                        if (live) cnt += __popcll(site_mask56(E, O, limit, Dlo, Dhi, asc, shf, thr));
+                        if (live)
+                            cnt += __popcll(all_exact ? site_mask56<true>(E, O, limit, Dlo, Dhi, asc, shf, thr)
+                                                      : site_mask56<false>(E, O, limit, Dlo, Dhi, asc, shf, thr));
                     } else if (live) {
                         const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
                         const bool full = limit >= 56;
@@ -929,13 +959,46 @@ struct PfShared {
     uint32_t tmem_slot, pad;
 };
 
-// bf16 pair (lo = a is a site, hi = b is a site) and the "needs the exact predicate" accumulator
+// bf16 pair (lo = a is a site, hi = b is a site); !EXACT: also the "needs the exact predicate" accumulator
+template <bool EXACT>
 __device__ __forceinline__ uint32_t site_pair(uint32_t a, uint32_t b, float Dlo, float Dhi, uint32_t& near) {
     const float za = __uint_as_float(a), zb = __uint_as_float(b);
     const uint32_t ha = __float_as_uint(za >= Dhi ? 1.0f : 0.0f), hb = __float_as_uint(zb >= Dhi ? 1.0f : 0.0f);
-    const uint32_t na = __float_as_uint(za > Dlo ? 1.0f : 0.0f), nb = __float_as_uint(zb > Dlo ? 1.0f : 0.0f);
-    near |= (ha ^ na) | (hb ^ nb);
+    if (!EXACT) {
+        const uint32_t na = __float_as_uint(za > Dlo ? 1.0f : 0.0f), nb = __float_as_uint(zb > Dlo ? 1.0f : 0.0f);
+        near |= (ha ^ na) | (hb ^ nb);
+    }
     return __byte_perm(ha, hb, 0x7632);                  // 1.0f >> 16 == bf16 1.0
+}
+
+// the seven 8-byte pieces (per parity) of one thread's share of H, handed to put(m, even lo, even hi, odd lo, odd hi)
+template <bool EXACT, typename Put>
+__device__ __forceinline__ void pfm_pieces(const uint32_t (&E)[28], const uint32_t (&O)[28], int limit, float dlo,
+                                           float dhi, uint32_t& near, Put put) {
+#pragma unroll
+    for (int m = 0; m < 7; ++m) {
+        if (limit >= 8 * m + 8) {
+            const uint32_t e0 = site_pair<EXACT>(E[4 * m], E[4 * m + 1], dlo, dhi, near);
+            const uint32_t e1 = site_pair<EXACT>(E[4 * m + 2], E[4 * m + 3], dlo, dhi, near);
+            const uint32_t o0 = site_pair<EXACT>(O[4 * m], O[4 * m + 1], dlo, dhi, near);
+            const uint32_t o1 = site_pair<EXACT>(O[4 * m + 2], O[4 * m + 3], dlo, dhi, near);
+            put(m, e0, e1, o0, o1);
+        } else if (limit > 8 * m) {                      // the piece straddles Lw: starts >= limit compare as NaN
+            uint32_t x[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t z = (i & 1) ? O[4 * m + (i >> 1)] : E[4 * m + (i >> 1)];
+                x[i] = (8 * m + i < limit) ? z : 0x7FC00000u;
+            }
+            const uint32_t e0 = site_pair<EXACT>(x[0], x[2], dlo, dhi, near);
+            const uint32_t e1 = site_pair<EXACT>(x[4], x[6], dlo, dhi, near);
+            const uint32_t o0 = site_pair<EXACT>(x[1], x[3], dlo, dhi, near);
+            const uint32_t o1 = site_pair<EXACT>(x[5], x[7], dlo, dhi, near);
+            put(m, e0, e1, o0, o1);
+        } else {
+            put(m, 0u, 0u, 0u, 0u);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS, 1)
@@ -981,6 +1044,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                                                           (size_t)blockIdx.x * a_bytes);
         uint4* dst = reinterpret_cast<uint4*>(a_smem);
         for (uint32_t i = tid; i < a_bytes / 16; i += SCAN_THREADS) dst[i] = src[i];
+        for (int i = tid; i < noh * 2 * Lbuf; i += SCAN_THREADS) oh[i] = make_uint2(0u, 0u);   // the zero tails stay
     }
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
@@ -995,6 +1059,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             umma::mbar_init(&sh->h_empty[s], 1);
         }
         umma::mbar_init(&sh->pfm_done, 1);
+        sh->pad = 0u;                                          // set by a row whose site predicate is not a clean step
     }
     umma::fence_proxy_async();
     umma::fence_before_sync();
@@ -1105,7 +1170,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             if (v >= noh) umma::mbar_wait(&sh->oh_empty[so], (uint32_t)(v / noh - 1) & 1u);
             __syncwarp();
             uint2* buf0 = oh + (size_t)so * 2 * Lbuf;
-            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, Lbuf, lane, false);
+            build_onehot_pair(buf0, buf0 + Lbuf, pl, Wp, L, lane, false);
             umma::fence_proxy_async();
             __syncwarp();
             if (lane == 0) umma::mbar_arrive(&sh->oh_full[so]);
@@ -1122,24 +1187,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             asc = shf = thr = 0.0f;
             if (row < ng) { asc = fabsf(__ldg(a.scale + g0 + row)); shf = __ldg(a.shift + g0 + row); thr = __ldg(a.thr + g0 + row); }
         };
-        float Dlo = INFINITY, Dhi = INFINITY;
+        const float qnan = __uint_as_float(0x7FC00000u);
+        float Dlo = qnan, Dhi = qnan;
         if (row < ng) {
             float asc, shf, thr;
             exact_consts(asc, shf, thr);
-            if (act16_of(asc, -INFINITY, shf) > thr) {
-                Dlo = -INFINITY; Dhi = -INFINITY;
-            } else if (act16_of(asc, INFINITY, shf) > thr) {
-                uint32_t lo = float_key(-INFINITY), hi = float_key(INFINITY);
-                while (hi - lo > 1u) {
-                    const uint32_t mid = lo + ((hi - lo) >> 1);
-                    if (act16_of(asc, key_float(mid), shf) > thr) hi = mid; else lo = mid;
-                }
-                const uint32_t kmin = float_key(-INFINITY), kmax = float_key(INFINITY);
-                Dlo = key_float(hi - kmin > 64u ? hi - 64u : kmin);
-                Dhi = key_float(kmax - hi > 64u ? hi + 64u : kmax);
-            }
+            if (!site_thresholds(asc, shf, thr, Dlo, Dhi)) sh->pad = 1u;
         }
-        const float qnan = __uint_as_float(0x7FC00000u);
+        epi_barrier();
+        const bool all_exact = sh->pad == 0u;                    // CTA-uniform: one compare per start, no band
         // this thread's 8-byte pieces of H: even-start index 28 wq + 4m -> chunk (28 wq + 4m) / 8, half ((7 wq + m) & 1)
         unsigned char* hrow = h_smem + (size_t)row * 16;
         int g = 0;
@@ -1173,7 +1229,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                         umma::tmem_ld28(tq + 28u * s2, E2);
                         umma::tmem_ld28(tq + 28u * s2 + TC_ODD_COL, O2);
                         umma::tmem_ld_wait();
-                        const int c2 = __popcll(site_mask56(E2, O2, lim2, dlo, dhi, asc, shf, thr));
+                        const int c2 = __popcll(site_mask56<false>(E2, O2, lim2, dlo, dhi, asc, shf, thr));
                         total += c2;
                         if (s2 < wq) before += c2;
                     }
@@ -1200,30 +1256,8 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                 };
                 uint32_t near = 0u;
                 if (live) {
-#pragma unroll
-                    for (int m = 0; m < 7; ++m) {
-                        if (limit >= 8 * m + 8) {
-                            const uint32_t e0 = site_pair(E[4 * m], E[4 * m + 1], dlo, dhi, near);
-                            const uint32_t e1 = site_pair(E[4 * m + 2], E[4 * m + 3], dlo, dhi, near);
-                            const uint32_t o0 = site_pair(O[4 * m], O[4 * m + 1], dlo, dhi, near);
-                            const uint32_t o1 = site_pair(O[4 * m + 2], O[4 * m + 3], dlo, dhi, near);
-                            put(m, e0, e1, o0, o1);
-                        } else if (limit > 8 * m) {              // the piece straddles Lw: starts >= limit compare as NaN
-                            uint32_t x[8];
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const uint32_t z = (i & 1) ? O[4 * m + (i >> 1)] : E[4 * m + (i >> 1)];
-                                x[i] = (8 * m + i < limit) ? z : 0x7FC00000u;
-                            }
-                            const uint32_t e0 = site_pair(x[0], x[2], dlo, dhi, near);
-                            const uint32_t e1 = site_pair(x[4], x[6], dlo, dhi, near);
-                            const uint32_t o0 = site_pair(x[1], x[3], dlo, dhi, near);
-                            const uint32_t o1 = site_pair(x[5], x[7], dlo, dhi, near);
-                            put(m, e0, e1, o0, o1);
-                        } else {
-                            put(m, 0u, 0u, 0u, 0u);
-                        }
-                    }
+                    if (all_exact) pfm_pieces<true>(E, O, limit, dlo, dhi, near, put);
+                    else pfm_pieces<false>(E, O, limit, dlo, dhi, near, put);
                 } else if (rows_live) {
 #pragma unroll
                     for (int m = 0; m < 7; ++m) put(m, 0u, 0u, 0u, 0u);
@@ -1232,7 +1266,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                     // rare: exact predicate and / or the cap, from the bit mask; the pieces are written again
                     float asc, shf, thr;
                     exact_consts(asc, shf, thr);
-                    unsigned long long mask = live ? site_mask56(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
+                    unsigned long long mask = live ? site_mask56<false>(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
                     if (crossing) {
                         const int own = __popcll(mask);
                         const int room = max(0, rem - seen - before);
