@@ -115,12 +115,15 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
 
     if (warp == BT_PRODUCERS / 32) {
         // ================= issuer warp =================
-        // every lane runs the loop and waits on the barriers (a lone lane spinning while its 31 siblings sit
-        // at the closing __syncthreads is a divergent warp, and MMAs issued under `if (lane == 0)` are wrapped by
-        // the compiler in ~25-instruction election/waterfall sequences each); elect.sync picks the issuing lane.
+        // every lane runs the loop and waits on the barriers; the MMAs of a tile are issued by ONE elected lane from
+        // operands made warp-uniform up front (shfl from lane 0), so the descriptor arithmetic runs in the uniform
+        // datapath: ~5 instructions per MMA.  (Per-MMA elect.sync on descriptors derived from threadIdx cost ~30
+        // instructions and ~170 cycles per MMA in R2UR / VOTEU chains; under a plain `if (lane == 0)` the compiler
+        // wraps every MMA in a waterfall loop.)
         const uint32_t idesc = umma::idesc_bf16_f32(BT_ROWS, npad) | (1u << 16);   // B is MN-major
-        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(g_smem), BT_LBO_A);
-        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), b_lbo);
+        const uint32_t a_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(g_smem), BT_LBO_A));
+        const uint32_t b_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(oh), b_lbo));
+        const uint32_t tmem_u = umma::warp_uniform(tmem);
         const uint32_t a_hi = umma::desc_hi(BT_SBO_A), b_hi = umma::desc_hi(b_sbo);
         uint32_t stage = 0, use = 0, any_mma = 0;
         for (int sq = 0; sq < nseq; ++sq) {
@@ -129,26 +132,27 @@ frontend_bwd_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp
             for (int t = 0; t < ntiles; ++t) {
                 umma::mbar_wait(&sh->full[stage], use & 1u);
                 umma::fence_after_sync();
-                {
+                if (umma::elect_one()) {
                     const uint32_t a_st = a_lo + stage * (BT_STAGE_BYTES >> 4);
                     const uint32_t b_t = b_sq + 56u * (uint32_t)t;                 // 8 windows * 7 positions
                     const int ksteps = (min(BT_WIN, n - t * BT_WIN) + 1) >> 1;
+                    uint32_t acc = any_mma;
 #pragma unroll
                     for (int s3 = 0; s3 < BT_SPLITS; ++s3) {
-#pragma unroll
-                        for (int ks = 0; ks < BT_WIN / 2; ++ks) {
-                            if (ks < ksteps) {
-                                const uint64_t ad = ((uint64_t)a_hi << 32) |
-                                                    (uint64_t)(a_st + (uint32_t)(s3 * BT_PIECE_BYTES + ks * 2 * BT_LBO_A) / 16u);
-                                const uint64_t bd = ((uint64_t)b_hi << 32) | (uint64_t)(b_t + 14u * ks);
-                                umma::mma_bf16_elect(tmem, ad, bd, idesc, any_mma);
-                                any_mma = 1;
-                            }
+                        uint32_t a_k = a_st + (uint32_t)(s3 * BT_PIECE_BYTES) / 16u, b_k = b_t;
+#pragma unroll 4
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma::mma_bf16(tmem_u, ((uint64_t)a_hi << 32) | (uint64_t)a_k, ((uint64_t)b_hi << 32) | (uint64_t)b_k,
+                                           idesc, acc);
+                            acc = 1;
+                            a_k += (uint32_t)(2 * BT_LBO_A) / 16u;
+                            b_k += 14u;
                         }
                     }
-                    umma::commit_elect(&sh->empty[stage]);
-                    if (t == ntiles - 1) umma::commit_elect(&sh->oh_empty[sq & 1]);   // pair buffer may be rewritten
+                    umma::commit(&sh->empty[stage]);
+                    if (t == ntiles - 1) umma::commit(&sh->oh_empty[sq & 1]);      // pair buffer may be rewritten
                 }
+                any_mma = 1;
                 __syncwarp();
                 if (++stage == (uint32_t)nstages) { stage = 0; ++use; }
             }

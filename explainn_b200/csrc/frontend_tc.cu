@@ -200,12 +200,14 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps =================
-        // issuing one MMA costs ~20 instructions (elect, R2UR of the descriptors) against 56 cycles of tensor
-        // time: one warp cannot keep the pipe fed.  The even- and odd-position accumulators are independent
-        // chains, so each gets its own issuer warp (on different schedulers); both commit to acc_full.
-        const int par = warp - TC_EPI_WARPS;
-        const uint32_t a_lo = umma::desc_lo(umma::smem_u32(a_smem), 2048u);
-        const uint32_t b_lo = umma::desc_lo(umma::smem_u32(oh), 16u);
+        // The even- and odd-position accumulators are independent chains with their own issuer warp (on different
+        // schedulers); both commit to acc_full.  Every operand is made warp-uniform up front and ONE elected lane issues
+        // the whole tile: five uniform-datapath instructions per MMA (per-MMA elect.sync on descriptors derived from
+        // threadIdx cost ~30 instructions and ~170 cycles each -- R2UR / VOTEU chains -- three times the MMA itself).
+        const uint32_t par = umma::warp_uniform((uint32_t)(warp - TC_EPI_WARPS));
+        const uint32_t a_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(a_smem), 2048u));
+        const uint32_t b_lo = umma::warp_uniform(umma::desc_lo(umma::smem_u32(oh), 16u)) + par * (uint32_t)(Lbuf >> 1);
+        const uint32_t d_par = umma::warp_uniform(tmem) + (par ? TC_ODD_COL : 0);
         const uint32_t hi128 = umma::desc_hi(128u);
         int g = 0;
         for (int sq = 0; sq < nseq; ++sq) {
@@ -216,29 +218,27 @@ frontend_tc_kernel(const uint32_t* __restrict__ planes, int B, int L, int Wp, in
                 const uint32_t stage = (uint32_t)g & 1u;
                 umma::mbar_wait(&sh->acc_empty[stage], (((uint32_t)g >> 1) & 1u) ^ 1u);
                 umma::fence_after_sync();
-                const int wins = min(TC_WIN, n - t * TC_WIN);
-                const int N = ((((wins * XNN_POOL + 1) >> 1) + 15) & ~15);
-                const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
-                {
-                    const uint32_t b_t = b_sq + (uint32_t)par * (uint32_t)(Lbuf >> 1) + 112u * (uint32_t)t;
-                    const uint32_t d = tmem + stage * TC_STAGE_COLS + (par ? TC_ODD_COL : 0);
+                if (umma::elect_one()) {
+                    const int wins = min(TC_WIN, n - t * TC_WIN);
+                    const int N = ((((wins * XNN_POOL + 1) >> 1) + 15) & ~15);
+                    const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
+                    const uint32_t b_t = b_sq + 112u * (uint32_t)t;
+                    const uint32_t d = d_par + stage * TC_STAGE_COLS;
                     uint32_t acc = 0;
-#pragma unroll
                     for (int s3 = 0; s3 < 3; ++s3) {
-#pragma unroll
-                        for (int ks = 0; ks < TC_KMAX / 4; ++ks) {
-                            if (ks < ksteps) {
-                                const uint64_t ad = ((uint64_t)hi128 << 32) |
-                                                    (uint64_t)(a_lo + (uint32_t)(s3 * chunks + 2 * ks) * 128u);
-                                const uint64_t bd = ((uint64_t)hi128 << 32) | (uint64_t)(b_t + 2u * ks);
-                                umma::mma_bf16_elect(d, ad, bd, idesc, acc);
-                                acc = 1;
-                            }
+                        uint32_t a_k = a_lo + (uint32_t)(s3 * chunks) * 128u, b_k = b_t;
+#pragma unroll 4
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma::mma_bf16(d, ((uint64_t)hi128 << 32) | (uint64_t)a_k, ((uint64_t)hi128 << 32) | (uint64_t)b_k,
+                                           idesc, acc);
+                            acc = 1;
+                            a_k += 256u;
+                            b_k += 2u;
                         }
                     }
+                    umma::commit(&sh->acc_full[stage]);
+                    if (t == ntiles - 1) umma::commit(&sh->oh_empty[so]);
                 }
-                umma::commit_elect(&sh->acc_full[stage]);
-                if (t == ntiles - 1) umma::commit_elect(&sh->oh_empty[so]);
                 __syncwarp();
             }
         }
