@@ -583,16 +583,17 @@ __device__ __forceinline__ bool site_thresholds(float asc, float shf, float thr,
     return step;
 }
 
-// Site predicate of one thread's 56 window starts (E = even, O = odd local starts of its share) as a bit mask,
+// Site predicate of one thread's 2 NH window starts (E = even, O = odd local starts of its share) as a bit mask,
 // bit pl <-> local start pl.  EXACT (every row of the CTA has a clean step): one compare and one predicated OR
 // per start.  Otherwise two of each, without a branch, and the starts inside the band are evaluated exactly
 // afterwards -- a warp almost never has one.
-template <bool EXACT>
-__device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28], const uint32_t (&O)[28], int limit,
-                                                          float Dlo, float Dhi, float asc, float shf, float thr) {
-    uint32_t h0 = 0u, h1 = 0u, n0 = 0u, n1 = 0u;               // starts 0..31 / 32..55
+template <bool EXACT, int NH>
+__device__ __forceinline__ unsigned long long site_mask(const uint32_t (&E)[NH], const uint32_t (&O)[NH], int limit,
+                                                        float Dlo, float Dhi, float asc, float shf, float thr) {
+    constexpr int NP = 2 * NH;
+    uint32_t h0 = 0u, h1 = 0u, n0 = 0u, n1 = 0u;               // starts 0..31 / 32..NP-1
 #pragma unroll
-    for (int pl = 0; pl < 56; ++pl) {
+    for (int pl = 0; pl < NP; ++pl) {
         const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
         if (pl < 32) {
             if (z >= Dhi) h0 |= 1u << pl;
@@ -606,7 +607,7 @@ __device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28
         n0 &= ~h0; n1 &= ~h1;
         if ((n0 | n1) != 0u) {
 #pragma unroll
-            for (int pl = 0; pl < 56; ++pl) {
+            for (int pl = 0; pl < NP; ++pl) {
                 const uint32_t bit = (pl < 32) ? (n0 >> pl) & 1u : (n1 >> (pl - 32)) & 1u;
                 if (bit) {
                     const float z = __uint_as_float((pl & 1) ? O[pl >> 1] : E[pl >> 1]);
@@ -616,7 +617,7 @@ __device__ __forceinline__ unsigned long long site_mask56(const uint32_t (&E)[28
         }
     }
     unsigned long long hit = ((unsigned long long)h1 << 32) | h0;
-    if (limit < 56) hit &= limit > 0 ? ((1ull << limit) - 1ull) : 0ull;
+    if (limit < NP) hit &= limit > 0 ? ((1ull << limit) - 1ull) : 0ull;
     return hit;
 }
 
@@ -815,8 +816,8 @@ scan_tc_kernel(ScanArgs a) {
                     if (MODE == SCAN_SITE_EMIT) {
                         // hit mask of this thread's 56 starts, ascending
                         unsigned long long mask = !live ? 0ull
-                                                  : all_exact ? site_mask56<true>(E, O, limit, Dlo, Dhi, asc, shf, thr)
-                                                              : site_mask56<false>(E, O, limit, Dlo, Dhi, asc, shf, thr);
+                                                  : all_exact ? site_mask<true, 28>(E, O, limit, Dlo, Dhi, asc, shf, thr)
+                                                              : site_mask<false, 28>(E, O, limit, Dlo, Dhi, asc, shf, thr);
                         const int tp = g & 1;
                         const int item = blockIdx.y + sq * ns;
                         uint8_t* codes = s_codes + (sq & 7) * code_bytes;
@@ -854,8 +855,8 @@ scan_tc_kernel(ScanArgs a) {
                         cnt += total;                              // sites at earlier starts of this sequence
                     } else if (MODE == SCAN_SITE_COUNT) {
                         if (live)
-                            cnt += __popcll(all_exact ? site_mask56<true>(E, O, limit, Dlo, Dhi, asc, shf, thr)
-                                                      : site_mask56<false>(E, O, limit, Dlo, Dhi, asc, shf, thr));
+                            cnt += __popcll(all_exact ? site_mask<true, 28>(E, O, limit, Dlo, Dhi, asc, shf, thr)
+                                                      : site_mask<false, 28>(E, O, limit, Dlo, Dhi, asc, shf, thr));
                     } else if (live) {
                         const int base = strand * Lw + p0;         // index on the [fwd | rev] axis
                         const bool full = limit >= 56;
@@ -931,14 +932,16 @@ scan_tc_kernel(ScanArgs a) {
 // 8 bytes after position q-1 in the one-hot buffer, so the even starts of a tile read through an MN-major view
 // (K row r <-> start 2r, 16 bytes apart; N chunk c <-> taps 2c, 2c+1, 16 bytes apart) ARE the Toeplitz
 // matrix, and the odd starts are the same view of the buffer shifted by one position (the pair the scan uses
-// for its odd window starts).  The epilogue turns the scan's accumulators into H -- bf16 0 / 1, two compares
-// and half a byte-permute per start, written K-major in 8-byte pieces -- and issuer warp 0 runs the PFM MMAs
+// for its odd window starts).  The epilogue turns the scan's accumulators into H -- bf16 0 / 1, one compare
+// and half a byte-permute per start, written K-major, 16 bytes per store -- and issuer warp 0 runs the PFM MMAs
 // of tile g-1 between the scan MMAs of tiles g and g+1.  The counts stay in TMEM (fp32, exact below 2^24, and
 // a unit emits at most `cap` sites) for the CTA's whole share of the list and are added to the PFM once.
 // No shared-memory atomics, no per-site loop, no CTA-wide barrier in the loop.
 //
-// TMEM: scan accumulator (one stage: the epilogue frees it right after the tcgen05.ld, and the PFM MMAs of the
-// previous tile fill the gap) in columns 0..255, PFM accumulator 128 x pad16(4k) from column 256.
+// Tiles are 192 window starts here (96 even + 96 odd accumulator columns), not 224: two scan stages of 192
+// columns leave 128 TMEM columns for the PFM accumulator (k <= 32; longer kernels take the site-record kernel).
+// With ONE scan stage the commit -> epilogue tcgen05.ld -> arrive -> issue round trip (~2 us, measured with
+// everything else switched off) sat between any two tiles; two stages hide it behind the other tile's MMAs.
 //
 // The cap: a row whose offset has reached the cap contributes nothing (its thresholds become NaN); a row with
 // room for every start of the sequence needs no ranks at all.  Only the ONE sequence per unit that crosses the
@@ -947,17 +950,35 @@ scan_tc_kernel(ScanArgs a) {
 // Sequences after the point where every unit of the CTA is capped are not visited at all (offsets are
 // exclusive prefix sums, so non-decreasing along the list; found by bisection at kernel start).
 // ===========================================================================
-#define PF_HCHUNKS 28                                    // 16-byte K chunks of H per tile: 14 even + 14 odd
-#define PF_HBYTES (PF_HCHUNKS * TC_ROWS * 16)            // 57344
-#define PF_COL TC_STAGE_COLS                             // first TMEM column of the PFM accumulator
+#define PF_TILE 192                                      // window starts per tile
+#define PF_HALF (PF_TILE / 2)                            // accumulator columns per parity = UMMA N max
+#define PF_SHARE (PF_TILE / 4)                           // starts per epilogue thread
+#define PF_NH (PF_SHARE / 2)                             // ... per parity (24)
+#define PF_PIECES (PF_SHARE / 8)                         // 8-byte pieces of H per thread and parity (6)
+#define PF_HCHUNKS (PF_TILE / 8)                         // 16-byte K chunks of H per tile: 12 even + 12 odd
+#define PF_HBYTES (PF_HCHUNKS * TC_ROWS * 16)            // 49152
+#define PF_COL (2 * PF_TILE)                             // first TMEM column of the PFM accumulator (384)
+#define PF_KMAX 32                                       // 4 k <= 128 accumulator columns
 
 struct PfShared {
-    uint64_t acc_full, acc_empty;          // scan accumulator: MMAs completed / read out (16 warp arrivals)
+    uint64_t acc_full[2], acc_empty[2];    // scan accumulator stages: MMAs completed / read out (16 warp arrivals)
     uint64_t oh_full[SCAN_NOH_MAX], oh_empty[SCAN_NOH_MAX];   // one-hot ring: written / both issuers done with it
     uint64_t h_full[2], h_empty[2];        // H buffers: written (16 warp arrivals) / PFM MMAs of the tile completed
     uint64_t pfm_done;                     // the last PFM MMA completed
     uint32_t tmem_slot, pad;
 };
+
+// 24 consecutive TMEM columns of this warp's lanes as 16 + 8
+__device__ __forceinline__ void tmem_ld24(uint32_t taddr, uint32_t (&r)[PF_NH]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    umma::tmem_ld8(taddr + 16, &r[16]);
+}
 
 // bf16 pair (lo = a is a site, hi = b is a site); !EXACT: also the "needs the exact predicate" accumulator
 template <bool EXACT>
@@ -971,33 +992,46 @@ __device__ __forceinline__ uint32_t site_pair(uint32_t a, uint32_t b, float Dlo,
     return __byte_perm(ha, hb, 0x7632);                  // 1.0f >> 16 == bf16 1.0
 }
 
-// the seven 8-byte pieces (per parity) of one thread's share of H, handed to put(m, even lo, even hi, odd lo, odd hi)
-template <bool EXACT, typename Put>
-__device__ __forceinline__ void pfm_pieces(const uint32_t (&E)[28], const uint32_t (&O)[28], int limit, float dlo,
-                                           float dhi, uint32_t& near, Put put) {
+// piece m (four even and four odd starts, 8 m .. 8 m + 7) of one thread's share of H as bf16 pairs
+template <bool EXACT>
+__device__ __forceinline__ void pfm_piece(int m, const uint32_t (&E)[PF_NH], const uint32_t (&O)[PF_NH], int limit,
+                                          float dlo, float dhi, uint32_t& near, uint32_t (&w)[4]) {
+    if (limit >= 8 * m + 8) {
+        w[0] = site_pair<EXACT>(E[4 * m], E[4 * m + 1], dlo, dhi, near);
+        w[1] = site_pair<EXACT>(E[4 * m + 2], E[4 * m + 3], dlo, dhi, near);
+        w[2] = site_pair<EXACT>(O[4 * m], O[4 * m + 1], dlo, dhi, near);
+        w[3] = site_pair<EXACT>(O[4 * m + 2], O[4 * m + 3], dlo, dhi, near);
+    } else if (limit > 8 * m) {                          // the piece straddles Lw: starts >= limit compare as NaN
+        uint32_t x[8];
 #pragma unroll
-    for (int m = 0; m < 7; ++m) {
-        if (limit >= 8 * m + 8) {
-            const uint32_t e0 = site_pair<EXACT>(E[4 * m], E[4 * m + 1], dlo, dhi, near);
-            const uint32_t e1 = site_pair<EXACT>(E[4 * m + 2], E[4 * m + 3], dlo, dhi, near);
-            const uint32_t o0 = site_pair<EXACT>(O[4 * m], O[4 * m + 1], dlo, dhi, near);
-            const uint32_t o1 = site_pair<EXACT>(O[4 * m + 2], O[4 * m + 3], dlo, dhi, near);
-            put(m, e0, e1, o0, o1);
-        } else if (limit > 8 * m) {                      // the piece straddles Lw: starts >= limit compare as NaN
-            uint32_t x[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint32_t z = (i & 1) ? O[4 * m + (i >> 1)] : E[4 * m + (i >> 1)];
-                x[i] = (8 * m + i < limit) ? z : 0x7FC00000u;
-            }
-            const uint32_t e0 = site_pair<EXACT>(x[0], x[2], dlo, dhi, near);
-            const uint32_t e1 = site_pair<EXACT>(x[4], x[6], dlo, dhi, near);
-            const uint32_t o0 = site_pair<EXACT>(x[1], x[3], dlo, dhi, near);
-            const uint32_t o1 = site_pair<EXACT>(x[5], x[7], dlo, dhi, near);
-            put(m, e0, e1, o0, o1);
-        } else {
-            put(m, 0u, 0u, 0u, 0u);
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t z = (i & 1) ? O[4 * m + (i >> 1)] : E[4 * m + (i >> 1)];
+            x[i] = (8 * m + i < limit) ? z : 0x7FC00000u;
         }
+        w[0] = site_pair<EXACT>(x[0], x[2], dlo, dhi, near);
+        w[1] = site_pair<EXACT>(x[4], x[6], dlo, dhi, near);
+        w[2] = site_pair<EXACT>(x[1], x[3], dlo, dhi, near);
+        w[3] = site_pair<EXACT>(x[5], x[7], dlo, dhi, near);
+    } else {
+        w[0] = w[1] = w[2] = w[3] = 0u;
+    }
+}
+
+// The six pieces (per parity) of one thread's share of H.  Piece m of column share wq is piece 6 wq + m of the
+// tile, 8 bytes at chunk (6 wq + m) / 2, half m & 1: two pieces fill one 16-byte chunk and go out as ONE store
+// (8-byte stores would leave every 16-byte slot of the row group half-filled: twice the shared-memory
+// wavefronts, on the pipe the MMAs read their operands through).
+//   hp: this thread's row of chunk 3 wq, even starts; the odd starts sit PF_HCHUNKS / 2 chunks further.
+template <bool EXACT>
+__device__ __forceinline__ void pfm_pieces(const uint32_t (&E)[PF_NH], const uint32_t (&O)[PF_NH], int limit, float dlo,
+                                           float dhi, uint32_t& near, unsigned char* hp) {
+#pragma unroll
+    for (int j = 0; j < PF_PIECES / 2; ++j) {
+        uint32_t a[4], b[4];
+        pfm_piece<EXACT>(2 * j, E, O, limit, dlo, dhi, near, a);
+        pfm_piece<EXACT>(2 * j + 1, E, O, limit, dlo, dhi, near, b);
+        *reinterpret_cast<uint4*>(hp + j * 2048) = make_uint4(a[0], a[1], b[0], b[1]);
+        *reinterpret_cast<uint4*>(hp + (j + PF_HCHUNKS / 2) * 2048) = make_uint4(a[2], a[3], b[2], b[3]);
     }
 }
 
@@ -1009,7 +1043,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
     const int chunks = kpad >> 3, ksteps = kpad >> 4;
     const uint32_t a_bytes = 3u * chunks * 2048u;
     unsigned char* a_smem = smem_raw;
-    unsigned char* h_smem = smem_raw + a_bytes;                              // [nh][28][128] x 16 B
+    unsigned char* h_smem = smem_raw + a_bytes;                              // [nh][24][128] x 16 B
     uint2* oh = reinterpret_cast<uint2*>(h_smem + (size_t)nh * PF_HBYTES);   // [noh][2][Lbuf]
     const int pl_words = (3 * Wp + 3) & ~3;
     uint32_t* s_pl = reinterpret_cast<uint32_t*>(oh + (size_t)noh * 2 * Lbuf);   // [one-hot warp][2][pl_words]
@@ -1019,7 +1053,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
     const int g0 = blockIdx.x * TC_ROWS;
     const int ng = min(TC_ROWS, a.R - g0);
     const int ns = gridDim.y;
-    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
+    const int ntiles = (Lw + PF_TILE - 1) / PF_TILE;
     int nseq = (a.n_items - 1 - (int)blockIdx.y) / ns + 1;
     {
         // sequences from the first one at which every unit of this CTA is capped contribute nothing
@@ -1048,15 +1082,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
     }
     if (warp == 0) umma::tmem_alloc(&sh->tmem_slot, TC_TMEM_COLS);
     if (tid == 0) {
-        umma::mbar_init(&sh->acc_full, 2);
-        umma::mbar_init(&sh->acc_empty, TC_EPI_WARPS);
+        for (int s = 0; s < 2; ++s) {
+            umma::mbar_init(&sh->acc_full[s], 2);
+            umma::mbar_init(&sh->acc_empty[s], TC_EPI_WARPS);
+            umma::mbar_init(&sh->h_full[s], TC_EPI_WARPS);
+            umma::mbar_init(&sh->h_empty[s], 1);
+        }
         for (int s = 0; s < SCAN_NOH_MAX; ++s) {
             umma::mbar_init(&sh->oh_full[s], 1);
             umma::mbar_init(&sh->oh_empty[s], 2);
-        }
-        for (int s = 0; s < 2; ++s) {
-            umma::mbar_init(&sh->h_full[s], TC_EPI_WARPS);
-            umma::mbar_init(&sh->h_empty[s], 1);
         }
         umma::mbar_init(&sh->pfm_done, 1);
         sh->pad = 0u;                                          // set by a row whose site predicate is not a clean step
@@ -1066,7 +1100,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
     __syncthreads();
     umma::fence_after_sync();
     const uint32_t tmem = sh->tmem_slot;
-    const int npfm = (4 * a.k + 15) & ~15;                                   // UMMA N of the PFM GEMM
+    const int npfm = (4 * a.k + 15) & ~15;                                   // UMMA N of the PFM GEMM (<= 128)
 
     if (warp == TC_EPI_WARPS || warp == TC_EPI_WARPS + 1) {
         // ================= issuer warps: scan MMAs of the even / odd window starts; warp 0 also the PFM GEMM ==========
@@ -1087,13 +1121,14 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             umma::mbar_wait(&sh->h_full[hb], (uint32_t)(gp / nh) & 1u);
             umma::fence_after_sync();
             if (umma::elect_one()) {
-                const int cnt = min(TC_TILE_POS, Lw - tp * TC_TILE_POS);
-                const uint32_t x_t = x_lo + (uint32_t)sp * (uint32_t)Lbuf + 112u * (uint32_t)tp;
+                const int cnt = min(PF_TILE, Lw - tp * PF_TILE);
+                const uint32_t x_t = x_lo + (uint32_t)sp * (uint32_t)Lbuf + (uint32_t)(PF_TILE / 2) * (uint32_t)tp;
                 const uint32_t h_b = h_lo + (uint32_t)hb * (uint32_t)(PF_HBYTES >> 4);
                 for (int p2 = 0; p2 < 2; ++p2) {
                     const int nk = (((cnt + 1 - p2) >> 1) + 15) >> 4;            // K steps of 16 even / odd starts
-                    uint32_t h_k = h_b + (uint32_t)(p2 * 14) * 128u, x_k = x_t + (uint32_t)p2 * (uint32_t)(Lbuf >> 1);
-#pragma unroll 4
+                    uint32_t h_k = h_b + (uint32_t)(p2 * (PF_HCHUNKS / 2)) * 128u,
+                             x_k = x_t + (uint32_t)p2 * (uint32_t)(Lbuf >> 1);
+#pragma unroll 3
                     for (int ks = 0; ks < nk; ++ks) {
                         umma::mma_bf16(tmem_u + PF_COL, ((uint64_t)hi128 << 32) | (uint64_t)h_k,
                                        ((uint64_t)hi16 << 32) | (uint64_t)x_k, idesc_p, pacc);
@@ -1114,14 +1149,15 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
             umma::mbar_wait(&sh->oh_full[so], (uint32_t)(v / noh) & 1u);
             const uint32_t b_sq = b_lo + (uint32_t)so * (uint32_t)Lbuf;
             for (int t = 0; t < ntiles; ++t, ++g) {
-                umma::mbar_wait(&sh->acc_empty, ((uint32_t)g & 1u) ^ 1u);
+                const uint32_t stage = (uint32_t)g & 1u;
+                umma::mbar_wait(&sh->acc_empty[stage], (((uint32_t)g >> 1) & 1u) ^ 1u);
                 umma::fence_after_sync();
                 if (umma::elect_one()) {
-                    const int cnt = min(TC_TILE_POS, Lw - t * TC_TILE_POS);
+                    const int cnt = min(PF_TILE, Lw - t * PF_TILE);
                     const int N = (((cnt + 1) >> 1) + 15) & ~15;
                     const uint32_t idesc = umma::idesc_bf16_f32(TC_ROWS, N);
-                    const uint32_t b_t = b_sq + 112u * (uint32_t)t;
-                    const uint32_t d = tmem_u + (par ? TC_ODD_COL : 0);
+                    const uint32_t b_t = b_sq + (uint32_t)(PF_TILE / 2) * (uint32_t)t;
+                    const uint32_t d = tmem_u + stage * PF_TILE + (par ? PF_HALF : 0);
                     uint32_t acc = 0;
                     for (int s3 = 0; s3 < 3; ++s3) {
                         uint32_t a_k = a_lo + (uint32_t)(s3 * chunks) * 128u, b_k = b_t;
@@ -1134,7 +1170,7 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                             b_k += 2u;
                         }
                     }
-                    umma::commit(&sh->acc_full);
+                    umma::commit(&sh->acc_full[stage]);
                     if (par == 1 && t == ntiles - 1) umma::commit(&sh->oh_empty[so]);
                 }
                 __syncwarp();
@@ -1181,7 +1217,6 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         const int row = quarter * 32 + lane;
         const bool rows_live = quarter * 32 < ng;
         const uint32_t tq = tmem + ((uint32_t)(quarter * 32) << 16);
-        const uint32_t tlane = tq + 28u * wq;
         // the exact predicate's constants are reloaded where it is evaluated (rare): three registers less in the loop
         auto exact_consts = [&](float& asc, float& shf, float& thr) {
             asc = shf = thr = 0.0f;
@@ -1196,24 +1231,28 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
         }
         epi_barrier();
         const bool all_exact = sh->pad == 0u;                    // CTA-uniform: one compare per start, no band
-        // this thread's 8-byte pieces of H: even-start index 28 wq + 4m -> chunk (28 wq + 4m) / 8, half ((7 wq + m) & 1)
-        unsigned char* hrow = h_smem + (size_t)row * 16;
+        // this thread's row of H; its pieces start at chunk 3 wq of each parity
+        unsigned char* hrow = h_smem + (size_t)row * 16 + (size_t)(3 * wq) * 2048;
         int g = 0;
+        // the offset of (row, next sequence) is in flight during this sequence: fetched at its first use, the load
+        // sat on the epilogue's critical path once per sequence
+        const long long* offp = a.offsets + (long long)(g0 + min(row, ng - 1)) * a.n_items + blockIdx.y;
+        long long off_next = nseq > 0 ? __ldg(offp) : 0ll;
         for (int sq = 0; sq < nseq; ++sq) {
             int rem = 0;                                         // sites this row may still emit, clamped to 0 .. Lw
-            if (row < ng) {
-                const long long r64 =
-                    a.cap - __ldg(a.offsets + (long long)(g0 + row) * a.n_items + (blockIdx.y + (long long)sq * ns));
-                rem = (int)max(0ll, min(r64, (long long)Lw));
-            }
+            const long long off = off_next;
+            if (sq + 1 < nseq) off_next = __ldg(offp + (long long)(sq + 1) * ns);
+            if (row < ng) rem = (int)max(0ll, min(a.cap - off, (long long)Lw));
             const bool crossing = rem > 0 && rem < Lw;           // the cap may fall inside this sequence
             const bool any_crossing = __any_sync(0xffffffffu, crossing);
             const float dlo = rem > 0 ? Dlo : qnan, dhi = rem > 0 ? Dhi : qnan;
             int seen = 0;                                        // crossing rows: sites at earlier tiles of the sequence
             for (int t = 0; t < ntiles; ++t, ++g) {
-                umma::mbar_wait(&sh->acc_full, (uint32_t)g & 1u);
+                const uint32_t stage = (uint32_t)g & 1u;
+                const uint32_t tst = tq + stage * PF_TILE;
+                umma::mbar_wait(&sh->acc_full[stage], ((uint32_t)g >> 1) & 1u);
                 umma::fence_after_sync();
-                const int p0 = t * TC_TILE_POS + 56 * wq;
+                const int p0 = t * PF_TILE + PF_SHARE * wq;
                 const int limit = Lw - p0;
                 const bool live = rows_live && limit > 0;
                 int before = 0, total = 0;
@@ -1223,50 +1262,45 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                     exact_consts(asc, shf, thr);
 #pragma unroll 1
                     for (int s2 = 0; s2 < 4; ++s2) {
-                        const int lim2 = Lw - (t * TC_TILE_POS + 56 * s2);
+                        const int lim2 = Lw - (t * PF_TILE + PF_SHARE * s2);
                         if (s2 == wq || lim2 <= 0) continue;
-                        uint32_t E2[28], O2[28];
-                        umma::tmem_ld28(tq + 28u * s2, E2);
-                        umma::tmem_ld28(tq + 28u * s2 + TC_ODD_COL, O2);
+                        uint32_t E2[PF_NH], O2[PF_NH];
+                        tmem_ld24(tst + (uint32_t)(PF_NH * s2), E2);
+                        tmem_ld24(tst + (uint32_t)(PF_NH * s2) + PF_HALF, O2);
                         umma::tmem_ld_wait();
-                        const int c2 = __popcll(site_mask56<false>(E2, O2, lim2, dlo, dhi, asc, shf, thr));
+                        const int c2 = __popcll(site_mask<false, PF_NH>(E2, O2, lim2, dlo, dhi, asc, shf, thr));
                         total += c2;
                         if (s2 < wq) before += c2;
                     }
                 }
-                uint32_t E[28], O[28];
+                uint32_t E[PF_NH], O[PF_NH];
                 if (live) {
-                    umma::tmem_ld28(tlane, E);
-                    umma::tmem_ld28(tlane + TC_ODD_COL, O);
+                    tmem_ld24(tst + (uint32_t)(PF_NH * wq), E);
+                    tmem_ld24(tst + (uint32_t)(PF_NH * wq) + PF_HALF, O);
                     umma::tmem_ld_wait();
                 }
                 umma::fence_before_sync();
                 __syncwarp();
-                if (lane == 0) umma::mbar_arrive(&sh->acc_empty);
+                if (lane == 0) umma::mbar_arrive(&sh->acc_empty[stage]);
 
                 const int hb = g % nh;
                 if (g >= nh) umma::mbar_wait(&sh->h_empty[hb], (uint32_t)(g / nh - 1) & 1u);
-                // piece m of this thread = piece 7 wq + m of the tile's even (and, 14 chunks further, odd) starts
-                unsigned char* hbuf = hrow + (size_t)hb * PF_HBYTES;
-                auto put = [&](int m, uint32_t e0, uint32_t e1, uint32_t o0, uint32_t o1) {
-                    const int e = 7 * wq + m;
-                    unsigned char* pe = hbuf + (e >> 1) * 2048 + (e & 1) * 8;
-                    *reinterpret_cast<uint2*>(pe) = make_uint2(e0, e1);
-                    *reinterpret_cast<uint2*>(pe + 14 * 2048) = make_uint2(o0, o1);
-                };
+                unsigned char* hp = hrow + (size_t)hb * PF_HBYTES;
                 uint32_t near = 0u;
                 if (live) {
-                    if (all_exact) pfm_pieces<true>(E, O, limit, dlo, dhi, near, put);
-                    else pfm_pieces<false>(E, O, limit, dlo, dhi, near, put);
+                    if (all_exact) pfm_pieces<true>(E, O, limit, dlo, dhi, near, hp);
+                    else pfm_pieces<false>(E, O, limit, dlo, dhi, near, hp);
                 } else if (rows_live) {
 #pragma unroll
-                    for (int m = 0; m < 7; ++m) put(m, 0u, 0u, 0u, 0u);
+                    for (int j = 0; j < PF_PIECES; ++j)
+                        *reinterpret_cast<uint4*>(hp + (j % (PF_PIECES / 2) + (j / (PF_PIECES / 2)) * (PF_HCHUNKS / 2)) * 2048) =
+                            make_uint4(0u, 0u, 0u, 0u);
                 }
                 if (__any_sync(0xffffffffu, near != 0u || (crossing && live))) {
                     // rare: exact predicate and / or the cap, from the bit mask; the pieces are written again
                     float asc, shf, thr;
                     exact_consts(asc, shf, thr);
-                    unsigned long long mask = live ? site_mask56<false>(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
+                    unsigned long long mask = live ? site_mask<false, PF_NH>(E, O, limit, dlo, dhi, asc, shf, thr) : 0ull;
                     if (crossing) {
                         const int own = __popcll(mask);
                         const int room = max(0, rem - seen - before);
@@ -1283,15 +1317,17 @@ site_pfm_tc_kernel(ScanArgs a, int nh) {
                     }
                     if (live) {
 #pragma unroll
-                        for (int m = 0; m < 7; ++m) {
-                            uint32_t w4[4];
+                        for (int j = 0; j < PF_PIECES / 2; ++j) {
+                            uint32_t w8[8];                      // [piece 2j, 2j+1][parity * 2 + half]
 #pragma unroll
-                            for (int q = 0; q < 4; ++q) {        // q: parity * 2 + half
-                                const int pl0 = 8 * m + 4 * (q & 1) + (q >> 1);
+                            for (int q = 0; q < 8; ++q) {
+                                const int m = 2 * j + (q >> 2), par2 = (q >> 1) & 1, half = q & 1;
+                                const int pl0 = 8 * m + 4 * half + par2;
                                 const uint32_t b0 = (uint32_t)(mask >> pl0) & 1u, b1 = (uint32_t)(mask >> (pl0 + 2)) & 1u;
-                                w4[q] = b0 * 0x3F80u + b1 * 0x3F800000u;
+                                w8[q] = b0 * 0x3F80u + b1 * 0x3F800000u;
                             }
-                            put(m, w4[0], w4[1], w4[2], w4[3]);
+                            *reinterpret_cast<uint4*>(hp + j * 2048) = make_uint4(w8[0], w8[1], w8[4], w8[5]);
+                            *reinterpret_cast<uint4*>(hp + (j + PF_HCHUNKS / 2) * 2048) = make_uint4(w8[2], w8[3], w8[6], w8[7]);
                         }
                     }
                 }
@@ -1348,10 +1384,10 @@ static bool pwm_tc_fits(int L, int w, int* noh_out, int* Lbuf_out, size_t* smem_
 // sequence lives until the PFM MMAs of its last tile, which are issued after the scan MMAs of the NEXT tile; a
 // ring of one would deadlock)
 static bool site_pfm_fits(int L, int w, int* noh_out, int* nh_out, int* Lbuf_out, size_t* smem_out) {
-    if (w < 1 || w > TC_KMAX || L < w) return false;
+    if (w < 1 || w > PF_KMAX || L < w) return false;
     const int Lw = L - w + 1, kpad = tc_kpad(w);
-    const int ntiles = (Lw + TC_TILE_POS - 1) / TC_TILE_POS;
-    const int Lbuf = ntiles * TC_TILE_POS + 2 * (kpad / 4) + 64;
+    const int ntiles = (Lw + PF_TILE - 1) / PF_TILE;
+    const int Lbuf = ntiles * PF_TILE + 2 * (kpad / 4) + 64;     // last tile reads up to start + 192 + kpad/4 + 2
     const int Wp = (L + 31) / 32, pl_words = (3 * Wp + 3) & ~3;
     for (int nh = 2; nh >= 1; --nh)
         for (int noh = SCAN_NOH_MAX; noh >= 2; --noh) {

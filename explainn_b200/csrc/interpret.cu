@@ -169,3 +169,66 @@ extern "C" int xnn_site_emit(const uint32_t* planes, int B, int L, int U, int k,
     if (r) { set_error("xnn_site_emit: %s", r < 0 ? "sequence too long" : "launch failed"); return r < 0 ? XNN_ERR_ARG : XNN_ERR_CUDA; }
     return XNN_OK;
 }
+
+
+// ---------------------------------------------------------------------------
+// Between passes 2a and 2b (interpret.py:414-417: the first 1e6 sites of a unit, in sequence order): the rank of
+// the first site of (unit, listed sequence) = carry[u] + the sites of the unit at earlier listed sequences.
+// One block per unit: exclusive scan of the row of int32 counts into int64 offsets, carry[u] += the row total.
+// (Was five ATen launches per chunk -- int64 copy, cumsum, subtract, add, slice-add -- over 8-byte temporaries.)
+// ---------------------------------------------------------------------------
+#define OFS_THREADS 1024
+__global__ void __launch_bounds__(OFS_THREADS)
+site_offsets_kernel(const int32_t* __restrict__ counts, int n, long long* __restrict__ carry,
+                    long long* __restrict__ offsets) {
+    __shared__ long long s_warp[OFS_THREADS / 32];
+    const int u = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int32_t* row = counts + (long long)u * n;
+    long long* out = offsets + (long long)u * n;
+    long long run = carry[u];                              // rank of the first site of the current tile
+    // tiles of 4 x 1024 consecutive counts, four per thread (coalesced), scanned through shuffles
+    for (int i0 = 0; i0 < n; i0 += 4 * OFS_THREADS) {
+        const int i = i0 + 4 * tid;
+        int c[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[j] = (i + j < n) ? row[i + j] : 0;
+        const long long sum = (long long)c[0] + c[1] + c[2] + c[3];
+        long long inc = sum;                               // inclusive scan over the threads
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            long long w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        long long r = run + (warp ? s_warp[warp - 1] : 0ll) + inc - sum;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (i + j < n) out[i + j] = r;
+            r += c[j];
+        }
+        run += s_warp[OFS_THREADS / 32 - 1];
+        __syncthreads();                                   // s_warp is rewritten by the next tile
+    }
+    if (tid == 0) carry[u] = run;
+}
+
+extern "C" int xnn_site_offsets(const int32_t* counts, int U, int n, long long* carry, long long* offsets,
+                                xnn_stream_t s) {
+    XNN_CHECK_ARG(counts && carry && offsets, "NULL pointer");
+    XNN_CHECK_ARG(U >= 1 && n >= 0, "bad sizes");
+    if (n == 0) return XNN_OK;
+    site_offsets_kernel<<<U, OFS_THREADS, 0, to_stream(s)>>>(counts, n, carry, offsets);
+    XNN_CHECK_LAUNCH();
+    return XNN_OK;
+}

@@ -242,19 +242,23 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t hint = 0x989680u) {
+// Wait for the phase of parity `parity` to complete.  try_wait WITHOUT a suspend-time hint: with the 10 ms hint used
+// before, a failed first check compiled to NANOSLEEP.SYNCS 0x989680 and the wake-up after the arrival cost several
+// hundred cycles per wait -- on every hop of the producer / issuer / epilogue chains (measured with clock64: no wait
+// section ever took less than ~400 cycles, even with nothing to wait for).
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t a = smem_u32(bar);
     uint32_t done = 0, spins = 0;
     while (!done) {
-        if (++spins > (1u << 24)) __trap();   // a lost arrival must fail loudly, never hang the GPU
+        if (++spins > (1u << 26)) __trap();   // a lost arrival must fail loudly, never hang the GPU
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t"
             "}\n"
             : "=r"(done)
-            : "r"(a), "r"(parity), "r"(hint)   // suspend-time hint: a waiting warp sleeps instead of spinning
+            : "r"(a), "r"(parity)
             : "memory");
     }
 }

@@ -111,10 +111,13 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
             counts = counts_cache.get((strand, c0)) if counts_cache is not None else None
             if counts is None:
                 counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
-            csum = torch.cumsum(counts.to(torch.int64), dim=1)
-            offsets = (csum - counts + carry[:, None]).contiguous()
             sites = None
-            if return_sites:
+            if not return_sites:
+                offsets = ops.site_offsets(counts, carry)              # carry advanced in place
+                ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm, None)
+            else:
+                csum = torch.cumsum(counts.to(torch.int64), dim=1)
+                offsets = (csum - counts + carry[:, None]).contiguous()
                 # rows are addressed by global rank: give the kernel a window starting at `carry`
                 width = int(min(site_capacity, int(csum[:, -1].max().item())))
                 sites = torch.full((U, max(width, 1), 2), -1, dtype=torch.int32, device=dev)
@@ -140,9 +143,7 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
                         rec[:, 1] = strand
                         rec[:, 2] = s[:, 1]
                         site_chunks[u].append(rec)
-            else:
-                ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm, None)
-            carry = carry + csum[:, -1]
+                carry = carry + csum[:, -1]
             if carry0 is None and bool((carry >= cap).all()):
                 break
     out = {

@@ -538,6 +538,18 @@ def site_counts(planes, L, conv_w, scale, shift, thr, idx=None, tensor_cores=Tru
     return counts
 
 
+def site_offsets(counts, carry, out=None):
+    """offsets[u, i] = carry[u] + counts[u, :i].sum() (int64), then carry[u] += counts[u].sum(), in one launch.
+    counts (U, n) int32 from site_counts; carry (U,) int64, updated in place."""
+    U, n = counts.shape
+    _req(counts, torch.int32, "counts")
+    _req(carry, torch.int64, "carry")
+    if out is None:
+        out = torch.empty((U, n), dtype=torch.int64, device=counts.device)
+    _call("xnn_site_offsets", _p(counts), U, n, _p(carry), _p(_req(out, torch.int64, "offsets")), _stream())
+    return out
+
+
 def site_emit(planes, L, conv_w, scale, shift, thr, offsets, cap, idx=None, pfm=None, sites=None, tensor_cores=True):
     B = planes.shape[0]
     U, _, k = conv_w.shape

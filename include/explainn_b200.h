@@ -349,6 +349,10 @@ int xnn_site_counts_tc(const uint32_t* planes, int B, int L, int U, int k,
  * (use the three of them together, or none: the conv summation order differs
  * from the gather-add passes in the last bit). */
 int xnn_interpret_tc_supported(int L, int k);
+/* Between passes 2a and 2b (interpret.py:414-417): offsets[u][i] = carry[u] + sum of counts[u][0..i-1] (the rank
+ * of the first site of unit u in listed sequence i), then carry[u] += sum of counts[u][:].  counts (U, n) int32
+ * from xnn_site_counts[_tc]; carry (U) int64 in/out; offsets (U, n) int64 out. */
+int xnn_site_offsets(const int32_t* counts, int U, int n, long long* carry, long long* offsets, xnn_stream_t s);
 int xnn_site_emit_tc(const uint32_t* planes, int B, int L, int U, int k,
                      const float* conv_w, const float* scale, const float* shift,
                      const float* thr, const int32_t* idx, int n_idx,

@@ -641,6 +641,23 @@ def test_interpret_pfm_gemm_vs_site_records(cfg):
                         assert (got[:, :, 0].sum(1) <= exp).all()
 
 
+@pytest.mark.parametrize("shape", [(1, 1), (3, 1000), (100, 65536), (7, 1025), (300, 40)])
+def test_site_offsets_vs_cumsum(shape):
+    """xnn_site_offsets (exclusive scan of the pass-2a counts + running carry, one launch) against the ATen
+    expression it replaces in interpret.sites_and_pfms."""
+    from explainn_b200 import ops
+    Uu, n = shape
+    g = torch.Generator().manual_seed(n)
+    counts = torch.randint(0, 583, (Uu, n), generator=g, dtype=torch.int32).to(DEV)
+    carry = (torch.arange(Uu, dtype=torch.int64) * (1 << 33) + 5).to(DEV)       # beyond 32 bits
+    c64 = counts.to(torch.int64)
+    csum = torch.cumsum(c64, dim=1)
+    ref_off = csum - c64 + carry[:, None]
+    ref_carry = carry + csum[:, -1]
+    got = ops.site_offsets(counts, carry)
+    assert torch.equal(got, ref_off) and torch.equal(carry, ref_carry)
+
+
 def test_interpret_sequence_shards_reproduce_the_unsharded_result():
     """contiguous shards + exclusive carries place the site cap on the same global prefix
     (both strands); the two-shard exchange is emulated in-process, the collective itself is covered by
