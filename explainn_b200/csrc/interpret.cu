@@ -178,47 +178,73 @@ extern "C" int xnn_site_emit(const uint32_t* planes, int B, int L, int U, int k,
 // (Was five ATen launches per chunk -- int64 copy, cumsum, subtract, add, slice-add -- over 8-byte temporaries.)
 // ---------------------------------------------------------------------------
 #define OFS_THREADS 1024
+#define OFS_PER 8                                          // counts per thread and tile
 __global__ void __launch_bounds__(OFS_THREADS)
 site_offsets_kernel(const int32_t* __restrict__ counts, int n, long long* __restrict__ carry,
                     long long* __restrict__ offsets) {
-    __shared__ long long s_warp[OFS_THREADS / 32];
+    __shared__ long long s_warp[2][OFS_THREADS / 32];
     const int u = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int32_t* row = counts + (long long)u * n;
     long long* out = offsets + (long long)u * n;
+    const bool vec = ((n & 3) == 0);                       // rows 16-byte aligned: vector loads / stores
     long long run = carry[u];                              // rank of the first site of the current tile
-    // tiles of 4 x 1024 consecutive counts, four per thread (coalesced), scanned through shuffles
-    for (int i0 = 0; i0 < n; i0 += 4 * OFS_THREADS) {
-        const int i = i0 + 4 * tid;
-        int c[4];
+    // tiles of 8 x 1024 consecutive counts, eight per thread, scanned through shuffles; the next tile's counts are
+    // loaded before this tile's scan (one barrier per tile: the warp totals are double buffered)
+    int c[OFS_PER], nx[OFS_PER];
+    auto load = [&](int i0, int (&v)[OFS_PER]) {
+        const int i = i0 + OFS_PER * tid;
+        if (vec && i + OFS_PER <= n) {
+            const int4 a = __ldg(reinterpret_cast<const int4*>(row + i));
+            const int4 b = __ldg(reinterpret_cast<const int4*>(row + i + 4));
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) c[j] = (i + j < n) ? row[i + j] : 0;
-        const long long sum = (long long)c[0] + c[1] + c[2] + c[3];
-        long long inc = sum;                               // inclusive scan over the threads
+            for (int j = 0; j < OFS_PER; ++j) v[j] = (i + j < n) ? __ldg(row + i + j) : 0;
+        }
+    };
+    load(0, c);
+    int buf = 0;
+    for (int i0 = 0; i0 < n; i0 += OFS_PER * OFS_THREADS, buf ^= 1) {
+        if (i0 + OFS_PER * OFS_THREADS < n) load(i0 + OFS_PER * OFS_THREADS, nx);
+        long long sum = 0;
+#pragma unroll
+        for (int j = 0; j < OFS_PER; ++j) sum += c[j];
+        long long inc = sum;                               // inclusive scan over the lanes
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const long long t = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += t;
         }
-        if (lane == 31) s_warp[warp] = inc;
+        if (lane == 31) s_warp[buf][warp] = inc;
         __syncthreads();
-        if (warp == 0) {
-            long long w = s_warp[lane];
+        // every warp scans the 32 warp totals itself: no second barrier
+        long long w = s_warp[buf][lane];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const long long t = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += t;
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        const long long tile_total = __shfl_sync(0xffffffffu, w, 31);
+        const long long before_warp = __shfl_sync(0xffffffffu, w - s_warp[buf][lane], warp);
+        long long r = run + before_warp + inc - sum;
+        const int i = i0 + OFS_PER * tid;
+        if (vec && i + OFS_PER <= n) {
+#pragma unroll
+            for (int j = 0; j < OFS_PER; j += 2) {
+                const long long r0 = r, r1 = r + c[j];
+                *reinterpret_cast<longlong2*>(out + i + j) = make_longlong2(r0, r1);
+                r = r1 + c[j + 1];
             }
-            s_warp[lane] = w;
-        }
-        __syncthreads();
-        long long r = run + (warp ? s_warp[warp - 1] : 0ll) + inc - sum;
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            if (i + j < n) out[i + j] = r;
-            r += c[j];
+            for (int j = 0; j < OFS_PER; ++j) {
+                if (i + j < n) out[i + j] = r;
+                r += c[j];
+            }
         }
-        run += s_warp[OFS_THREADS / 32 - 1];
-        __syncthreads();                                   // s_warp is rewritten by the next tile
+        run += tile_total;
+#pragma unroll
+        for (int j = 0; j < OFS_PER; ++j) c[j] = nx[j];
     }
     if (tid == 0) carry[u] = run;
 }

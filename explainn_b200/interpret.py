@@ -58,6 +58,15 @@ def act_thresholds(model, seqs, idxs=None, rev_complement=False):
     return (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
 
 
+def _chunk_of(planes, idx_dev_all, base, c0, n):
+    """One chunk of the listed sequences for the chunked passes: without a list, a contiguous slice of the planes
+    (no index array at all); with one, the device-resident list sliced and shifted by the strand's base.
+    Returns (planes, idx or None)."""
+    if idx_dev_all is None:
+        return planes[base + c0:base + c0 + n], None
+    return planes, (idx_dev_all[c0:c0 + n] + base) if base else idx_dev_all[c0:c0 + n].contiguous()
+
+
 def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=65536, keep_counts=None):
     """Pass 2a alone: uncapped number of above-threshold positions per (strand, unit) -> int64 (S,U)
     device tensor.  A sequence shard needs the totals of the shards before it (parallel.exclusive_carry)
@@ -73,10 +82,11 @@ def site_totals(model, seqs, thresholds, idxs=None, rev_complement=False, chunk=
     thr = torch.as_tensor(np.asarray(thresholds, dtype=np.float16).astype(np.float32), device=dev)
     strands = (0, 1) if rev_complement else (0,)
     tot = torch.zeros((len(strands), U), dtype=torch.int64, device=dev)
+    idx_dev_all = None if idxs is None else torch.as_tensor(idx_all, dtype=torch.int32, device=dev)
     for strand in strands:
         for c0 in range(0, len(idx_all), chunk):
-            idx_dev = torch.as_tensor(idx_all[c0:c0 + chunk] + strand * half, dtype=torch.int32, device=dev)
-            counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
+            pl, idx_dev = _chunk_of(packed.planes, idx_dev_all, strand * half, c0, min(chunk, len(idx_all) - c0))
+            counts = ops.site_counts(pl, packed.length, cw, scale, shift, thr, idx_dev)
             if keep_counts is not None:
                 keep_counts[(strand, c0)] = counts         # (U, chunk) int32: 4*U bytes per listed sequence
             tot[strand] += counts.sum(dim=1, dtype=torch.int64)
@@ -102,19 +112,20 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
     site_chunks = [[] for _ in range(U)] if return_sites else None
     if return_sites and site_capacity is None:
         site_capacity = cap
+    idx_dev_all = None if idxs is None else torch.as_tensor(idx_all, dtype=torch.int32, device=dev)
     for strand in ((0, 1) if rev_complement else (0,)):
         if carry0 is not None:
             carry = torch.as_tensor(carry0[strand], dtype=torch.int64, device=dev).clone()
         for c0 in range(0, len(idx_all), chunk):
             ids = idx_all[c0:c0 + chunk]
-            idx_dev = torch.as_tensor(ids + strand * half, dtype=torch.int32, device=dev)
+            planes_c, idx_dev = _chunk_of(packed.planes, idx_dev_all, strand * half, c0, len(ids))
             counts = counts_cache.get((strand, c0)) if counts_cache is not None else None
             if counts is None:
-                counts = ops.site_counts(packed.planes, packed.length, cw, scale, shift, thr, idx_dev)
+                counts = ops.site_counts(planes_c, packed.length, cw, scale, shift, thr, idx_dev)
             sites = None
             if not return_sites:
                 offsets = ops.site_offsets(counts, carry)              # carry advanced in place
-                ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm, None)
+                ops.site_emit(planes_c, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm, None)
             else:
                 csum = torch.cumsum(counts.to(torch.int64), dim=1)
                 offsets = (csum - counts + carry[:, None]).contiguous()
@@ -126,10 +137,10 @@ def sites_and_pfms(model, seqs, thresholds, idxs=None, rev_complement=False, cap
                 # per-unit caps differ once carries differ: emit with offsets shifted so that rank < cap
                 # is equivalent to local rank < cap - carry; done by passing global offsets and a
                 # global cap for the PFM, and a second call layout for the site window.
-                ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm,
+                ops.site_emit(planes_c, packed.length, cw, scale, shift, thr, offsets, cap, idx_dev, pfm,
                               None)
                 tmp_pfm = torch.zeros_like(pfm)
-                ops.site_emit(packed.planes, packed.length, cw, scale, shift, thr, local_off, 1 << 62, idx_dev,
+                ops.site_emit(planes_c, packed.length, cw, scale, shift, thr, local_off, 1 << 62, idx_dev,
                               tmp_pfm, sites)
                 sites_h = sites.cpu().numpy()
                 lc = local_cap.cpu().numpy()

@@ -244,10 +244,9 @@ def interpret_sharded(model, local_seqs, rev_complement=False, cap=None, group=N
     from . import ops
     N = len(packed)
     half = N // 2 if rev_complement else N
-    idx = torch.arange(half, dtype=torch.int32, device=packed.planes.device)
-    amax = ops.act_max(packed.planes, packed.length, cw, scale, shift, idx)
+    amax = ops.act_max(packed.planes[:half], packed.length, cw, scale, shift)
     if rev_complement:
-        amax = torch.maximum(amax, ops.act_max(packed.planes, packed.length, cw, scale, shift, idx + half))
+        amax = torch.maximum(amax, ops.act_max(packed.planes[half:2 * half], packed.length, cw, scale, shift))
     allreduce_max_(amax, group)
     thr = (0.5 * amax.cpu().numpy().astype(np.float16)).astype(np.float16)
     cache = {}                                                  # pass 2a's counts, reused by pass 2b
