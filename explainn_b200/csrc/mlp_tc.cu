@@ -380,14 +380,17 @@ mlp_fc1_kernel(MlpArgs a) {
             prefetch(i + 1);                    // global loads of the next tile fly under the MMAs
         }
     } else if (warp == WS_P_WARPS + WS_E_WARPS) {
-        // ================= issuer =================
+        // ================= issuer: one elected lane per tile, descriptors in the uniform datapath =================
+        const uint32_t w_base = umma::warp_uniform(umma::desc_lo(w_addr, wlbo));
+        const uint32_t p_base = umma::warp_uniform(umma::desc_lo(p_addr, 2048u));
+        const uint32_t tmem_u = umma::warp_uniform(tmem);
         for (int i = 0; i < ntl; ++i) {
             const uint32_t st = (uint32_t)i & 1u;
             umma::mbar_wait(&sh->staged[st], ((uint32_t)i >> 1) & 1u);
             umma::mbar_wait(&sh->acc_free[st], (((uint32_t)i >> 1) & 1u) ^ 1u);
             umma::fence_after_sync();
-            if (lane == 0) {
-                const uint32_t poff = st * (pstage >> 4);            // pool stage, in descriptor units
+            if (umma::elect_one()) {
+                const uint32_t pst = p_base + st * (pstage >> 4);    // pool stage, in descriptor units
                 const bool img = (MODE == MLP_STATS) && a.image_out != nullptr;
                 // the staged tile IS its image (mlp_image layout): one bulk store, no LSU work; the later passes of
                 // the step fetch their operand stages from it with one bulk load each
@@ -396,8 +399,12 @@ mlp_fc1_kernel(MlpArgs a) {
                                      reinterpret_cast<unsigned char*>(ps) + (size_t)st * pstage, pstage);
                     umma::bulk_commit_group();
                 }
-                umma::issue_table2(s_tab, 6 * kstepsQ, umma::desc_hi(128u), umma::desc_hi(128u),
-                                   MODE == MLP_APPLY ? poff : 0u, MODE == MLP_APPLY ? 0u : poff, tmem + st * 128u, idesc);
+                if (MODE == MLP_APPLY)      // A = pool tile, B = W1
+                    umma::issue_split6(pst, ppiece >> 4, 256u, umma::desc_hi(128u), w_base, wpiece >> 4, (2u * wlbo) >> 4,
+                                       umma::desc_hi(128u), kstepsQ, tmem_u + st * 128u, idesc);
+                else                        // A = W1, B = pool tile
+                    umma::issue_split6(w_base, wpiece >> 4, (2u * wlbo) >> 4, umma::desc_hi(128u), pst, ppiece >> 4, 256u,
+                                       umma::desc_hi(128u), kstepsQ, tmem_u + st * 128u, idesc);
                 // mma_done[st] releases the stage to the producers: the store must have read it by then
                 if (img) umma::bulk_wait_read_all();
                 umma::commit(&sh->mma_done[st]);
@@ -922,16 +929,23 @@ mlp_img_kernel(MlpArgs a) {
             __syncwarp();
         }
     } else if (warp == IMG_E_WARPS + 1) {
-        // ================= issuer =================
+        // ================= issuer: one elected lane per tile, descriptors in the uniform datapath =================
+        const uint32_t w_base = umma::warp_uniform(umma::desc_lo(w_addr, wlbo));
+        const uint32_t p_base = umma::warp_uniform(umma::desc_lo(p_addr, 2048u));
+        const uint32_t tmem_u = umma::warp_uniform(tmem);
         for (int i = 0; i < ntl; ++i) {
             const uint32_t st = (uint32_t)i & 1u;
             umma::mbar_wait(&sh->full[st], ((uint32_t)i >> 1) & 1u);
             umma::mbar_wait(&sh->acc_free[st], (((uint32_t)i >> 1) & 1u) ^ 1u);
             umma::fence_after_sync();
-            if (lane == 0) {
-                const uint32_t poff = st * (pstage >> 4);
-                umma::issue_table2(s_tab, 6 * kstepsQ, umma::desc_hi(128u), umma::desc_hi(128u),
-                                   MODE == MLP_APPLY ? poff : 0u, MODE == MLP_APPLY ? 0u : poff, tmem + st * 128u, idesc);
+            if (umma::elect_one()) {
+                const uint32_t pst = p_base + st * (pstage >> 4);
+                if (MODE == MLP_APPLY)      // A = pool tile, B = W1
+                    umma::issue_split6(pst, ppiece >> 4, 256u, umma::desc_hi(128u), w_base, wpiece >> 4, (2u * wlbo) >> 4,
+                                       umma::desc_hi(128u), kstepsQ, tmem_u + st * 128u, idesc);
+                else                        // A = W1, B = pool tile
+                    umma::issue_split6(w_base, wpiece >> 4, (2u * wlbo) >> 4, umma::desc_hi(128u), pst, ppiece >> 4, 256u,
+                                       umma::desc_hi(128u), kstepsQ, tmem_u + st * 128u, idesc);
                 umma::commit(&sh->mma_done[st]);
             }
             __syncwarp();
@@ -1754,10 +1768,16 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
             __syncwarp();
         }
     } else if (warp == MBP_E1_WARPS + MBP_E2_WARPS) {
-        // ================= issuer =================
+        // ================= issuer: one elected lane per MMA group, descriptors in the uniform datapath =================
         const uint32_t idesc1 = umma::idesc_bf16_f32(128, MB_ROWS);
         const uint32_t idesc2 = umma::idesc_bf16_f32(128, MB_ROWS) | (1u << 15) | (1u << 16);
         const uint32_t idesc3 = umma::idesc_bf16_f32(128, Nq) | (1u << 16);
+        const uint32_t w_a = umma::warp_uniform(umma::desc_lo(umma::smem_u32(w1s), 0u)),
+                       p_a = umma::warp_uniform(umma::desc_lo(umma::smem_u32(ps), 0u)),
+                       t_a = umma::warp_uniform(umma::desc_lo(umma::smem_u32(ts), 0u));
+        const uint32_t tm = umma::warp_uniform(tmem);
+        const uint32_t uD1 = tm, uD2 = tm + MB_ROWS, uD3 = tm + 3 * MB_ROWS;
+        const uint32_t lb_w = ((wcol >> 4) & 0x3FFFu) << 16, lb_p = ((pcol >> 4) & 0x3FFFu) << 16, lb_128 = 8u << 16;
         int ui = 0;                                                   // units started by this CTA
         for (int g = 0; g < ntl; ++g) {
             int v, t; bool first, last;
@@ -1767,9 +1787,11 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
             umma::mbar_wait(&sh->full[st], (uint32_t)(g >> 1) & 1u);
             umma::mbar_wait(&sh->d1_free, ((uint32_t)g & 1u) ^ 1u);
             umma::fence_after_sync();
-            if (lane == 0) {
-                umma::issue_table<false>(s_tab, n1, umma::desc_hi(128u), umma::desc_hi(128u), st * (pstage2 >> 4), D1,
-                                         idesc1, 0u);
+            const uint32_t p_st = p_a + st * (pstage2 >> 4);
+            if (umma::elect_one()) {
+                // D1[hidden][batch] = W1 . pool^T: A = W1 (K chunk pitch wcol), B = pool stage (pitch pcol)
+                umma::issue_split3(w_a | lb_w, wpiece >> 4, (2u * wcol) >> 4, umma::desc_hi(128u),
+                                   p_st | lb_p, ppiece >> 4, (2u * pcol) >> 4, umma::desc_hi(128u), kstepsQ, uD1, idesc1, 0u);
                 umma::commit(&sh->d1_full);
             }
             __syncwarp();
@@ -1777,11 +1799,12 @@ mlp_bwd_pipe_kernel(MlpBwdArgs a, const unsigned char* __restrict__ image, const
             umma::mbar_wait(&sh->d2_free[st], (((uint32_t)g >> 1) & 1u) ^ 1u);
             if (first && ui > 0) umma::mbar_wait(&sh->d3_free, (uint32_t)(ui - 1) & 1u);
             umma::fence_after_sync();
-            if (lane == 0) {
-                umma::issue_table<false>(s_tab + n1, n3, umma::desc_hi(wcol), umma::desc_hi(wcol), 0u, D2 + st * MB_ROWS,
-                                         idesc2, 0u);
-                umma::issue_table<false>(s_tab + n1 + n3, n4, umma::desc_hi(128u), umma::desc_hi(pcol),
-                                         st * (pstage2 >> 4), D3, idesc3, first ? 0u : 1u);
+            if (umma::elect_one()) {
+                // D2[pool dim][batch] = W1^T . dh^T (both MN-major views), D3[hidden][pool dim] += dh . pool
+                umma::issue_split3(w_a | lb_128, wpiece >> 4, 16u, umma::desc_hi(wcol), t_a | lb_128, tpiece >> 4, 16u,
+                                   umma::desc_hi(wcol), 7, uD2 + st * MB_ROWS, idesc2, 0u);
+                umma::issue_split3(t_a | lb_w, tpiece >> 4, (2u * wcol) >> 4, umma::desc_hi(128u), p_st | lb_128, ppiece >> 4,
+                                   16u, umma::desc_hi(pcol), MB_ROWS / 16, uD3, idesc3, first ? 0u : 1u);
                 umma::commit(&sh->d2_full[st]);
             }
             __syncwarp();

@@ -263,6 +263,50 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// The six significant products of a three-way bf16 split (A piece, B piece), smallest first:
+// lo*hi, hi*lo, mid*mid, mid*hi, hi*mid, hi*hi  (0 = hi, 1 = mid, 2 = lo); each runs `ksteps` K steps.
+// To be called by ONE elected lane (`if (elect_one())`) with warp-uniform bases (warp_uniform()): the descriptor
+// arithmetic then stays in the uniform datapath, ~5 instructions per MMA.  (Descriptor tables read under
+// `if (lane == 0)` cost an election / R2UR waterfall of ~30 instructions around every MMA.)
+//   a_base / b_base: desc_lo of piece 0, K step 0 (LBO folded in);  *_piece, *_kstep: strides in 16-byte units
+__device__ __forceinline__ void issue_split6(uint32_t a_base, uint32_t a_piece, uint32_t a_kstep, uint32_t hi_a,
+                                             uint32_t b_base, uint32_t b_piece, uint32_t b_kstep, uint32_t hi_b,
+                                             int ksteps, uint32_t d_tmem, uint32_t idesc) {
+    uint32_t acc = 0;
+#pragma unroll
+    for (int pass = 0; pass < 6; ++pass) {
+        const uint32_t pa = pass == 0 ? 2u : pass == 1 ? 0u : pass == 2 ? 1u : pass == 3 ? 1u : 0u;
+        const uint32_t pb = pass == 0 ? 0u : pass == 1 ? 2u : pass == 2 ? 1u : pass == 3 ? 0u : pass == 4 ? 1u : 0u;
+        uint32_t ad = a_base + pa * a_piece, bd = b_base + pb * b_piece;
+#pragma unroll 2
+        for (int ks = 0; ks < ksteps; ++ks) {
+            mma_bf16(d_tmem, ((uint64_t)hi_a << 32) | (uint64_t)ad, ((uint64_t)hi_b << 32) | (uint64_t)bd, idesc, acc);
+            acc = 1;
+            ad += a_kstep;
+            bd += b_kstep;
+        }
+    }
+}
+
+// The three significant products of a two-way bf16 split (A piece, B piece), smallest first: mid*hi, hi*mid, hi*hi
+// (0 = hi, 1 = mid).  Same calling convention as issue_split6; first_acc = 0 overwrites the accumulator.
+__device__ __forceinline__ void issue_split3(uint32_t a_base, uint32_t a_piece, uint32_t a_kstep, uint32_t hi_a,
+                                             uint32_t b_base, uint32_t b_piece, uint32_t b_kstep, uint32_t hi_b,
+                                             int ksteps, uint32_t d_tmem, uint32_t idesc, uint32_t first_acc) {
+    uint32_t acc = first_acc;
+#pragma unroll
+    for (int pass = 0; pass < 3; ++pass) {
+        uint32_t ad = a_base + (pass == 0 ? a_piece : 0u), bd = b_base + (pass == 1 ? b_piece : 0u);
+#pragma unroll 2
+        for (int ks = 0; ks < ksteps; ++ks) {
+            mma_bf16(d_tmem, ((uint64_t)hi_a << 32) | (uint64_t)ad, ((uint64_t)hi_b << 32) | (uint64_t)bd, idesc, acc);
+            acc = 1;
+            ad += a_kstep;
+            bd += b_kstep;
+        }
+    }
+}
+
 // ---- bulk asynchronous copies (the TMA engine's non-tensor mode; SASS: UBLKCP) --------------------------------
 // global -> shared, completion counted in bytes on an mbarrier: the operand stage of a tile whose image in global
 // memory already IS the shared-memory layout arrives without a single LSU instruction
