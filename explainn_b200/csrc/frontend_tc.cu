@@ -1514,3 +1514,69 @@ extern "C" int xnn_site_emit_tc(const uint32_t* planes, int B, int L, int U, int
     if (r) { set_error("xnn_site_emit_tc: %s", r == 1 ? "shape outside the tensor-core path" : "launch failed"); return r == 1 ? XNN_ERR_ARG : XNN_ERR_CUDA; }
     return XNN_OK;
 }
+
+// ===========================================================================
+// xnn_pwm_scan_tc_noalloc: xnn_pwm_scan_tc for callers that cannot provide (or allocate) the work buffer -- code under
+// CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc.  No counterpart in the reference.
+// The scratch (the three bf16 pieces of the G matrices in UMMA core-matrix
+// order) lives in a file-scope device array of XNN_PWM_SCAN_NOALLOC_BYTES = 1 MiB, which every GPU that loads the
+// library holds until exit.  In host code `pwm_scan_static_work` is only a host-side stand-in for the symbol: the
+// device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// Every call on a device shares the one array: calls that overlap on the GPU (different streams) race.  Nothing in
+// it has to start at zero -- tc_split_weights_kernel rewrites every byte the scan reads (padding rows and taps
+// included) at the start of each call -- so the contents the previous call left behind are harmless.
+// ===========================================================================
+#define XNN_PWM_SCAN_NOALLOC_BYTES (1u << 20)
+static __device__ __align__(256) unsigned char pwm_scan_static_work[XNN_PWM_SCAN_NOALLOC_BYTES];
+
+#include <mutex>
+static void* g_static_work_ptr[64];       // device address of pwm_scan_static_work, per device ordinal
+static std::mutex g_static_work_mutex;
+
+// device address of the static scratch on the CURRENT device (looked up on first use per device); nullptr + error
+static void* pwm_scan_static_work_ptr() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("xnn_pwm_scan_tc_noalloc: cudaGetDevice failed or device ordinal >= 64");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_static_work_mutex);
+    if (g_static_work_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, pwm_scan_static_work);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("xnn_pwm_scan_tc_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_static_work_ptr[dev] = p;
+    }
+    return g_static_work_ptr[dev];
+}
+
+extern "C" size_t xnn_pwm_scan_tc_noalloc_max_bytes(void) { return XNN_PWM_SCAN_NOALLOC_BYTES; }
+
+extern "C" int xnn_pwm_scan_tc_noalloc(const uint32_t* planes, int B, int L, int G, int w, const float* pwm_w, int mode,
+                                       float* out, int32_t* argmax, xnn_stream_t s) {
+    XNN_CHECK_ARG(planes && pwm_w && out, "NULL pointer");
+    XNN_CHECK_ARG(w >= 1 && L >= w && G >= 1 && B >= 0 && (mode == 0 || mode == 1), "bad sizes");
+    XNN_CHECK_ARG(argmax == nullptr || mode == 1, "argmax goes with mode 1 (max)");
+    const size_t need = xnn_pwm_scan_tc_work_bytes(G, w);
+    if (need == 0 || !pwm_tc_fits(L, w, nullptr, nullptr, nullptr)) {
+        set_error("xnn_pwm_scan_tc_noalloc: shape outside the tensor-core path (see xnn_pwm_scan_tc_supported)");
+        return XNN_ERR_ARG;
+    }
+    if (need > (size_t)XNN_PWM_SCAN_NOALLOC_BYTES) {
+        set_error("xnn_pwm_scan_tc_noalloc: G = %d matrices of width %d need %zu bytes of scratch, the static array "
+                  "holds %u; use xnn_pwm_scan_tc with a caller-provided work buffer", G, w, need,
+                  (unsigned)XNN_PWM_SCAN_NOALLOC_BYTES);
+        return XNN_ERR_ARG;
+    }
+    void* work = pwm_scan_static_work_ptr();
+    if (work == nullptr) return XNN_ERR_CUDA;
+    if (B == 0) return XNN_OK;
+    const int m = mode == 0 ? SCAN_SUM : (argmax ? SCAN_MAX_ARG : SCAN_MAX);
+    const int r = launch_scan_tc(m, planes, B, nullptr, L, G, w, pwm_w, nullptr, nullptr, nullptr, out, argmax, nullptr,
+                                 nullptr, work, to_stream(s));
+    if (r != 0) { set_error("xnn_pwm_scan_tc_noalloc: launch failed: %s", cudaGetErrorString(cudaGetLastError())); return XNN_ERR_CUDA; }
+    return XNN_OK;
+}

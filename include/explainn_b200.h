@@ -383,6 +383,19 @@ size_t xnn_pwm_scan_tc_work_bytes(int G, int w);
 int xnn_pwm_scan_tc(const uint32_t* planes, int B, int L, int G, int w,
                     const float* pwm_w /* (G,4,w) */, int mode,
                     float* out, int32_t* argmax, void* work, xnn_stream_t s);
+/* xnn_pwm_scan_tc without a work buffer and without any allocation (no cudaMalloc / cudaFree, nothing from an
+ * allocating library): for callers under CUDA-graph capture, in tight serving loops or in harnesses that forbid
+ * allocation.  NO COUNTERPART IN THE REFERENCE.  The scratch (the
+ * bf16 pieces of the G matrices) is a file-scope device array of xnn_pwm_scan_tc_noalloc_max_bytes() = 1 MiB that
+ * every GPU loading the library holds until exit; shapes with xnn_pwm_scan_tc_work_bytes(G, w) above it (e.g.
+ * more than 896 matrices of width 48, or 1152 of width 35) are rejected with XNN_ERR_ARG and a message naming both
+ * sizes.  Same arguments (minus `work`) and bit-identical results to xnn_pwm_scan_tc.  All calls on one device
+ * share the array: calls that overlap on the GPU (different streams) race; calls on one stream are safe, each call
+ * rewrites every byte it reads. */
+size_t xnn_pwm_scan_tc_noalloc_max_bytes(void);
+int xnn_pwm_scan_tc_noalloc(const uint32_t* planes, int B, int L, int G, int w,
+                            const float* pwm_w /* (G,4,w) */, int mode,
+                            float* out, int32_t* argmax, xnn_stream_t s);
 
 /* ---- a13/a14: PWMScan pwm_scoring semantics, pwmscan/pwm_scoring.c ---------
  * Sequences are int8 codes 0..4 (A C G T N) as pwm_scoring.c:627-655, one
