@@ -273,3 +273,29 @@ def test_interpret_postprocessing_matches_reference_functions():
     assert text.startswith("MEME version 4\n\nALPHABET= ACGT\n\nstrands: + -\n\n")
     assert "\nMOTIF filter0 filter0 ACA\nletter-probability matrix: alength= 4 w= 3 nsites= 4 E= 0\n" in text
     assert "       0.75         0.0        0.25         0.0\n" in text and "filter1" not in text
+
+
+def test_interpret_chunks_are_plane_slices_or_shifted_index_slices():
+    """interpret._chunk_of: without a selection a chunk is a contiguous slice of the planes (no index list); with one,
+    the device-resident list sliced and shifted by the strand's base (interpret.py:375-421 walks fwd then rev halves)."""
+    import torch
+    from explainn_b200 import interpret as I
+    planes = torch.arange(10 * 3 * 2, dtype=torch.int32).reshape(10, 3, 2)
+    pl, idx = I._chunk_of(planes, None, 5, 2, 3)
+    assert idx is None and torch.equal(pl, planes[7:10])
+    sel = torch.tensor([4, 1, 3, 0], dtype=torch.int32)
+    pl, idx = I._chunk_of(planes, sel, 0, 1, 2)
+    assert pl is planes and idx.tolist() == [1, 3] and idx.is_contiguous()
+    pl, idx = I._chunk_of(planes, sel, 5, 2, 2)
+    assert pl is planes and idx.tolist() == [8, 5] and idx.dtype == torch.int32
+
+
+def test_noalloc_limits_are_host_queries():
+    """xnn_pwm_scan_tc_noalloc: the static scratch size and the work size it is compared with need no GPU"""
+    from explainn_b200 import _lib
+    lib = _lib.load()
+    cap = lib.xnn_pwm_scan_tc_noalloc_max_bytes()
+    assert cap == 1 << 20
+    assert 0 < lib.xnn_pwm_scan_tc_work_bytes(750, 35) <= cap          # the cfg5 scan fits
+    assert lib.xnn_pwm_scan_tc_work_bytes(1152, 35) <= cap < lib.xnn_pwm_scan_tc_work_bytes(1153, 35)
+    assert lib.xnn_pwm_scan_tc_work_bytes(896, 48) <= cap < lib.xnn_pwm_scan_tc_work_bytes(897, 48)
