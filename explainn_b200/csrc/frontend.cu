@@ -470,7 +470,7 @@ frontend_bwd_scatter_kernel(const uint32_t* __restrict__ planes, int B, int L, i
     }
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(160)      // 4k + 2 <= 130 columns
 frontend_bwd_finalize_kernel(const double* __restrict__ part, int slices, int U, int k,
                              const float* __restrict__ gamma, const double* __restrict__ stats,
                              const double* __restrict__ cov_w, const long long* __restrict__ cnt1, long long n_pos,
@@ -478,18 +478,22 @@ frontend_bwd_finalize_kernel(const double* __restrict__ part, int slices, int U,
                              float* __restrict__ dbeta) {
     const int u = blockIdx.x, f = threadIdx.x, K4 = 4 * k, stride = K4 + 2;
     __shared__ double s_bg[2];
-    if (f < 2) {
-        double v = 0.0;
-        for (int sl = 0; sl < slices; ++sl) v += part[((long long)sl * U + u) * stride + K4 + f];
-        s_bg[f] = v;
+    // every thread f < 4k + 2 sums its column of the slice partials (same order as before: bit-identical), the loads of
+    // eight slices in flight; the two BatchNorm sums are columns 4k and 4k + 1 (they used to be a second serial chain of
+    // `slices` dependent loads in front of the barrier)
+    double G = 0.0;
+    if (f < stride) {
+        const double* p = part + (long long)u * stride + f;
+        const long long step = (long long)U * stride;
+#pragma unroll 8
+        for (int sl = 0; sl < slices; ++sl) G += p[sl * step];
+        if (f >= K4) s_bg[f - K4] = G;
     }
     __syncthreads();
     const double db = s_bg[0], dg = s_bg[1];
     const double invstd = stats[4 * u + 2];
     const double N = (double)n_pos;
     if (f < K4) {
-        double G = 0.0;
-        for (int sl = 0; sl < slices; ++sl) G += part[((long long)sl * U + u) * stride + f];
         const double v = (double)gamma[u] * invstd *
                          (G - (db / N) * (double)cnt1[f] - dg * invstd * cov_w[(long long)u * K4 + f]);
         dconv_w[(long long)u * K4 + f] = (float)v;
@@ -506,7 +510,7 @@ int frontend_bwd_simt_slices(int B) { return bwd_slices(B); }
 int launch_frontend_bwd_finalize(const double* part, int slices, int U, int k, const float* gamma,
                                  const double* stats, const double* cov_w, const long long* cnt1, long long n_pos,
                                  float* dconv_w, float* dconv_b, float* dgamma, float* dbeta, cudaStream_t st) {
-    frontend_bwd_finalize_kernel<<<U, 128, 0, st>>>(part, slices, U, k, gamma, stats, cov_w, cnt1, n_pos, dconv_w,
+    frontend_bwd_finalize_kernel<<<U, 160, 0, st>>>(part, slices, U, k, gamma, stats, cov_w, cnt1, n_pos, dconv_w,
                                                     dconv_b, dgamma, dbeta);
     return cudaGetLastError() != cudaSuccess;
 }
@@ -533,7 +537,7 @@ extern "C" int xnn_frontend_bwd_simt(const uint32_t* planes, int B, int L, int U
     frontend_bwd_scatter_kernel<<<grid, 32 * k, smem, to_stream(s)>>>(planes, B, L, planes_words(L), U, k, n, dy,
                                                                       zmax, argmax, stats, (double*)work);
     XNN_CHECK_LAUNCH();
-    frontend_bwd_finalize_kernel<<<U, 128, 0, to_stream(s)>>>((const double*)work, slices, U, k, gamma, stats,
+    frontend_bwd_finalize_kernel<<<U, 160, 0, to_stream(s)>>>((const double*)work, slices, U, k, gamma, stats,
                                                               cov_w, cnt1, n_pos, dconv_w, dconv_b, dgamma, dbeta);
     XNN_CHECK_LAUNCH();
     return XNN_OK;
