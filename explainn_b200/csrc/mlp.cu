@@ -155,6 +155,7 @@ colsums_kernel(const float* __restrict__ x, const float* __restrict__ y, const f
     const int r0 = blockIdx.y * rows_per, r1 = min(B, r0 + rows_per);
     double a1 = 0.0, a2 = 0.0;
     if (c < C) {
+#pragma unroll 4                                       // four rows' loads in flight (the sums keep their order)
         for (int r = r0 + warp; r < r1; r += 8) {
             float xv = x[(long long)r * C + c];
             if (relu_out && !(relu_out[(long long)r * C + c] > 0.0f)) xv = 0.0f;

@@ -120,12 +120,23 @@ loss_fwd_kernel(const float* __restrict__ x, const float* __restrict__ y, long l
         last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
     }
     __syncthreads();
-    if (last && threadIdx.x == 0) {
+    if (last) {
+        // the last block adds the partials as a fixed tree (thread b holds block b's partial: gridDim.x <= LOSS_THREADS):
+        // deterministic whatever the order in which the blocks finished; a serial walk over 256 partials by one thread
+        // was most of the kernel's 13 us
         __threadfence();
-        double t = 0.0;
-        for (unsigned int b = 0; b < gridDim.x; ++b) t += ((volatile double*)part)[b];
-        *loss = (float)(t / (double)n);
-        *ticket = 0u;                    // ready for the next launch (graph replays reuse the work buffer)
+        double t = threadIdx.x < gridDim.x ? ((volatile double*)part)[threadIdx.x] : 0.0;
+        t = warp_sum(t);
+        __syncthreads();                 // sh[] of the first reduction has been read by thread 0
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = t;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tot = 0.0;
+#pragma unroll
+            for (int w = 0; w < LOSS_THREADS / 32; ++w) tot += sh[w];
+            *loss = (float)(tot / (double)n);
+            *ticket = 0u;                // ready for the next launch (graph replays reuse the work buffer)
+        }
     }
 }
 
